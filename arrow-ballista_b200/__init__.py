@@ -1,0 +1,9 @@
+"""arrow-ballista_b200: B200-native aggregation + shuffle hot path for Ballista.
+
+The compute lives in libbgpu.so (hand-written sm_100a CUDA behind the C ABI of include/bgpu.h); this package is
+the host-side mirror of the reference operator interfaces for that path. Import it via `import ballista_b200`
+(the directory name contains a hyphen).
+"""
+from ._lib import LIB_PATH, SIGNATURES, BgpuError, lib  # noqa: F401
+from .runtime import Context, DeviceBatch, create_hashes  # noqa: F401
+from .partitioner import BatchPartitioner, Partitioning  # noqa: F401

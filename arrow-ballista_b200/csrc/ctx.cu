@@ -1,0 +1,79 @@
+// Context: one CUDA stream + stream-ordered pool allocations per task (SURVEY.md §8b "Threading").
+#include "internal.h"
+
+extern "C" const char* bgpu_version(void) { return "libbgpu 0.1 (sm_100a)"; }
+
+static int ctx_create(int device, cudaStream_t external, bool has_external, bgpu_ctx** out) {
+  if (!out) return BGPU_EINVAL;
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  bgpu_ctx* ctx = new bgpu_ctx();
+  *out = ctx;  // returned even on failure so the caller can read the error, must still be destroyed
+  if (e != cudaSuccess || n == 0)
+    return ctx->fail(BGPU_ENODEVICE, std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                                         " (libbgpu has no CPU fallback)");
+  if (device < 0 || device >= n) return ctx->fail(BGPU_EINVAL, "device index out of range");
+  ctx->device = device;
+  BGPU_CUDA(ctx, cudaSetDevice(device));
+  cudaDeviceProp prop;
+  BGPU_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10)
+    return ctx->fail(BGPU_ENODEVICE, std::string("device ") + prop.name + " is sm_" + std::to_string(prop.major) +
+                                         std::to_string(prop.minor) + "; libbgpu is built for sm_100a only");
+  ctx->sm_count = prop.multiProcessorCount;
+  ctx->smem_optin = prop.sharedMemPerBlockOptin;
+  if (has_external) {
+    ctx->stream = external;
+    ctx->owns_stream = false;
+  } else {
+    BGPU_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  }
+  // keep freed blocks in the pool: operators allocate/free every batch
+  cudaMemPool_t pool;
+  BGPU_CUDA(ctx, cudaDeviceGetDefaultMemPool(&pool, device));
+  uint64_t thresh = UINT64_MAX;
+  BGPU_CUDA(ctx, cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+  ctx->has_device = true;
+  ctx->pinned_bytes = 1 << 20;
+  BGPU_CUDA(ctx, cudaMallocHost(&ctx->pinned, ctx->pinned_bytes));
+  return BGPU_OK;
+}
+
+extern "C" int bgpu_ctx_create(int device, bgpu_ctx** out) { return ctx_create(device, nullptr, false, out); }
+extern "C" int bgpu_ctx_create_on_stream(int device, void* stream, bgpu_ctx** out) {
+  return ctx_create(device, (cudaStream_t)stream, true, out);
+}
+
+extern "C" void bgpu_ctx_destroy(bgpu_ctx* ctx) {
+  if (!ctx) return;
+  if (ctx->has_device) {
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);
+  }
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  delete ctx;
+}
+
+extern "C" const char* bgpu_last_error(const bgpu_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+extern "C" int bgpu_ctx_synchronize(bgpu_ctx* ctx) {
+  if (!ctx || !ctx->has_device) return BGPU_EINVAL;
+  BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return BGPU_OK;
+}
+
+extern "C" void* bgpu_ctx_stream(bgpu_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+extern "C" uint64_t bgpu_ctx_kernel_launches(const bgpu_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int dev_alloc(bgpu_ctx* ctx, size_t bytes, DevAllocPtr* out) {
+  if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device");
+  auto a = std::make_shared<DevAlloc>();
+  a->bytes = bytes < 16 ? 16 : bytes;
+  a->stream = ctx->stream;
+  BGPU_CUDA(ctx, cudaMallocAsync(&a->p, a->bytes, ctx->stream));
+  *out = a;
+  return BGPU_OK;
+}

@@ -1,0 +1,97 @@
+// libbgpu internals: context, device-resident columns, error plumbing.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/bgpu.h"
+
+struct bgpu_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool owns_stream = true;
+  bool has_device = false;  // false: creation failed (no GPU); every compute call fails loudly
+  int sm_count = 148;
+  size_t smem_optin = 0;
+  std::string err;
+  uint64_t launches = 0;
+  // small pinned scratch for device->host scalars (partition offsets, group counts)
+  void* pinned = nullptr;
+  size_t pinned_bytes = 0;
+
+  int fail(int code, const std::string& msg) {
+    err = msg;
+    return code;
+  }
+};
+
+#define BGPU_CUDA(ctx, call)                                                                         \
+  do {                                                                                               \
+    cudaError_t _e = (call);                                                                         \
+    if (_e != cudaSuccess)                                                                           \
+      return (ctx)->fail(BGPU_ECUDA, std::string(#call) + ": " + cudaGetErrorString(_e) + " at " +  \
+                                         __FILE__ + ":" + std::to_string(__LINE__));                 \
+  } while (0)
+
+#define BGPU_TRY(expr)        \
+  do {                        \
+    int _rc = (expr);         \
+    if (_rc != BGPU_OK) return _rc; \
+  } while (0)
+
+// A device allocation freed (stream-ordered) when the last column referencing it goes away.
+struct DevAlloc {
+  void* p = nullptr;
+  size_t bytes = 0;
+  cudaStream_t stream = nullptr;
+  bool owned = true;
+  ~DevAlloc() {
+    if (p && owned) cudaFreeAsync(p, stream);
+  }
+};
+using DevAllocPtr = std::shared_ptr<DevAlloc>;
+
+// Allocate `bytes` (at least 16, 256-byte aligned by the pool) on the ctx stream.
+int dev_alloc(bgpu_ctx* ctx, size_t bytes, DevAllocPtr* out);
+
+enum ColKind : int32_t { K_FIXED = 0, K_BOOL = 1, K_UTF8 = 2, K_BINARY = 3, K_DICT32 = 4 };
+
+struct Column {
+  std::string name;
+  std::string format;  // Arrow C format string of this column (index type for dictionaries)
+  int64_t flags = ARROW_FLAG_NULLABLE;
+  ColKind kind = K_FIXED;
+  int32_t width = 0;           // K_FIXED byte width; K_DICT32: 4
+  void* values = nullptr;      // fixed values / bool bits / utf8 data / dictionary keys
+  int32_t* offsets = nullptr;  // utf8/binary: length+1 entries, offsets[0] may be non-zero
+  uint8_t* validity = nullptr; // nullptr = all valid
+  int64_t length = 0;
+  int64_t null_count = 0;      // -1 = unknown
+  int64_t data_bytes = 0;      // utf8/binary: bytes addressable behind `values`
+  std::shared_ptr<Column> dict;  // K_DICT32: dictionary values column
+  std::vector<DevAllocPtr> owned;  // keeps buffers alive (shared with other batches when passed through)
+};
+
+struct bgpu_batch {
+  bgpu_ctx* ctx = nullptr;
+  int64_t n_rows = 0;
+  std::vector<Column> cols;
+};
+
+// Parse one Arrow C schema node into kind/width/format. Returns BGPU_EUNSUPPORTED for types off the path.
+int parse_field(bgpu_ctx* ctx, const struct ArrowSchema* s, Column* out);
+
+// Plain-old-data view of a column handed to kernels.
+struct KCol {
+  const void* values;
+  const int32_t* offsets;
+  const uint8_t* validity;
+  const uint64_t* dict_hashes;  // K_DICT32 key columns: create_hashes of the dictionary values
+  int32_t kind;
+  int32_t width;
+};
+
+static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -1,0 +1,135 @@
+/* libbgpu — C ABI of the B200-native aggregation + shuffle hot path for Ballista.
+ *
+ * This is the drop-in boundary: the entry points a Rust `GpuShuffleWriterExec` /
+ * `GpuAggregateExec` would bind through `extern "C"` (see INTEGRATION.md for the Rust stub). Every entry
+ * point names the reference interface it replaces. Paths are relative to /root/reference.
+ *
+ * Conventions (mirror the reference's contracts):
+ *  - every call returns 0 on success, a BGPU_E* category otherwise; the message is in bgpu_last_error(ctx).
+ *    Nothing aborts or throws across the ABI (reference: Result<_, DataFusionError>, shuffle_writer.rs:451-453).
+ *  - inputs are *borrowed* Arrow C-Data structs valid for the call; outputs are library-allocated Arrow C-Data
+ *    whose release callback frees them; opaque handles are freed by the matching *_destroy.
+ *  - one bgpu_ctx per task (CUDA stream + memory pool); no global mutable state; contexts are independent and
+ *    may be used from different threads concurrently (reference: DedicatedExecutor runs many tasks per
+ *    process, executor_server.rs:1027-1032).
+ *  - there is no CPU fallback: without a CUDA device every compute call fails with BGPU_ENODEVICE.
+ */
+#ifndef BGPU_H
+#define BGPU_H
+#include <stdint.h>
+
+#include "bgpu_arrow_abi.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BGPU_OK 0
+#define BGPU_EINVAL 1       /* bad argument / plan (DataFusionError::Plan / Internal) */
+#define BGPU_EUNSUPPORTED 2 /* type or shape not handled on the GPU path (DataFusionError::NotImplemented) */
+#define BGPU_ECUDA 3        /* CUDA runtime failure (DataFusionError::Execution) */
+#define BGPU_ENODEVICE 4    /* no usable CUDA device */
+#define BGPU_EOVERFLOW 5    /* arithmetic overflow the reference reports as an error (ArrowError::ComputeError) */
+#define BGPU_ENCCL 6        /* exchange failure; maps to BallistaError::FetchFailed (shuffle_reader.rs:697-704) */
+
+typedef struct bgpu_ctx bgpu_ctx;     /* one per task: device, stream, pool, last error */
+typedef struct bgpu_batch bgpu_batch; /* a RecordBatch resident in device memory */
+typedef struct bgpu_agg bgpu_agg;     /* a GroupedHashAggregateStream's state */
+
+/* ---- context ------------------------------------------------------------------------------------------ */
+int bgpu_ctx_create(int device, bgpu_ctx** out);
+/* same, but all work is ordered on a caller-owned cudaStream_t (e.g. the harness's stream, so its CUDA events
+ * time this library's kernels); NULL = the legacy default stream */
+int bgpu_ctx_create_on_stream(int device, void* cuda_stream, bgpu_ctx** out);
+void bgpu_ctx_destroy(bgpu_ctx* ctx);
+const char* bgpu_last_error(const bgpu_ctx* ctx); /* never NULL; "" when no error */
+int bgpu_ctx_synchronize(bgpu_ctx* ctx);
+void* bgpu_ctx_stream(bgpu_ctx* ctx); /* the cudaStream_t all work of this ctx is ordered on */
+const char* bgpu_version(void);
+/* number of kernels this ctx has launched so far (bench.py's gpu_launches) */
+uint64_t bgpu_ctx_kernel_launches(const bgpu_ctx* ctx);
+
+/* ---- batches: RecordBatch <-> device -------------------------------------------------------------------
+ * The struct-typed ArrowArray/ArrowSchema pair is a RecordBatch exactly as arrow-rs exports one
+ * (format "+s", one child per column). */
+/* host -> device copy (one cudaMemcpyAsync per buffer on the ctx stream) */
+int bgpu_batch_upload(bgpu_ctx* ctx, const struct ArrowArray* batch, const struct ArrowSchema* schema,
+                      bgpu_batch** out);
+/* borrow buffers that already live in device memory (array->buffers[] are device pointers); array offsets
+ * must be 0. The caller keeps them alive until bgpu_batch_destroy. */
+int bgpu_batch_wrap_device(bgpu_ctx* ctx, const struct ArrowArray* batch, const struct ArrowSchema* schema,
+                           bgpu_batch** out);
+/* device -> host copy into library-owned host memory; rows [row_offset, row_offset+num_rows) */
+int bgpu_batch_download(bgpu_ctx* ctx, const bgpu_batch* batch, int64_t row_offset, int64_t num_rows,
+                        struct ArrowArray* out, struct ArrowSchema* out_schema);
+/* export device pointers (no copy); valid until the batch is destroyed */
+int bgpu_batch_export_device(bgpu_ctx* ctx, const bgpu_batch* batch, struct ArrowArray* out,
+                             struct ArrowSchema* out_schema);
+int64_t bgpu_batch_num_rows(const bgpu_batch* batch);
+int32_t bgpu_batch_num_columns(const bgpu_batch* batch);
+void bgpu_batch_destroy(bgpu_batch* batch);
+
+/* ---- create_hashes ---------------------------------------------------------------------------------------
+ * Replaces datafusion_common::hash_utils::create_hashes(arrays, &RandomState::with_seeds(0,0,0,0), buf)
+ * as called by BatchPartitioner (call site shuffle_writer.rs:336-346; restated SURVEY.md A.1).
+ * out_hashes_device: device pointer to n_rows u64. */
+int bgpu_create_hashes(bgpu_ctx* ctx, const bgpu_batch* batch, const int32_t* key_cols, int32_t n_keys,
+                       uint64_t* out_hashes_device);
+
+/* ---- BatchPartitioner::partition, hash arm -----------------------------------------------------------------
+ * Replaces `partitioner.partition(batch, |partition, out_batch| ...)` (shuffle_writer.rs:346-391):
+ * partition = create_hashes(keys) % n_partitions; every column is gathered per partition in input order
+ * (arrow `take`). The result is ONE batch whose rows are grouped by partition ascending and stable within a
+ * partition; partition p is rows [out_offsets[p], out_offsets[p+1]) (empty partitions have equal offsets —
+ * the caller skips them as the reference does, shuffle_writer.rs:349).
+ * out_offsets: HOST pointer to n_partitions+1 u64. out_hashes_device: optional device pointer (n_rows u64). */
+int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* batch, const int32_t* key_cols, int32_t n_keys,
+                        uint32_t n_partitions, bgpu_batch** out_partitioned, uint64_t* out_offsets,
+                        uint64_t* out_hashes_device);
+/* Host-buffer convenience used by the operator layer: upload + partition + download in one call. */
+int bgpu_hash_partition_host(bgpu_ctx* ctx, const struct ArrowArray* batch, const struct ArrowSchema* schema,
+                             const int32_t* key_cols, int32_t n_keys, uint32_t n_partitions,
+                             struct ArrowArray* out_partitioned, struct ArrowSchema* out_schema,
+                             uint64_t* out_offsets);
+
+/* ---- AggregateExec / GroupedHashAggregateStream ------------------------------------------------------------
+ * Replaces AggregateExec(mode=Partial|FinalPartitioned) (plan shape planner.rs:376-427, proto
+ * datafusion.proto:1405-1411,1437-1450; restated SURVEY.md A.3). */
+#define BGPU_AGG_MODE_PARTIAL 0           /* AggregateMode::PARTIAL */
+#define BGPU_AGG_MODE_FINAL 1             /* AggregateMode::FINAL */
+#define BGPU_AGG_MODE_FINAL_PARTITIONED 2 /* AggregateMode::FINAL_PARTITIONED */
+#define BGPU_AGG_MODE_SINGLE 3            /* AggregateMode::SINGLE (raw rows -> final values) */
+#define BGPU_AGG_MIN 0 /* AggregateFunction numbering, datafusion.proto:631-636 */
+#define BGPU_AGG_MAX 1
+#define BGPU_AGG_SUM 2
+#define BGPU_AGG_AVG 3
+#define BGPU_AGG_COUNT 4
+
+/* input_schema: schema of the *raw* input of the Partial aggregate (AggregateExecNode.input_schema,
+ * datafusion.proto:1444-1445) — also required in Final modes, where the batches fed to update() are state
+ * batches (group columns first, then state columns in aggregate order: Sum -> sum; Count -> count Int64;
+ * Avg -> count UInt64, sum). group_cols / agg_cols index input_schema; agg_cols[i] = -1 means COUNT(*).
+ * Integer arguments of AVG are cast to Float64 (the planner's coercion). */
+int bgpu_agg_create(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema* input_schema,
+                    const int32_t* group_cols, int32_t n_group, const int32_t* agg_fns,
+                    const int32_t* agg_cols, int32_t n_agg, bgpu_agg** out);
+/* update_batch (Partial/Single) or merge_batch (Final*) with one device-resident batch */
+int bgpu_agg_update(bgpu_agg* agg, const bgpu_batch* batch);
+/* end of input: state() (Partial) or evaluate() (Final modes and Single). Group order is unspecified, as in the
+ * reference (GroupValues uses a randomly seeded table). The aggregate may not be updated afterwards. */
+int bgpu_agg_emit(bgpu_agg* agg, bgpu_batch** out);
+int64_t bgpu_agg_num_groups(bgpu_agg* agg); /* synchronizes */
+void bgpu_agg_destroy(bgpu_agg* agg);
+
+/* ---- intra-node exchange (replaces shuffle files + Flight do_get + ShuffleReaderExec fan-in;
+ * shuffle_writer.rs:351-385, flight_service.rs:124-166, shuffle_reader.rs:539-624) --------------------------
+ * nccl_comm: an ncclComm_t created by the host harness (one rank per process/GPU). Output partition p is
+ * owned by rank p % world. `partitioned`/`offsets` come from bgpu_hash_partition with the same n_partitions on
+ * every rank. out_received holds this rank's partitions from all ranks, grouped by (partition, source rank). */
+int bgpu_all_to_all(bgpu_ctx* ctx, void* nccl_comm, int32_t rank, int32_t world, const bgpu_batch* partitioned,
+                    const uint64_t* offsets, uint32_t n_partitions, bgpu_batch** out_received);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
