@@ -7,3 +7,4 @@ the host-side mirror of the reference operator interfaces for that path. Import 
 from ._lib import LIB_PATH, SIGNATURES, BgpuError, lib  # noqa: F401
 from .runtime import Context, DeviceBatch, create_hashes  # noqa: F401
 from .partitioner import BatchPartitioner, Partitioning  # noqa: F401
+from .aggregate import AggregateFunction, AggregateMode, GpuAggregateExec  # noqa: F401

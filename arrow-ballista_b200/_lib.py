@@ -64,7 +64,8 @@ SIGNATURES = {
                                            C.POINTER(C.c_int32), C.c_int32, C.c_uint32, C.POINTER(ArrowArray),
                                            C.POINTER(ArrowSchema), C.POINTER(C.c_uint64)]),
     "bgpu_agg_create": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(ArrowSchema), C.POINTER(C.c_int32), C.c_int32,
-                                  C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_void_p)]),
+                                  C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_char_p), C.c_int32,
+                                  C.POINTER(C.c_void_p)]),
     "bgpu_agg_update": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bgpu_agg_emit": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "bgpu_agg_num_groups": (C.c_int64, [C.c_void_p]),

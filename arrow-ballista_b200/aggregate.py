@@ -1,0 +1,91 @@
+"""Host mirror of DataFusion's `AggregateExec` for the modes on Ballista's hot path
+(plan shape /root/reference/ballista/scheduler/src/planner.rs:376-427; AggregateMode / AggregateFunction
+numbering /root/reference/ballista/core/proto/datafusion.proto:1405-1411, 631-636).
+
+`GpuAggregateExec` is what the north star calls the operator; the arithmetic runs in libbgpu
+(bgpu_agg_create / update / emit).
+"""
+import ctypes as C
+
+import pyarrow as pa
+
+from ._lib import ArrowSchema, lib
+from .runtime import DeviceBatch, _release
+
+
+class AggregateMode:
+    Partial = 0
+    Final = 1
+    FinalPartitioned = 2
+    Single = 3
+
+
+class AggregateFunction:
+    Min = 0
+    Max = 1
+    Sum = 2
+    Avg = 3
+    Count = 4
+
+    @staticmethod
+    def parse(fn):
+        if isinstance(fn, int):
+            return fn
+        return {"min": 0, "max": 1, "sum": 2, "avg": 3, "count": 4}[fn.lower()]
+
+
+class GpuAggregateExec:
+    """AggregateExec(mode, group_by, aggr_expr, input, input_schema).
+
+    group_by: column indices into `input_schema` (the raw input of the Partial aggregate).
+    aggr_expr: [(fn, arg_col | None, name)]; None = COUNT(*).
+    In Final modes the batches passed to `update` are Partial state batches (group columns first).
+    """
+
+    def __init__(self, ctx, mode, group_by, aggr_expr, input_schema):
+        self.ctx, self.mode, self.input_schema = ctx, mode, input_schema
+        self.group_by = list(group_by)
+        self.aggr_expr = [(AggregateFunction.parse(f), (-1 if c is None else int(c)), str(n)) for f, c, n in aggr_expr]
+        s = ArrowSchema()
+        input_schema._export_to_c(C.addressof(s))
+        n = len(self.aggr_expr)
+        gcols = (C.c_int32 * len(self.group_by))(*self.group_by)
+        fns = (C.c_int32 * max(n, 1))(*[f for f, _, _ in self.aggr_expr])
+        cols = (C.c_int32 * max(n, 1))(*[c for _, c, _ in self.aggr_expr])
+        names = (C.c_char_p * max(n, 1))(*[nm.encode() for _, _, nm in self.aggr_expr])
+        self._h = C.c_void_p()
+        try:
+            ctx.check(lib().bgpu_agg_create(ctx._h, mode, C.byref(s), gcols, len(self.group_by), fns, cols, names, n,
+                                            C.byref(self._h)))
+        finally:
+            _release(s)
+
+    def update(self, batch):
+        """update_batch / merge_batch with one batch (DeviceBatch, or a host RecordBatch that is uploaded)."""
+        if not isinstance(batch, DeviceBatch):
+            batch = DeviceBatch.upload(self.ctx, batch)
+        self.ctx.check(lib().bgpu_agg_update(self._h, batch._h))
+
+    def emit(self):
+        """End of input: the state batch (Partial) or the final values. Returns a DeviceBatch."""
+        out = C.c_void_p()
+        self.ctx.check(lib().bgpu_agg_emit(self._h, C.byref(out)))
+        return DeviceBatch(self.ctx, out)
+
+    @property
+    def num_groups(self):
+        return int(lib().bgpu_agg_num_groups(self._h))
+
+    def execute(self, batches):
+        """Run over an iterable of batches and return the output as a host RecordBatch."""
+        for b in batches:
+            self.update(b)
+        return self.emit().download()
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().bgpu_agg_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()

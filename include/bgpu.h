@@ -109,10 +109,11 @@ int bgpu_hash_partition_host(bgpu_ctx* ctx, const struct ArrowArray* batch, cons
  * datafusion.proto:1444-1445) — also required in Final modes, where the batches fed to update() are state
  * batches (group columns first, then state columns in aggregate order: Sum -> sum; Count -> count Int64;
  * Avg -> count UInt64, sum). group_cols / agg_cols index input_schema; agg_cols[i] = -1 means COUNT(*).
- * Integer arguments of AVG are cast to Float64 (the planner's coercion). */
+ * Integer arguments of AVG are cast to Float64 (the planner's coercion). agg_names (may be NULL) name the
+ * output columns: Partial emits "<name>[sum]" / "<name>[count]" state columns, Final modes emit "<name>". */
 int bgpu_agg_create(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema* input_schema,
                     const int32_t* group_cols, int32_t n_group, const int32_t* agg_fns,
-                    const int32_t* agg_cols, int32_t n_agg, bgpu_agg** out);
+                    const int32_t* agg_cols, const char* const* agg_names, int32_t n_agg, bgpu_agg** out);
 /* update_batch (Partial/Single) or merge_batch (Final*) with one device-resident batch */
 int bgpu_agg_update(bgpu_agg* agg, const bgpu_batch* batch);
 /* end of input: state() (Partial) or evaluate() (Final modes and Single). Group order is unspecified, as in the

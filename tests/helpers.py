@@ -47,8 +47,8 @@ def random_batch(rng, n, null_frac=0.1, with_strings=True, with_dict=True):
     }
     if with_strings:
         words = ["", "a", "bc", "def", "ghij", "klmnopqr", "stuvwxyz0", "0123456789abcdef", "0123456789abcdefg" * 3]
-        cols["s"] = pa.array([words[i] for i in rng.integers(0, len(words), n)], mask=mask())
-        cols["flag"] = pa.array(rng.choice(["A", "N", "R"], n))
+        cols["s"] = pa.array([words[i] for i in rng.integers(0, len(words), n)], type=pa.string(), mask=mask())
+        cols["flag"] = pa.array(rng.choice(["A", "N", "R"], n).tolist(), type=pa.string())
     if with_dict:
-        cols["d"] = pa.array([f"id{int(i):03d}" for i in rng.integers(1, 100, n)], mask=mask()).dictionary_encode()
+        cols["d"] = pa.array([f"id{int(i):03d}" for i in rng.integers(1, 100, n)], type=pa.string(), mask=mask()).dictionary_encode()
     return pa.RecordBatch.from_arrays(list(cols.values()), names=list(cols.keys()))

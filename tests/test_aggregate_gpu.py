@@ -1,0 +1,132 @@
+"""GPU parity: GpuAggregateExec (Partial, FinalPartitioned) against the oracle's GroupedHashAggregateStream
+restatement. Integer / Decimal128 sums, counts and decimal averages are bit-exact; Float64 within 1e-9 relative
+(the north star's tolerance — the reference's own float sum order is not deterministic)."""
+import numpy as np
+import pyarrow as pa
+import pyarrow.compute as pc
+import pytest
+
+from helpers import random_batch
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-9
+
+
+def _sorted(rb, n_keys):
+    t = pa.Table.from_batches([rb])
+    cols = []
+    for i in range(n_keys):
+        c = t.column(i)
+        if pa.types.is_dictionary(c.type):
+            c = c.cast(c.type.value_type)
+        cols.append(c)
+    key_tbl = pa.table({f"k{i}": c for i, c in enumerate(cols)})
+    idx = pc.sort_indices(key_tbl, sort_keys=[(f"k{i}", "ascending") for i in range(n_keys)], null_placement="at_end")
+    return t.take(idx), key_tbl.take(idx)
+
+
+def assert_same_groups(got, want, n_keys):
+    assert got.schema.names == want.schema.names
+    assert got.num_rows == want.num_rows
+    g, gk = _sorted(got, n_keys)
+    w, wk = _sorted(want, n_keys)
+    assert gk.equals(wk), "group keys differ"
+    for i in range(n_keys, g.num_columns):
+        a, b = g.column(i).combine_chunks(), w.column(i).combine_chunks()
+        name = g.schema.names[i]
+        assert a.type == b.type, (name, a.type, b.type)
+        if pa.types.is_floating(a.type):
+            assert a.is_null().equals(b.is_null()), name
+            x, y = a.fill_null(0).to_numpy(), b.fill_null(0).to_numpy()
+            assert np.allclose(x, y, rtol=RTOL, atol=0), name
+        else:
+            assert a.equals(b), f"column {name} differs"
+
+
+def run_both(bb, ctx, oracle, batches, group_names, aggs, n_partials=2):
+    schema = batches[0].schema
+    gi = [schema.names.index(g) for g in group_names]
+    spec = [(f, (None if c is None else schema.names.index(c)), nm) for f, c, nm in aggs]
+    # oracle: partial per input partition, then final
+    OP = [oracle.GroupedAggregate("partial", gi, spec) for _ in range(n_partials)]
+    GP = [bb.GpuAggregateExec(ctx, bb.AggregateMode.Partial, gi, spec, schema) for _ in range(n_partials)]
+    for i, b in enumerate(batches):
+        OP[i % n_partials].update(b)
+        GP[i % n_partials].update(b)
+    ostates = [p.emit() for p in OP]
+    gstates = [p.emit().download() for p in GP]
+    for o, g_ in zip(ostates, gstates):
+        assert_same_groups(g_, o, len(gi))
+    arg_types = [schema.field(c).type if c is not None else None for _, c, _ in spec]
+    OF = oracle.GroupedAggregate("final", list(range(len(gi))), spec, arg_types=arg_types)
+    GF = bb.GpuAggregateExec(ctx, bb.AggregateMode.FinalPartitioned, gi, spec, schema)
+    for o, g_ in zip(ostates, gstates):
+        OF.update(o)
+        GF.update(g_)
+    of, gf = OF.emit(), GF.emit().download()
+    assert_same_groups(gf, of, len(gi))
+    return gf
+
+
+Q1_AGGS = [("sum", "dec", "sum_qty"), ("avg", "dec", "avg_qty"), ("avg", "f", "avg_f"), ("count", None, "count_order"),
+           ("sum", "k32", "sum_i"), ("avg", "k32", "avg_i"), ("count", "k32", "cnt_i"), ("sum", "f", "sum_f"),
+           ("sum", "u8", "sum_u")]
+
+
+@pytest.mark.parametrize("groups", [["flag"], ["flag", "small"], ["small"], ["d"], ["d", "flag"], ["k32"], ["date", "b"],
+                                    ["i16", "u8"], ["k64"], ["dec"]])
+def test_partial_final_match_oracle(bb, ctx, oracle, groups):
+    rng = np.random.default_rng(17)
+    whole = random_batch(rng, 40_000)
+    batches = [whole.slice(i, 8192) for i in range(0, whole.num_rows, 8192)]
+    run_both(bb, ctx, oracle, batches, groups, Q1_AGGS, n_partials=2)
+
+
+def test_no_nulls_then_nulls(bb, ctx, oracle):
+    rng = np.random.default_rng(3)
+    a = random_batch(rng, 5000, null_frac=0)
+    b = random_batch(rng, 5000, null_frac=0.3)
+    run_both(bb, ctx, oracle, [a, b, a.slice(0, 100)], ["flag", "small"], Q1_AGGS, n_partials=1)
+
+
+def test_all_null_group_gives_null_sum(bb, ctx, oracle):
+    k = pa.array([1, 1, 2, 2, 3], type=pa.int64())
+    v = pa.array([None, None, 5, None, 7], type=pa.int64())
+    b = pa.RecordBatch.from_arrays([k, v], names=["k", "v"])
+    out = run_both(bb, ctx, oracle, [b], ["k"], [("sum", "v", "s"), ("avg", "v", "a"), ("count", "v", "c")], 1)
+    t = pa.Table.from_batches([out]).sort_by("k")
+    assert t["s"].to_pylist() == [None, 5, 7] and t["c"].to_pylist() == [0, 1, 1] and t["a"].to_pylist() == [None, 5.0, 7.0]
+
+
+def test_high_cardinality_grows_table(bb, ctx, oracle):
+    rng = np.random.default_rng(9)
+    n = 400_000
+    b = pa.RecordBatch.from_arrays([pa.array(rng.integers(0, 300_000, n), type=pa.int64()),
+                                    pa.array(rng.integers(-100, 100, n), type=pa.int64()),
+                                    pa.array(rng.random(n))], names=["k", "v", "f"])
+    run_both(bb, ctx, oracle, [b.slice(0, 250_000), b.slice(250_000)], ["k"],
+             [("sum", "v", "s"), ("count", None, "c"), ("avg", "f", "a")], 2)
+
+
+def test_int64_sum_wraps(bb, ctx, oracle):
+    b = pa.RecordBatch.from_arrays([pa.array([0, 0, 0, 1], type=pa.int64()),
+                                    pa.array([2**62, 2**62, 2**62, -5], type=pa.int64())], names=["k", "v"])
+    out = run_both(bb, ctx, oracle, [b], ["k"], [("sum", "v", "s")], 1)
+    assert sorted(out.column(1).to_pylist()) == [-(2**62), -5]
+
+
+def test_long_string_key_is_an_error(bb, ctx):
+    b = pa.RecordBatch.from_arrays([pa.array(["short", "this string is far too long to pack"]), pa.array([1, 2])],
+                                   names=["k", "v"])
+    agg = bb.GpuAggregateExec(ctx, bb.AggregateMode.Partial, [0], [("sum", 1, "s")], b.schema)
+    with pytest.raises(bb.BgpuError):
+        agg.update(b)
+
+
+def test_empty_input(bb, ctx):
+    b = random_batch(np.random.default_rng(0), 0, with_dict=False)
+    agg = bb.GpuAggregateExec(ctx, bb.AggregateMode.Partial, [b.schema.names.index("small")],
+                              [("sum", b.schema.names.index("dec"), "s")], b.schema)
+    agg.update(b)
+    out = agg.emit().download()
+    assert out.num_rows == 0 and out.schema.names == ["small", "s[sum]"]
