@@ -8,3 +8,5 @@ from ._lib import LIB_PATH, SIGNATURES, BgpuError, lib  # noqa: F401
 from .runtime import Context, DeviceBatch, create_hashes  # noqa: F401
 from .partitioner import BatchPartitioner, Partitioning  # noqa: F401
 from .aggregate import AggregateFunction, AggregateMode, GpuAggregateExec  # noqa: F401
+from .expr import Column, Literal, BinaryExpr, col, lit  # noqa: F401
+from . import expr  # noqa: F401

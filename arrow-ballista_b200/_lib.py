@@ -29,6 +29,12 @@ class ArrowArray(C.Structure):
     pass
 
 
+class ExprNode(C.Structure):
+    """bgpu_expr_node (include/bgpu.h)."""
+    _fields_ = [("op", C.c_int32), ("a", C.c_int32), ("precision", C.c_int32), ("scale", C.c_int32),
+                ("lo", C.c_uint64), ("hi", C.c_uint64)]
+
+
 ArrowSchema._fields_ = [
     ("format", C.c_char_p), ("name", C.c_char_p), ("metadata", C.c_char_p), ("flags", C.c_int64),
     ("n_children", C.c_int64), ("children", C.POINTER(C.POINTER(ArrowSchema))),
@@ -66,6 +72,10 @@ SIGNATURES = {
     "bgpu_agg_create": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(ArrowSchema), C.POINTER(C.c_int32), C.c_int32,
                                   C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_char_p), C.c_int32,
                                   C.POINTER(C.c_void_p)]),
+    "bgpu_agg_create_expr": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(ArrowSchema), C.POINTER(C.c_int32), C.c_int32,
+                                       C.POINTER(C.c_int32), C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_char_p),
+                                       C.c_int32, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]),
+    "bgpu_agg_last_path": (C.c_char_p, [C.c_void_p]),
     "bgpu_agg_update": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bgpu_agg_emit": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "bgpu_agg_num_groups": (C.c_int64, [C.c_void_p]),

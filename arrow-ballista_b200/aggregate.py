@@ -42,23 +42,44 @@ class GpuAggregateExec:
     In Final modes the batches passed to `update` are Partial state batches (group columns first).
     """
 
-    def __init__(self, ctx, mode, group_by, aggr_expr, input_schema):
+    def __init__(self, ctx, mode, group_by, aggr_expr, input_schema, filter=None):
+        """aggr_expr: [(fn, arg, name)], arg = None (COUNT(*)), a column index, or an `expr.Expr` tree evaluated
+        inside the aggregate as DataFusion does; `filter` = an optional `expr.Expr` predicate fused below the
+        aggregate (Q1's FilterExec, /root/reference/benchmarks/queries/q1.sql)."""
+        from ._lib import ExprNode
+        from .expr import Expr, col
+
         self.ctx, self.mode, self.input_schema = ctx, mode, input_schema
         self.group_by = list(group_by)
-        self.aggr_expr = [(AggregateFunction.parse(f), (-1 if c is None else int(c)), str(n)) for f, c, n in aggr_expr]
+        self.aggr_expr = []
+        nodes, offsets = [], [0]
+        for f, c, n in aggr_expr:
+            e = None if c is None else (c if hasattr(c, "to_nodes") else col(int(c)))
+            self.aggr_expr.append((AggregateFunction.parse(f), e, str(n)))
+            if e is not None:
+                nodes.extend(e.to_nodes())
+            offsets.append(len(nodes))
+        fnodes = filter.to_nodes() if filter is not None else []
         s = ArrowSchema()
         input_schema._export_to_c(C.addressof(s))
         n = len(self.aggr_expr)
         gcols = (C.c_int32 * len(self.group_by))(*self.group_by)
         fns = (C.c_int32 * max(n, 1))(*[f for f, _, _ in self.aggr_expr])
-        cols = (C.c_int32 * max(n, 1))(*[c for _, c, _ in self.aggr_expr])
         names = (C.c_char_p * max(n, 1))(*[nm.encode() for _, _, nm in self.aggr_expr])
+        node_arr = (ExprNode * max(len(nodes), 1))(*nodes)
+        off_arr = (C.c_int32 * len(offsets))(*offsets)
+        filt_arr = (ExprNode * max(len(fnodes), 1))(*fnodes)
         self._h = C.c_void_p()
         try:
-            ctx.check(lib().bgpu_agg_create(ctx._h, mode, C.byref(s), gcols, len(self.group_by), fns, cols, names, n,
-                                            C.byref(self._h)))
+            ctx.check(lib().bgpu_agg_create_expr(ctx._h, mode, C.byref(s), gcols, len(self.group_by), fns, node_arr,
+                                                 off_arr, names, n, filt_arr, len(fnodes), C.byref(self._h)))
         finally:
             _release(s)
+
+    @property
+    def last_path(self):
+        """Which kernel path the last update took (introspection)."""
+        return lib().bgpu_agg_last_path(self._h).decode()
 
     def update(self, batch):
         """update_batch / merge_batch with one batch (DeviceBatch, or a host RecordBatch that is uploaded)."""

@@ -1,0 +1,74 @@
+// Host-side state of one grouped aggregate (bgpu_agg), shared by aggregate.cu (plan building) and
+// aggregate_run.cu (update / emit).
+#pragma once
+#include <memory>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "agg_plan.h"
+
+struct PhysAcc {
+  int32_t op = 0;
+  int32_t value = -1;  // index into bgpu_agg::values
+  int32_t words = 1;
+  DevAllocPtr buf;  // words * max_groups u64
+};
+struct LogicalAgg {
+  int32_t fn = 0;
+  int32_t phys[2] = {-1, -1};  // Sum: [sum]; Count: [count]; Avg: [count, sum]
+  std::string name;
+  std::string sum_format, result_format;  // Arrow formats of the state sum and of the final value
+  bool decimal = false;
+  int scale_up = 0;  // Avg(decimal): result scale - sum scale
+};
+
+constexpr int kFusedRungs = 3;
+
+struct bgpu_agg {
+  bgpu_ctx* ctx = nullptr;
+  int32_t mode = 0;
+  bool final_mode = false;
+  std::vector<Column> fields;       // raw input schema
+  std::vector<int32_t> group_cols;  // indices into `fields`
+  std::vector<int32_t> key_off, key_width;  // packed-key layout per group column
+  int32_t key_words = 1;
+  std::vector<bgpu::HValue> values;  // distinct aggregate arguments; a value that extends another follows it
+  std::vector<bool> value_from_prev;
+  std::vector<bgpu::HFilterTerm> filter;
+  std::vector<PhysAcc> phys;  // sorted by value
+  std::vector<LogicalAgg> aggs;
+  // group table
+  uint32_t max_groups = 0, n_groups = 0;
+  DevAllocPtr entries, key0, key1, kmeta, counters /* u32 [0]=n_groups, [1..4]=flags */, seen, scratch;
+  bool seen_tracking = false;
+  int fused_rung = 0;  // first rung of the fused ladder still worth trying; kFusedRungs = two-pass only
+  // dictionary-typed group columns are keyed by value: the aggregate keeps one canonical dictionary per column
+  // (host copy; uploaded at emit) and maps every batch dictionary onto it
+  struct DictState {
+    std::unordered_map<std::string, int32_t> index;
+    std::vector<std::string> values;
+    std::string value_format = "u";
+    ColKind value_kind = K_UTF8;
+    std::shared_ptr<Column> last;  // last batch dictionary seen (kept alive so its identity cannot be recycled)
+    DevAllocPtr last_remap;        // nullptr = identity
+  };
+  std::vector<DictState> dicts;
+  bool emitted = false;
+  // introspection for tests / bench: which path the last update took ("fused256x2", "fused256", "fused128",
+  // "shared", "global")
+  std::string last_path;
+
+  explicit bgpu_agg(bgpu_ctx* c) : ctx(c) { ctx_retain(c); }
+  ~bgpu_agg() { ctx_release(ctx); }
+  uint32_t* d_n_groups() { return (uint32_t*)counters->p; }
+  int32_t* d_flags() { return (int32_t*)counters->p + 1; }
+  bgpu::GroupTable table() {
+    return bgpu::GroupTable{(unsigned long long*)entries->p, max_groups * 2 - 1, max_groups, (uint64_t*)key0->p,
+                            key1 ? (uint64_t*)key1->p : nullptr, (uint32_t*)kmeta->p, d_n_groups(), d_flags()};
+  }
+};
+
+int agg_launch_grid(bgpu_ctx* ctx, int64_t n, int per_block);
+// (Re)allocate the table and accumulators for `new_max` groups, keeping the first `keep` groups.
+int agg_resize(bgpu_agg* g, uint32_t new_max, uint32_t keep);

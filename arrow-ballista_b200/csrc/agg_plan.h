@@ -1,0 +1,157 @@
+// Kernel-side plans of the grouped aggregate (POD, passed as __grid_constant__ kernel parameters) and the host-side
+// compiler from the ABI's postfix expression programs (include/bgpu.h, bgpu_agg_create_expr) to those plans.
+//
+// Reference semantics restated here (none of it is in /root/reference):
+//   * aggregate input expressions are evaluated inside the aggregate stream (plan text planner.rs:379);
+//   * arrow-arith 49 numeric.rs decimal_op: +/- rescale both sides to max(s1,s2) and are i128-checked, * adds the
+//     scales and is i128-checked; DataFusion coerces an Int64 literal next to a Decimal128 to Decimal128(20,0);
+//   * Int64 arithmetic in DataFusion 34's BinaryExpr is add_wrapping/sub_wrapping/mul_wrapping; Float64 is IEEE.
+#pragma once
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "internal.h"
+
+namespace bgpu {
+
+enum ValKind : int32_t { V_NONE = 0, V_I8, V_I16, V_I32, V_I64, V_U8, V_U16, V_U32, V_U64, V_F32, V_F64, V_I128 };
+enum AccOp : int32_t { OP_ADD_I64 = 0, OP_ADD_I128 = 1, OP_ADD_F64 = 2, OP_COUNT = 3 };
+enum ValClass : int32_t { CLS_NONE = 0 /* COUNT(*): no value */, CLS_I64 = 1, CLS_I128 = 2, CLS_F64 = 3 };
+
+constexpr int kMaxGroupCols = 8;
+constexpr int kMaxAcc = 24;
+constexpr int kMaxValues = 24;
+constexpr int kMaxFactors = 3;
+constexpr int kMaxFilterTerms = 4;
+
+// ---- group keys ---------------------------------------------------------------------------------------------
+struct KeyCol {
+  const void* values;
+  const int32_t* offsets;
+  const uint8_t* validity;
+  const int32_t* remap;  // K_DICT32: batch dictionary index -> canonical index (-1 = null value); nullptr = identity
+  int32_t kind;          // ColKind
+  int32_t width;         // fixed width; utf8: max inline bytes (excluding the length byte)
+  int32_t byte_off;      // position inside the 16-byte packed key
+  int32_t pad;
+};
+struct KeyPlan {
+  KeyCol cols[kMaxGroupCols];
+  int32_t n;
+  int32_t words;  // 1: packed key fits 8 bytes, 2: 16 bytes
+};
+
+struct GroupTable {
+  unsigned long long* entries;  // (tag << 32) | state; state 0 empty, 1 busy, >= 2: gid + 2
+  uint32_t mask;                // capacity - 1 (capacity = 2 * max_groups, power of two)
+  uint32_t max_groups;
+  uint64_t* key0;               // packed keys of group gid (dense)
+  uint64_t* key1;
+  uint32_t* kmeta;              // null bits of the key columns
+  uint32_t* n_groups;           // device counter
+  int32_t* flags;               // [0] capacity overflow, [1] string key too long, [2] arithmetic overflow,
+                                // [3] private tier abort (a group id beyond the private capacity)
+};
+
+// ---- value expressions: product of up to three factors, each `x`, `x + y` or `x - y` ------------------------------
+struct Atom {
+  const void* col;          // nullptr: literal
+  const uint8_t* validity;  // nullptr: no nulls in this batch
+  uint64_t lit_lo, lit_hi;  // literal, already rescaled to the factor's scale
+  uint64_t mul;             // column rescale multiplier 10^k (1 = none)
+  int32_t vk;               // ValKind of the column
+  int32_t pad;
+};
+struct Factor {
+  Atom x, y;
+  int32_t op;  // 0: x only, 1: x + y, 2: x - y
+  int32_t pad;
+};
+struct ValueExpr {
+  Factor f[kMaxFactors];
+  int32_t n_factors;
+  int32_t cls;          // ValClass
+  int32_t from_prev;    // 1: the first factor is the previous value's result (common sub-expression)
+  int32_t acc_begin;    // accumulators [acc_begin, acc_end) consume this value
+  int32_t acc_end;
+  int32_t pad;
+};
+struct ValuePlan {
+  ValueExpr v[kMaxValues];
+  int32_t n;
+  int32_t pad;
+};
+
+struct FilterTerm {
+  const void* col;
+  const uint8_t* validity;
+  uint64_t lit_lo, lit_hi;  // i128 literal (integers, dates, decimals at the column's scale) or f64 bits in lit_lo
+  int32_t vk;
+  int32_t cmp;  // BGPU_X_LT .. BGPU_X_NE
+};
+struct FilterPlan {
+  FilterTerm t[kMaxFilterTerms];
+  int32_t n;
+  int32_t pad;
+};
+
+// ---- accumulators -------------------------------------------------------------------------------------------
+struct AccK {
+  uint64_t* out;     // dense accumulator array: words * max_groups u64
+  int32_t op;        // AccOp
+  int32_t words;     // 1 or 2
+  int32_t word0;     // first word of this accumulator inside a group's private/shared state
+  int32_t seen_bit;  // bit in seen[gid]
+  int32_t alias;     // >= 0: this batch it equals accumulator `alias` (counts over null-free values); skip in the
+                     // row loop and add the alias' partial at flush time. -1 otherwise
+  int32_t pad;
+};
+struct AccPlan {
+  AccK a[kMaxAcc];
+  int32_t n;
+  int32_t total_words;
+  uint32_t* seen;  // per-group bitmask of accumulators that saw a non-null input; nullptr = not tracked yet
+};
+
+// ---- host-side logical description (independent of any batch) -----------------------------------------------------
+struct HAtom {
+  bool is_col = false;
+  int32_t col = -1;
+  __int128 lit = 0;       // literal at its own scale
+  double flit = 0.0;
+  int32_t precision = 0, scale = 0;  // decimal type of this atom (ints: scale 0)
+  int32_t cls = CLS_NONE;
+  int32_t vk = V_NONE;    // column: ValKind of the column it must be bound to
+};
+struct HFactor {
+  HAtom x, y;
+  int32_t op = 0;
+  int32_t precision = 0, scale = 0;
+  __int128 x_mul = 1, y_mul = 1;  // rescale multipliers to the factor's scale
+};
+struct HValue {
+  std::vector<HFactor> f;
+  int32_t cls = CLS_NONE;
+  int32_t precision = 0, scale = 0;  // decimal result type
+  int32_t vk = V_NONE;               // plain column: its ValKind (drives Sum's result type)
+  bool plain_column() const { return f.size() == 1 && f[0].op == 0 && f[0].x.is_col; }
+};
+struct HFilterTerm {
+  int32_t col = -1, cmp = 0, vk = V_NONE;
+  __int128 lit = 0;
+  double flit = 0.0;
+};
+
+// Compile one aggregate-argument program. `fields` is the raw input schema. Returns BGPU_OK or fails ctx.
+int compile_value(bgpu_ctx* ctx, const std::vector<Column>& fields, const bgpu_expr_node* nodes, int32_t n,
+                  HValue* out);
+int compile_filter(bgpu_ctx* ctx, const std::vector<Column>& fields, const bgpu_expr_node* nodes, int32_t n,
+                   std::vector<HFilterTerm>* out);
+ValKind vk_of(const Column& c);
+bool values_equal(const HValue& a, const HValue& b);
+// b == a * (one more factor)?
+bool value_extends(const HValue& a, const HValue& b);
+
+}  // namespace bgpu

@@ -1,0 +1,619 @@
+// K4/K5 host side, part 2: binding a batch to the kernel plans, choosing the path, update and emit.
+//
+// The reference's stream does, per batch: evaluate group and argument expressions, intern keys -> dense group ids,
+// then one update per accumulator. Here (kernels in agg_kernels.cuh):
+//   fused path     one kernel does all of that per row with thread-private shared-memory accumulators; used while
+//                  the number of groups fits the private capacity (a ladder of three configurations), committed by a
+//                  second tiny kernel. Aborts cleanly (nothing committed) when a CTA meets too many groups.
+//   two-pass path  intern_kernel (idempotent; re-run after growing the table on overflow) then accumulate_kernel
+//                  with replicated shared-memory atomics or global atomics.
+// Int64/Decimal128 sums are wrapping two's-complement adds, so any order is bit-exact; Float64 sums carry the north
+// star's 1e-9 tolerance (the fused path is reproducible run to run, the atomic path is not).
+#include <string.h>
+
+#include <algorithm>
+
+#include <cub/device/device_scan.cuh>
+
+#include "agg_host.h"
+#include "agg_kernels.cuh"
+
+using namespace bgpu;
+
+namespace {
+uint32_t next_pow2(uint64_t x) {
+  uint64_t p = 1;
+  while (p < x) p <<= 1;
+  return (uint32_t)std::min<uint64_t>(p, 1ULL << 31);
+}
+int vk_width(int vk) {
+  switch (vk) {
+    case V_I128: return 16;
+    case V_I64: case V_U64: case V_F64: return 8;
+    case V_I32: case V_U32: case V_F32: return 4;
+    case V_I16: case V_U16: return 2;
+    default: return 1;
+  }
+}
+bool same_shape(const Column& a, const Column& b) { return a.kind == b.kind && a.width == b.width; }
+}  // namespace
+
+int agg_resize(bgpu_agg* g, uint32_t new_max, uint32_t keep) {
+  bgpu_ctx* ctx = g->ctx;
+  DevAllocPtr entries, key0, key1, kmeta, seen;
+  BGPU_TRY(dev_alloc(ctx, (size_t)new_max * 2 * 8, &entries));
+  BGPU_TRY(dev_alloc(ctx, (size_t)new_max * 8, &key0));
+  if (g->key_words > 1) BGPU_TRY(dev_alloc(ctx, (size_t)new_max * 8, &key1));
+  BGPU_TRY(dev_alloc(ctx, (size_t)new_max * 4, &kmeta));
+  BGPU_CUDA(ctx, cudaMemsetAsync(entries->p, 0, (size_t)new_max * 2 * 8, ctx->stream));
+  if (keep) {
+    BGPU_CUDA(ctx, cudaMemcpyAsync(key0->p, g->key0->p, (size_t)keep * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (key1) BGPU_CUDA(ctx, cudaMemcpyAsync(key1->p, g->key1->p, (size_t)keep * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    BGPU_CUDA(ctx, cudaMemcpyAsync(kmeta->p, g->kmeta->p, (size_t)keep * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+  }
+  for (PhysAcc& p : g->phys) {
+    DevAllocPtr nb;
+    const size_t bytes = (size_t)new_max * p.words * 8;
+    BGPU_TRY(dev_alloc(ctx, bytes, &nb));
+    const size_t keep_bytes = (size_t)keep * p.words * 8;
+    if (keep) BGPU_CUDA(ctx, cudaMemcpyAsync(nb->p, p.buf->p, keep_bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    BGPU_CUDA(ctx, cudaMemsetAsync((char*)nb->p + keep_bytes, 0, bytes - keep_bytes, ctx->stream));
+    p.buf = nb;
+  }
+  if (g->seen_tracking) {
+    BGPU_TRY(dev_alloc(ctx, (size_t)new_max * 4, &seen));
+    if (keep) BGPU_CUDA(ctx, cudaMemcpyAsync(seen->p, g->seen->p, (size_t)keep * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    BGPU_CUDA(ctx, cudaMemsetAsync((char*)seen->p + (size_t)keep * 4, 0, (size_t)(new_max - keep) * 4, ctx->stream));
+    g->seen = seen;
+  }
+  g->entries = entries; g->key0 = key0; g->key1 = key1; g->kmeta = kmeta;
+  g->max_groups = new_max;
+  if (keep) {
+    rehash_kernel<<<agg_launch_grid(ctx, keep, kAggThreads), kAggThreads, 0, ctx->stream>>>(g->table(), keep, g->key_words);
+    ctx->launches++;
+    BGPU_CUDA(ctx, cudaGetLastError());
+  }
+  return BGPU_OK;
+}
+
+// Map the batch's dictionary onto the aggregate's canonical dictionary of group column i (host side: dictionaries
+// are small next to the batches that reference them). *remap = device array or nullptr for the identity.
+static int canonicalize_dictionary(bgpu_agg* g, int32_t i, const Column& c, const int32_t** remap) {
+  bgpu_ctx* ctx = g->ctx;
+  bgpu_agg::DictState& ds = g->dicts[(size_t)i];
+  *remap = nullptr;
+  if (ds.last && ds.last == c.dict && !c.dict->owned.empty()) {
+    *remap = ds.last_remap ? (const int32_t*)ds.last_remap->p : nullptr;
+    return BGPU_OK;
+  }
+  const Column& d = *c.dict;
+  if (d.kind != K_UTF8 && d.kind != K_BINARY)
+    return ctx->fail(BGPU_EUNSUPPORTED, "group column " + c.name + ": only Dictionary<Int32, Utf8|Binary> keys are supported");
+  ds.value_format = d.format;
+  ds.value_kind = d.kind;
+  const int64_t n = d.length;
+  std::vector<int32_t> offs((size_t)n + 1, 0);
+  std::vector<uint8_t> valid;
+  std::vector<char> bytes;
+  if (n) {
+    BGPU_CUDA(ctx, cudaMemcpyAsync(offs.data(), d.offsets, (size_t)(n + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (d.validity) {
+      valid.resize((size_t)((n + 7) / 8));
+      BGPU_CUDA(ctx, cudaMemcpyAsync(valid.data(), d.validity, valid.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    bytes.resize((size_t)(offs[(size_t)n] - offs[0]));
+    if (!bytes.empty()) {
+      BGPU_CUDA(ctx, cudaMemcpyAsync(bytes.data(), (const char*)d.values + offs[0], bytes.size(), cudaMemcpyDeviceToHost, ctx->stream));
+      BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+  }
+  std::vector<int32_t> map((size_t)n);
+  bool identity = true;
+  for (int64_t j = 0; j < n; j++) {
+    int32_t id = -1;
+    if (valid.empty() || ((valid[(size_t)(j >> 3)] >> (j & 7)) & 1)) {
+      std::string v(bytes.data() + (offs[(size_t)j] - offs[0]), (size_t)(offs[(size_t)j + 1] - offs[(size_t)j]));
+      auto it = ds.index.find(v);
+      if (it == ds.index.end()) {
+        id = (int32_t)ds.values.size();
+        ds.index.emplace(v, id);
+        ds.values.push_back(std::move(v));
+      } else {
+        id = it->second;
+      }
+    }
+    map[(size_t)j] = id;
+    identity &= id == (int32_t)j;
+  }
+  ds.last = c.dict;
+  ds.last_remap = nullptr;
+  if (!identity) {
+    BGPU_TRY(dev_alloc(ctx, (size_t)n * 4, &ds.last_remap));
+    BGPU_CUDA(ctx, cudaMemcpyAsync(ds.last_remap->p, map.data(), (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // `map` dies here
+    *remap = (const int32_t*)ds.last_remap->p;
+  }
+  return BGPU_OK;
+}
+
+// The canonical dictionary of group column i as a device column (emit).
+static int upload_canonical_dictionary(bgpu_agg* g, size_t i, std::shared_ptr<Column>* out) {
+  bgpu_ctx* ctx = g->ctx;
+  const bgpu_agg::DictState& ds = g->dicts[i];
+  auto d = std::make_shared<Column>();
+  d->name = ""; d->format = ds.value_format; d->kind = ds.value_kind; d->flags = ARROW_FLAG_NULLABLE;
+  d->length = (int64_t)ds.values.size(); d->null_count = 0;
+  std::vector<int32_t> offs(ds.values.size() + 1, 0);
+  std::string bytes;
+  for (size_t j = 0; j < ds.values.size(); j++) {
+    bytes += ds.values[j];
+    offs[j + 1] = (int32_t)bytes.size();
+  }
+  DevAllocPtr o, b;
+  BGPU_TRY(dev_alloc(ctx, offs.size() * 4, &o));
+  BGPU_TRY(dev_alloc(ctx, bytes.size(), &b));
+  BGPU_CUDA(ctx, cudaMemcpyAsync(o->p, offs.data(), offs.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+  if (!bytes.empty()) BGPU_CUDA(ctx, cudaMemcpyAsync(b->p, bytes.data(), bytes.size(), cudaMemcpyHostToDevice, ctx->stream));
+  BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  d->offsets = (int32_t*)o->p; d->values = b->p; d->data_bytes = (int64_t)bytes.size();
+  d->owned.push_back(o); d->owned.push_back(b);
+  *out = d;
+  return BGPU_OK;
+}
+
+// ---- binding ----------------------------------------------------------------------------------------------------
+struct Bound {
+  KeyPlan kp{};
+  FilterPlan fp{};
+  ValuePlan vp{};
+  AccPlan ap{};
+  bool any_validity = false;
+  std::vector<bool> value_nullable;
+};
+
+static int bind_atom(bgpu_ctx* ctx, const bgpu_batch* batch, const HAtom& h, __int128 mul, int32_t cls, Atom* a,
+                     bool* nullable) {
+  *a = Atom{};
+  a->mul = 1;
+  if (!h.is_col) {
+    if (cls == CLS_F64) {
+      memcpy(&a->lit_lo, &h.flit, 8);
+    } else {
+      __int128 v = h.lit;
+      if (cls == CLS_I128 && __builtin_mul_overflow(h.lit, mul, &v))
+        return ctx->fail(BGPU_EOVERFLOW, "Overflow happened on rescaling a decimal literal");
+      a->lit_lo = (uint64_t)v;
+      a->lit_hi = (uint64_t)((unsigned __int128)v >> 64);
+    }
+    return BGPU_OK;
+  }
+  if (h.col < 0 || h.col >= (int32_t)batch->cols.size()) return ctx->fail(BGPU_EINVAL, "batch has too few columns");
+  const Column& c = batch->cols[(size_t)h.col];
+  if (c.kind != K_FIXED || c.width != vk_width(h.vk))
+    return ctx->fail(BGPU_EINVAL, "aggregate input column " + c.name + " has an unexpected type");
+  a->col = c.values;
+  a->validity = c.validity;
+  a->vk = h.vk;
+  if (mul != 1) {
+    if (mul > (__int128)UINT64_MAX) return ctx->fail(BGPU_EUNSUPPORTED, "decimal rescale factor beyond 10^19");
+    a->mul = (uint64_t)mul;
+  }
+  if (c.validity) *nullable = true;
+  return BGPU_OK;
+}
+
+static int bind_batch(bgpu_agg* g, const bgpu_batch* batch, Bound* b) {
+  bgpu_ctx* ctx = g->ctx;
+  const int32_t n_group = (int32_t)g->group_cols.size();
+  b->kp.n = n_group;
+  b->kp.words = g->key_words;
+  for (int32_t i = 0; i < n_group; i++) {
+    const int32_t bc = g->final_mode ? i : g->group_cols[(size_t)i];
+    if (bc >= (int32_t)batch->cols.size()) return ctx->fail(BGPU_EINVAL, "batch has too few columns");
+    const Column& c = batch->cols[(size_t)bc];
+    const Column& f = g->fields[(size_t)g->group_cols[(size_t)i]];
+    if (!same_shape(c, f)) return ctx->fail(BGPU_EINVAL, "group column " + f.name + " does not match input_schema");
+    const int32_t* remap = nullptr;
+    if (c.kind == K_DICT32) BGPU_TRY(canonicalize_dictionary(g, i, c, &remap));
+    b->kp.cols[i] = KeyCol{c.values, c.offsets, c.validity, remap, c.kind, g->key_width[(size_t)i], g->key_off[(size_t)i], 0};
+  }
+  b->fp.n = (int32_t)g->filter.size();
+  for (size_t i = 0; i < g->filter.size(); i++) {
+    const HFilterTerm& h = g->filter[i];
+    if (h.col >= (int32_t)batch->cols.size()) return ctx->fail(BGPU_EINVAL, "batch has too few columns");
+    const Column& c = batch->cols[(size_t)h.col];
+    if (c.kind != K_FIXED || c.width != vk_width(h.vk))
+      return ctx->fail(BGPU_EINVAL, "filter column " + c.name + " has an unexpected type");
+    FilterTerm& t = b->fp.t[i];
+    t = FilterTerm{c.values, c.validity, 0, 0, h.vk, h.cmp};
+    if (h.vk == V_F64 || h.vk == V_F32) {
+      memcpy(&t.lit_lo, &h.flit, 8);
+    } else {
+      t.lit_lo = (uint64_t)h.lit;
+      t.lit_hi = (uint64_t)((unsigned __int128)h.lit >> 64);
+    }
+  }
+  b->vp.n = (int32_t)g->values.size();
+  b->value_nullable.assign(g->values.size(), false);
+  for (size_t vi = 0; vi < g->values.size(); vi++) {
+    const HValue& h = g->values[vi];
+    ValueExpr& e = b->vp.v[vi];
+    e = ValueExpr{};
+    e.cls = h.cls;
+    e.n_factors = (int32_t)h.f.size();
+    e.from_prev = g->value_from_prev[vi] ? 1 : 0;
+    bool nullable = e.from_prev ? (bool)b->value_nullable[vi - 1] : false;
+    for (size_t fi = 0; fi < h.f.size(); fi++) {
+      const HFactor& hf = h.f[fi];
+      Factor& f = e.f[fi];
+      f.op = hf.op;
+      BGPU_TRY(bind_atom(ctx, batch, hf.x, hf.x_mul, h.cls, &f.x, &nullable));
+      if (hf.op) BGPU_TRY(bind_atom(ctx, batch, hf.y, hf.y_mul, h.cls, &f.y, &nullable));
+    }
+    b->value_nullable[vi] = nullable;
+    b->any_validity |= nullable;
+  }
+  b->ap.n = (int32_t)g->phys.size();
+  for (int32_t i = 0; i < b->ap.n; i++) {
+    const PhysAcc& p = g->phys[(size_t)i];
+    b->ap.a[i] = AccK{(uint64_t*)p.buf->p, p.op, p.words, 0, i, -1, 0};
+  }
+  for (int32_t vi = 0; vi < b->vp.n; vi++) {
+    int32_t lo = b->ap.n, hi = 0;
+    for (int32_t i = 0; i < b->ap.n; i++)
+      if (g->phys[(size_t)i].value == vi) { lo = std::min(lo, i); hi = std::max(hi, i + 1); }
+    b->vp.v[vi].acc_begin = lo < hi ? lo : 0;
+    b->vp.v[vi].acc_end = lo < hi ? hi : 0;
+  }
+  return BGPU_OK;
+}
+
+// Assign private/shared word offsets; with `alias_counts`, counts over null-free values all equal the row count of
+// the group, so only the first is kept live and the others alias it (fused path only).
+static void layout_words(const bgpu_agg* g, Bound* b, bool alias_counts) {
+  int32_t first_count = -1, w = 0;
+  for (int32_t i = 0; i < b->ap.n; i++) {
+    AccK& a = b->ap.a[i];
+    a.alias = -1;
+    if (alias_counts && a.op == OP_COUNT && !b->value_nullable[(size_t)g->phys[(size_t)i].value]) {
+      if (first_count < 0) first_count = i;
+      else a.alias = first_count;
+    }
+    if (a.alias < 0) {
+      a.word0 = w;
+      w += a.words;
+    }
+  }
+  b->ap.total_words = w;
+}
+
+static int read_counters(bgpu_agg* g, uint32_t* h) {
+  bgpu_ctx* ctx = g->ctx;
+  uint32_t* pin = (uint32_t*)ctx->pinned;
+  BGPU_CUDA(ctx, cudaMemcpyAsync(pin, g->counters->p, 32, cudaMemcpyDeviceToHost, ctx->stream));
+  BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(h, pin, 32);
+  return BGPU_OK;
+}
+static int write_counters(bgpu_agg* g, const uint32_t* h) {
+  bgpu_ctx* ctx = g->ctx;
+  uint32_t* pin = (uint32_t*)ctx->pinned + 16;
+  memcpy(pin, h, 32);
+  BGPU_CUDA(ctx, cudaMemcpyAsync(g->counters->p, pin, 32, cudaMemcpyHostToDevice, ctx->stream));
+  BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return BGPU_OK;
+}
+
+// counters layout: [0] n_groups, [1] table overflow, [2] string key too long, [3] arithmetic overflow, [4] fused abort
+static int check_common_flags(bgpu_agg* g, const uint32_t* h) {
+  bgpu_ctx* ctx = g->ctx;
+  if (h[2]) return ctx->fail(BGPU_EUNSUPPORTED, "string group key longer than the packed-key budget (" +
+                                                    std::to_string(16 / std::max<size_t>(1, g->group_cols.size()) - 1) + " bytes)");
+  if (h[3]) return ctx->fail(BGPU_EOVERFLOW, "Arithmetic overflow in an aggregate argument (Decimal128)");
+  return BGPU_OK;
+}
+
+// Table overflowed during a pass: groups [0, max_groups) are intact; size for the distinct count observed, rebuild.
+static int grow_after_overflow(bgpu_agg* g, uint32_t counter) {
+  const uint32_t keep = g->max_groups;
+  if (counter > 0x70000000u) return g->ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
+  const uint32_t new_max = next_pow2(std::max<uint64_t>((uint64_t)counter + counter / 4, (uint64_t)keep * 2));
+  const uint32_t reset[8] = {keep, 0, 0, 0, 0, 0, 0, 0};
+  BGPU_TRY(write_counters(g, reset));
+  return agg_resize(g, new_max, keep);
+}
+
+// accumulator / seen arrays move when the table grows
+static void refresh_pointers(bgpu_agg* g, Bound* b) {
+  for (int32_t i = 0; i < b->ap.n; i++) b->ap.a[i].out = (uint64_t*)g->phys[(size_t)i].buf->p;
+  b->ap.seen = g->seen_tracking ? (uint32_t*)g->seen->p : nullptr;
+}
+
+struct Rung { int threads; int rows; size_t smem_cap; const char* name; };
+
+template <int T, int R>
+static int launch_fused(bgpu_agg* g, const Bound& b, const FusedArgs& fa, int grid, size_t smem, int64_t n_rows) {
+  bgpu_ctx* ctx = g->ctx;
+  BGPU_CUDA(ctx, cudaFuncSetAttribute(fused_private_kernel<T, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  fused_private_kernel<T, R><<<grid, T, smem, ctx->stream>>>(b.kp, g->table(), b.fp, b.vp, b.ap, fa, n_rows);
+  ctx->launches++;
+  BGPU_CUDA(ctx, cudaGetLastError());
+  return BGPU_OK;
+}
+
+// Try the fused ladder. *done = true when the batch has been committed.
+static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
+  bgpu_ctx* ctx = g->ctx;
+  *done = false;
+  layout_words(g, b, true);
+  const int W = b->ap.total_words;
+  if (W == 0) { g->fused_rung = kFusedRungs; return BGPU_OK; }
+  const size_t smem_max = ctx->smem_optin - 1024;
+  const Rung rungs[kFusedRungs] = {{256, 4, smem_max / 2 - 1024, "fused256x2"}, {256, 4, smem_max, "fused256"},
+                                   {128, 8, smem_max, "fused128"}};
+  while (g->fused_rung < kFusedRungs) {
+    const Rung& rg = rungs[g->fused_rung];
+    const int T = rg.threads;
+    // private capacity: largest G with G*W*T*8 + seen + key cache <= cap (cache = 2G slots rounded up, 24 B each)
+    uint32_t G = (uint32_t)(rg.smem_cap / ((size_t)W * T * 8 + 4 + 4 * 24));
+    if (G > 4096) G = 4096;
+    if (G < 1 || G < g->n_groups) { g->fused_rung++; continue; }
+    const uint32_t slots = std::max<uint32_t>(16, next_pow2((uint64_t)G * 2));
+    const size_t smem = (size_t)G * W * T * 8 + (size_t)((G + 1) & ~1u) * 4 + (size_t)slots * 24;
+    if (smem > smem_max) { g->fused_rung++; continue; }
+    int occ = 1;
+    if (T == 256) {
+      BGPU_CUDA(ctx, cudaFuncSetAttribute(fused_private_kernel<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      BGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_private_kernel<256, 4>, T, smem));
+    } else {
+      BGPU_CUDA(ctx, cudaFuncSetAttribute(fused_private_kernel<128, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      BGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_private_kernel<128, 8>, T, smem));
+    }
+    occ = std::max(1, occ);
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ceil_div64(n_rows, (int64_t)T * rg.rows), (int64_t)ctx->sm_count * occ));
+    const size_t scratch_bytes = (size_t)grid * fused_slab_words(G, W) * 8;
+    if (!g->scratch || g->scratch->bytes < scratch_bytes) BGPU_TRY(dev_alloc(ctx, scratch_bytes, &g->scratch));
+    FusedArgs fa{(uint64_t*)g->scratch->p, G, slots, rg.rows, 0};
+    for (int attempt = 0;; attempt++) {
+      if (T == 256) BGPU_TRY((launch_fused<256, 4>(g, *b, fa, grid, smem, n_rows)));
+      else BGPU_TRY((launch_fused<128, 8>(g, *b, fa, grid, smem, n_rows)));
+      uint32_t h[8];
+      BGPU_TRY(read_counters(g, h));
+      BGPU_TRY(check_common_flags(g, h));
+      if (h[1]) {  // global table overflow: grow and run the same rung again
+        if (attempt >= 4) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
+        BGPU_TRY(grow_after_overflow(g, h[0]));
+        refresh_pointers(g, b);
+        continue;
+      }
+      if (h[4]) {  // some CTA met a group id >= G: nothing was committed; the groups interned so far stay
+        h[4] = 0;
+        BGPU_TRY(write_counters(g, h));
+        g->n_groups = h[0];
+        break;
+      }
+      g->n_groups = h[0];
+      if (b->any_validity && !g->seen_tracking) return ctx->fail(BGPU_EINVAL, "internal: seen tracking not set up");
+      commit_kernel<<<agg_launch_grid(ctx, std::max<uint32_t>(1, g->n_groups * (uint32_t)b->ap.n), kAggThreads), kAggThreads, 0,
+                      ctx->stream>>>(b->ap, (const uint64_t*)g->scratch->p, (uint32_t)grid, G, g->n_groups);
+      ctx->launches++;
+      BGPU_CUDA(ctx, cudaGetLastError());
+      g->last_path = rg.name;
+      *done = true;
+      return BGPU_OK;
+    }
+    g->fused_rung++;
+  }
+  return BGPU_OK;
+}
+
+static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
+  bgpu_ctx* ctx = g->ctx;
+  layout_words(g, b, false);
+  DevAllocPtr gids;
+  BGPU_TRY(dev_alloc(ctx, (size_t)n_rows * 4, &gids));
+  for (int attempt = 0;; attempt++) {
+    const int grid = (int)std::min<int64_t>(ceil_div64(n_rows, kAggThreads), (int64_t)ctx->sm_count * 8);
+    intern_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(b->kp, g->table(), b->fp, n_rows, (uint32_t*)gids->p);
+    ctx->launches++;
+    BGPU_CUDA(ctx, cudaGetLastError());
+    uint32_t h[8];
+    BGPU_TRY(read_counters(g, h));
+    BGPU_TRY(check_common_flags(g, h));
+    if (!h[1]) {
+      g->n_groups = h[0];
+      break;
+    }
+    if (attempt >= 4) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
+    BGPU_TRY(grow_after_overflow(g, h[0]));
+  }
+  refresh_pointers(g, b);
+  if (b->ap.n == 0) { g->last_path = "intern"; return BGPU_OK; }
+  const uint32_t ng = g->n_groups;
+  const size_t limit = std::min<size_t>(ctx->smem_optin, 200 * 1024);
+  const size_t group_bytes = (size_t)b->ap.total_words * 8;
+  if ((size_t)ng * group_bytes + (size_t)ng * 4 <= limit / 2) {
+    int replicas = (int)std::min<size_t>(32, (limit / 2 - (size_t)ng * 4) / std::max<size_t>(1, (size_t)ng * group_bytes));
+    if (replicas < 1) replicas = 1;
+    const size_t smem = (size_t)ng * group_bytes * replicas + (size_t)ng * 4;
+    BGPU_CUDA(ctx, cudaFuncSetAttribute(accumulate_kernel<TIER_SHARED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 1;
+    BGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, accumulate_kernel<TIER_SHARED>, kAggThreads, smem));
+    const int grid = (int)std::min<int64_t>(ceil_div64(n_rows, kAggThreads * kRowsPerIter), (int64_t)ctx->sm_count * std::max(1, occ));
+    accumulate_kernel<TIER_SHARED><<<grid, kAggThreads, smem, ctx->stream>>>(b->vp, b->ap, (const uint32_t*)gids->p, n_rows, ng,
+                                                                            replicas, g->d_flags());
+    g->last_path = "shared";
+  } else {
+    const int grid = (int)std::min<int64_t>(ceil_div64(n_rows, kAggThreads * kRowsPerIter), (int64_t)ctx->sm_count * 8);
+    accumulate_kernel<TIER_GLOBAL><<<grid, kAggThreads, 0, ctx->stream>>>(b->vp, b->ap, (const uint32_t*)gids->p, n_rows, ng, 1,
+                                                                         g->d_flags());
+    g->last_path = "global";
+  }
+  ctx->launches++;
+  BGPU_CUDA(ctx, cudaGetLastError());
+  return BGPU_OK;
+}
+
+extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) {
+  if (!g || !batch) return BGPU_EINVAL;
+  bgpu_ctx* ctx = g->ctx;
+  if (g->emitted) return ctx->fail(BGPU_EINVAL, "aggregate already emitted");
+  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int64_t n_rows = batch->n_rows;
+  if (n_rows > 0xfffffff0LL) return ctx->fail(BGPU_EUNSUPPORTED, "more than 2^32 rows in one batch");
+  Bound b;
+  BGPU_TRY(bind_batch(g, batch, &b));
+  if (n_rows == 0) return BGPU_OK;
+  if (b.any_validity && !g->seen_tracking) {
+    // first batch with nulls in an aggregate input: groups created by earlier (null-free) batches have seen
+    // every accumulator; groups new in this batch start at 0
+    BGPU_TRY(dev_alloc(ctx, (size_t)g->max_groups * 4, &g->seen));
+    BGPU_CUDA(ctx, cudaMemsetAsync(g->seen->p, 0, (size_t)g->max_groups * 4, ctx->stream));
+    if (g->n_groups) {
+      fill_u32_kernel<<<agg_launch_grid(ctx, g->n_groups, kAggThreads), kAggThreads, 0, ctx->stream>>>(
+          (uint32_t*)g->seen->p, g->n_groups, 0xffffffffu);
+      ctx->launches++;
+    }
+    g->seen_tracking = true;
+  }
+  b.ap.seen = g->seen_tracking ? (uint32_t*)g->seen->p : nullptr;
+  bool done = false;
+  if (g->fused_rung < kFusedRungs) BGPU_TRY(try_fused(g, &b, n_rows, &done));
+  if (!done) BGPU_TRY(run_two_pass(g, &b, n_rows));
+  return BGPU_OK;
+}
+
+extern "C" const char* bgpu_agg_last_path(const bgpu_agg* g) { return g ? g->last_path.c_str() : ""; }
+
+// ---- emit ---------------------------------------------------------------------------------------------------------
+static int emit_validity(bgpu_agg* g, int phys_idx, uint32_t n, Column* col) {
+  bgpu_ctx* ctx = g->ctx;
+  if (!g->seen_tracking || n == 0) return BGPU_OK;
+  DevAllocPtr v;
+  BGPU_TRY(dev_alloc(ctx, (size_t)ceil_div64(n, 32) * 4, &v));
+  seen_bitmap_kernel<<<agg_launch_grid(ctx, n, kAggThreads), kAggThreads, 0, ctx->stream>>>(
+      (const uint32_t*)g->seen->p, n, phys_idx, (uint32_t*)v->p);
+  ctx->launches++;
+  BGPU_CUDA(ctx, cudaGetLastError());
+  col->validity = (uint8_t*)v->p;
+  col->null_count = -1;
+  col->owned.push_back(v);
+  return BGPU_OK;
+}
+
+extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
+  if (!g || !out_batch) return BGPU_EINVAL;
+  *out_batch = nullptr;
+  bgpu_ctx* ctx = g->ctx;
+  if (g->emitted) return ctx->fail(BGPU_EINVAL, "aggregate already emitted");
+  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  const uint32_t n = g->n_groups;
+  std::unique_ptr<bgpu_batch> out(new bgpu_batch(ctx));
+  out->n_rows = n;
+  const int grid = agg_launch_grid(ctx, std::max<uint32_t>(n, 1), kAggThreads);
+  const uint64_t* key0 = (const uint64_t*)g->key0->p;
+  const uint64_t* key1 = g->key1 ? (const uint64_t*)g->key1->p : nullptr;
+  const uint32_t* kmeta = (const uint32_t*)g->kmeta->p;
+  // group key columns
+  for (size_t i = 0; i < g->group_cols.size(); i++) {
+    const Column& f = g->fields[(size_t)g->group_cols[i]];
+    Column c;
+    c.name = f.name; c.format = f.format; c.flags = f.flags | ARROW_FLAG_NULLABLE; c.kind = f.kind; c.width = f.width;
+    c.length = n; c.null_count = -1;
+    DevAllocPtr valid;
+    BGPU_TRY(dev_alloc(ctx, (size_t)ceil_div64(std::max<uint32_t>(n, 1), 32) * 4, &valid));
+    c.owned.push_back(valid);
+    c.validity = (uint8_t*)valid->p;
+    if (f.kind == K_UTF8 || f.kind == K_BINARY) {
+      DevAllocPtr lens, offs, data;
+      BGPU_TRY(dev_alloc(ctx, (size_t)(n + 1) * 4, &lens));
+      BGPU_TRY(dev_alloc(ctx, (size_t)(n + 1) * 4, &offs));
+      BGPU_CUDA(ctx, cudaMemsetAsync(offs->p, 0, 4, ctx->stream));
+      int32_t total = 0;
+      if (n) {
+        unpack_utf8_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(key0, key1, kmeta, n, (int)i, g->key_off[i], 0,
+                                                                 (int32_t*)lens->p, nullptr, (uint32_t*)valid->p);
+        size_t tmp_bytes = 0;
+        cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, (const int32_t*)lens->p, (int32_t*)offs->p + 1, (int)n, ctx->stream);
+        DevAllocPtr tmp;
+        BGPU_TRY(dev_alloc(ctx, tmp_bytes, &tmp));
+        BGPU_CUDA(ctx, cub::DeviceScan::InclusiveSum(tmp->p, tmp_bytes, (const int32_t*)lens->p, (int32_t*)offs->p + 1, (int)n, ctx->stream));
+        BGPU_CUDA(ctx, cudaMemcpyAsync(&total, (int32_t*)offs->p + n, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+      }
+      BGPU_TRY(dev_alloc(ctx, (size_t)total, &data));
+      if (n)
+        unpack_utf8_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(key0, key1, kmeta, n, (int)i, g->key_off[i], 1,
+                                                                 (int32_t*)offs->p, (uint8_t*)data->p, nullptr);
+      ctx->launches += 3;
+      c.offsets = (int32_t*)offs->p; c.values = data->p; c.data_bytes = total;
+      c.owned.push_back(offs); c.owned.push_back(data);
+    } else {
+      DevAllocPtr vals;
+      const size_t bytes = f.kind == K_BOOL ? (size_t)ceil_div64(std::max<uint32_t>(n, 1), 32) * 4
+                                            : (size_t)std::max<uint32_t>(n, 1) * f.width;
+      BGPU_TRY(dev_alloc(ctx, bytes, &vals));
+      if (n)
+        unpack_fixed_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(key0, key1, kmeta, n, (int)i, f.kind, f.width,
+                                                                  g->key_off[i], vals->p, (uint32_t*)valid->p);
+      ctx->launches++;
+      c.values = vals->p;
+      c.owned.push_back(vals);
+      if (f.kind == K_DICT32) BGPU_TRY(upload_canonical_dictionary(g, i, &c.dict));
+    }
+    BGPU_CUDA(ctx, cudaGetLastError());
+    out->cols.push_back(std::move(c));
+  }
+  // aggregate columns
+  auto acc_column = [&](int phys_idx, const std::string& name, const std::string& format, bool nullable_by_seen,
+                        Column* c) -> int {
+    const PhysAcc& p = g->phys[(size_t)phys_idx];
+    c->name = name; c->format = format; c->flags = ARROW_FLAG_NULLABLE; c->kind = K_FIXED; c->width = p.words * 8;
+    c->length = n; c->null_count = 0; c->values = p.buf->p;
+    c->owned.push_back(p.buf);  // accumulators are dense arrays: they are the Arrow buffer
+    if (nullable_by_seen) BGPU_TRY(emit_validity(g, phys_idx, n, c));
+    return BGPU_OK;
+  };
+  for (const LogicalAgg& a : g->aggs) {
+    if (!g->final_mode && g->mode != BGPU_AGG_MODE_SINGLE) {  // Partial: state columns
+      if (a.fn == BGPU_AGG_COUNT) {
+        Column c; BGPU_TRY(acc_column(a.phys[0], a.name + "[count]", "l", false, &c)); out->cols.push_back(std::move(c));
+      } else if (a.fn == BGPU_AGG_SUM) {
+        Column c; BGPU_TRY(acc_column(a.phys[0], a.name + "[sum]", a.sum_format, true, &c)); out->cols.push_back(std::move(c));
+      } else {
+        Column c0; BGPU_TRY(acc_column(a.phys[0], a.name + "[count]", "L", false, &c0)); out->cols.push_back(std::move(c0));
+        Column c1; BGPU_TRY(acc_column(a.phys[1], a.name + "[sum]", a.sum_format, true, &c1)); out->cols.push_back(std::move(c1));
+      }
+      continue;
+    }
+    if (a.fn == BGPU_AGG_COUNT) {
+      Column c; BGPU_TRY(acc_column(a.phys[0], a.name, "l", false, &c)); out->cols.push_back(std::move(c));
+    } else if (a.fn == BGPU_AGG_SUM) {
+      Column c; BGPU_TRY(acc_column(a.phys[0], a.name, a.result_format, true, &c)); out->cols.push_back(std::move(c));
+    } else {  // Avg: evaluate
+      Column c;
+      c.name = a.name; c.format = a.result_format; c.flags = ARROW_FLAG_NULLABLE; c.kind = K_FIXED;
+      c.width = a.decimal ? 16 : 8; c.length = n; c.null_count = -1;
+      DevAllocPtr vals, valid;
+      BGPU_TRY(dev_alloc(ctx, (size_t)std::max<uint32_t>(n, 1) * c.width, &vals));
+      BGPU_TRY(dev_alloc(ctx, (size_t)ceil_div64(std::max<uint32_t>(n, 1), 32) * 4, &valid));
+      if (n) {
+        avg_evaluate_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(
+            (const uint64_t*)g->phys[(size_t)a.phys[1]].buf->p, (const uint64_t*)g->phys[(size_t)a.phys[0]].buf->p, n,
+            a.decimal ? 1 : 0, a.scale_up, (uint64_t*)vals->p, (uint32_t*)valid->p, g->d_flags());
+        ctx->launches++;
+        BGPU_CUDA(ctx, cudaGetLastError());
+      }
+      c.values = vals->p; c.validity = (uint8_t*)valid->p;
+      c.owned.push_back(vals); c.owned.push_back(valid);
+      out->cols.push_back(std::move(c));
+    }
+  }
+  uint32_t h[8];
+  BGPU_TRY(read_counters(g, h));
+  if (h[3]) return ctx->fail(BGPU_EOVERFLOW, "Arithmetic overflow in a Decimal128 aggregate argument or AVG");
+  g->emitted = true;
+  *out_batch = out.release();
+  return BGPU_OK;
+}

@@ -142,8 +142,7 @@ static int import_batch(bgpu_ctx* ctx, const struct ArrowArray* a, const struct 
   if (a->n_children != s->n_children) return ctx->fail(BGPU_EINVAL, "array/schema children mismatch");
   if (a->offset != 0) return ctx->fail(BGPU_EINVAL, "struct-level offset is not supported");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-  std::unique_ptr<bgpu_batch> b(new bgpu_batch());
-  b->ctx = ctx;
+  std::unique_ptr<bgpu_batch> b(new bgpu_batch(ctx));
   b->n_rows = a->length;
   b->cols.resize((size_t)a->n_children);
   for (int64_t i = 0; i < a->n_children; i++) {

@@ -45,8 +45,9 @@ extern "C" int bgpu_ctx_create_on_stream(int device, void* stream, bgpu_ctx** ou
   return ctx_create(device, (cudaStream_t)stream, true, out);
 }
 
-extern "C" void bgpu_ctx_destroy(bgpu_ctx* ctx) {
-  if (!ctx) return;
+void ctx_retain(bgpu_ctx* ctx) { ctx->refs.fetch_add(1, std::memory_order_relaxed); }
+
+static void ctx_teardown(bgpu_ctx* ctx) {
   if (ctx->has_device) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
@@ -54,6 +55,19 @@ extern "C" void bgpu_ctx_destroy(bgpu_ctx* ctx) {
   }
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   delete ctx;
+}
+
+void ctx_release(bgpu_ctx* ctx) {
+  if (ctx->refs.fetch_sub(1, std::memory_order_acq_rel) == 1) ctx_teardown(ctx);
+}
+
+extern "C" void bgpu_ctx_destroy(bgpu_ctx* ctx) {
+  if (!ctx) return;
+  if (ctx->has_device) {
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+  }
+  ctx_release(ctx);
 }
 
 extern "C" const char* bgpu_last_error(const bgpu_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
@@ -72,8 +86,9 @@ int dev_alloc(bgpu_ctx* ctx, size_t bytes, DevAllocPtr* out) {
   if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device");
   auto a = std::make_shared<DevAlloc>();
   a->bytes = bytes < 16 ? 16 : bytes;
-  a->stream = ctx->stream;
   BGPU_CUDA(ctx, cudaMallocAsync(&a->p, a->bytes, ctx->stream));
+  a->ctx = ctx;
+  ctx_retain(ctx);
   *out = a;
   return BGPU_OK;
 }

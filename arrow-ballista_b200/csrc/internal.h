@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <memory>
 #include <string>
 #include <vector>
@@ -18,6 +19,9 @@ struct bgpu_ctx {
   size_t smem_optin = 0;
   std::string err;
   uint64_t launches = 0;
+  // lifetime: the creator holds one reference (dropped by bgpu_ctx_destroy); every device allocation, batch and
+  // aggregate holds one too, so destroying handles in any order (e.g. at interpreter shutdown) is safe
+  std::atomic<int> refs{1};
   // small pinned scratch for device->host scalars (partition offsets, group counts)
   void* pinned = nullptr;
   size_t pinned_bytes = 0;
@@ -42,14 +46,21 @@ struct bgpu_ctx {
     if (_rc != BGPU_OK) return _rc; \
   } while (0)
 
+void ctx_retain(bgpu_ctx* ctx);
+void ctx_release(bgpu_ctx* ctx);  // tears the context down when the last reference goes
+
 // A device allocation freed (stream-ordered) when the last column referencing it goes away.
 struct DevAlloc {
   void* p = nullptr;
   size_t bytes = 0;
-  cudaStream_t stream = nullptr;
+  bgpu_ctx* ctx = nullptr;
   bool owned = true;
   ~DevAlloc() {
-    if (p && owned) cudaFreeAsync(p, stream);
+    if (p && owned && ctx) {
+      cudaSetDevice(ctx->device);
+      cudaFreeAsync(p, ctx->stream);
+    }
+    if (ctx) ctx_release(ctx);
   }
 };
 using DevAllocPtr = std::shared_ptr<DevAlloc>;
@@ -79,6 +90,13 @@ struct bgpu_batch {
   bgpu_ctx* ctx = nullptr;
   int64_t n_rows = 0;
   std::vector<Column> cols;
+  explicit bgpu_batch(bgpu_ctx* c) : ctx(c) { ctx_retain(c); }
+  ~bgpu_batch() {
+    cols.clear();
+    ctx_release(ctx);
+  }
+  bgpu_batch(const bgpu_batch&) = delete;
+  bgpu_batch& operator=(const bgpu_batch&) = delete;
 };
 
 // Parse one Arrow C schema node into kind/width/format. Returns BGPU_EUNSUPPORTED for types off the path.

@@ -398,8 +398,7 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
   const int64_t n_rows = in->n_rows;
   const uint32_t n = n_partitions;
 
-  std::unique_ptr<bgpu_batch> out(new bgpu_batch());
-  out->ctx = ctx;
+  std::unique_ptr<bgpu_batch> out(new bgpu_batch(ctx));
   out->n_rows = n_rows;
   out->cols.resize(in->cols.size());
 

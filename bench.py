@@ -1,0 +1,359 @@
+"""bench.py — TPC-H Q1 aggregation + shuffle hot path on B200 (BASELINE.json metric: input rows/s and HBM GB/s).
+
+One "step" = one pass of the hot path over one synthetic `lineitem` shard per GPU:
+    Partial GroupedHashAggregate (Q1 filter + decimal expressions fused)  ->  hash repartition of the state batch
+    (create_hashes, seeds 0,0,0,0, hash % n)  ->  [N>1: all-to-all over NVLink]  ->  FinalPartitioned aggregate.
+`value` times it with the shard resident in HBM; `e2e` runs the same path from pinned HOST buffers through the C ABI
+(upload inside the timed region, result downloaded). `--impl reference` times the CPU restatement of the reference's
+path (oracle/pipeline.cpp; the Rust reference cannot be built here) on the host cores.
+
+usage: python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--rows R]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SF100_ROWS = 600_037_902  # lineitem rows at SF100
+Q1_BYTES_PER_ROW = 78     # 4 x Decimal128 + 2 x (4 B offset + 1 B) Utf8 + Date32 filter column (fused filter)
+N_PARTITIONS = 16         # ballista.shuffle.partitions default (/root/reference/ballista/core/src/config.rs:177-179)
+SHIP_LO, SHIP_HI, CUTOFF, Q1_DATE = 8036, 10561, 9298, 10471  # 1992-01-02, 1998-12-01, 1995-06-17, 1998-09-02
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=int(os.environ.get("BENCH_ROWS", SF100_ROWS)), help="lineitem rows per GPU")
+    ap.add_argument("--e2e-rows", type=int, default=int(os.environ.get("BENCH_E2E_ROWS", 60_000_000)),
+                    help="rows of the shard kept in pinned host memory for the end-to-end leg")
+    ap.add_argument("--cpu-rows", type=int, default=int(os.environ.get("BENCH_CPU_ROWS", 60_000_000)),
+                    help="bounded sample for the CPU baseline")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    return ap.parse_args()
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop, self.t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.1)
+
+    def __enter__(self):
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.t.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(int(float(r[0])) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": int(float(self.rows[0][1])), "reasons": reasons,
+                "samples": len(sm), "power_w_max": max(float(r[2]) for r in self.rows)}
+
+
+# ---- synthetic lineitem (schema of /root/reference/benchmarks/src/bin/tpch.rs:923-940) -------------
+def gen_lineitem_torch(n, seed, device):
+    """Columns as torch tensors: Decimal128 as int64 [n, 2] (lo, hi), Utf8 as int32 offsets + uint8 bytes, Date32."""
+    import torch
+
+    g = torch.Generator(device=device).manual_seed(seed)
+
+    def dec(lo, hi):
+        t = torch.zeros((n, 2), dtype=torch.int64, device=device)
+        t[:, 0] = torch.randint(lo, hi + 1, (n,), generator=g, device=device)
+        return t
+    qty = dec(1, 50)
+    qty[:, 0] *= 100
+    price, disc, tax = dec(90000, 10495000), dec(0, 10), dec(0, 8)
+    ship = torch.randint(SHIP_LO, SHIP_HI + 1, (n,), generator=g, device=device, dtype=torch.int32)
+    receipt = ship + torch.randint(1, 31, (n,), generator=g, device=device, dtype=torch.int32)
+    coin = torch.rand(n, generator=g, device=device) < 0.5
+    rf = torch.where(receipt <= CUTOFF, torch.where(coin, ord("R"), ord("A")), ord("N")).to(torch.uint8)
+    ls = torch.where(ship > CUTOFF, ord("O"), ord("F")).to(torch.uint8)
+    offs = torch.arange(n + 1, dtype=torch.int32, device=device)
+    del receipt, coin
+    return {"l_quantity": qty, "l_extendedprice": price, "l_discount": disc, "l_tax": tax, "rf_offsets": offs, "rf_data": rf,
+            "ls_offsets": offs, "ls_data": ls, "l_shipdate": ship}
+
+
+def lineitem_schema():
+    import pyarrow as pa
+
+    d = pa.decimal128(15, 2)
+    return pa.schema([("l_quantity", d), ("l_extendedprice", d), ("l_discount", d), ("l_tax", d),
+                      ("l_returnflag", pa.string()), ("l_linestatus", pa.string()), ("l_shipdate", pa.date32())])
+
+
+def q1_plan():
+    """Q1's Partial aggregate (/root/reference/benchmarks/queries/q1.sql) over lineitem_schema()."""
+    from ballista_b200.expr import col, lit
+
+    qty, price, disc, tax = col(0), col(1), col(2), col(3)
+    disc_price = price * (lit(1) - disc)
+    aggs = [("sum", qty, "sum_qty"), ("sum", price, "sum_base_price"), ("sum", disc_price, "sum_disc_price"),
+            ("sum", disc_price * (lit(1) + tax), "sum_charge"), ("avg", qty, "avg_qty"), ("avg", price, "avg_price"),
+            ("avg", disc, "avg_disc"), ("count", None, "count_order")]
+    return [4, 5], aggs, col(6) <= lit(Q1_DATE, 3)
+
+
+def wrap_lineitem(bb, ctx, cols, n):
+    c = cols
+    columns = [dict(values=c[k].data_ptr()) for k in ("l_quantity", "l_extendedprice", "l_discount", "l_tax")]
+    columns += [dict(values=c["rf_data"].data_ptr(), offsets=c["rf_offsets"].data_ptr()),
+                dict(values=c["ls_data"].data_ptr(), offsets=c["ls_offsets"].data_ptr()),
+                dict(values=c["l_shipdate"].data_ptr())]
+    return bb.DeviceBatch.wrap_device(ctx, lineitem_schema(), columns, n, keepalive=cols)
+
+
+def host_lineitem_batches(cols_host, n, chunk):
+    """pyarrow RecordBatches (zero-copy over pinned torch host tensors) of <= chunk rows."""
+    import pyarrow as pa
+
+    schema = lineitem_schema()
+    out = []
+    for lo in range(0, n, chunk):
+        m = min(chunk, n - lo)
+
+        def fixed(name, typ, width):
+            t = cols_host[name]
+            buf = pa.foreign_buffer(t.data_ptr() + lo * width, m * width, base=t)
+            return pa.Array.from_buffers(typ, m, [None, buf])
+
+        def utf8(prefix):
+            o, d = cols_host[prefix + "_offsets"], cols_host[prefix + "_data"]
+            ob = pa.foreign_buffer(o.data_ptr() + lo * 4, (m + 1) * 4, base=o)
+            db = pa.foreign_buffer(d.data_ptr(), d.numel(), base=d)
+            return pa.Array.from_buffers(pa.string(), m, [None, ob, db])
+        d = pa.decimal128(15, 2)
+        arrays = [fixed("l_quantity", d, 16), fixed("l_extendedprice", d, 16), fixed("l_discount", d, 16), fixed("l_tax", d, 16),
+                  utf8("rf"), utf8("ls"), fixed("l_shipdate", pa.date32(), 4)]
+        out.append(pa.RecordBatch.from_arrays(arrays, schema=schema))
+    return out
+
+
+# ---- the hot path through the host mirror of the reference operators ---------------------------------------------
+class HotPath:
+    """Partial aggregate -> hash repartition -> (exchange) -> FinalPartitioned aggregate on one GPU/rank."""
+
+    def __init__(self, bb, ctx, rank=0, world=1, comm=None):
+        self.bb, self.ctx, self.rank, self.world, self.comm = bb, ctx, rank, world, comm
+        self.schema = lineitem_schema()
+        self.group_by, self.aggs, self.filter = q1_plan()
+        self.partitioner = bb.BatchPartitioner.try_new(bb.Partitioning.Hash(list(range(len(self.group_by))), N_PARTITIONS), ctx)
+        self.last_path = ""
+
+    def partial(self, device_batches):
+        bb = self.bb
+        agg = bb.GpuAggregateExec(self.ctx, bb.AggregateMode.Partial, self.group_by, self.aggs, self.schema, filter=self.filter)
+        for b in device_batches:
+            agg.update(b)
+        self.last_path = agg.last_path
+        return agg.emit()
+
+    def shuffle_and_final(self, state):
+        bb = self.bb
+        part, offsets = self.partitioner.partition_device(state)
+        if self.world > 1:
+            part = self.comm.all_to_all(part, offsets, N_PARTITIONS)
+        # the partitions this rank owns hold disjoint keys: one merged FinalPartitioned table gives the union of the
+        # per-partition results
+        fin = bb.GpuAggregateExec(self.ctx, bb.AggregateMode.FinalPartitioned, self.group_by, self.aggs, self.schema)
+        fin.update(part)
+        return fin.emit()
+
+    def step(self, device_batches):
+        return self.shuffle_and_final(self.partial(device_batches))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import ballista_b200 as bb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    ctx = bb.Context(local, stream=stream.cuda_stream)
+    comm = bb.Exchange(ctx, rank, world) if world > 1 else None
+    n = args.rows
+    cols = gen_lineitem_torch(n, 42 + rank, dev)
+    batch = wrap_lineitem(bb, ctx, cols, n)
+    hp = HotPath(bb, ctx, rank, world, comm)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    result = None
+    for _ in range(max(args.warmup, 3)):
+        result = hp.step([batch]).download()
+    barrier()
+    launches0 = ctx.kernel_launches
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    with ClockSampler(local) as clocks:
+        ev0.record(stream)
+        for i in range(args.steps):
+            k_ev[i][0].record(stream)
+            state = hp.partial([batch])
+            k_ev[i][1].record(stream)
+            out = hp.shuffle_and_final(state)
+        ev1.record(stream)
+        barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = ctx.kernel_launches - launches0
+    kernel_ms = sum(a.elapsed_time(b) for a, b in k_ev) / args.steps
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / args.steps
+    total_rows = n * world
+    value = total_rows / (ms_per_step * 1e-3)
+
+    # ---- end to end: pinned host buffers -> C ABI -> host result --------------------------------------------------
+    ne = min(args.e2e_rows, n)
+    host = {k: v[: (ne + 1 if k.endswith("offsets") else ne)].cpu().pin_memory() for k, v in cols.items()}
+    chunk = 8_000_000
+    hbatches = host_lineitem_batches(host, ne, chunk)
+    h2d = sum(sum(b.size for b in col.buffers() if b is not None) for hb in hbatches for col in hb.columns)
+
+    def e2e_step():
+        up = (bb.DeviceBatch.upload(ctx, hb) for hb in hbatches)
+        return hp.step(up).download()
+
+    for _ in range(2):
+        r = e2e_step()
+    barrier()
+    e2e_steps = max(2, min(args.steps, 5))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        r = e2e_step()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    if world > 1:
+        t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    d2h = sum(sum(b.size for b in col.buffers() if b is not None) for col in r.columns)
+
+    peak, peak_src = load_peaks()
+    achieved = n * Q1_BYTES_PER_ROW / (kernel_ms * 1e-3) / 1e9
+    line = {
+        "metric": "input rows/s & HBM GB/s (% roofline), TPC-H Q1 agg+shuffle", "value": value, "unit": "rows/s",
+        "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "i128", "data": "synthetic",
+        "config": {"workload": "TPC-H Q1 Partial agg (fused filter+decimal exprs) + hash repartition n=16 + FinalPartitioned, "
+                               f"lineitem {n} rows/GPU (SF100 = {SF100_ROWS})", "rows_per_gpu": n, "partitions": N_PARTITIONS,
+                   "l2": "input (>= 46 GB at SF100) is larger than L2; no flush needed", "agg_path": hp.last_path,
+                   "result_rows": result.num_rows},
+        "clocks": clocks.summary(),
+        "e2e": {"value": ne * world / e2e_s, "unit": "rows/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "rows_per_gpu": ne, "note": "pinned host Arrow buffers -> bgpu_batch_upload -> hot path -> bgpu_batch_download"},
+        "gpu_launches": launches,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "kernel": "fused_private_kernel (Partial aggregate pass)", "kernel_ms": kernel_ms,
+                     "bytes_per_row": Q1_BYTES_PER_ROW, "peak_source": peak_src},
+    }
+    if rank == 0 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(args.cpu_rows)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ---- CPU arm: the oracle's restatement of the reference path, timed on the host cores --------------------------------
+def cpu_baseline(rows, steps=1):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+
+    cores = os.cpu_count() or 1
+    best = None
+    res = None
+    for _ in range(max(1, steps)):
+        res = O.q1_pipeline(rows, seed=42, threads=cores, partitions=N_PARTITIONS)
+        best = res["seconds"] if best is None else min(best, res["seconds"])
+    return {"value": rows / best, "unit": "rows/s", "cores": cores, "kind": "port",
+            "sample": f"{rows} synthetic lineitem rows (in host memory), {cores} threads = {cores} input partitions of "
+                      f"8192-row batches, Partial agg + hash repartition n={N_PARTITIONS} + FinalPartitioned; oracle/pipeline.cpp",
+            "seconds": best, "result_rows": res["groups"]}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warm = max(1, args.steps), max(0, args.warmup)
+    rows = args.cpu_rows
+    for _ in range(min(warm, 1)):
+        cpu_baseline(rows)
+    t0 = time.perf_counter()
+    base = None
+    for _ in range(min(steps, 3)):
+        base = cpu_baseline(rows)
+    n_done = min(steps, 3)
+    sec = (time.perf_counter() - t0) / n_done
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    line = {"impl": "reference", "metric": "input rows/s & HBM GB/s (% roofline), TPC-H Q1 agg+shuffle",
+            "value": base["value"], "unit": "rows/s", "n_gpus": world, "steps": n_done, "warmup": min(warm, 1),
+            "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "i128",
+            "data": "synthetic",
+            "config": {"workload": f"TPC-H Q1 Partial agg + hash repartition n=16 + FinalPartitioned, CPU restatement "
+                                   f"(Ballista standalone cannot be built here: no Rust toolchain), bounded sample {rows} rows",
+                       "rows": rows, "partitions": N_PARTITIONS},
+            "cpu_baseline": base, "gpu_launches": 0,
+            "e2e": {"value": base["value"], "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -114,12 +114,61 @@ int bgpu_hash_partition_host(bgpu_ctx* ctx, const struct ArrowArray* batch, cons
 int bgpu_agg_create(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema* input_schema,
                     const int32_t* group_cols, int32_t n_group, const int32_t* agg_fns,
                     const int32_t* agg_cols, const char* const* agg_names, int32_t n_agg, bgpu_agg** out);
+/* Same, with the aggregate arguments given as physical expressions and an optional fused row filter.
+ * DataFusion evaluates each aggregate's input expressions inside the aggregate stream (the plan prints
+ * `aggr=[SUM(lineitem.l_extendedprice * Int64(1))]`, planner.rs:379), and Q1's `l_shipdate <= date` FilterExec
+ * sits directly below the Partial aggregate (benchmarks/queries/q1.sql); both are evaluated per row inside the
+ * aggregate kernels instead of materialising intermediate columns.
+ * Expressions are postfix programs over the raw input schema (Partial/Single modes only):
+ *   COLUMN a            push input column a
+ *   LITERAL t,p,s,lo,hi push a literal of type t (BGPU_T_*); Decimal128(p,s) / Int64 / Date32 in lo,hi (i128,
+ *                       two's complement, low word first); Float64 as its bit pattern in lo
+ *   ADD SUB MUL         arrow-arith numeric.rs semantics: Decimal128 operands are rescaled to max(s1,s2) for +/-
+ *                       (result precision max(s1,s2)+max(p1-s1,p2-s2)+1), multiply adds scales (precision p1+p2+1),
+ *                       both capped at 38, and every step is i128-checked: overflow is BGPU_EOVERFLOW (the reference
+ *                       returns ArrowError::ComputeError). Int64 literals next to decimals are coerced to
+ *                       Decimal128(20,0) as DataFusion's type coercion does. Int64 arithmetic wraps; Float64 is IEEE.
+ *   LT LE GT GE EQ NE   comparisons (filter only);  AND  conjunction (filter only)
+ * A null operand makes the value null; SUM/AVG skip null values, COUNT counts non-null ones; a null or false
+ * filter drops the row. agg_expr_offsets[i] .. agg_expr_offsets[i+1] delimit aggregate i's program inside
+ * `nodes` (an empty program = COUNT(*)). */
+#define BGPU_X_COLUMN 0
+#define BGPU_X_LITERAL 1
+#define BGPU_X_ADD 2
+#define BGPU_X_SUB 3
+#define BGPU_X_MUL 4
+#define BGPU_X_LT 5
+#define BGPU_X_LE 6
+#define BGPU_X_GT 7
+#define BGPU_X_GE 8
+#define BGPU_X_EQ 9
+#define BGPU_X_NE 10
+#define BGPU_X_AND 11
+#define BGPU_T_INT64 0
+#define BGPU_T_FLOAT64 1
+#define BGPU_T_DECIMAL128 2
+#define BGPU_T_DATE32 3
+typedef struct bgpu_expr_node {
+  int32_t op;        /* BGPU_X_* */
+  int32_t a;         /* COLUMN: column index; LITERAL: BGPU_T_* */
+  int32_t precision; /* LITERAL Decimal128 */
+  int32_t scale;
+  uint64_t lo, hi;   /* LITERAL value */
+} bgpu_expr_node;
+int bgpu_agg_create_expr(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema* input_schema,
+                         const int32_t* group_cols, int32_t n_group, const int32_t* agg_fns,
+                         const bgpu_expr_node* nodes, const int32_t* agg_expr_offsets,
+                         const char* const* agg_names, int32_t n_agg, const bgpu_expr_node* filter,
+                         int32_t n_filter, bgpu_agg** out);
 /* update_batch (Partial/Single) or merge_batch (Final*) with one device-resident batch */
 int bgpu_agg_update(bgpu_agg* agg, const bgpu_batch* batch);
 /* end of input: state() (Partial) or evaluate() (Final modes and Single). Group order is unspecified, as in the
  * reference (GroupValues uses a randomly seeded table). The aggregate may not be updated afterwards. */
 int bgpu_agg_emit(bgpu_agg* agg, bgpu_batch** out);
-int64_t bgpu_agg_num_groups(bgpu_agg* agg); /* synchronizes */
+int64_t bgpu_agg_num_groups(bgpu_agg* agg); /* groups seen so far */
+/* which kernel path the last update took ("fused256x2", "fused256", "fused128", "shared", "global", "intern");
+ * introspection for tests and the bench, not part of the reference's interface */
+const char* bgpu_agg_last_path(const bgpu_agg* agg);
 void bgpu_agg_destroy(bgpu_agg* agg);
 
 /* ---- intra-node exchange (replaces shuffle files + Flight do_get + ShuffleReaderExec fan-in;

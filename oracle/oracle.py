@@ -198,6 +198,154 @@ def partition(batch, key_cols, n_partitions):
     return out, hashes
 
 
+
+# ---- PhysicalExpr evaluation restated (arrow-arith 49 numeric.rs decimal_op; DataFusion 34 BinaryExpr) ---------
+# Expression trees are nested tuples: ("col", i) | ("lit", value, type[, precision, scale]) | (op, left, right) with
+# op in + - * < <= > >= = != and; type in "int64" "float64" "decimal128" "date32". Evaluated generically (any
+# nesting), one whole column at a time like the reference — the product instead compiles a restricted shape.
+I128_MIN, I128_MAX = -(1 << 127), (1 << 127) - 1
+
+
+class ArithmeticOverflow(Exception):
+    """arrow's ArrowError::ComputeError("Overflow happened on: ...")."""
+
+
+class _Val:
+    def __init__(self, kind, values, valid, precision=0, scale=0, width=8):
+        # kind: "int" (wrapping two's complement of `width` bytes), "float", "decimal", "bool"
+        self.kind, self.values, self.valid, self.precision, self.scale, self.width = kind, values, valid, precision, scale, width
+
+
+def _int_precision(width):
+    return {1: 3, 2: 5, 4: 10, 8: 20}[width]
+
+
+def _column_val(arr):
+    if isinstance(arr, pa.ChunkedArray):
+        arr = arr.combine_chunks()
+    n = len(arr)
+    valid = np.ones(n, dtype=bool) if arr.null_count == 0 else np.array(arr.is_valid().to_pylist(), dtype=bool)
+    t = arr.type
+    if pa.types.is_decimal128(t):
+        raw = np.frombuffer(arr.buffers()[1], dtype=np.uint64, count=2 * (arr.offset + n))[2 * arr.offset:]
+        vals = np.empty(n, dtype=object)
+        for i in range(n):
+            v = int(raw[2 * i]) | (int(raw[2 * i + 1]) << 64)
+            vals[i] = v - (1 << 128) if v >> 127 else v
+        return _Val("decimal", vals, valid, t.precision, t.scale)
+    if pa.types.is_floating(t):
+        return _Val("float", np.nan_to_num(arr.cast(pa.float64()).fill_null(0.0).to_numpy(zero_copy_only=False), nan=np.nan), valid)
+    if pa.types.is_date32(t):
+        arr = arr.cast(pa.int32())
+        t = arr.type
+    if pa.types.is_integer(t):
+        vals = np.array([int(x) for x in arr.fill_null(0).to_pylist()], dtype=object)
+        return _Val("int", vals, valid, width=t.bit_width // 8)
+    raise TypeError(f"oracle: expression over {t}")
+
+
+def _to_decimal(v):
+    """DataFusion coercion of an integer operand next to a decimal: Decimal128(int_precision, 0)."""
+    if v.kind == "decimal":
+        return v
+    if v.kind == "int":
+        return _Val("decimal", v.values, v.valid, _int_precision(v.width), 0)
+    raise TypeError("oracle: cannot mix Float64 and Decimal128")
+
+
+def _checked(vals, what):
+    for x in vals:
+        if x < I128_MIN or x > I128_MAX:
+            raise ArithmeticOverflow(f"Overflow happened on: {what}")
+    return vals
+
+
+def _wrap(vals, width):
+    bits = 8 * width
+    out = np.empty(len(vals), dtype=object)
+    for i, x in enumerate(vals):
+        x &= (1 << bits) - 1
+        out[i] = x - (1 << bits) if x >> (bits - 1) else x
+    return out
+
+
+def eval_expr(batch, tree):
+    op = tree[0]
+    n = batch.num_rows
+    if op == "col":
+        return _column_val(batch.column(tree[1]))
+    if op == "lit":
+        value, typ = tree[1], tree[2]
+        valid = np.ones(n, dtype=bool)
+        if typ == "float64":
+            return _Val("float", np.full(n, float(value)), valid)
+        vals = np.empty(n, dtype=object)
+        vals[:] = int(value)
+        if typ == "decimal128":
+            return _Val("decimal", vals, valid, tree[3], tree[4])
+        return _Val("int", vals, valid, width=4 if typ == "date32" else 8)
+    a, b = eval_expr(batch, tree[1]), eval_expr(batch, tree[2])
+    valid = a.valid & b.valid
+    if op == "and":
+        return _Val("bool", a.values & b.values, valid)
+    if a.kind == "decimal" or b.kind == "decimal":
+        a, b = _to_decimal(a), _to_decimal(b)
+        if op in ("+", "-"):
+            s = max(a.scale, b.scale)
+            p = min(38, s + max(a.precision - a.scale, b.precision - b.scale) + 1)
+            x = _checked(a.values * (10 ** (s - a.scale)), "rescale")
+            y = _checked(b.values * (10 ** (s - b.scale)), "rescale")
+            return _Val("decimal", _checked(x + y if op == "+" else x - y, op), valid, p, s)
+        if op == "*":
+            s = a.scale + b.scale
+            if s > 38:
+                raise ValueError("Output scale of decimal multiply would exceed max scale of 38")
+            return _Val("decimal", _checked(a.values * b.values, "*"), valid, min(38, a.precision + b.precision + 1), s)
+        s = max(a.scale, b.scale)  # comparison at a common scale
+        x, y = a.values * (10 ** (s - a.scale)), b.values * (10 ** (s - b.scale))
+    elif a.kind == "float" or b.kind == "float":
+        x = a.values.astype(np.float64) if a.kind != "float" else a.values
+        y = b.values.astype(np.float64) if b.kind != "float" else b.values
+        if op in ("+", "-", "*"):
+            with np.errstate(all="ignore"):
+                return _Val("float", x + y if op == "+" else x - y if op == "-" else x * y, valid)
+    else:
+        x, y = a.values, b.values
+        if op in ("+", "-", "*"):  # DataFusion 34 BinaryExpr: add_wrapping / sub_wrapping / mul_wrapping
+            w = max(a.width, b.width)
+            return _Val("int", _wrap(x + y if op == "+" else x - y if op == "-" else x * y, w), valid, width=w)
+    cmp = {"<": lambda: x < y, "<=": lambda: x <= y, ">": lambda: x > y, ">=": lambda: x >= y,
+           "=": lambda: x == y, "!=": lambda: x != y}[op]()
+    return _Val("bool", np.asarray(cmp, dtype=bool), valid)
+
+
+def val_to_array(v):
+    """_Val -> pyarrow array (Decimal128(p,s), Int64 or Float64)."""
+    n = len(v.values)
+    validity, nulls = None, 0
+    if not v.valid.all():
+        validity = pa.py_buffer(np.packbits(v.valid, bitorder="little").tobytes())
+        nulls = int(n - v.valid.sum())
+    if v.kind == "decimal":
+        raw = np.zeros(2 * n, dtype=np.uint64)
+        for i, x in enumerate(v.values):
+            x &= (1 << 128) - 1
+            raw[2 * i], raw[2 * i + 1] = x & ((1 << 64) - 1), x >> 64
+        return pa.Array.from_buffers(pa.decimal128(v.precision, v.scale), n, [validity, pa.py_buffer(raw.tobytes())], nulls)
+    if v.kind == "float":
+        return pa.Array.from_buffers(pa.float64(), n, [validity, pa.py_buffer(np.ascontiguousarray(v.values, dtype=np.float64).tobytes())], nulls)
+    if v.kind == "int":
+        t = {1: pa.int8(), 2: pa.int16(), 4: pa.int32(), 8: pa.int64()}[v.width]
+        return pa.array([int(x) for x in v.values], type=t, mask=~v.valid if nulls else None)
+    raise TypeError(v.kind)
+
+
+def filter_batch(batch, tree):
+    """FilterExec: keep rows whose predicate is true (null = dropped)."""
+    v = eval_expr(batch, tree)
+    assert v.kind == "bool"
+    return batch.filter(pa.array(v.values & v.valid))
+
 # ---- GroupedHashAggregateStream restated (SURVEY.md A.3) --------------------------------------------
 def sum_type(t):
     """Sum's result/state type (sum.rs): Int*->Int64, UInt*->UInt64, Float->Float64, Decimal(p,s)->(min(38,p+10),s)."""
@@ -297,9 +445,10 @@ class GroupedAggregate:
     aggregate's original argument type. Output group order = first-seen (the reference's is unspecified).
     """
 
-    def __init__(self, mode, group_cols, aggs, arg_types=None):
+    def __init__(self, mode, group_cols, aggs, arg_types=None, filter=None):
         assert mode in ("partial", "final")
         self.mode, self.group_cols, self.aggs, self.arg_types = mode, list(group_cols), list(aggs), arg_types
+        self.filter = filter  # expression tree (tuples); the FilterExec below the Partial aggregate
         self.groups = C.c_void_p(lib().orc_groups_new())
         self.accs = None
         self.batches = []  # kept to take() group keys at emit
@@ -315,7 +464,7 @@ class GroupedAggregate:
         col = len(self.group_cols)
         for i, (fn, arg, _name) in enumerate(self.aggs):
             if self.mode == "partial":
-                t = batch.column(arg).type if arg is not None else None
+                t = self._arg(batch, arg).type if arg is not None else None
             else:
                 t = self.arg_types[i]
             self.in_types.append(t)
@@ -331,7 +480,14 @@ class GroupedAggregate:
             else:
                 raise ValueError(fn)
 
+    @staticmethod
+    def _arg(batch, arg):
+        """Aggregate argument: a column index or an expression tree evaluated over the batch."""
+        return val_to_array(eval_expr(batch, arg)) if isinstance(arg, tuple) else batch.column(arg)
+
     def update(self, batch):
+        if self.filter is not None:
+            batch = filter_batch(batch, self.filter)
         if self.accs is None:
             self._init_accs(batch)
         n = batch.num_rows
@@ -343,7 +499,7 @@ class GroupedAggregate:
         col = len(self.group_cols)
         for (fn, arg, _), accs in zip(self.aggs, self.accs):
             if self.mode == "partial":
-                a = _cast_for(fn, batch.column(arg)) if arg is not None else None
+                a = _cast_for(fn, self._arg(batch, arg)) if arg is not None else None
                 if fn == "count":
                     accs[0].update(a, gid, self.n_groups)
                 elif fn == "sum":
@@ -404,3 +560,75 @@ class GroupedAggregate:
         with np.errstate(divide="ignore", invalid="ignore"):
             out = s.v / cnt.v.view(np.uint64).astype(np.float64)
         return pa.Array.from_buffers(rt, n, [validity, pa.py_buffer(out.tobytes())], nulls)
+
+
+# ---- synthetic lineitem + the timed CPU pipeline (oracle/pipeline.cpp) -----------------------------------------------
+Q1_DATE = 10471  # 1998-09-02 = date '1998-12-01' - interval '90' day
+
+
+def gen_lineitem_numpy(rows, seed=42, row0=0, threads=None):
+    """Deterministic synthetic lineitem columns (pure function of seed and row number) as numpy arrays."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    L = lib()
+    c = {k: np.zeros((rows, 2), dtype=np.uint64) for k in ("l_quantity", "l_extendedprice", "l_discount", "l_tax")}
+    c["rf"] = np.zeros(rows, dtype=np.uint8)
+    c["ls"] = np.zeros(rows, dtype=np.uint8)
+    c["l_shipdate"] = np.zeros(rows, dtype=np.int32)
+    threads = threads or os.cpu_count() or 1
+    step = max(1, (rows + threads - 1) // threads)
+
+    def work(lo):
+        n = min(step, rows - lo)
+        L.orc_gen_lineitem(C.c_int64(row0 + lo), C.c_int64(n), C.c_uint64(seed),
+                           *[C.c_void_p(c[k][lo:].ctypes.data) for k in ("l_quantity", "l_extendedprice", "l_discount", "l_tax")],
+                           C.c_void_p(c["rf"][lo:].ctypes.data), C.c_void_p(c["ls"][lo:].ctypes.data),
+                           C.c_void_p(c["l_shipdate"][lo:].ctypes.data))
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(work, range(0, rows, step)))
+    return c
+
+
+def lineitem_record_batch(c):
+    """numpy columns of gen_lineitem_numpy -> pyarrow RecordBatch with the reference's lineitem schema
+    (/root/reference/benchmarks/src/bin/tpch.rs:923-940), zero-copy."""
+    n = len(c["rf"])
+    d = pa.decimal128(15, 2)
+    offs = np.arange(n + 1, dtype=np.int32)
+
+    def fixed(a, t):
+        return pa.Array.from_buffers(t, n, [None, pa.py_buffer(a)])
+
+    def utf8(a):
+        return pa.Array.from_buffers(pa.string(), n, [None, pa.py_buffer(offs), pa.py_buffer(a)])
+    return pa.RecordBatch.from_arrays(
+        [fixed(c["l_quantity"], d), fixed(c["l_extendedprice"], d), fixed(c["l_discount"], d), fixed(c["l_tax"], d),
+         utf8(c["rf"]), utf8(c["ls"]), fixed(c["l_shipdate"], pa.date32())],
+        names=["l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_returnflag", "l_linestatus", "l_shipdate"])
+
+
+def q1_pipeline(rows, seed=42, threads=None, partitions=16, cols=None):
+    """Run the timed CPU restatement of the Q1 hot path over `rows` synthetic rows. Returns seconds (of the pipeline
+    only; generation is outside), the number of final groups and the final sums/counts per group."""
+    threads = threads or os.cpu_count() or 1
+    c = cols if cols is not None else gen_lineitem_numpy(rows, seed, threads=threads)
+    L = lib()
+    sec, ng = C.c_double(0), C.c_int32(0)
+    mg = 64
+    rf, ls = np.zeros(mg, dtype=np.uint8), np.zeros(mg, dtype=np.uint8)
+    sums = np.zeros((mg, 5, 2), dtype=np.uint64)
+    cnt = np.zeros(mg, dtype=np.int64)
+    part = np.zeros(mg, dtype=np.uint32)
+    rc = L.orc_q1_pipeline(*[C.c_void_p(c[k].ctypes.data) for k in ("l_quantity", "l_extendedprice", "l_discount", "l_tax",
+                                                                    "rf", "ls", "l_shipdate")],
+                           C.c_int64(rows), C.c_int32(Q1_DATE), C.c_int32(threads), C.c_uint32(partitions), C.byref(sec),
+                           C.byref(ng), C.c_int32(mg), _p(rf), _p(ls), _p(sums), _p(cnt), _p(part))
+    assert rc == 0, f"orc_q1_pipeline rc={rc}"
+    n = ng.value
+
+    def i128(x):
+        v = int(x[0]) | (int(x[1]) << 64)
+        return v - (1 << 128) if v >> 127 else v
+    groups = {(chr(rf[i]), chr(ls[i])): {"sums": [i128(sums[i, a]) for a in range(5)], "count": int(cnt[i]),
+                                         "partition": int(part[i])} for i in range(n)}
+    return {"seconds": sec.value, "groups": n, "result": groups}
