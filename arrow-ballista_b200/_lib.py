@@ -75,6 +75,9 @@ SIGNATURES = {
     "bgpu_agg_create_expr": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(ArrowSchema), C.POINTER(C.c_int32), C.c_int32,
                                        C.POINTER(C.c_int32), C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_char_p),
                                        C.c_int32, C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]),
+    "bgpu_agg_debug_compile": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(ArrowSchema), C.POINTER(C.c_int32), C.c_int32,
+                                         C.POINTER(C.c_int32), C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_void_p,
+                                         C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_char_p]),
     "bgpu_agg_last_path": (C.c_char_p, [C.c_void_p]),
     "bgpu_agg_update": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bgpu_agg_emit": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),

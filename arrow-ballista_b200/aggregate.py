@@ -110,3 +110,38 @@ class GpuAggregateExec:
 
     def __del__(self):
         self.close()
+
+
+def debug_compile(mode, group_by, aggr_expr, input_schema, filter=None, flags=0, threads=256, rows_per_thread=4,
+                  min_ctas=2, out_prefix=None):
+    """Generate and NVRTC-compile the run-time specialised kernels of a plan without a device
+    (bgpu_agg_debug_compile): used by the CPU test-suite and to inspect the SASS offline. Raises BgpuError."""
+    from ._lib import BgpuError, ExprNode
+    from .expr import col
+
+    L = lib()
+    h = C.c_void_p()
+    L.bgpu_ctx_create(0, C.byref(h))  # fails with ENODEVICE on a CPU box; the handle still carries error text
+    try:
+        nodes, offsets, fns = [], [0], []
+        for f, c, _ in aggr_expr:
+            e = None if c is None else (c if hasattr(c, "to_nodes") else col(int(c)))
+            fns.append(AggregateFunction.parse(f))
+            if e is not None:
+                nodes.extend(e.to_nodes())
+            offsets.append(len(nodes))
+        fnodes = filter.to_nodes() if filter is not None else []
+        s = ArrowSchema()
+        input_schema._export_to_c(C.addressof(s))
+        try:
+            rc = L.bgpu_agg_debug_compile(
+                h, mode, C.byref(s), (C.c_int32 * len(group_by))(*group_by), len(group_by),
+                (C.c_int32 * max(len(fns), 1))(*fns), (ExprNode * max(len(nodes), 1))(*nodes),
+                (C.c_int32 * len(offsets))(*offsets), len(fns), (ExprNode * max(len(fnodes), 1))(*fnodes), len(fnodes),
+                flags, threads, rows_per_thread, min_ctas, out_prefix.encode() if out_prefix else None)
+        finally:
+            _release(s)
+        if rc != 0:
+            raise BgpuError(rc, L.bgpu_last_error(h).decode())
+    finally:
+        L.bgpu_ctx_destroy(h)

@@ -1,12 +1,15 @@
 // Host-side state of one grouped aggregate (bgpu_agg), shared by aggregate.cu (plan building) and
 // aggregate_run.cu (update / emit).
 #pragma once
+#include <map>
 #include <memory>
 #include <string>
 #include <unordered_map>
 #include <vector>
 
 #include "agg_plan.h"
+
+namespace bgpu { struct JitModule; }
 
 struct PhysAcc {
   int32_t op = 0;
@@ -54,6 +57,9 @@ struct bgpu_agg {
     DevAllocPtr last_remap;        // nullptr = identity
   };
   std::vector<DictState> dicts;
+  // runtime-specialised kernel modules of this aggregate, keyed by the generated plan source (one per batch shape
+  // and launch geometry; the modules themselves live in jit.cu's process-wide cache)
+  std::map<std::string, const bgpu::JitModule*> modules;
   bool emitted = false;
   // introspection for tests / bench: which path the last update took ("fused256x2", "fused256", "fused128",
   // "shared", "global")
@@ -68,6 +74,35 @@ struct bgpu_agg {
                             key1 ? (uint64_t*)key1->p : nullptr, (uint32_t*)kmeta->p, d_n_groups(), d_flags()};
   }
 };
+
+// ---- binding of one batch to the runtime-specialised kernels ------------------------------------------------------
+// One slot per distinct batch column the kernels read. Everything in JitShape is baked into the generated source;
+// the pointers go into JitArgs.
+struct JitSlot {
+  int32_t batch_col = -1;
+  int32_t kind = 0;   // ColKind
+  int32_t width = 0;  // fixed width
+  int32_t vk = 0;     // ValKind when read as a value / filter operand
+  bool nullable = false, remap = false;
+  bool key_use = false, value_use = false, filter_use = false;
+};
+struct JitShape {
+  std::vector<JitSlot> slots;
+  std::vector<int32_t> key_slot;             // per group column
+  std::vector<int32_t> filter_slot;          // per filter term
+  std::vector<bool> value_nullable;          // per value (in this batch)
+  std::vector<int32_t> acc_alias, acc_word0; // per physical accumulator
+  int32_t W = 0;                             // accumulator words per group
+  bool has_seen = false;
+  int32_t T = 256, R = 4, min_ctas = 1;
+  bool any_validity = false;
+};
+// slot of batch column `batch_col` (created on first use); -1 when the table is full
+int32_t jit_slot(JitShape* sh, int32_t batch_col);
+// CUDA source of the plan-specific part for (aggregate, shape): the generated `Plan` + extern "C" entry points
+// bgpu_fused, bgpu_intern, bgpu_acc_shared, bgpu_acc_global. Compiled behind agg_jit_prelude().
+int agg_generate_source(const bgpu_agg* g, const JitShape& sh, std::string* out);
+const char* agg_jit_prelude();
 
 int agg_launch_grid(bgpu_ctx* ctx, int64_t n, int per_block);
 // (Re)allocate the table and accumulators for `new_max` groups, keeping the first `keep` groups.

@@ -1,0 +1,537 @@
+// Device code of the grouped aggregate (K4 Partial / K5 Final): the kernel templates and their building blocks.
+// This file is compiled at run time by NVRTC for sm_100a (jit.cu) with a plan-specific `struct Plan` appended by
+// agg_codegen.cu; it is embedded into libbgpu.so as a string (Makefile). It therefore uses no host headers.
+//
+//   fused_body<Plan>       ONE pass over the batch for low-cardinality inputs (TPC-H Q1, db-benchmark K=100):
+//                          phase 1 issues every column load of R rows per thread back to back (memory-level
+//                          parallelism), phase 2 filters, packs the key, resolves the group id from the CTA's
+//                          shared-memory key cache (global table behind it), evaluates the aggregate arguments and adds
+//                          into THREAD-PRIVATE accumulators in shared memory (no atomics, deterministic). Each CTA
+//                          reduces its private copies into a scratch slab; commit_kernel (aggregate_run.cu) folds the
+//                          slabs into the dense accumulator arrays once the host has seen that no CTA aborted.
+//   intern_body<Plan> +    the general two-pass path: pass 1 assigns group ids (idempotent, so a table overflow is
+//   accumulate_body<Plan>  handled by growing and re-running), pass 2 adds with replicated shared-memory atomics
+//                          (TIER 1) or global atomics (TIER 2).
+typedef unsigned char uint8_t;
+typedef signed char int8_t;
+typedef unsigned short uint16_t;
+typedef short int16_t;
+typedef unsigned int uint32_t;
+typedef int int32_t;
+typedef unsigned long long uint64_t;
+typedef long long int64_t;
+typedef unsigned long size_t;
+
+namespace bgpu {
+
+enum AccOp : int32_t { OP_ADD_I64 = 0, OP_ADD_I128 = 1, OP_ADD_F64 = 2, OP_COUNT = 3 };
+constexpr uint32_t kNoGroup = 0xffffffffu;      // row dropped by the filter
+constexpr uint32_t kGidOverflow = 0xfffffff0u;  // "no room": always >= max_groups
+constexpr int kJitSlots = 24;
+constexpr int kJitAcc = 24;
+
+struct GroupTable {
+  unsigned long long* entries;  // (tag << 32) | state; state 0 empty, 1 busy, >= 2: gid + 2
+  uint32_t mask;                // capacity - 1 (capacity = 2 * max_groups, power of two)
+  uint32_t max_groups;
+  uint64_t* key0;               // packed keys of group gid (dense)
+  uint64_t* key1;
+  uint32_t* kmeta;              // null bits of the key columns
+  uint32_t* n_groups;           // device counter
+  int32_t* flags;               // [0] capacity overflow, [1] string key too long, [2] arithmetic overflow,
+                                // [3] private tier abort (a group id beyond the private capacity)
+};
+
+// The single by-value kernel argument; the host mirror is agg_plan.h's JitArgs (same layout).
+struct JitArgs {
+  const void* col[kJitSlots];        // slot s: fixed values / bool bits / utf8 bytes / dictionary keys
+  const int32_t* aux[kJitSlots];     // slot s: utf8 offsets, or the dictionary remap (nullptr = identity)
+  const uint8_t* valid[kJitSlots];   // slot s: validity bitmap (only read when the plan marks the slot nullable)
+  GroupTable t;
+  uint64_t* acc_out[kJitAcc];        // dense accumulator arrays (words * max_groups u64)
+  uint32_t* seen;                    // per-group bitmask of accumulators that saw a non-null input
+  uint64_t* scratch;                 // fused path: per-CTA slabs
+  uint32_t* gids;                    // two-pass path: group id per row
+  int64_t n_rows;
+  uint32_t g_cap;                    // fused: private group capacity (ids >= g_cap abort the pass)
+  uint32_t cache_slots;              // fused: key cache slots (power of two)
+  uint32_t n_groups;                 // accumulate: groups so far
+  uint32_t replicas;                 // accumulate TIER 1: shared-memory copies per CTA
+};
+
+__device__ __forceinline__ bool bit_set(const uint8_t* bits, int64_t i) { return (bits[i >> 3] >> (i & 7)) & 1; }
+
+__device__ __forceinline__ uint64_t mix64(uint64_t x) {  // murmur3 fmix64: table hash (not the partition hash)
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+  return x;
+}
+
+struct PackedKey { uint64_t k0, k1; uint32_t meta; };
+
+template <int WORDS>
+__device__ __forceinline__ uint64_t key_hash(const PackedKey& k) {
+  // must equal agg_device.cuh's key_hash (rehash_kernel rebuilds the table with it); k1 == 0 when WORDS == 1
+  return mix64(k.k0 ^ mix64((WORDS > 1 ? k.k1 : 0ULL) + 0x9e3779b97f4a7c15ULL * (k.meta + 1)));
+}
+
+// Find or insert in the global table; returns the dense group id (>= max_groups when the table overflowed: the
+// pass is void and is re-run by the host after growing).
+template <int WORDS>
+__device__ __noinline__ uint32_t intern(const GroupTable& t, const PackedKey& k) {
+  const uint64_t h = key_hash<WORDS>(k);
+  const unsigned long long tag = (h >> 32) << 32;
+  uint32_t i = (uint32_t)h & t.mask;
+  for (uint32_t probes = 0; probes <= t.mask; probes++) {
+    unsigned long long e = *(volatile unsigned long long*)&t.entries[i];
+    if (e == 0) {
+      if (*(volatile int32_t*)&t.flags[0]) return kGidOverflow;  // the pass is void already: do not fill the table
+      e = atomicCAS(&t.entries[i], 0ULL, tag | 1ULL);
+      if (e == 0) {  // we own the slot: allocate the dense id, publish the key, then the entry
+        const uint32_t gid = atomicAdd(t.n_groups, 1u);
+        if (gid < t.max_groups) {
+          t.key0[gid] = k.k0;
+          if (WORDS > 1) t.key1[gid] = k.k1;
+          t.kmeta[gid] = k.meta;
+        } else {
+          atomicOr(&t.flags[0], 1);
+        }
+        __threadfence();
+        *(volatile unsigned long long*)&t.entries[i] = tag | (unsigned long long)(gid + 2u);
+        return gid;
+      }
+    }
+    if ((e & 0xffffffff00000000ULL) == tag) {
+      while ((uint32_t)e == 1u) e = *(volatile unsigned long long*)&t.entries[i];  // inserter is publishing
+      const uint32_t gid = (uint32_t)e - 2u;
+      if (gid >= t.max_groups) return gid;
+      // dense key arrays share cache lines between groups: read through L2 (L1 may hold a stale line)
+      if (__ldcg(&t.key0[gid]) == k.k0 && (WORDS == 1 || __ldcg(&t.key1[gid]) == k.k1) && __ldcg(&t.kmeta[gid]) == k.meta)
+        return gid;
+    }
+    i = (i + 1) & t.mask;
+  }
+  atomicOr(&t.flags[0], 1);  // table full
+  return kGidOverflow;
+}
+
+// Per-CTA cache of (key -> gid) in shared memory in front of the global table: low-cardinality inputs resolve
+// every row from shared memory after the first few rows of the CTA.
+struct KeyCache {
+  uint32_t* state;  // 0 empty, 1 busy, gid + 2
+  uint64_t* k0;
+  uint64_t* k1;
+  uint32_t* meta;
+  uint32_t mask;  // slots - 1
+};
+
+template <int WORDS>
+__device__ __forceinline__ uint32_t cached_intern(const KeyCache& c, const GroupTable& t, const PackedKey& k) {
+  // cheap slot hash (one multiply): the cache holds a handful of keys, the strong hash is only needed behind it
+  uint32_t i = (uint32_t)(((k.k0 ^ (WORDS > 1 ? k.k1 * 0xc2b2ae3d27d4eb4fULL : 0ULL) ^ k.meta) * 0x9e3779b97f4a7c15ULL) >> 40) & c.mask;
+#pragma unroll 1
+  for (uint32_t probe = 0; probe <= c.mask; probe++) {
+    const uint32_t s = *(volatile uint32_t*)&c.state[i];
+    if (s >= 2u) {
+      if (*(volatile uint64_t*)&c.k0[i] == k.k0 && (WORDS == 1 || *(volatile uint64_t*)&c.k1[i] == k.k1) &&
+          *(volatile uint32_t*)&c.meta[i] == k.meta)
+        return s - 2u;
+      i = (i + 1) & c.mask;
+      continue;
+    }
+    const uint32_t gid = intern<WORDS>(t, k);
+    if (s == 0u && probe * 2 < c.mask && atomicCAS(&c.state[i], 0u, 1u) == 0u) {
+      c.k0[i] = k.k0;
+      if (WORDS > 1) c.k1[i] = k.k1;
+      c.meta[i] = k.meta;
+      __threadfence_block();
+      *(volatile uint32_t*)&c.state[i] = gid + 2u;
+    }
+    return gid;
+  }
+  return intern<WORDS>(t, k);
+}
+
+// ---- values ---------------------------------------------------------------------------------------------------
+struct Val { uint64_t lo, hi; };  // i128, or i64 in lo, or the bits of a double in lo
+
+__device__ __forceinline__ Val ld_i128(const void* col, int64_t r) {
+  const ulonglong2 x = __ldg((const ulonglong2*)col + r);
+  return Val{x.x, x.y};
+}
+__device__ __forceinline__ Val sext(int64_t v) { return Val{(uint64_t)v, (uint64_t)(v >> 63)}; }
+__device__ __forceinline__ Val zext(uint64_t v) { return Val{v, 0}; }
+__device__ __forceinline__ double as_f64(uint64_t b) { return __longlong_as_double((long long)b); }
+__device__ __forceinline__ uint64_t f64_bits(double d) { return (uint64_t)__double_as_longlong(d); }
+
+__device__ __forceinline__ Val i128_neg(Val a) {
+  Val r;
+  r.lo = ~a.lo + 1;
+  r.hi = ~a.hi + (r.lo == 0);
+  return r;
+}
+__device__ __forceinline__ bool i128_is_neg(Val a) { return (int64_t)a.hi < 0; }
+__device__ __forceinline__ bool fits_i64(Val a) { return a.hi == (uint64_t)((int64_t)a.lo >> 63); }
+// checked add/sub: *ovf is set on signed overflow (arrow-arith add_checked / sub_checked on i128)
+__device__ __forceinline__ Val i128_add_checked(Val a, Val b, bool* ovf) {
+  Val r;
+  r.lo = a.lo + b.lo;
+  r.hi = a.hi + b.hi + (r.lo < a.lo);
+  if ((~(a.hi ^ b.hi) & (a.hi ^ r.hi)) >> 63) *ovf = true;
+  return r;
+}
+__device__ __forceinline__ Val i128_sub_checked(Val a, Val b, bool* ovf) {
+  Val r;
+  r.lo = a.lo - b.lo;
+  r.hi = a.hi - b.hi - (a.lo < b.lo);
+  if (((a.hi ^ b.hi) & (a.hi ^ r.hi)) >> 63) *ovf = true;
+  return r;
+}
+// general checked signed multiply (i128::mul_checked): magnitudes as u128, product must fit 127 bits (or be MIN)
+__device__ __noinline__ Val i128_mul_slow(Val a, Val b, bool* ovf) {
+  const bool neg = i128_is_neg(a) != i128_is_neg(b);
+  const Val ua = i128_is_neg(a) ? i128_neg(a) : a, ub = i128_is_neg(b) ? i128_neg(b) : b;
+  bool ok = (ua.hi == 0) || (ub.hi == 0);
+  const uint64_t p0_lo = ua.lo * ub.lo, p0_hi = __umul64hi(ua.lo, ub.lo);
+  const uint64_t cross_a = ua.hi * ub.lo, cross_a_hi = __umul64hi(ua.hi, ub.lo);
+  const uint64_t cross_b = ua.lo * ub.hi, cross_b_hi = __umul64hi(ua.lo, ub.hi);
+  ok = ok && cross_a_hi == 0 && cross_b_hi == 0;
+  const uint64_t hi = p0_hi + cross_a;
+  ok = ok && hi >= p0_hi;
+  const uint64_t hi2 = hi + cross_b;
+  ok = ok && hi2 >= hi;
+  Val r{p0_lo, hi2};
+  if (neg) {
+    ok = ok && (hi2 < 0x8000000000000000ULL || (hi2 == 0x8000000000000000ULL && p0_lo == 0));
+    r = i128_neg(r);
+  } else {
+    ok = ok && hi2 < 0x8000000000000000ULL;
+  }
+  if (!ok) *ovf = true;
+  return r;
+}
+// checked multiply with the common case inline: both operands fit i64 -> one signed 64x64->128 product, which
+// cannot overflow i128
+__device__ __forceinline__ Val i128_mul_checked(Val a, Val b, bool* ovf) {
+  if (fits_i64(a) && fits_i64(b)) return Val{a.lo * b.lo, (uint64_t)__mul64hi((int64_t)a.lo, (int64_t)b.lo)};
+  return i128_mul_slow(a, b, ovf);
+}
+__device__ __forceinline__ bool i128_lt(Val a, Val b) {
+  return (int64_t)a.hi < (int64_t)b.hi || (a.hi == b.hi && a.lo < b.lo);
+}
+// three-way compare of i128 values: -1, 0, 1
+__device__ __forceinline__ int i128_cmp(Val a, Val b) { return i128_lt(a, b) ? -1 : (i128_lt(b, a) ? 1 : 0); }
+__device__ __forceinline__ int f64_cmp(double a, double b) { return a < b ? -1 : (a > b ? 1 : 0); }
+
+// ---- accumulator sinks: where Plan::accumulate sends each (accumulator, value) ---------------------------------------
+// thread-private slots in shared memory: word w of group g of thread t lives at s_acc[(g * W + w) * T + t]
+template <int T>
+struct PrivateSink {
+  static constexpr bool kSkipAliased = true;
+  uint64_t* base;  // &s_acc[g * W * T + threadIdx.x]
+  template <int OP, int WORD0, int IDX>
+  __device__ __forceinline__ void add(const JitArgs&, Val v) {
+    uint64_t* p = base + WORD0 * T;
+    if (OP == OP_ADD_F64) {
+      *(double*)p += as_f64(v.lo);
+    } else if (OP == OP_ADD_I128) {
+      const uint64_t old = p[0], lo = old + v.lo;
+      p[0] = lo;
+      p[T] += v.hi + (lo < old);
+    } else if (OP == OP_COUNT) {
+      p[0] += 1;
+    } else {
+      p[0] += v.lo;
+    }
+  }
+};
+
+template <int OP>
+__device__ __forceinline__ void add_atomic(uint64_t* p, Val v) {
+  if (OP == OP_ADD_F64) {
+    atomicAdd((double*)p, as_f64(v.lo));
+  } else if (OP == OP_ADD_I128) {  // two u64 adds; the carry out of the low word goes to the high word
+    const uint64_t old = atomicAdd((unsigned long long*)p, (unsigned long long)v.lo);
+    const uint64_t hi = v.hi + ((old + v.lo) < old);
+    if (hi) atomicAdd((unsigned long long*)(p + 1), (unsigned long long)hi);
+  } else if (OP == OP_COUNT) {
+    atomicAdd((unsigned long long*)p, 1ULL);
+  } else {
+    atomicAdd((unsigned long long*)p, (unsigned long long)v.lo);
+  }
+}
+
+struct SharedAtomicSink {  // one of `replicas` copies of [n_groups][W] in shared memory
+  static constexpr bool kSkipAliased = true;
+  uint64_t* base;  // &s_acc[(rep * n_groups + g) * W]
+  template <int OP, int WORD0, int IDX>
+  __device__ __forceinline__ void add(const JitArgs&, Val v) { add_atomic<OP>(base + WORD0, v); }
+};
+
+struct GlobalAtomicSink {
+  static constexpr bool kSkipAliased = false;
+  uint32_t g;
+  template <int OP, int WORD0, int IDX>
+  __device__ __forceinline__ void add(const JitArgs& a, Val v) {
+    add_atomic<OP>(a.acc_out[IDX] + (size_t)g * (OP == OP_ADD_I128 ? 2 : 1), v);
+  }
+};
+
+// warp-wide sum of per-lane (lo, hi) partials / doubles
+__device__ __forceinline__ Val warp_sum_u128(Val v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    const uint64_t lo = __shfl_down_sync(0xffffffffu, v.lo, d);
+    const uint64_t hi = __shfl_down_sync(0xffffffffu, v.hi, d);
+    const uint64_t s = v.lo + lo;
+    v.hi += hi + (s < lo);
+    v.lo = s;
+  }
+  return v;
+}
+__device__ __forceinline__ double warp_sum_f64(double v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+  return v;
+}
+
+__host__ __device__ __forceinline__ size_t fused_slab_words(uint32_t g_cap, int W) {
+  return (size_t)g_cap * W + ((size_t)g_cap + 1) / 2;
+}
+
+// fused path: reduce the T private copies of one accumulator of every group into the CTA's slab (one warp per group)
+template <int T>
+struct FlushPrivate {
+  const uint64_t* s_acc;
+  uint64_t* slab;
+  uint32_t G;
+  int W;
+  template <int OP, int WORD0, int WORDS, int IDX, bool ALIASED>
+  __device__ __forceinline__ void acc() {
+    if (ALIASED) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t grp = warp; grp < G; grp += T / 32) {
+      const uint64_t* p = s_acc + ((size_t)grp * W + WORD0) * T;
+      uint64_t* o = slab + (size_t)grp * W + WORD0;
+      if (OP == OP_ADD_F64) {
+        double f = 0.0;
+        for (int th = lane; th < T; th += 32) f += as_f64(p[th]);
+        f = warp_sum_f64(f);
+        if (lane == 0) o[0] = f64_bits(f);
+      } else {
+        Val s{0, 0};
+        for (int th = lane; th < T; th += 32) {
+          const uint64_t lo = p[th];
+          s.lo += lo;
+          s.hi += (s.lo < lo);
+          if (WORDS > 1) s.hi += p[T + th];
+        }
+        s = warp_sum_u128(s);
+        if (lane == 0) {
+          o[0] = s.lo;
+          if (WORDS > 1) o[1] = s.hi;
+        }
+      }
+    }
+  }
+};
+
+// shared-atomic tier: fold this CTA's replicas into the dense accumulator arrays (one warp per group)
+struct FlushShared {
+  const uint64_t* s_acc;
+  const JitArgs* a;
+  uint32_t n_groups, replicas;
+  int W, T;
+  template <int OP, int WORD0, int WORDS, int IDX, bool ALIASED>
+  __device__ __forceinline__ void acc() {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t grp = warp; grp < n_groups; grp += T / 32) {
+      uint64_t* o = a->acc_out[IDX] + (size_t)grp * (OP == OP_ADD_I128 ? 2 : 1);
+      if (OP == OP_ADD_F64) {
+        double f = 0.0;
+        for (uint32_t t = lane; t < replicas; t += 32) f += as_f64(s_acc[((size_t)t * n_groups + grp) * W + WORD0]);
+        f = warp_sum_f64(f);
+        if (lane == 0 && f != 0.0) atomicAdd((double*)o, f);
+      } else {
+        Val s{0, 0};
+        for (uint32_t t = lane; t < replicas; t += 32) {
+          const uint64_t* p = &s_acc[((size_t)t * n_groups + grp) * W + WORD0];
+          const uint64_t lo = p[0];
+          s.lo += lo;
+          s.hi += (s.lo < lo);
+          if (WORDS > 1) s.hi += p[1];
+        }
+        s = warp_sum_u128(s);
+        // partial counts are sums by now; an aliased count adds its source's partial
+        if (lane == 0 && (s.lo | s.hi)) {
+          if (OP == OP_ADD_I128) add_atomic<OP_ADD_I128>(o, s);
+          else add_atomic<OP_ADD_I64>(o, s);
+        }
+      }
+    }
+  }
+};
+
+// ---- kernel bodies ---------------------------------------------------------------------------------------------------
+// `Plan` (generated per aggregate and per batch shape by agg_codegen.cu) provides:
+//   constants  T (threads), R (rows per thread per tile), W (accumulator words per group), KEY_WORDS, HAS_SEEN
+//   struct Raw                                   the raw column values of one row
+//   load1<NEED>(a, r, x), load2<NEED>(a, r, x)   independent loads, then the loads that depend on them (utf8 bytes,
+//                                                dictionary remap); NEED = bit 0 filter, bit 1 key, bit 2 values
+//   filter(a, x) -> bool, key(a, x) -> PackedKey
+//   accumulate(a, x, sink, &ovf) -> seen mask    evaluates every aggregate argument and feeds the sink
+//   for_each_acc(f)                              f.acc<OP, WORD0, WORDS, IDX, ALIASED>() per accumulator
+constexpr int NEED_FILTER = 1, NEED_KEY = 2, NEED_VALUES = 4;
+
+// Shared memory: acc u64[g_cap * W * T] | seen u32[g_cap] | key cache (slots)
+// Scratch slab of CTA b: u64[g_cap * W] partial accumulators, then u32[g_cap] seen masks (padded to 8 bytes).
+template <class Plan>
+__device__ __forceinline__ void fused_body(const JitArgs& a) {
+  constexpr int T = Plan::T, R = Plan::R, W = Plan::W, KW = Plan::KEY_WORDS;
+  extern __shared__ __align__(16) uint64_t smem[];
+  const uint32_t G = a.g_cap;
+  uint64_t* s_acc = smem;
+  uint32_t* s_seen = (uint32_t*)(s_acc + (size_t)G * W * T);
+  KeyCache cache;
+  {
+    unsigned char* p = (unsigned char*)(s_seen + ((G + 1) & ~1u));
+    cache.k0 = (uint64_t*)p;      p += (size_t)a.cache_slots * 8;
+    cache.k1 = (uint64_t*)p;      p += (size_t)a.cache_slots * 8;
+    cache.state = (uint32_t*)p;   p += (size_t)a.cache_slots * 4;
+    cache.meta = (uint32_t*)p;
+    cache.mask = a.cache_slots - 1;
+  }
+  __shared__ int s_abort;
+  for (uint32_t i = threadIdx.x; i < G * W * T; i += T) s_acc[i] = 0;
+  for (uint32_t i = threadIdx.x; i < G; i += T) s_seen[i] = 0;
+  for (uint32_t i = threadIdx.x; i < a.cache_slots; i += T) cache.state[i] = 0;
+  if (threadIdx.x == 0) s_abort = 0;
+  __syncthreads();
+
+  bool ovf = false;
+  const int64_t tile = (int64_t)T * R, last = a.n_rows - 1;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < a.n_rows; base += (int64_t)gridDim.x * tile) {
+    typename Plan::Raw x[R];
+    // phase 1: every load of the tile in flight before anything is consumed (rows past the end re-read the last row)
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      Plan::template load1<7>(a, r < last ? r : last, x[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      Plan::template load2<7>(a, r < last ? r : last, x[u]);
+    }
+    // phase 2
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      if (r > last || !Plan::filter(a, x[u])) continue;
+      const PackedKey k = Plan::key(a, x[u]);
+      const uint32_t gid = cached_intern<KW>(cache, a.t, k);
+      if (gid >= G) { s_abort = 1; continue; }  // beyond the private capacity (or the global table overflowed)
+      PrivateSink<T> sink{s_acc + (size_t)gid * W * T + threadIdx.x};
+      const uint32_t seen = Plan::accumulate(a, x[u], sink, &ovf);
+      if (Plan::HAS_SEEN && seen) atomicOr(&s_seen[gid], seen);
+    }
+    if (*(volatile int*)&s_abort || *(volatile int*)&a.t.flags[3]) break;  // some CTA gave up: the pass is void
+  }
+  if (ovf) atomicOr(&a.t.flags[2], 1);
+  __syncthreads();
+  if (s_abort) {
+    if (threadIdx.x == 0) atomicOr(&a.t.flags[3], 1);
+    return;
+  }
+  uint64_t* slab = a.scratch + (size_t)blockIdx.x * fused_slab_words(G, W);
+  FlushPrivate<T> fl{s_acc, slab, G, W};
+  Plan::for_each_acc(fl);
+  uint32_t* slab_seen = (uint32_t*)(slab + (size_t)G * W);
+  for (uint32_t i = threadIdx.x; i < G; i += T) slab_seen[i] = s_seen[i];
+}
+
+// two-pass path, pass 1
+template <class Plan>
+__device__ __forceinline__ void intern_body(const JitArgs& a) {
+  constexpr int T = Plan::T, R = Plan::R;
+  const int64_t tile = (int64_t)T * R, last = a.n_rows - 1;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < a.n_rows; base += (int64_t)gridDim.x * tile) {
+    typename Plan::Raw x[R];
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      Plan::template load1<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      Plan::template load2<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      if (r > last) continue;
+      uint32_t gid = kNoGroup;
+      if (Plan::filter(a, x[u])) gid = intern<Plan::KEY_WORDS>(a.t, Plan::key(a, x[u]));
+      a.gids[r] = gid;
+    }
+  }
+}
+
+// two-pass path, pass 2. TIER 1: `replicas` shared-memory copies of [n_groups][W] + atomics; TIER 2: global atomics.
+template <class Plan, int TIER>
+__device__ __forceinline__ void accumulate_body(const JitArgs& a) {
+  constexpr int T = Plan::T, R = Plan::R, W = Plan::W;
+  extern __shared__ __align__(16) uint64_t smem[];
+  uint64_t* s_acc = smem;
+  uint32_t* s_seen = nullptr;
+  const uint32_t n_groups = a.n_groups;
+  if (TIER == 1) {
+    for (uint32_t i = threadIdx.x; i < n_groups * W * a.replicas; i += T) s_acc[i] = 0;
+    s_seen = (uint32_t*)(s_acc + (size_t)n_groups * W * a.replicas);
+    if (Plan::HAS_SEEN)
+      for (uint32_t i = threadIdx.x; i < n_groups; i += T) s_seen[i] = 0;
+    __syncthreads();
+  }
+  const uint32_t rep = TIER == 1 ? (threadIdx.x % a.replicas) : 0;
+  bool ovf = false;
+  const int64_t tile = (int64_t)T * R, last = a.n_rows - 1;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < a.n_rows; base += (int64_t)gridDim.x * tile) {
+    typename Plan::Raw x[R];
+    uint32_t g[R];
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      g[u] = r <= last ? a.gids[r] : kNoGroup;
+      Plan::template load1<NEED_VALUES>(a, r < last ? r : last, x[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      Plan::template load2<NEED_VALUES>(a, r < last ? r : last, x[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      if (g[u] == kNoGroup) continue;
+      uint32_t seen;
+      if (TIER == 1) {
+        SharedAtomicSink sink{s_acc + ((size_t)rep * n_groups + g[u]) * W};
+        seen = Plan::accumulate(a, x[u], sink, &ovf);
+        if (Plan::HAS_SEEN && seen) atomicOr(&s_seen[g[u]], seen);
+      } else {
+        GlobalAtomicSink sink{g[u]};
+        seen = Plan::accumulate(a, x[u], sink, &ovf);
+        if (Plan::HAS_SEEN && seen) atomicOr(&a.seen[g[u]], seen);
+      }
+    }
+  }
+  if (ovf) atomicOr(&a.t.flags[2], 1);
+  if (TIER != 1) return;
+  __syncthreads();
+  FlushShared fl{s_acc, &a, n_groups, a.replicas, W, T};
+  Plan::for_each_acc(fl);
+  if (Plan::HAS_SEEN)
+    for (uint32_t i = threadIdx.x; i < n_groups; i += T)
+      if (s_seen[i]) atomicOr(&a.seen[i], s_seen[i]);
+}
+
+}  // namespace bgpu

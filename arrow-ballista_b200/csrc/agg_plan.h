@@ -144,6 +144,23 @@ struct HFilterTerm {
   double flit = 0.0;
 };
 
+// ---- runtime-specialised kernels (agg_jit_prelude.cuh + agg_codegen.cu) ------------------------------------------------
+constexpr int kJitSlots = 24;
+constexpr int kJitAcc = 24;
+// Host mirror of the prelude's JitArgs: the single by-value argument of every generated kernel (same layout).
+struct JitArgs {
+  const void* col[kJitSlots];
+  const int32_t* aux[kJitSlots];
+  const uint8_t* valid[kJitSlots];
+  GroupTable t;
+  uint64_t* acc_out[kJitAcc];
+  uint32_t* seen;
+  uint64_t* scratch;
+  uint32_t* gids;
+  int64_t n_rows;
+  uint32_t g_cap, cache_slots, n_groups, replicas;
+};
+
 // Compile one aggregate-argument program. `fields` is the raw input schema. Returns BGPU_OK or fails ctx.
 int compile_value(bgpu_ctx* ctx, const std::vector<Column>& fields, const bgpu_expr_node* nodes, int32_t n,
                   HValue* out);

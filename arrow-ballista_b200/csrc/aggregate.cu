@@ -9,6 +9,7 @@
 #include <algorithm>
 
 #include "agg_host.h"
+#include "jit.h"
 
 using namespace bgpu;
 
@@ -22,17 +23,19 @@ static bool is_unsigned(int vk) { return vk == V_U8 || vk == V_U16 || vk == V_U3
 static int agg_create_impl(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema* input_schema,
                            const int32_t* group_cols, int32_t n_group, const int32_t* agg_fns,
                            const bgpu_expr_node* nodes, const int32_t* agg_expr_offsets, const char* const* agg_names,
-                           int32_t n_agg, const bgpu_expr_node* filter, int32_t n_filter, bgpu_agg** out) {
+                           int32_t n_agg, const bgpu_expr_node* filter, int32_t n_filter, bool plan_only,
+                           bgpu_agg** out) {
   if (!ctx || !out) return BGPU_EINVAL;
   *out = nullptr;
-  if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
+  if (!plan_only && !ctx->has_device)
+    return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
   if (!input_schema || !input_schema->format || strcmp(input_schema->format, "+s") != 0)
     return ctx->fail(BGPU_EINVAL, "input_schema must be a struct schema");
   if (mode < BGPU_AGG_MODE_PARTIAL || mode > BGPU_AGG_MODE_SINGLE) return ctx->fail(BGPU_EINVAL, "bad aggregate mode");
   if (n_group < 1 || n_group > kMaxGroupCols)
     return ctx->fail(BGPU_EUNSUPPORTED, "1..8 group columns supported (no-GROUP-BY aggregates use AggregateStream)");
   if (n_agg < 0 || n_agg > 16) return ctx->fail(BGPU_EUNSUPPORTED, "at most 16 aggregates");
-  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (!plan_only) BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
   std::unique_ptr<bgpu_agg> g(new bgpu_agg(ctx));
   g->mode = mode;
   g->final_mode = mode == BGPU_AGG_MODE_FINAL || mode == BGPU_AGG_MODE_FINAL_PARTITIONED;
@@ -176,9 +179,11 @@ static int agg_create_impl(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema
       for (int k = 0; k < 2; k++)
         if (a.phys[k] >= 0) a.phys[k] = pnew[(size_t)a.phys[k]];
   }
-  BGPU_TRY(dev_alloc(ctx, 32, &g->counters));
-  BGPU_CUDA(ctx, cudaMemsetAsync(g->counters->p, 0, 32, ctx->stream));
-  BGPU_TRY(agg_resize(g.get(), 1u << 16, 0));
+  if (!plan_only) {
+    BGPU_TRY(dev_alloc(ctx, 32, &g->counters));
+    BGPU_CUDA(ctx, cudaMemsetAsync(g->counters->p, 0, 32, ctx->stream));
+    BGPU_TRY(agg_resize(g.get(), 1u << 16, 0));
+  }
   *out = g.release();
   return BGPU_OK;
 }
@@ -190,7 +195,7 @@ extern "C" int bgpu_agg_create_expr(bgpu_ctx* ctx, int32_t mode, const struct Ar
                                     int32_t n_filter, bgpu_agg** out) {
   if (!group_cols || (n_agg > 0 && (!agg_fns || !agg_expr_offsets))) return BGPU_EINVAL;
   return agg_create_impl(ctx, mode, input_schema, group_cols, n_group, agg_fns, nodes, agg_expr_offsets, agg_names, n_agg,
-                         filter, n_filter, out);
+                         filter, n_filter, false, out);
 }
 
 extern "C" int bgpu_agg_create(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema* input_schema,
@@ -209,7 +214,80 @@ extern "C" int bgpu_agg_create(bgpu_ctx* ctx, int32_t mode, const struct ArrowSc
     offs.push_back((int32_t)nodes.size());
   }
   return agg_create_impl(ctx, mode, input_schema, group_cols, n_group, agg_fns, nodes.data(), offs.data(), agg_names, n_agg,
-                         nullptr, 0, out);
+                         nullptr, 0, false, out);
+}
+
+// Introspection (no device needed): generate the kernels of this plan for a synthetic batch shape and compile them
+// with NVRTC. flags bit 0: every column carries validity; bit 1: dictionary keys need a remap; bit 2: seen tracking on.
+// Writes <out_prefix>.cu and <out_prefix>.cubin when out_prefix is not NULL.
+extern "C" int bgpu_agg_debug_compile(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema* input_schema,
+                                      const int32_t* group_cols, int32_t n_group, const int32_t* agg_fns,
+                                      const bgpu_expr_node* nodes, const int32_t* agg_expr_offsets, int32_t n_agg,
+                                      const bgpu_expr_node* filter, int32_t n_filter, int32_t flags, int32_t threads,
+                                      int32_t rows_per_thread, int32_t min_ctas, const char* out_prefix) {
+  bgpu_agg* gp = nullptr;
+  BGPU_TRY(agg_create_impl(ctx, mode, input_schema, group_cols, n_group, agg_fns, nodes, agg_expr_offsets, nullptr, n_agg,
+                           filter, n_filter, true, &gp));
+  std::unique_ptr<bgpu_agg> g(gp);
+  const bool nullable = flags & 1;
+  JitShape sh;
+  auto use = [&](int32_t col, const Column& f, int32_t vk) -> JitSlot& {
+    JitSlot& sl = sh.slots[(size_t)jit_slot(&sh, col)];
+    sl.kind = f.kind; sl.width = f.width; sl.nullable = nullable;
+    if (vk != V_NONE) sl.vk = vk;
+    return sl;
+  };
+  for (size_t i = 0; i < g->group_cols.size(); i++) {
+    const int32_t bc = g->final_mode ? (int32_t)i : g->group_cols[i];
+    JitSlot& sl = use(bc, g->fields[(size_t)g->group_cols[i]], V_NONE);
+    sl.key_use = true;
+    sl.remap = sl.kind == K_DICT32 && (flags & 2);
+    sh.key_slot.push_back(jit_slot(&sh, bc));
+  }
+  for (const HFilterTerm& t : g->filter) {
+    use(t.col, g->fields[(size_t)t.col], t.vk).filter_use = true;
+    sh.filter_slot.push_back(jit_slot(&sh, t.col));
+  }
+  for (size_t vi = 0; vi < g->values.size(); vi++) {
+    bool has_col = g->value_from_prev[vi] ? (bool)sh.value_nullable[vi - 1] : false;
+    for (const HFactor& f : g->values[vi].f)
+      for (const HAtom* a : {&f.x, &f.y}) {
+        if ((a == &f.y && !f.op) || !a->is_col) continue;
+        Column c;  // Final modes read state columns: fixed width by ValKind
+        c.kind = K_FIXED;
+        c.width = a->vk == V_I128 ? 16 : 8;
+        use(a->col, g->final_mode ? c : g->fields[(size_t)a->col], a->vk).value_use = true;
+        has_col = true;
+      }
+    sh.value_nullable.push_back(nullable && has_col);
+  }
+  int32_t first_count = -1, w = 0;
+  for (size_t i = 0; i < g->phys.size(); i++) {
+    int32_t alias = -1;
+    if (g->phys[i].op == OP_COUNT && !sh.value_nullable[(size_t)g->phys[i].value]) {
+      if (first_count < 0) first_count = (int32_t)i;
+      else alias = first_count;
+    }
+    sh.acc_alias.push_back(alias);
+    sh.acc_word0.push_back(alias < 0 ? w : 0);
+    if (alias < 0) w += g->phys[i].words;
+  }
+  sh.W = w;
+  sh.has_seen = flags & 4;
+  sh.T = threads; sh.R = rows_per_thread; sh.min_ctas = min_ctas;
+  std::string src, cubin;
+  BGPU_TRY(agg_generate_source(g.get(), sh, &src));
+  src = std::string(agg_jit_prelude()) + src;
+  if (out_prefix) {
+    FILE* f = fopen((std::string(out_prefix) + ".cu").c_str(), "w");
+    if (f) { fwrite(src.data(), 1, src.size(), f); fclose(f); }
+  }
+  BGPU_TRY(jit_compile_cubin(ctx, src, &cubin));
+  if (out_prefix) {
+    FILE* f = fopen((std::string(out_prefix) + ".cubin").c_str(), "wb");
+    if (f) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
+  }
+  return BGPU_OK;
 }
 
 extern "C" void bgpu_agg_destroy(bgpu_agg* g) {

@@ -17,6 +17,7 @@
 
 #include "agg_host.h"
 #include "agg_kernels.cuh"
+#include "jit.h"
 
 using namespace bgpu;
 
@@ -163,42 +164,29 @@ static int upload_canonical_dictionary(bgpu_agg* g, size_t i, std::shared_ptr<Co
 }
 
 // ---- binding ----------------------------------------------------------------------------------------------------
+// One batch bound to the aggregate: the shape the kernels are specialised for (JitShape), their argument struct
+// (JitArgs) and the interpreted accumulator plan the small AOT commit kernel still uses (AccPlan).
 struct Bound {
-  KeyPlan kp{};
-  FilterPlan fp{};
-  ValuePlan vp{};
+  JitShape sh;
+  JitArgs args{};
   AccPlan ap{};
-  bool any_validity = false;
-  std::vector<bool> value_nullable;
+  const JitModule* mod = nullptr;
 };
+enum JitKernel : int { JK_FUSED = 0, JK_INTERN = 1, JK_ACC_SHARED = 2, JK_ACC_GLOBAL = 3 };
 
-static int bind_atom(bgpu_ctx* ctx, const bgpu_batch* batch, const HAtom& h, __int128 mul, int32_t cls, Atom* a,
-                     bool* nullable) {
-  *a = Atom{};
-  a->mul = 1;
-  if (!h.is_col) {
-    if (cls == CLS_F64) {
-      memcpy(&a->lit_lo, &h.flit, 8);
-    } else {
-      __int128 v = h.lit;
-      if (cls == CLS_I128 && __builtin_mul_overflow(h.lit, mul, &v))
-        return ctx->fail(BGPU_EOVERFLOW, "Overflow happened on rescaling a decimal literal");
-      a->lit_lo = (uint64_t)v;
-      a->lit_hi = (uint64_t)((unsigned __int128)v >> 64);
-    }
-    return BGPU_OK;
-  }
+static int bind_value_atom(bgpu_ctx* ctx, const bgpu_batch* batch, const HAtom& h, Bound* b, bool* nullable) {
+  if (!h.is_col) return BGPU_OK;
   if (h.col < 0 || h.col >= (int32_t)batch->cols.size()) return ctx->fail(BGPU_EINVAL, "batch has too few columns");
   const Column& c = batch->cols[(size_t)h.col];
   if (c.kind != K_FIXED || c.width != vk_width(h.vk))
     return ctx->fail(BGPU_EINVAL, "aggregate input column " + c.name + " has an unexpected type");
-  a->col = c.values;
-  a->validity = c.validity;
-  a->vk = h.vk;
-  if (mul != 1) {
-    if (mul > (__int128)UINT64_MAX) return ctx->fail(BGPU_EUNSUPPORTED, "decimal rescale factor beyond 10^19");
-    a->mul = (uint64_t)mul;
-  }
+  const int32_t s = jit_slot(&b->sh, h.col);
+  if (s < 0) return ctx->fail(BGPU_EUNSUPPORTED, "aggregate reads more than 24 distinct columns");
+  JitSlot& sl = b->sh.slots[(size_t)s];
+  sl.kind = c.kind; sl.width = c.width; sl.vk = h.vk; sl.value_use = true;
+  sl.nullable = c.validity != nullptr;
+  b->args.col[s] = c.values;
+  b->args.valid[s] = c.validity;
   if (c.validity) *nullable = true;
   return BGPU_OK;
 }
@@ -206,8 +194,6 @@ static int bind_atom(bgpu_ctx* ctx, const bgpu_batch* batch, const HAtom& h, __i
 static int bind_batch(bgpu_agg* g, const bgpu_batch* batch, Bound* b) {
   bgpu_ctx* ctx = g->ctx;
   const int32_t n_group = (int32_t)g->group_cols.size();
-  b->kp.n = n_group;
-  b->kp.words = g->key_words;
   for (int32_t i = 0; i < n_group; i++) {
     const int32_t bc = g->final_mode ? i : g->group_cols[(size_t)i];
     if (bc >= (int32_t)batch->cols.size()) return ctx->fail(BGPU_EINVAL, "batch has too few columns");
@@ -216,67 +202,52 @@ static int bind_batch(bgpu_agg* g, const bgpu_batch* batch, Bound* b) {
     if (!same_shape(c, f)) return ctx->fail(BGPU_EINVAL, "group column " + f.name + " does not match input_schema");
     const int32_t* remap = nullptr;
     if (c.kind == K_DICT32) BGPU_TRY(canonicalize_dictionary(g, i, c, &remap));
-    b->kp.cols[i] = KeyCol{c.values, c.offsets, c.validity, remap, c.kind, g->key_width[(size_t)i], g->key_off[(size_t)i], 0};
+    const int32_t s = jit_slot(&b->sh, bc);
+    if (s < 0) return ctx->fail(BGPU_EUNSUPPORTED, "aggregate reads more than 24 distinct columns");
+    JitSlot& sl = b->sh.slots[(size_t)s];
+    sl.kind = c.kind; sl.width = c.width; sl.key_use = true;
+    sl.nullable = c.validity != nullptr;
+    sl.remap = remap != nullptr;
+    b->args.col[s] = c.values;
+    b->args.valid[s] = c.validity;
+    b->args.aux[s] = c.kind == K_DICT32 ? remap : c.offsets;
+    b->sh.key_slot.push_back(s);
   }
-  b->fp.n = (int32_t)g->filter.size();
   for (size_t i = 0; i < g->filter.size(); i++) {
     const HFilterTerm& h = g->filter[i];
     if (h.col >= (int32_t)batch->cols.size()) return ctx->fail(BGPU_EINVAL, "batch has too few columns");
     const Column& c = batch->cols[(size_t)h.col];
     if (c.kind != K_FIXED || c.width != vk_width(h.vk))
       return ctx->fail(BGPU_EINVAL, "filter column " + c.name + " has an unexpected type");
-    FilterTerm& t = b->fp.t[i];
-    t = FilterTerm{c.values, c.validity, 0, 0, h.vk, h.cmp};
-    if (h.vk == V_F64 || h.vk == V_F32) {
-      memcpy(&t.lit_lo, &h.flit, 8);
-    } else {
-      t.lit_lo = (uint64_t)h.lit;
-      t.lit_hi = (uint64_t)((unsigned __int128)h.lit >> 64);
-    }
+    const int32_t s = jit_slot(&b->sh, h.col);
+    if (s < 0) return ctx->fail(BGPU_EUNSUPPORTED, "aggregate reads more than 24 distinct columns");
+    JitSlot& sl = b->sh.slots[(size_t)s];
+    sl.kind = c.kind; sl.width = c.width; sl.vk = h.vk; sl.filter_use = true;
+    sl.nullable = c.validity != nullptr;
+    b->args.col[s] = c.values;
+    b->args.valid[s] = c.validity;
+    b->sh.filter_slot.push_back(s);
   }
-  b->vp.n = (int32_t)g->values.size();
-  b->value_nullable.assign(g->values.size(), false);
+  b->sh.value_nullable.assign(g->values.size(), false);
   for (size_t vi = 0; vi < g->values.size(); vi++) {
     const HValue& h = g->values[vi];
-    ValueExpr& e = b->vp.v[vi];
-    e = ValueExpr{};
-    e.cls = h.cls;
-    e.n_factors = (int32_t)h.f.size();
-    e.from_prev = g->value_from_prev[vi] ? 1 : 0;
-    bool nullable = e.from_prev ? (bool)b->value_nullable[vi - 1] : false;
-    for (size_t fi = 0; fi < h.f.size(); fi++) {
-      const HFactor& hf = h.f[fi];
-      Factor& f = e.f[fi];
-      f.op = hf.op;
-      BGPU_TRY(bind_atom(ctx, batch, hf.x, hf.x_mul, h.cls, &f.x, &nullable));
-      if (hf.op) BGPU_TRY(bind_atom(ctx, batch, hf.y, hf.y_mul, h.cls, &f.y, &nullable));
+    bool nullable = g->value_from_prev[vi] ? (bool)b->sh.value_nullable[vi - 1] : false;
+    for (const HFactor& hf : h.f) {
+      BGPU_TRY(bind_value_atom(ctx, batch, hf.x, b, &nullable));
+      if (hf.op) BGPU_TRY(bind_value_atom(ctx, batch, hf.y, b, &nullable));
     }
-    b->value_nullable[vi] = nullable;
-    b->any_validity |= nullable;
+    b->sh.value_nullable[vi] = nullable;
+    b->sh.any_validity |= nullable;
   }
+  // accumulator words. Counts over null-free values all equal the row count of the group, so only the first is
+  // kept live and the others alias it (the flush adds the alias' partial; the global-atomic tier adds all of them).
   b->ap.n = (int32_t)g->phys.size();
-  for (int32_t i = 0; i < b->ap.n; i++) {
-    const PhysAcc& p = g->phys[(size_t)i];
-    b->ap.a[i] = AccK{(uint64_t*)p.buf->p, p.op, p.words, 0, i, -1, 0};
-  }
-  for (int32_t vi = 0; vi < b->vp.n; vi++) {
-    int32_t lo = b->ap.n, hi = 0;
-    for (int32_t i = 0; i < b->ap.n; i++)
-      if (g->phys[(size_t)i].value == vi) { lo = std::min(lo, i); hi = std::max(hi, i + 1); }
-    b->vp.v[vi].acc_begin = lo < hi ? lo : 0;
-    b->vp.v[vi].acc_end = lo < hi ? hi : 0;
-  }
-  return BGPU_OK;
-}
-
-// Assign private/shared word offsets; with `alias_counts`, counts over null-free values all equal the row count of
-// the group, so only the first is kept live and the others alias it (fused path only).
-static void layout_words(const bgpu_agg* g, Bound* b, bool alias_counts) {
   int32_t first_count = -1, w = 0;
   for (int32_t i = 0; i < b->ap.n; i++) {
+    const PhysAcc& p = g->phys[(size_t)i];
     AccK& a = b->ap.a[i];
-    a.alias = -1;
-    if (alias_counts && a.op == OP_COUNT && !b->value_nullable[(size_t)g->phys[(size_t)i].value]) {
+    a = AccK{(uint64_t*)p.buf->p, p.op, p.words, 0, i, -1, 0};
+    if (p.op == OP_COUNT && !b->sh.value_nullable[(size_t)p.value]) {
       if (first_count < 0) first_count = i;
       else a.alias = first_count;
     }
@@ -284,8 +255,37 @@ static void layout_words(const bgpu_agg* g, Bound* b, bool alias_counts) {
       a.word0 = w;
       w += a.words;
     }
+    b->sh.acc_alias.push_back(a.alias);
+    b->sh.acc_word0.push_back(a.word0);
   }
   b->ap.total_words = w;
+  b->sh.W = w;
+  return BGPU_OK;
+}
+
+// accumulator / seen arrays and the table move when the table grows
+static void refresh_pointers(bgpu_agg* g, Bound* b) {
+  for (int32_t i = 0; i < b->ap.n; i++) {
+    b->ap.a[i].out = (uint64_t*)g->phys[(size_t)i].buf->p;
+    b->args.acc_out[i] = b->ap.a[i].out;
+  }
+  b->ap.seen = g->seen_tracking ? (uint32_t*)g->seen->p : nullptr;
+  b->args.seen = b->ap.seen;
+  b->args.t = g->table();
+}
+
+// Generate + compile (cached) the kernels for this batch shape at the given launch geometry.
+static int specialise(bgpu_agg* g, Bound* b, int T, int R, int min_ctas) {
+  b->sh.T = T; b->sh.R = R; b->sh.min_ctas = min_ctas;
+  b->sh.has_seen = g->seen_tracking;
+  std::string src;
+  BGPU_TRY(agg_generate_source(g, b->sh, &src));
+  auto it = g->modules.find(src);
+  if (it != g->modules.end()) { b->mod = it->second; return BGPU_OK; }
+  static const std::vector<std::string> names{"bgpu_fused", "bgpu_intern", "bgpu_acc_shared", "bgpu_acc_global"};
+  BGPU_TRY(jit_compile(g->ctx, agg_jit_prelude(), src, names, &b->mod));
+  g->modules.emplace(std::move(src), b->mod);
+  return BGPU_OK;
 }
 
 static int read_counters(bgpu_agg* g, uint32_t* h) {
@@ -324,34 +324,17 @@ static int grow_after_overflow(bgpu_agg* g, uint32_t counter) {
   return agg_resize(g, new_max, keep);
 }
 
-// accumulator / seen arrays move when the table grows
-static void refresh_pointers(bgpu_agg* g, Bound* b) {
-  for (int32_t i = 0; i < b->ap.n; i++) b->ap.a[i].out = (uint64_t*)g->phys[(size_t)i].buf->p;
-  b->ap.seen = g->seen_tracking ? (uint32_t*)g->seen->p : nullptr;
-}
-
-struct Rung { int threads; int rows; size_t smem_cap; const char* name; };
-
-template <int T, int R>
-static int launch_fused(bgpu_agg* g, const Bound& b, const FusedArgs& fa, int grid, size_t smem, int64_t n_rows) {
-  bgpu_ctx* ctx = g->ctx;
-  BGPU_CUDA(ctx, cudaFuncSetAttribute(fused_private_kernel<T, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  fused_private_kernel<T, R><<<grid, T, smem, ctx->stream>>>(b.kp, g->table(), b.fp, b.vp, b.ap, fa, n_rows);
-  ctx->launches++;
-  BGPU_CUDA(ctx, cudaGetLastError());
-  return BGPU_OK;
-}
+struct Rung { int threads; int rows; int min_ctas; size_t smem_cap; const char* name; };
 
 // Try the fused ladder. *done = true when the batch has been committed.
 static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
   bgpu_ctx* ctx = g->ctx;
   *done = false;
-  layout_words(g, b, true);
-  const int W = b->ap.total_words;
+  const int W = b->sh.W;
   if (W == 0) { g->fused_rung = kFusedRungs; return BGPU_OK; }
   const size_t smem_max = ctx->smem_optin - 1024;
-  const Rung rungs[kFusedRungs] = {{256, 4, smem_max / 2 - 1024, "fused256x2"}, {256, 4, smem_max, "fused256"},
-                                   {128, 8, smem_max, "fused128"}};
+  const Rung rungs[kFusedRungs] = {{256, 4, 2, smem_max / 2 - 1024, "fused256x2"}, {256, 4, 1, smem_max, "fused256"},
+                                   {128, 8, 1, smem_max, "fused128"}};
   while (g->fused_rung < kFusedRungs) {
     const Rung& rg = rungs[g->fused_rung];
     const int T = rg.threads;
@@ -362,29 +345,27 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
     const uint32_t slots = std::max<uint32_t>(16, next_pow2((uint64_t)G * 2));
     const size_t smem = (size_t)G * W * T * 8 + (size_t)((G + 1) & ~1u) * 4 + (size_t)slots * 24;
     if (smem > smem_max) { g->fused_rung++; continue; }
+    BGPU_TRY(specialise(g, b, T, rg.rows, rg.min_ctas));
+    const CUfunction fn = b->mod->fn[JK_FUSED];
+    BGPU_TRY(jit_set_max_smem(ctx, fn, smem));
     int occ = 1;
-    if (T == 256) {
-      BGPU_CUDA(ctx, cudaFuncSetAttribute(fused_private_kernel<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      BGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_private_kernel<256, 4>, T, smem));
-    } else {
-      BGPU_CUDA(ctx, cudaFuncSetAttribute(fused_private_kernel<128, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      BGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fused_private_kernel<128, 8>, T, smem));
-    }
+    BGPU_TRY(jit_occupancy(ctx, fn, T, smem, &occ));
     occ = std::max(1, occ);
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ceil_div64(n_rows, (int64_t)T * rg.rows), (int64_t)ctx->sm_count * occ));
     const size_t scratch_bytes = (size_t)grid * fused_slab_words(G, W) * 8;
     if (!g->scratch || g->scratch->bytes < scratch_bytes) BGPU_TRY(dev_alloc(ctx, scratch_bytes, &g->scratch));
-    FusedArgs fa{(uint64_t*)g->scratch->p, G, slots, rg.rows, 0};
+    b->args.scratch = (uint64_t*)g->scratch->p;
+    b->args.g_cap = G;
+    b->args.cache_slots = slots;
     for (int attempt = 0;; attempt++) {
-      if (T == 256) BGPU_TRY((launch_fused<256, 4>(g, *b, fa, grid, smem, n_rows)));
-      else BGPU_TRY((launch_fused<128, 8>(g, *b, fa, grid, smem, n_rows)));
+      refresh_pointers(g, b);
+      BGPU_TRY(jit_launch(ctx, fn, grid, T, smem, &b->args));
       uint32_t h[8];
       BGPU_TRY(read_counters(g, h));
       BGPU_TRY(check_common_flags(g, h));
       if (h[1]) {  // global table overflow: grow and run the same rung again
         if (attempt >= 4) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
         BGPU_TRY(grow_after_overflow(g, h[0]));
-        refresh_pointers(g, b);
         continue;
       }
       if (h[4]) {  // some CTA met a group id >= G: nothing was committed; the groups interned so far stay
@@ -394,7 +375,7 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
         break;
       }
       g->n_groups = h[0];
-      if (b->any_validity && !g->seen_tracking) return ctx->fail(BGPU_EINVAL, "internal: seen tracking not set up");
+      if (b->sh.any_validity && !g->seen_tracking) return ctx->fail(BGPU_EINVAL, "internal: seen tracking not set up");
       commit_kernel<<<agg_launch_grid(ctx, std::max<uint32_t>(1, g->n_groups * (uint32_t)b->ap.n), kAggThreads), kAggThreads, 0,
                       ctx->stream>>>(b->ap, (const uint64_t*)g->scratch->p, (uint32_t)grid, G, g->n_groups);
       ctx->launches++;
@@ -410,14 +391,17 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
 
 static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
   bgpu_ctx* ctx = g->ctx;
-  layout_words(g, b, false);
+  constexpr int T = 256, R = 4;
+  // the module of the first fused rung has the same geometry: reuse it when this batch already built it
+  if (!(b->mod && b->sh.T == T && b->sh.R == R)) BGPU_TRY(specialise(g, b, T, R, 2));
   DevAllocPtr gids;
   BGPU_TRY(dev_alloc(ctx, (size_t)n_rows * 4, &gids));
+  b->args.gids = (uint32_t*)gids->p;
+  const int64_t tiles = ceil_div64(n_rows, (int64_t)T * R);
   for (int attempt = 0;; attempt++) {
-    const int grid = (int)std::min<int64_t>(ceil_div64(n_rows, kAggThreads), (int64_t)ctx->sm_count * 8);
-    intern_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(b->kp, g->table(), b->fp, n_rows, (uint32_t*)gids->p);
-    ctx->launches++;
-    BGPU_CUDA(ctx, cudaGetLastError());
+    refresh_pointers(g, b);
+    const int grid = (int)std::min<int64_t>(tiles, (int64_t)ctx->sm_count * 8);
+    BGPU_TRY(jit_launch(ctx, b->mod->fn[JK_INTERN], grid, T, 0, &b->args));
     uint32_t h[8];
     BGPU_TRY(read_counters(g, h));
     BGPU_TRY(check_common_flags(g, h));
@@ -431,27 +415,27 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
   refresh_pointers(g, b);
   if (b->ap.n == 0) { g->last_path = "intern"; return BGPU_OK; }
   const uint32_t ng = g->n_groups;
+  b->args.n_groups = ng;
   const size_t limit = std::min<size_t>(ctx->smem_optin, 200 * 1024);
-  const size_t group_bytes = (size_t)b->ap.total_words * 8;
+  const size_t group_bytes = (size_t)b->sh.W * 8;
   if ((size_t)ng * group_bytes + (size_t)ng * 4 <= limit / 2) {
     int replicas = (int)std::min<size_t>(32, (limit / 2 - (size_t)ng * 4) / std::max<size_t>(1, (size_t)ng * group_bytes));
     if (replicas < 1) replicas = 1;
     const size_t smem = (size_t)ng * group_bytes * replicas + (size_t)ng * 4;
-    BGPU_CUDA(ctx, cudaFuncSetAttribute(accumulate_kernel<TIER_SHARED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const CUfunction fn = b->mod->fn[JK_ACC_SHARED];
+    BGPU_TRY(jit_set_max_smem(ctx, fn, smem));
     int occ = 1;
-    BGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, accumulate_kernel<TIER_SHARED>, kAggThreads, smem));
-    const int grid = (int)std::min<int64_t>(ceil_div64(n_rows, kAggThreads * kRowsPerIter), (int64_t)ctx->sm_count * std::max(1, occ));
-    accumulate_kernel<TIER_SHARED><<<grid, kAggThreads, smem, ctx->stream>>>(b->vp, b->ap, (const uint32_t*)gids->p, n_rows, ng,
-                                                                            replicas, g->d_flags());
+    BGPU_TRY(jit_occupancy(ctx, fn, T, smem, &occ));
+    const int grid = (int)std::min<int64_t>(tiles, (int64_t)ctx->sm_count * std::max(1, occ));
+    b->args.replicas = (uint32_t)replicas;
+    BGPU_TRY(jit_launch(ctx, fn, grid, T, smem, &b->args));
     g->last_path = "shared";
   } else {
-    const int grid = (int)std::min<int64_t>(ceil_div64(n_rows, kAggThreads * kRowsPerIter), (int64_t)ctx->sm_count * 8);
-    accumulate_kernel<TIER_GLOBAL><<<grid, kAggThreads, 0, ctx->stream>>>(b->vp, b->ap, (const uint32_t*)gids->p, n_rows, ng, 1,
-                                                                         g->d_flags());
+    const int grid = (int)std::min<int64_t>(tiles, (int64_t)ctx->sm_count * 8);
+    b->args.replicas = 1;
+    BGPU_TRY(jit_launch(ctx, b->mod->fn[JK_ACC_GLOBAL], grid, T, 0, &b->args));
     g->last_path = "global";
   }
-  ctx->launches++;
-  BGPU_CUDA(ctx, cudaGetLastError());
   return BGPU_OK;
 }
 
@@ -465,7 +449,7 @@ extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) {
   Bound b;
   BGPU_TRY(bind_batch(g, batch, &b));
   if (n_rows == 0) return BGPU_OK;
-  if (b.any_validity && !g->seen_tracking) {
+  if (b.sh.any_validity && !g->seen_tracking) {
     // first batch with nulls in an aggregate input: groups created by earlier (null-free) batches have seen
     // every accumulator; groups new in this batch start at 0
     BGPU_TRY(dev_alloc(ctx, (size_t)g->max_groups * 4, &g->seen));
@@ -477,7 +461,7 @@ extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) {
     }
     g->seen_tracking = true;
   }
-  b.ap.seen = g->seen_tracking ? (uint32_t*)g->seen->p : nullptr;
+  b.args.n_rows = n_rows;
   bool done = false;
   if (g->fused_rung < kFusedRungs) BGPU_TRY(try_fused(g, &b, n_rows, &done));
   if (!done) BGPU_TRY(run_two_pass(g, &b, n_rows));

@@ -1,0 +1,176 @@
+// NVRTC + driver-API plumbing for the runtime-specialised aggregate kernels (see jit.h).
+#include "jit.h"
+
+#include <dlfcn.h>
+#include <nvrtc.h>
+
+#include <map>
+#include <mutex>
+
+namespace bgpu {
+namespace {
+
+struct Api {
+  bool ok = false;
+  std::string why;
+  // nvrtc
+  nvrtcResult (*CreateProgram)(nvrtcProgram*, const char*, const char*, int, const char* const*, const char* const*) = nullptr;
+  nvrtcResult (*CompileProgram)(nvrtcProgram, int, const char* const*) = nullptr;
+  nvrtcResult (*GetCUBINSize)(nvrtcProgram, size_t*) = nullptr;
+  nvrtcResult (*GetCUBIN)(nvrtcProgram, char*) = nullptr;
+  nvrtcResult (*GetProgramLogSize)(nvrtcProgram, size_t*) = nullptr;
+  nvrtcResult (*GetProgramLog)(nvrtcProgram, char*) = nullptr;
+  nvrtcResult (*DestroyProgram)(nvrtcProgram*) = nullptr;
+  // driver
+  CUresult (*ModuleLoadData)(CUmodule*, const void*) = nullptr;
+  CUresult (*ModuleGetFunction)(CUfunction*, CUmodule, const char*) = nullptr;
+  CUresult (*LaunchKernel)(CUfunction, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, CUstream,
+                           void**, void**) = nullptr;
+  CUresult (*FuncSetAttribute)(CUfunction, CUfunction_attribute, int) = nullptr;
+  CUresult (*Occupancy)(int*, CUfunction, int, size_t) = nullptr;
+  CUresult (*GetErrorString)(CUresult, const char**) = nullptr;
+};
+
+void* open_first(const std::vector<const char*>& names) {
+  for (const char* n : names) {
+    void* h = dlopen(n, RTLD_NOW | RTLD_LOCAL);
+    if (h) return h;
+  }
+  return nullptr;
+}
+
+const Api& api() {
+  static Api a;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* rtc = open_first({"libnvrtc.so.12", "libnvrtc.so", "/usr/local/cuda/lib64/libnvrtc.so.12",
+                            "/usr/local/cuda/lib64/libnvrtc.so"});
+    if (!rtc) { a.why = std::string("cannot load libnvrtc: ") + dlerror(); return; }
+    void* drv = open_first({"libcuda.so.1", "libcuda.so"});
+    if (!drv) { a.why = std::string("cannot load libcuda: ") + dlerror(); return; }
+    bool ok = true;
+    auto sym = [&](void* h, const char* n) { void* p = dlsym(h, n); if (!p) { ok = false; a.why = std::string("missing symbol ") + n; } return p; };
+    *(void**)&a.CreateProgram = sym(rtc, "nvrtcCreateProgram");
+    *(void**)&a.CompileProgram = sym(rtc, "nvrtcCompileProgram");
+    *(void**)&a.GetCUBINSize = sym(rtc, "nvrtcGetCUBINSize");
+    *(void**)&a.GetCUBIN = sym(rtc, "nvrtcGetCUBIN");
+    *(void**)&a.GetProgramLogSize = sym(rtc, "nvrtcGetProgramLogSize");
+    *(void**)&a.GetProgramLog = sym(rtc, "nvrtcGetProgramLog");
+    *(void**)&a.DestroyProgram = sym(rtc, "nvrtcDestroyProgram");
+    *(void**)&a.ModuleLoadData = sym(drv, "cuModuleLoadData");
+    *(void**)&a.ModuleGetFunction = sym(drv, "cuModuleGetFunction");
+    *(void**)&a.LaunchKernel = sym(drv, "cuLaunchKernel");
+    *(void**)&a.FuncSetAttribute = sym(drv, "cuFuncSetAttribute");
+    *(void**)&a.Occupancy = sym(drv, "cuOccupancyMaxActiveBlocksPerMultiprocessor");
+    *(void**)&a.GetErrorString = sym(drv, "cuGetErrorString");
+    a.ok = ok;
+  });
+  return a;
+}
+
+std::string cu_err(const Api& a, CUresult r) {
+  const char* s = nullptr;
+  if (a.GetErrorString) a.GetErrorString(r, &s);
+  return s ? s : ("CUresult " + std::to_string((int)r));
+}
+
+std::mutex g_mu;
+std::map<std::pair<int, std::string>, JitModule*> g_cache;  // (device, source) -> module; never freed
+
+}  // namespace
+
+// Host-side compile only (no driver needed): used by the CPU test-suite to check that every plan shape the tests
+// use generates source NVRTC accepts.
+int jit_compile_cubin(bgpu_ctx* ctx, const std::string& source, std::string* cubin) {
+  static Api rtc_only;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* rtc = open_first({"libnvrtc.so.12", "libnvrtc.so", "/usr/local/cuda/lib64/libnvrtc.so.12",
+                            "/usr/local/cuda/lib64/libnvrtc.so"});
+    if (!rtc) { rtc_only.why = std::string("cannot load libnvrtc: ") + dlerror(); return; }
+    bool ok = true;
+    auto sym = [&](const char* n) { void* p = dlsym(rtc, n); if (!p) ok = false; return p; };
+    *(void**)&rtc_only.CreateProgram = sym("nvrtcCreateProgram");
+    *(void**)&rtc_only.CompileProgram = sym("nvrtcCompileProgram");
+    *(void**)&rtc_only.GetCUBINSize = sym("nvrtcGetCUBINSize");
+    *(void**)&rtc_only.GetCUBIN = sym("nvrtcGetCUBIN");
+    *(void**)&rtc_only.GetProgramLogSize = sym("nvrtcGetProgramLogSize");
+    *(void**)&rtc_only.GetProgramLog = sym("nvrtcGetProgramLog");
+    *(void**)&rtc_only.DestroyProgram = sym("nvrtcDestroyProgram");
+    rtc_only.ok = ok;
+  });
+  const Api& a = rtc_only;
+  if (!a.ok) return ctx->fail(BGPU_ECUDA, "NVRTC unavailable: " + a.why);
+  nvrtcProgram prog;
+  if (a.CreateProgram(&prog, source.c_str(), "bgpu_agg.cu", 0, nullptr, nullptr) != NVRTC_SUCCESS)
+    return ctx->fail(BGPU_ECUDA, "nvrtcCreateProgram failed");
+  const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "-default-device"};
+  const nvrtcResult rc = a.CompileProgram(prog, 4, opts);
+  if (rc != NVRTC_SUCCESS) {
+    size_t n = 0;
+    a.GetProgramLogSize(prog, &n);
+    std::string log(n, '\0');
+    if (n) a.GetProgramLog(prog, &log[0]);
+    a.DestroyProgram(&prog);
+    if (log.size() > 4000) log.resize(4000);
+    return ctx->fail(BGPU_ECUDA, "NVRTC compile failed:\n" + log);
+  }
+  size_t n = 0;
+  a.GetCUBINSize(prog, &n);
+  cubin->assign(n, '\0');
+  a.GetCUBIN(prog, &(*cubin)[0]);
+  a.DestroyProgram(&prog);
+  return BGPU_OK;
+}
+
+int jit_compile(bgpu_ctx* ctx, const char* prelude, const std::string& source, const std::vector<std::string>& names,
+                const JitModule** out) {
+  const Api& a = api();
+  if (!a.ok) return ctx->fail(BGPU_ECUDA, "JIT unavailable: " + a.why);
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto key = std::make_pair(ctx->device, source);
+  auto it = g_cache.find(key);
+  if (it != g_cache.end()) { *out = it->second; return BGPU_OK; }
+  std::string cubin;
+  BGPU_TRY(jit_compile_cubin(ctx, std::string(prelude) + source, &cubin));
+  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  BGPU_CUDA(ctx, cudaFree(0));  // make sure the primary context is current for the driver calls
+  auto* m = new JitModule();
+  CUresult r = a.ModuleLoadData(&m->module, cubin.data());
+  if (r != CUDA_SUCCESS) { delete m; return ctx->fail(BGPU_ECUDA, "cuModuleLoadData: " + cu_err(a, r)); }
+  for (const std::string& n : names) {
+    CUfunction f;
+    r = a.ModuleGetFunction(&f, m->module, n.c_str());
+    if (r != CUDA_SUCCESS) { delete m; return ctx->fail(BGPU_ECUDA, "cuModuleGetFunction(" + n + "): " + cu_err(a, r)); }
+    m->fn.push_back(f);
+  }
+  g_cache[key] = m;
+  *out = m;
+  return BGPU_OK;
+}
+
+int jit_launch(bgpu_ctx* ctx, CUfunction fn, int grid, int block, size_t smem, const void* arg_struct) {
+  const Api& a = api();
+  void* params[] = {const_cast<void*>(arg_struct)};
+  const CUresult r = a.LaunchKernel(fn, (unsigned)grid, 1, 1, (unsigned)block, 1, 1, (unsigned)smem, (CUstream)ctx->stream,
+                                    params, nullptr);
+  if (r != CUDA_SUCCESS) return ctx->fail(BGPU_ECUDA, "cuLaunchKernel: " + cu_err(a, r));
+  ctx->launches++;
+  return BGPU_OK;
+}
+
+int jit_set_max_smem(bgpu_ctx* ctx, CUfunction fn, size_t smem) {
+  const Api& a = api();
+  const CUresult r = a.FuncSetAttribute(fn, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)smem);
+  if (r != CUDA_SUCCESS) return ctx->fail(BGPU_ECUDA, "cuFuncSetAttribute(max dynamic smem): " + cu_err(a, r));
+  return BGPU_OK;
+}
+
+int jit_occupancy(bgpu_ctx* ctx, CUfunction fn, int block, size_t smem, int* out) {
+  const Api& a = api();
+  const CUresult r = a.Occupancy(out, fn, block, smem);
+  if (r != CUDA_SUCCESS) return ctx->fail(BGPU_ECUDA, "cuOccupancyMaxActiveBlocksPerMultiprocessor: " + cu_err(a, r));
+  return BGPU_OK;
+}
+
+}  // namespace bgpu

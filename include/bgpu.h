@@ -170,6 +170,16 @@ int64_t bgpu_agg_num_groups(bgpu_agg* agg); /* groups seen so far */
  * introspection for tests and the bench, not part of the reference's interface */
 const char* bgpu_agg_last_path(const bgpu_agg* agg);
 void bgpu_agg_destroy(bgpu_agg* agg);
+/* Introspection, no device needed: generate the run-time specialised kernels of this plan (arguments as
+ * bgpu_agg_create_expr) for a synthetic batch shape and compile them for sm_100a with NVRTC. flags bit 0: every column
+ * carries validity; bit 1: dictionary keys need a remap; bit 2: per-accumulator seen masks are tracked.
+ * threads / rows_per_thread / min_ctas = launch geometry baked into the kernels. When out_prefix is not NULL the
+ * source and the cubin are written to <out_prefix>.cu / <out_prefix>.cubin (for cuobjdump -sass / -res-usage). */
+int bgpu_agg_debug_compile(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema* input_schema,
+                           const int32_t* group_cols, int32_t n_group, const int32_t* agg_fns,
+                           const bgpu_expr_node* nodes, const int32_t* agg_expr_offsets, int32_t n_agg,
+                           const bgpu_expr_node* filter, int32_t n_filter, int32_t flags, int32_t threads,
+                           int32_t rows_per_thread, int32_t min_ctas, const char* out_prefix);
 
 /* ---- intra-node exchange (replaces shuffle files + Flight do_get + ShuffleReaderExec fan-in;
  * shuffle_writer.rs:351-385, flight_service.rs:124-166, shuffle_reader.rs:539-624) --------------------------
