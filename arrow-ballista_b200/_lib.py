@@ -79,6 +79,7 @@ SIGNATURES = {
                                          C.POINTER(C.c_int32), C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_void_p,
                                          C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_char_p]),
     "bgpu_agg_last_path": (C.c_char_p, [C.c_void_p]),
+    "bgpu_agg_hot_kernel_ms": (C.c_double, [C.c_void_p]),
     "bgpu_agg_update": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bgpu_agg_emit": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "bgpu_agg_num_groups": (C.c_int64, [C.c_void_p]),

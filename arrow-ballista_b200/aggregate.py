@@ -81,6 +81,11 @@ class GpuAggregateExec:
         """Which kernel path the last update took (introspection)."""
         return lib().bgpu_agg_last_path(self._h).decode()
 
+    @property
+    def hot_kernel_ms(self):
+        """Device time (ms) of this aggregate's fused single-pass kernel launches so far (introspection)."""
+        return float(lib().bgpu_agg_hot_kernel_ms(self._h))
+
     def update(self, batch):
         """update_batch / merge_batch with one batch (DeviceBatch, or a host RecordBatch that is uploaded)."""
         if not isinstance(batch, DeviceBatch):

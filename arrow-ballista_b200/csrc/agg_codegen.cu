@@ -6,6 +6,7 @@
 // Reference semantics restated (none of it is in /root/reference): see agg_plan.h.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "agg_host.h"
@@ -107,18 +108,36 @@ struct Gen {
     return -1;
   }
 
+  // "early" slots feed the addresses of other loads (utf8 offsets; dictionary keys that go through a remap): they are
+  // loaded one tile ahead (load0 / Raw0) so that the dependent loads can be issued together with everything else
+  static bool early(const JitSlot& sl) {
+    return sl.key_use && (sl.kind == K_UTF8 || sl.kind == K_BINARY || (sl.kind == K_DICT32 && sl.remap));
+  }
+
   void raw_struct() {
-    o.line("  struct Raw {");
+    o.line("  struct Raw0 {");
     for (size_t s = 0; s < sh.slots.size(); s++) {
       const JitSlot& sl = sh.slots[s];
-      if (sl.nullable) o.fmt("    bool v%zu;", s);
+      if (!early(sl)) continue;
+      if (sl.kind == K_DICT32) {
+        if (sl.nullable) o.fmt("    bool v%zu;", s);
+        o.fmt("    int32_t k%zu;", s);
+      } else {
+        o.fmt("    int32_t b%zu, l%zu;", s, s);
+      }
+    }
+    o.line("  };");
+    o.line("  struct Raw : Raw0 {");
+    for (size_t s = 0; s < sh.slots.size(); s++) {
+      const JitSlot& sl = sh.slots[s];
+      if (sl.nullable && !(early(sl) && sl.kind == K_DICT32)) o.fmt("    bool v%zu;", s);
       if (sl.value_use || sl.filter_use) o.fmt("    %s c%zu;", vk_ctype(sl.vk), s);
       if (sl.key_use) {
         switch (sl.kind) {
           case K_FIXED: o.fmt("    %s k%zu;", width_utype(sl.width), s); break;
           case K_BOOL: o.fmt("    bool k%zu;", s); break;
-          case K_DICT32: o.fmt("    int32_t k%zu;", s); break;
-          default: o.fmt("    int32_t b%zu, l%zu; uint64_t u%zu_0, u%zu_1;", s, s, s, s); break;
+          case K_DICT32: if (!early(sl)) o.fmt("    int32_t k%zu;", s); break;
+          default: o.fmt("    StrWords w%zu;", s); break;
         }
       }
     }
@@ -137,6 +156,40 @@ struct Gen {
     return n;
   }
 
+  void load0() {
+    o.line("  template <int NEED> static __device__ __forceinline__ void load0(const JitArgs& a, int64_t r, Raw0& x) {");
+    for (size_t s = 0; s < sh.slots.size(); s++) {
+      const JitSlot& sl = sh.slots[s];
+      if (!early(sl)) continue;
+      if (sl.kind == K_DICT32) {
+        if (sl.nullable) o.fmt("    if (NEED & NEED_KEY) x.v%zu = bit_set(a.valid[%zu], r);", s, s);
+        o.fmt("    if (NEED & NEED_KEY) x.k%zu = __ldg((const int32_t*)a.col[%zu] + r);", s, s);
+      } else {
+        o.fmt("    if (NEED & NEED_KEY) { x.b%zu = __ldg(a.aux[%zu] + r); x.l%zu = __ldg(a.aux[%zu] + r + 1) - x.b%zu; }", s, s, s, s, s);
+      }
+    }
+    o.line("  }");
+  }
+
+  // bulk L2 prefetch of rows [row0, row0 + n) of every fixed-width buffer the kernels stream (one thread per buffer)
+  void prefetch() {
+    o.line("  template <int NEED> static __device__ __forceinline__ void prefetch_l2(const JitArgs& a, int64_t row0, int64_t n) {");
+    int lane = 0;
+    for (size_t s = 0; s < sh.slots.size(); s++) {
+      const JitSlot& sl = sh.slots[s];
+      std::string any;
+      if (sl.filter_use) any += "NEED_FILTER";
+      if (sl.value_use) any += std::string(any.empty() ? "" : " | ") + "NEED_VALUES";
+      if (sl.key_use) any += std::string(any.empty() ? "" : " | ") + "NEED_KEY";
+      if (sl.kind == K_FIXED || sl.kind == K_DICT32)
+        o.fmt("    if ((NEED & (%s)) && threadIdx.x == %d) bulk_prefetch_l2((const char*)a.col[%zu] + row0 * %d, n * %d);", any.c_str(),
+              lane++, s, sl.kind == K_DICT32 ? 4 : sl.width, sl.kind == K_DICT32 ? 4 : sl.width);
+      else if (sl.kind == K_UTF8 || sl.kind == K_BINARY)
+        o.fmt("    if ((NEED & NEED_KEY) && threadIdx.x == %d) bulk_prefetch_l2((const char*)(a.aux[%zu] + row0), (n + 1) * 4);", lane++, s);
+    }
+    o.line("  }");
+  }
+
   void load1() {
     o.line("  template <int NEED> static __device__ __forceinline__ void load1(const JitArgs& a, int64_t r, Raw& x) {");
     for (size_t s = 0; s < sh.slots.size(); s++) {
@@ -145,23 +198,21 @@ struct Gen {
       if (sl.filter_use) any += "NEED_FILTER";
       if (sl.value_use) any += std::string(any.empty() ? "" : " | ") + "NEED_VALUES";
       if (sl.key_use) any += std::string(any.empty() ? "" : " | ") + "NEED_KEY";
-      if (sl.nullable) o.fmt("    if (NEED & (%s)) x.v%zu = bit_set(a.valid[%zu], r);", any.c_str(), s, s);
+      const bool dict_early = early(sl) && sl.kind == K_DICT32;
+      if (sl.nullable && !dict_early) o.fmt("    if (NEED & (%s)) x.v%zu = bit_set(a.valid[%zu], r);", any.c_str(), s, s);
       if (sl.value_use || sl.filter_use) {
         const std::string need = need_of(sl, true);
         if (sl.vk == V_I128) o.fmt("    if (NEED & (%s)) x.c%zu = ld_i128(a.col[%zu], r);", need.c_str(), s, s);
         else o.fmt("    if (NEED & (%s)) x.c%zu = __ldg((const %s*)a.col[%zu] + r);", need.c_str(), s, vk_ctype(sl.vk), s);
       }
-      if (sl.key_use) {
+      if (sl.key_use && !early(sl)) {
         switch (sl.kind) {
           case K_FIXED:
             if (sl.width == 16) o.fmt("    if (NEED & NEED_KEY) x.k%zu = ld_i128(a.col[%zu], r);", s, s);
             else o.fmt("    if (NEED & NEED_KEY) x.k%zu = __ldg((const %s*)a.col[%zu] + r);", s, width_utype(sl.width), s);
             break;
           case K_BOOL: o.fmt("    if (NEED & NEED_KEY) x.k%zu = bit_set((const uint8_t*)a.col[%zu], r);", s, s); break;
-          case K_DICT32: o.fmt("    if (NEED & NEED_KEY) x.k%zu = __ldg((const int32_t*)a.col[%zu] + r);", s, s); break;
-          default:
-            o.fmt("    if (NEED & NEED_KEY) { x.b%zu = __ldg(a.aux[%zu] + r); x.l%zu = __ldg(a.aux[%zu] + r + 1) - x.b%zu; }", s, s, s, s, s);
-            break;
+          default: o.fmt("    if (NEED & NEED_KEY) x.k%zu = __ldg((const int32_t*)a.col[%zu] + r);", s, s); break;
         }
       }
     }
@@ -173,20 +224,14 @@ struct Gen {
     for (size_t ki = 0; ki < sh.key_slot.size(); ki++) {
       const size_t s = (size_t)sh.key_slot[ki];
       const JitSlot& sl = sh.slots[s];
-      const int off = g->key_off[ki], width = g->key_width[ki];
+      const int width = g->key_width[ki];
       const std::string guard = sl.nullable ? " && x.v" + std::to_string(s) : "";
       if (sl.kind == K_DICT32 && sl.remap) {
         o.fmt("    if ((NEED & NEED_KEY)%s) x.k%zu = __ldg(a.aux[%zu] + x.k%zu);", guard.c_str(), s, s, s);
       } else if (sl.kind == K_UTF8 || sl.kind == K_BINARY) {
-        // the length byte, then up to `width` bytes, already at their position inside the 16-byte packed key
-        o.fmt("    if (NEED & NEED_KEY) {");
-        o.fmt("      x.u%zu_0 = 0; x.u%zu_1 = 0;", s, s);
-        o.fmt("      if (true%s && x.l%zu <= %d) {", guard.c_str(), s, width);
-        o.fmt("        const uint8_t* p = (const uint8_t*)a.col[%zu] + x.b%zu;", s, s);
-        o.fmt("        put_bytes(x.u%zu_0, x.u%zu_1, %d, (uint64_t)x.l%zu);", s, s, off, s);
-        o.fmt("        for (int i = 0; i < x.l%zu; i++) put_bytes(x.u%zu_0, x.u%zu_1, %d + i, (uint64_t)__ldg(p + i));", s, s, s, off + 1);
-        o.line("      }");
-        o.line("    }");
+        // the words holding the string's bytes (assembled into the key field by key())
+        // (offsets are valid for null rows too: no need to wait for the validity bit)
+        o.fmt("    if (NEED & NEED_KEY) x.w%zu = str_load<%d>(a.col[%zu], x.b%zu, x.l%zu);", s, width, s, s, s);
       }
     }
     o.line("  }");
@@ -238,7 +283,8 @@ struct Gen {
                    word.c_str(), s, shift);
           break;
         default:
-          snprintf(buf, sizeof buf, "if (x.l%zu > %d) atomicOr(&a.t.flags[1], 1); k.k0 |= x.u%zu_0; k.k1 |= x.u%zu_1;", s, width, s, s);
+          snprintf(buf, sizeof buf, "if (x.l%zu > %d) atomicOr(&a.t.flags[1], 1); str_field<%d, %d>(a.col[%zu], x.b%zu, x.l%zu, x.w%zu, k.k0, k.k1);",
+                   s, width, off, width, s, s, s, s);
           break;
       }
       body = buf;
@@ -358,13 +404,13 @@ int agg_generate_source(const bgpu_agg* g, const JitShape& sh, std::string* out)
   Out& o = gen.o;
   o.s.reserve(8192);
   o.line("namespace bgpu {");
-  o.line("__device__ __forceinline__ void put_bytes(uint64_t& k0, uint64_t& k1, int off, uint64_t v) {");
-  o.line("  if (off < 8) k0 |= v << (8 * off); else k1 |= v << (8 * (off - 8));");
-  o.line("}");
   o.line("struct Plan {");
   o.fmt("  static constexpr int T = %d, R = %d, W = %d, KEY_WORDS = %d, MIN_CTAS = %d;", sh.T, sh.R, sh.W, g->key_words, sh.min_ctas);
   o.fmt("  static constexpr bool HAS_SEEN = %s;", sh.has_seen ? "true" : "false");
+  o.fmt("  static constexpr bool L2_PREFETCH = %s;", getenv("BGPU_L2_PREFETCH") ? "true" : "false");
   gen.raw_struct();
+  gen.load0();
+  gen.prefetch();
   gen.load1();
   gen.load2();
   gen.filter();
@@ -376,10 +422,13 @@ int agg_generate_source(const bgpu_agg* g, const JitShape& sh, std::string* out)
   o.line("};");
   o.line("}  // namespace bgpu");
   o.line("using namespace bgpu;");
-  o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T, Plan::MIN_CTAS) bgpu_fused(const __grid_constant__ JitArgs a) { fused_body<Plan>(a); }");
-  o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_intern(const __grid_constant__ JitArgs a) { intern_body<Plan>(a); }");
-  o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_acc_shared(const __grid_constant__ JitArgs a) { accumulate_body<Plan, 1>(a); }");
-  o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_acc_global(const __grid_constant__ JitArgs a) { accumulate_body<Plan, 2>(a); }");
+  if (sh.kernels & 1)
+    o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T, Plan::MIN_CTAS) bgpu_fused(const __grid_constant__ JitArgs a) { fused_body<Plan>(a); }");
+  if (sh.kernels & 2) {
+    o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_intern(const __grid_constant__ JitArgs a) { intern_body<Plan>(a); }");
+    o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_acc_shared(const __grid_constant__ JitArgs a) { accumulate_body<Plan, 1>(a); }");
+    o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_acc_global(const __grid_constant__ JitArgs a) { accumulate_body<Plan, 2>(a); }");
+  }
   *out = std::move(o.s);
   return BGPU_OK;
 }

@@ -61,12 +61,19 @@ struct bgpu_agg {
   // and launch geometry; the modules themselves live in jit.cu's process-wide cache)
   std::map<std::string, const bgpu::JitModule*> modules;
   bool emitted = false;
-  // introspection for tests / bench: which path the last update took ("fused256x2", "fused256", "fused128",
+  // introspection for tests / bench: which path the last update took ("fused512", "fused256", "fused128",
   // "shared", "global")
   std::string last_path;
+  // device time of the fused kernel launches so far (CUDA events on the ctx stream): bench.py's roofline numerator
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  double hot_kernel_ms = 0.0;
 
   explicit bgpu_agg(bgpu_ctx* c) : ctx(c) { ctx_retain(c); }
-  ~bgpu_agg() { ctx_release(ctx); }
+  ~bgpu_agg() {
+    for (cudaEvent_t e : ev)
+      if (e) cudaEventDestroy(e);
+    ctx_release(ctx);
+  }
   uint32_t* d_n_groups() { return (uint32_t*)counters->p; }
   int32_t* d_flags() { return (int32_t*)counters->p + 1; }
   bgpu::GroupTable table() {
@@ -95,6 +102,7 @@ struct JitShape {
   int32_t W = 0;                             // accumulator words per group
   bool has_seen = false;
   int32_t T = 256, R = 4, min_ctas = 1;
+  int32_t kernels = 3;  // which entry points to emit: bit 0 bgpu_fused, bit 1 bgpu_intern + bgpu_acc_shared + bgpu_acc_global
   bool any_validity = false;
 };
 // slot of batch column `batch_col` (created on first use); -1 when the table is full

@@ -77,7 +77,8 @@ __device__ __forceinline__ uint64_t key_hash(const PackedKey& k) {
 // Find or insert in the global table; returns the dense group id (>= max_groups when the table overflowed: the
 // pass is void and is re-run by the host after growing).
 template <int WORDS>
-__device__ __noinline__ uint32_t intern(const GroupTable& t, const PackedKey& k) {
+__device__ __noinline__ uint32_t intern_slow(const GroupTable& t, uint64_t k0, uint64_t k1, uint32_t meta) {
+  const PackedKey k{k0, k1, meta};  // by value: a reference would force the caller's key into local memory
   const uint64_t h = key_hash<WORDS>(k);
   const unsigned long long tag = (h >> 32) << 32;
   uint32_t i = (uint32_t)h & t.mask;
@@ -112,6 +113,10 @@ __device__ __noinline__ uint32_t intern(const GroupTable& t, const PackedKey& k)
   }
   atomicOr(&t.flags[0], 1);  // table full
   return kGidOverflow;
+}
+template <int WORDS>
+__device__ __forceinline__ uint32_t intern(const GroupTable& t, const PackedKey& k) {
+  return intern_slow<WORDS>(t, k.k0, WORDS > 1 ? k.k1 : 0ULL, k.meta);
 }
 
 // Per-CTA cache of (key -> gid) in shared memory in front of the global table: low-cardinality inputs resolve
@@ -186,8 +191,10 @@ __device__ __forceinline__ Val i128_sub_checked(Val a, Val b, bool* ovf) {
   if (((a.hi ^ b.hi) & (a.hi ^ r.hi)) >> 63) *ovf = true;
   return r;
 }
-// general checked signed multiply (i128::mul_checked): magnitudes as u128, product must fit 127 bits (or be MIN)
-__device__ __noinline__ Val i128_mul_slow(Val a, Val b, bool* ovf) {
+// general checked signed multiply (i128::mul_checked): magnitudes as u128, product must fit 127 bits (or be MIN).
+// Returns the overflow flag by value (a pointer argument would force the caller's flag into local memory).
+struct ValOvf { Val v; uint32_t ovf; };
+__device__ __noinline__ ValOvf i128_mul_slow(Val a, Val b) {
   const bool neg = i128_is_neg(a) != i128_is_neg(b);
   const Val ua = i128_is_neg(a) ? i128_neg(a) : a, ub = i128_is_neg(b) ? i128_neg(b) : b;
   bool ok = (ua.hi == 0) || (ub.hi == 0);
@@ -206,14 +213,15 @@ __device__ __noinline__ Val i128_mul_slow(Val a, Val b, bool* ovf) {
   } else {
     ok = ok && hi2 < 0x8000000000000000ULL;
   }
-  if (!ok) *ovf = true;
-  return r;
+  return ValOvf{r, ok ? 0u : 1u};
 }
 // checked multiply with the common case inline: both operands fit i64 -> one signed 64x64->128 product, which
 // cannot overflow i128
 __device__ __forceinline__ Val i128_mul_checked(Val a, Val b, bool* ovf) {
   if (fits_i64(a) && fits_i64(b)) return Val{a.lo * b.lo, (uint64_t)__mul64hi((int64_t)a.lo, (int64_t)b.lo)};
-  return i128_mul_slow(a, b, ovf);
+  const ValOvf r = i128_mul_slow(a, b);
+  if (r.ovf) *ovf = true;
+  return r.v;
 }
 __device__ __forceinline__ bool i128_lt(Val a, Val b) {
   return (int64_t)a.hi < (int64_t)b.hi || (a.hi == b.hi && a.lo < b.lo);
@@ -221,6 +229,47 @@ __device__ __forceinline__ bool i128_lt(Val a, Val b) {
 // three-way compare of i128 values: -1, 0, 1
 __device__ __forceinline__ int i128_cmp(Val a, Val b) { return i128_lt(a, b) ? -1 : (i128_lt(b, a) ? 1 : 0); }
 __device__ __forceinline__ int f64_cmp(double a, double b) { return a < b ? -1 : (a > b ? 1 : 0); }
+
+// ---- utf8 / binary group keys ------------------------------------------------------------------------------------------
+// The key field of a string is [length byte][bytes...] placed at byte OFF of the 16-byte packed key. The bytes are
+// fetched as the aligned 8-byte words that contain them (one LDG.64 for short strings instead of a dependent byte
+// loop); words that hold no byte of the string are not read, so no access leaves the 8-byte-aligned extent of the
+// string itself.
+// Ask the L2 to fetch [p, p + bytes) from HBM (TMA-style bulk prefetch, one instruction per buffer and tile). The
+// range is shrunk to 16-byte granules inside itself, so nothing outside the caller's rows is touched.
+__device__ __forceinline__ void bulk_prefetch_l2(const char* p, int64_t bytes) {
+  const uint64_t lo = ((uint64_t)p + 15) & ~15ULL, hi = ((uint64_t)p + (uint64_t)bytes) & ~15ULL;
+  if (hi > lo) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(lo), "r"((uint32_t)(hi - lo)) : "memory");
+}
+
+struct StrWords { uint64_t w0, w1, w2; };
+// stage 1 (load phase): just the loads, so that the words of every string of the tile are in flight together
+template <int MAXLEN>
+__device__ __forceinline__ StrWords str_load(const void* data, int32_t b, int32_t len) {
+  const uint64_t addr = (uint64_t)data + (uint64_t)(int64_t)b;
+  const uint64_t* w = (const uint64_t*)(addr & ~7ULL);
+  const int end = (int)(addr & 7) + len;
+  StrWords r;
+  r.w0 = (len > 0 && len <= MAXLEN) ? __ldg(w) : 0ULL;
+  r.w1 = (end > 8 && len <= MAXLEN) ? __ldg(w + 1) : 0ULL;
+  r.w2 = (MAXLEN + 7 > 16 && end > 16 && len <= MAXLEN) ? __ldg(w + 2) : 0ULL;
+  return r;
+}
+// stage 2: assemble the key field; strings longer than MAXLEN contribute nothing (the caller raises the flag)
+template <int OFF, int MAXLEN>
+__device__ __forceinline__ void str_field(const void* data, int32_t b, int32_t len, const StrWords& r, uint64_t& k0, uint64_t& k1) {
+  if (len > MAXLEN) return;
+  const int sh = (int)(((uint64_t)data + (uint64_t)(int64_t)b) & 7) * 8;
+  uint64_t lo = sh ? (r.w0 >> sh) | (r.w1 << (64 - sh)) : r.w0;
+  uint64_t hi = sh ? (r.w1 >> sh) | (r.w2 << (64 - sh)) : r.w1;
+  if (len < 8) { lo &= (1ULL << (8 * len)) - 1; hi = 0; }
+  else if (len < 16) hi &= (1ULL << (8 * (len - 8))) - 1;
+  // F = len | bytes << 8 (len <= 15 bytes: fits 128 bits), then F << 8 * OFF
+  const uint64_t f_lo = (uint64_t)len | (lo << 8), f_hi = (hi << 8) | (lo >> 56);
+  if (OFF == 0) { k0 |= f_lo; k1 |= f_hi; }
+  else if (OFF < 8) { k0 |= f_lo << (8 * OFF); k1 |= (f_hi << (8 * OFF)) | (f_lo >> (64 - 8 * OFF)); }
+  else { k1 |= f_lo << (8 * (OFF - 8)); }
+}
 
 // ---- accumulator sinks: where Plan::accumulate sends each (accumulator, value) ---------------------------------------
 // thread-private slots in shared memory: word w of group g of thread t lives at s_acc[(g * W + w) * T + t]
@@ -408,19 +457,37 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
   __syncthreads();
 
   bool ovf = false;
-  const int64_t tile = (int64_t)T * R, last = a.n_rows - 1;
-  for (int64_t base = (int64_t)blockIdx.x * tile; base < a.n_rows; base += (int64_t)gridDim.x * tile) {
-    typename Plan::Raw x[R];
-    // phase 1: every load of the tile in flight before anything is consumed (rows past the end re-read the last row)
+  uint32_t tiles_done = 0;
+  const int64_t tile = (int64_t)T * R, last = a.n_rows - 1, stride = (int64_t)gridDim.x * tile;
+  // Software pipeline over this CTA's tiles (rows past the end re-read the last row):
+  //   tile i+1: bulk L2 prefetch of every streamed buffer; its "early" loads (utf8 offsets, remapped dictionary keys)
+  //             are issued into registers while tile i is processed
+  //   tile i:   all remaining loads are issued back to back (phase 1), then consumed (phase 2)
+  typename Plan::Raw0 nx[R];
+  {
+    const int64_t base = (int64_t)blockIdx.x * tile;
 #pragma unroll
     for (int u = 0; u < R; u++) {
       const int64_t r = base + u * T + threadIdx.x;
+      Plan::template load0<7>(a, r < last ? r : last, nx[u]);
+    }
+  }
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < a.n_rows; base += stride) {
+    typename Plan::Raw x[R];
+    const int64_t next = base + stride;
+    if (Plan::L2_PREFETCH && next < a.n_rows)
+      Plan::template prefetch_l2<7>(a, next, next + tile <= a.n_rows ? tile : a.n_rows - next);
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      static_cast<typename Plan::Raw0&>(x[u]) = nx[u];
       Plan::template load1<7>(a, r < last ? r : last, x[u]);
+      Plan::template load2<7>(a, r < last ? r : last, x[u]);
     }
 #pragma unroll
     for (int u = 0; u < R; u++) {
-      const int64_t r = base + u * T + threadIdx.x;
-      Plan::template load2<7>(a, r < last ? r : last, x[u]);
+      const int64_t r = next + u * T + threadIdx.x;
+      Plan::template load0<7>(a, r < last ? r : last, nx[u]);
     }
     // phase 2
 #pragma unroll
@@ -434,7 +501,8 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
       const uint32_t seen = Plan::accumulate(a, x[u], sink, &ovf);
       if (Plan::HAS_SEEN && seen) atomicOr(&s_seen[gid], seen);
     }
-    if (*(volatile int*)&s_abort || *(volatile int*)&a.t.flags[3]) break;  // some CTA gave up: the pass is void
+    // some CTA gave up: the pass is void (the global flag is polled every 16th tile: it only saves work)
+    if (*(volatile int*)&s_abort || ((++tiles_done & 15) == 0 && *(volatile int*)&a.t.flags[3])) break;
   }
   if (ovf) atomicOr(&a.t.flags[2], 1);
   __syncthreads();
@@ -459,6 +527,7 @@ __device__ __forceinline__ void intern_body(const JitArgs& a) {
 #pragma unroll
     for (int u = 0; u < R; u++) {
       const int64_t r = base + u * T + threadIdx.x;
+      Plan::template load0<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
       Plan::template load1<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
     }
 #pragma unroll

@@ -25,45 +25,61 @@ __host__ __device__ __forceinline__ size_t fused_slab_words(uint32_t g_cap, int 
   return (size_t)g_cap * W + ((size_t)g_cap + 1) / 2;
 }
 
-// Fold the per-CTA slabs into the dense accumulator arrays: one thread per (group, accumulator), slabs in CTA order
-// (so Float64 sums are reproducible for a fixed grid).
+// Fold the per-CTA slabs into the dense accumulator arrays: one WARP per (group, accumulator); lanes stride over the
+// slabs and the partials are combined by shuffles in a fixed order (Float64 sums are reproducible for a fixed grid).
 __global__ void __launch_bounds__(kAggThreads)
     commit_kernel(const __grid_constant__ AccPlan plan, const uint64_t* __restrict__ scratch, uint32_t n_ctas,
                   uint32_t g_cap, uint32_t n_groups) {
   const int W = plan.total_words;
   const size_t slab = fused_slab_words(g_cap, W);
   const uint32_t items = n_groups * (uint32_t)plan.n;
-  for (uint32_t item = blockIdx.x * blockDim.x + threadIdx.x; item < items; item += gridDim.x * blockDim.x) {
+  const uint32_t lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+  for (uint32_t item = warp; item < items; item += n_warps) {
     const uint32_t grp = item / plan.n;
     const AccK& a = plan.a[item % plan.n];
     const AccK& src = a.alias >= 0 ? plan.a[a.alias] : a;
-    unsigned __int128 isum = 0;
+    uint64_t lo = 0, hi = 0;
     double fsum = 0.0;
-    for (uint32_t b = 0; b < n_ctas; b++) {
+    for (uint32_t b = lane; b < n_ctas; b += 32) {
       const uint64_t* p = scratch + (size_t)b * slab + (size_t)grp * W + src.word0;
-      if (src.op == OP_ADD_F64) fsum += __longlong_as_double((long long)p[0]);
-      else if (src.op == OP_ADD_I128) isum += ((unsigned __int128)p[1] << 64) | p[0];
-      else isum += p[0];
+      if (src.op == OP_ADD_F64) {
+        fsum += __longlong_as_double((long long)p[0]);
+      } else {
+        const uint64_t x = p[0];
+        lo += x;
+        hi += (lo < x) + (src.op == OP_ADD_I128 ? p[1] : 0ULL);
+      }
     }
-    uint64_t* o = a.out + (size_t)grp * a.words;
-    if (a.op == OP_ADD_F64) {
-      *(double*)o += fsum;
-    } else {
-      unsigned __int128 cur = o[0];
-      if (a.words > 1) cur |= (unsigned __int128)o[1] << 64;
-      cur += isum;
-      o[0] = (uint64_t)cur;
-      if (a.words > 1) o[1] = (uint64_t)(cur >> 64);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      fsum += __shfl_down_sync(0xffffffffu, fsum, d);
+      const uint64_t olo = __shfl_down_sync(0xffffffffu, lo, d), ohi = __shfl_down_sync(0xffffffffu, hi, d);
+      lo += olo;
+      hi += ohi + (lo < olo);
+    }
+    if (lane == 0) {
+      uint64_t* o = a.out + (size_t)grp * a.words;
+      if (a.op == OP_ADD_F64) {
+        *(double*)o += fsum;
+      } else {
+        const uint64_t cur = o[0], nlo = cur + lo;
+        o[0] = nlo;
+        if (a.words > 1) o[1] += hi + (nlo < cur);
+      }
     }
   }
   if (plan.seen) {
-    for (uint32_t grp = blockIdx.x * blockDim.x + threadIdx.x; grp < n_groups; grp += gridDim.x * blockDim.x) {
+    for (uint32_t grp = warp; grp < n_groups; grp += n_warps) {
       uint32_t m = 0;
-      for (uint32_t b = 0; b < n_ctas; b++) m |= ((const uint32_t*)(scratch + (size_t)b * slab + (size_t)g_cap * W))[grp];
-      // aliased accumulators saw whatever their source saw
-      for (int i = 0; i < plan.n; i++)
-        if (plan.a[i].alias >= 0 && ((m >> plan.a[plan.a[i].alias].seen_bit) & 1)) m |= 1u << plan.a[i].seen_bit;
-      if (m) plan.seen[grp] |= m;
+      for (uint32_t b = lane; b < n_ctas; b += 32) m |= ((const uint32_t*)(scratch + (size_t)b * slab + (size_t)g_cap * W))[grp];
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) m |= __shfl_down_sync(0xffffffffu, m, d);
+      if (lane == 0) {
+        // aliased accumulators saw whatever their source saw
+        for (int i = 0; i < plan.n; i++)
+          if (plan.a[i].alias >= 0 && ((m >> plan.a[plan.a[i].alias].seen_bit) & 1)) m |= 1u << plan.a[i].seen_bit;
+        if (m) plan.seen[grp] |= m;
+      }
     }
   }
 }

@@ -183,6 +183,8 @@ static int agg_create_impl(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema
     BGPU_TRY(dev_alloc(ctx, 32, &g->counters));
     BGPU_CUDA(ctx, cudaMemsetAsync(g->counters->p, 0, 32, ctx->stream));
     BGPU_TRY(agg_resize(g.get(), 1u << 16, 0));
+    BGPU_CUDA(ctx, cudaEventCreate(&g->ev[0]));
+    BGPU_CUDA(ctx, cudaEventCreate(&g->ev[1]));
   }
   *out = g.release();
   return BGPU_OK;
@@ -274,7 +276,7 @@ extern "C" int bgpu_agg_debug_compile(bgpu_ctx* ctx, int32_t mode, const struct 
   }
   sh.W = w;
   sh.has_seen = flags & 4;
-  sh.T = threads; sh.R = rows_per_thread; sh.min_ctas = min_ctas;
+  sh.T = threads; sh.R = rows_per_thread; sh.min_ctas = min_ctas; sh.kernels = 3;
   std::string src, cubin;
   BGPU_TRY(agg_generate_source(g.get(), sh, &src));
   src = std::string(agg_jit_prelude()) + src;

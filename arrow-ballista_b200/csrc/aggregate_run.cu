@@ -9,6 +9,8 @@
 //                  with replicated shared-memory atomics or global atomics.
 // Int64/Decimal128 sums are wrapping two's-complement adds, so any order is bit-exact; Float64 sums carry the north
 // star's 1e-9 tolerance (the fused path is reproducible run to run, the atomic path is not).
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -172,7 +174,7 @@ struct Bound {
   AccPlan ap{};
   const JitModule* mod = nullptr;
 };
-enum JitKernel : int { JK_FUSED = 0, JK_INTERN = 1, JK_ACC_SHARED = 2, JK_ACC_GLOBAL = 3 };
+enum JitKernel : int { JK_FUSED = 0, JK_INTERN = 0, JK_ACC_SHARED = 1, JK_ACC_GLOBAL = 2 };  // index into the module of its kind
 
 static int bind_value_atom(bgpu_ctx* ctx, const bgpu_batch* batch, const HAtom& h, Bound* b, bool* nullable) {
   if (!h.is_col) return BGPU_OK;
@@ -274,16 +276,17 @@ static void refresh_pointers(bgpu_agg* g, Bound* b) {
   b->args.t = g->table();
 }
 
-// Generate + compile (cached) the kernels for this batch shape at the given launch geometry.
-static int specialise(bgpu_agg* g, Bound* b, int T, int R, int min_ctas) {
-  b->sh.T = T; b->sh.R = R; b->sh.min_ctas = min_ctas;
+// Generate + compile (cached) the fused kernel (kernels = 1) or the two-pass kernels (kernels = 2) for this batch
+// shape at the given launch geometry. b->mod->fn is indexed by JitKernel.
+static int specialise(bgpu_agg* g, Bound* b, int kernels, int T, int R, int min_ctas) {
+  b->sh.T = T; b->sh.R = R; b->sh.min_ctas = min_ctas; b->sh.kernels = kernels;
   b->sh.has_seen = g->seen_tracking;
   std::string src;
   BGPU_TRY(agg_generate_source(g, b->sh, &src));
   auto it = g->modules.find(src);
   if (it != g->modules.end()) { b->mod = it->second; return BGPU_OK; }
-  static const std::vector<std::string> names{"bgpu_fused", "bgpu_intern", "bgpu_acc_shared", "bgpu_acc_global"};
-  BGPU_TRY(jit_compile(g->ctx, agg_jit_prelude(), src, names, &b->mod));
+  static const std::vector<std::string> fused{"bgpu_fused"}, two_pass{"bgpu_intern", "bgpu_acc_shared", "bgpu_acc_global"};
+  BGPU_TRY(jit_compile(g->ctx, agg_jit_prelude(), src, kernels == 1 ? fused : two_pass, &b->mod));
   g->modules.emplace(std::move(src), b->mod);
   return BGPU_OK;
 }
@@ -333,8 +336,15 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
   const int W = b->sh.W;
   if (W == 0) { g->fused_rung = kFusedRungs; return BGPU_OK; }
   const size_t smem_max = ctx->smem_optin - 1024;
-  const Rung rungs[kFusedRungs] = {{256, 4, 2, smem_max / 2 - 1024, "fused256x2"}, {256, 4, 1, smem_max, "fused256"},
-                                   {128, 8, 1, smem_max, "fused128"}};
+  // Thread-private accumulators cost G * W * 8 bytes of shared memory per thread, so shared memory (not registers)
+  // bounds the threads per SM; one large CTA per SM with 2 rows per thread in flight measured best on B200 (Q1:
+  // 512x2 1.27 ms vs 256x4x2 1.59 ms per 60M rows). Lower rungs trade threads for private group capacity.
+  Rung rungs[kFusedRungs] = {{512, 2, 1, smem_max, "fused512"}, {256, 4, 1, smem_max, "fused256"}, {128, 8, 1, smem_max, "fused128"}};
+  if (const char* e = getenv("BGPU_FUSED_GEOMETRY")) {  // tuning knob: "threads,rows,ctas_per_sm" for the first rung
+    int t = 0, r = 0, c = 0;
+    if (sscanf(e, "%d,%d,%d", &t, &r, &c) == 3 && t >= 32 && t <= 1024 && t % 32 == 0 && r >= 1 && r <= 16 && c >= 1 && c <= 8)
+      rungs[0] = Rung{t, r, c, smem_max / (size_t)c - 1024, "fused512"};
+  }
   while (g->fused_rung < kFusedRungs) {
     const Rung& rg = rungs[g->fused_rung];
     const int T = rg.threads;
@@ -345,13 +355,18 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
     const uint32_t slots = std::max<uint32_t>(16, next_pow2((uint64_t)G * 2));
     const size_t smem = (size_t)G * W * T * 8 + (size_t)((G + 1) & ~1u) * 4 + (size_t)slots * 24;
     if (smem > smem_max) { g->fused_rung++; continue; }
-    BGPU_TRY(specialise(g, b, T, rg.rows, rg.min_ctas));
+    BGPU_TRY(specialise(g, b, 1, T, rg.rows, rg.min_ctas));
     const CUfunction fn = b->mod->fn[JK_FUSED];
     BGPU_TRY(jit_set_max_smem(ctx, fn, smem));
     int occ = 1;
     BGPU_TRY(jit_occupancy(ctx, fn, T, smem, &occ));
     occ = std::max(1, occ);
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ceil_div64(n_rows, (int64_t)T * rg.rows), (int64_t)ctx->sm_count * occ));
+    // several CTAs per SM slot: the hardware block scheduler then evens out the per-SM speed differences that a
+    // one-wave persistent grid leaves as a 20% idle tail (ncu: SM active 77% of elapsed), at ~10 us of prologue +
+    // flush per extra CTA
+    int waves = 4;
+    if (const char* e = getenv("BGPU_FUSED_WAVES")) waves = std::max(1, atoi(e));
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ceil_div64(n_rows, (int64_t)T * rg.rows), (int64_t)ctx->sm_count * occ * waves));
     const size_t scratch_bytes = (size_t)grid * fused_slab_words(G, W) * 8;
     if (!g->scratch || g->scratch->bytes < scratch_bytes) BGPU_TRY(dev_alloc(ctx, scratch_bytes, &g->scratch));
     b->args.scratch = (uint64_t*)g->scratch->p;
@@ -359,9 +374,13 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
     b->args.cache_slots = slots;
     for (int attempt = 0;; attempt++) {
       refresh_pointers(g, b);
+      BGPU_CUDA(ctx, cudaEventRecord(g->ev[0], ctx->stream));
       BGPU_TRY(jit_launch(ctx, fn, grid, T, smem, &b->args));
+      BGPU_CUDA(ctx, cudaEventRecord(g->ev[1], ctx->stream));
       uint32_t h[8];
-      BGPU_TRY(read_counters(g, h));
+      BGPU_TRY(read_counters(g, h));  // synchronises the stream
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, g->ev[0], g->ev[1]) == cudaSuccess) g->hot_kernel_ms += ms;
       BGPU_TRY(check_common_flags(g, h));
       if (h[1]) {  // global table overflow: grow and run the same rung again
         if (attempt >= 4) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
@@ -376,7 +395,7 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
       }
       g->n_groups = h[0];
       if (b->sh.any_validity && !g->seen_tracking) return ctx->fail(BGPU_EINVAL, "internal: seen tracking not set up");
-      commit_kernel<<<agg_launch_grid(ctx, std::max<uint32_t>(1, g->n_groups * (uint32_t)b->ap.n), kAggThreads), kAggThreads, 0,
+      commit_kernel<<<agg_launch_grid(ctx, (int64_t)std::max<uint32_t>(1, g->n_groups * (uint32_t)b->ap.n) * 32, kAggThreads), kAggThreads, 0,
                       ctx->stream>>>(b->ap, (const uint64_t*)g->scratch->p, (uint32_t)grid, G, g->n_groups);
       ctx->launches++;
       BGPU_CUDA(ctx, cudaGetLastError());
@@ -392,8 +411,7 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
 static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
   bgpu_ctx* ctx = g->ctx;
   constexpr int T = 256, R = 4;
-  // the module of the first fused rung has the same geometry: reuse it when this batch already built it
-  if (!(b->mod && b->sh.T == T && b->sh.R == R)) BGPU_TRY(specialise(g, b, T, R, 2));
+  BGPU_TRY(specialise(g, b, 2, T, R, 1));
   DevAllocPtr gids;
   BGPU_TRY(dev_alloc(ctx, (size_t)n_rows * 4, &gids));
   b->args.gids = (uint32_t*)gids->p;
@@ -469,6 +487,7 @@ extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) {
 }
 
 extern "C" const char* bgpu_agg_last_path(const bgpu_agg* g) { return g ? g->last_path.c_str() : ""; }
+extern "C" double bgpu_agg_hot_kernel_ms(const bgpu_agg* g) { return g ? g->hot_kernel_ms : 0.0; }
 
 // ---- emit ---------------------------------------------------------------------------------------------------------
 static int emit_validity(bgpu_agg* g, int phys_idx, uint32_t n, Column* col) {

@@ -166,9 +166,12 @@ int bgpu_agg_update(bgpu_agg* agg, const bgpu_batch* batch);
  * reference (GroupValues uses a randomly seeded table). The aggregate may not be updated afterwards. */
 int bgpu_agg_emit(bgpu_agg* agg, bgpu_batch** out);
 int64_t bgpu_agg_num_groups(bgpu_agg* agg); /* groups seen so far */
-/* which kernel path the last update took ("fused256x2", "fused256", "fused128", "shared", "global", "intern");
+/* which kernel path the last update took ("fused512", "fused256", "fused128", "shared", "global", "intern");
  * introspection for tests and the bench, not part of the reference's interface */
 const char* bgpu_agg_last_path(const bgpu_agg* agg);
+/* device time (ms, CUDA events on the ctx stream) spent so far in this aggregate's single-pass fused kernel launches:
+ * the per-launch duration bench.py's roofline line is computed from */
+double bgpu_agg_hot_kernel_ms(const bgpu_agg* agg);
 void bgpu_agg_destroy(bgpu_agg* agg);
 /* Introspection, no device needed: generate the run-time specialised kernels of this plan (arguments as
  * bgpu_agg_create_expr) for a synthetic batch shape and compile them for sm_100a with NVRTC. flags bit 0: every column
