@@ -10,3 +10,4 @@ from .partitioner import BatchPartitioner, Partitioning  # noqa: F401
 from .aggregate import AggregateFunction, AggregateMode, GpuAggregateExec  # noqa: F401
 from .expr import Column, Literal, BinaryExpr, col, lit  # noqa: F401
 from . import expr  # noqa: F401
+from .exchange import Exchange, exchange_plan, owner_of  # noqa: F401

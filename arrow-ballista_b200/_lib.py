@@ -84,6 +84,11 @@ SIGNATURES = {
     "bgpu_agg_emit": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "bgpu_agg_num_groups": (C.c_int64, [C.c_void_p]),
     "bgpu_agg_destroy": (None, [C.c_void_p]),
+    "bgpu_nccl_unique_id": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "bgpu_nccl_comm_create": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    "bgpu_nccl_comm_destroy": (None, [C.c_void_p]),
+    "bgpu_exchange_plan": (C.c_uint64, [C.POINTER(C.c_uint64), C.c_int32, C.c_int32, C.c_uint32, C.POINTER(C.c_uint64),
+                                        C.POINTER(C.c_uint32)]),
     "bgpu_all_to_all": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_uint64),
                                   C.c_uint32, C.POINTER(C.c_void_p)]),
 }

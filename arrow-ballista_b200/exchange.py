@@ -1,0 +1,72 @@
+"""Intra-node exchange of hash-partitioned batches (bgpu_all_to_all): the B200-native replacement, inside one
+NVSwitch node, for the reference's shuffle files + Flight `do_get` + `ShuffleReaderExec` fan-in
+(/root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:351-385,
+/root/reference/ballista/executor/src/flight_service.rs:124-166,
+/root/reference/ballista/core/src/execution_plans/shuffle_reader.rs:539-624).
+
+One process per GPU. Output partition p is owned by rank p % world. `torch.distributed` is only the rendezvous
+(it carries the 128-byte ncclUniqueId); the data moves through libbgpu's own NCCL communicator on the ctx stream.
+"""
+import ctypes as C
+
+from ._lib import lib
+from .runtime import DeviceBatch
+
+
+def owner_of(partition, world):
+    """Rank that owns output partition `partition`."""
+    return partition % world
+
+
+def exchange_plan(all_offsets, rank, world, n_partitions):
+    """Layout of the batch rank `rank` receives (bgpu_exchange_plan; pure host logic, no device).
+
+    all_offsets[s] = the n_partitions+1 partition offsets of rank s's partitioned batch. Returns (recv_off, owned):
+    recv_off[k * world + s] = first row of owned partition owned[k] coming from source s; recv_off[-1] = total rows.
+    """
+    flat = (C.c_uint64 * (world * (n_partitions + 1)))(*[int(x) for offs in all_offsets for x in offs])
+    n_owned = len(range(rank, n_partitions, world))
+    recv = (C.c_uint64 * (n_owned * world + 1))()
+    got = C.c_uint32()
+    total = lib().bgpu_exchange_plan(flat, rank, world, n_partitions, recv, C.byref(got))
+    assert got.value == n_owned and total == recv[n_owned * world]
+    return list(recv), list(range(rank, n_partitions, world))
+
+
+class Exchange:
+    """All-to-all of partitioned DeviceBatches between the ranks of one node."""
+
+    def __init__(self, ctx, rank, world):
+        # torch bundles its own libnccl.so.2: load it first so that libbgpu's dlopen("libnccl.so.2") reuses that copy
+        # instead of pulling the system one into the process under the same soname
+        import torch  # noqa: F401
+
+        self.ctx, self.rank, self.world = ctx, int(rank), int(world)
+        ident = [None]
+        if self.rank == 0:
+            buf = (C.c_char * 128)()
+            ctx.check(lib().bgpu_nccl_unique_id(ctx._h, buf))
+            ident[0] = bytes(buf)
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.broadcast_object_list(ident, src=0)
+        self._comm = C.c_void_p()
+        ctx.check(lib().bgpu_nccl_comm_create(ctx._h, ident[0], self.rank, self.world, C.byref(self._comm)))
+
+    def all_to_all(self, partitioned, offsets, n_partitions):
+        """partitioned / offsets: the result of BatchPartitioner.partition_device with the same n on every rank.
+        Returns this rank's partitions from all ranks, grouped by (partition, source rank)."""
+        offs = (C.c_uint64 * (n_partitions + 1))(*[int(o) for o in offsets])
+        out = C.c_void_p()
+        self.ctx.check(lib().bgpu_all_to_all(self.ctx._h, self._comm, self.rank, self.world, partitioned._h, offs,
+                                             n_partitions, C.byref(out)))
+        return DeviceBatch(self.ctx, out)
+
+    def close(self):
+        if getattr(self, "_comm", None):
+            lib().bgpu_nccl_comm_destroy(self._comm)
+            self._comm = None
+
+    def __del__(self):
+        self.close()

@@ -191,6 +191,18 @@ int bgpu_agg_debug_compile(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema
  * every rank. out_received holds this rank's partitions from all ranks, grouped by (partition, source rank). */
 int bgpu_all_to_all(bgpu_ctx* ctx, void* nccl_comm, int32_t rank, int32_t world, const bgpu_batch* partitioned,
                     const uint64_t* offsets, uint32_t n_partitions, bgpu_batch** out_received);
+/* NCCL plumbing for harnesses that have no ncclComm_t of their own (libnccl.so.2 is dlopen'ed; the copy the process
+ * already loaded is reused): rank 0 makes a 128-byte ncclUniqueId, the harness broadcasts it by its own means (the
+ * Python mirror uses torch.distributed), every rank creates its communicator on the ctx's device. */
+int bgpu_nccl_unique_id(bgpu_ctx* ctx, void* out_id128);
+int bgpu_nccl_comm_create(bgpu_ctx* ctx, const void* id128, int32_t rank, int32_t world, void** out_comm);
+void bgpu_nccl_comm_destroy(void* comm);
+/* Host-side layout of the received batch (no device needed; also what the gloo CPU tests check): all_offsets =
+ * [world][n_partitions + 1] partition offsets of every rank's partitioned batch; recv_off[(k * world + s)] = first
+ * row, in this rank's received batch, of its k-th owned partition (p = rank + k * world) coming from source s, with
+ * one trailing total. Returns the total. */
+uint64_t bgpu_exchange_plan(const uint64_t* all_offsets, int32_t rank, int32_t world, uint32_t n_partitions,
+                            uint64_t* recv_off, uint32_t* n_owned);
 
 #ifdef __cplusplus
 }
