@@ -48,6 +48,16 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def load_traffic(rows):
+    """dram__bytes_read + dram__bytes_write of one bgpu_fused launch from the committed ncu capture (profiles/), or None
+    when this run's row count is not the one that was captured."""
+    p = os.path.join(ROOT, "profiles", "r1_fused_traffic.json")
+    if not os.path.exists(p):
+        return None
+    t = json.load(open(p))
+    return t["dram_bytes_read"] + t["dram_bytes_write"] if t.get("rows") == rows else None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -300,7 +310,7 @@ def run_ours(args):
                 "rows_per_gpu": ne, "note": "pinned host Arrow buffers -> bgpu_batch_upload -> hot path -> bgpu_batch_download"},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "bgpu_fused (Partial aggregate, one launch per step)", "kernel_ms": kernel_ms,
+                     "traffic": load_traffic(n), "kernel": "bgpu_fused (Partial aggregate, one launch per step)", "kernel_ms": kernel_ms,
                      "partial_stage_ms": partial_ms,
                      "bytes_per_row": Q1_BYTES_PER_ROW, "peak_source": peak_src},
     }
