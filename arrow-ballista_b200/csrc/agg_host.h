@@ -53,6 +53,7 @@ struct bgpu_agg {
     std::vector<std::string> values;
     std::string value_format = "u";
     ColKind value_kind = K_UTF8;
+    std::shared_ptr<Column> canon_dev;  // fast path: the first dictionary seen IS the canonical one (device resident)
     std::shared_ptr<Column> last;  // last batch dictionary seen (kept alive so its identity cannot be recycled)
     DevAllocPtr last_remap;        // nullptr = identity
   };

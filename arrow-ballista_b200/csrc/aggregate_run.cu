@@ -15,6 +15,7 @@
 
 #include <algorithm>
 
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
 #include "agg_host.h"
@@ -79,21 +80,72 @@ int agg_resize(bgpu_agg* g, uint32_t new_max, uint32_t keep) {
   return BGPU_OK;
 }
 
-// Map the batch's dictionary onto the aggregate's canonical dictionary of group column i (host side: dictionaries
-// are small next to the batches that reference them). *remap = device array or nullptr for the identity.
-static int canonicalize_dictionary(bgpu_agg* g, int32_t i, const Column& c, const int32_t** remap) {
+__global__ void adjacent_equal_kernel(const uint64_t* __restrict__ sorted, int64_t n, uint32_t* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i + 1 < n; i += (int64_t)gridDim.x * blockDim.x)
+    if (sorted[i] == sorted[i + 1]) atomicAdd(out, 1u);
+}
+
+// Are the values of dictionary `d` pairwise distinct? Decided on the device from their 64-bit hashes (create_hashes,
+// radix sort, adjacent compare): distinct hashes prove distinct values; equal hashes (a duplicate or a collision)
+// answer "no", which only sends the caller down the exact host path.
+static int dict_values_unique(bgpu_agg* g, const std::shared_ptr<Column>& dict, bool* unique) {
   bgpu_ctx* ctx = g->ctx;
-  bgpu_agg::DictState& ds = g->dicts[(size_t)i];
-  *remap = nullptr;
-  if (ds.last && ds.last == c.dict && !c.dict->owned.empty()) {
-    *remap = ds.last_remap ? (const int32_t*)ds.last_remap->p : nullptr;
-    return BGPU_OK;
+  *unique = false;
+  const int64_t n = dict->length;
+  if (dict->validity) return BGPU_OK;  // null dictionary values: host path
+  if (n <= 1) { *unique = true; return BGPU_OK; }
+  if (n > 0x7fffffffLL) return BGPU_OK;
+  bgpu_batch tmp(ctx);
+  tmp.n_rows = n;
+  tmp.cols.push_back(*dict);
+  DevAllocPtr h0, h1, cnt, scratch;
+  BGPU_TRY(dev_alloc(ctx, (size_t)n * 8, &h0));
+  BGPU_TRY(dev_alloc(ctx, (size_t)n * 8, &h1));
+  BGPU_TRY(dev_alloc(ctx, 16, &cnt));
+  const int32_t key0 = 0;
+  BGPU_TRY(bgpu_create_hashes(ctx, &tmp, &key0, 1, (uint64_t*)h0->p));
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortKeys(nullptr, bytes, (const uint64_t*)h0->p, (uint64_t*)h1->p, (int)n, 0, 64, ctx->stream);
+  BGPU_TRY(dev_alloc(ctx, bytes, &scratch));
+  BGPU_CUDA(ctx, cub::DeviceRadixSort::SortKeys(scratch->p, bytes, (const uint64_t*)h0->p, (uint64_t*)h1->p, (int)n, 0, 64, ctx->stream));
+  BGPU_CUDA(ctx, cudaMemsetAsync(cnt->p, 0, 16, ctx->stream));
+  adjacent_equal_kernel<<<agg_launch_grid(ctx, n, kAggThreads), kAggThreads, 0, ctx->stream>>>((const uint64_t*)h1->p, n, (uint32_t*)cnt->p);
+  ctx->launches += 3;
+  uint32_t* pin = (uint32_t*)ctx->pinned + 32;
+  BGPU_CUDA(ctx, cudaMemcpyAsync(pin, cnt->p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *unique = *pin == 0;
+  return BGPU_OK;
+}
+
+// A library-owned device copy of a (borrowed) utf8 dictionary column.
+static int own_dictionary(bgpu_agg* g, const Column& d, std::shared_ptr<Column>* out) {
+  bgpu_ctx* ctx = g->ctx;
+  auto c = std::make_shared<Column>(d);
+  c->owned.clear();
+  const int64_t n = d.length;
+  int32_t ends[2] = {0, 0};
+  if (n) {
+    BGPU_CUDA(ctx, cudaMemcpyAsync(&ends[0], d.offsets, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BGPU_CUDA(ctx, cudaMemcpyAsync(&ends[1], d.offsets + n, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   }
-  const Column& d = *c.dict;
-  if (d.kind != K_UTF8 && d.kind != K_BINARY)
-    return ctx->fail(BGPU_EUNSUPPORTED, "group column " + c.name + ": only Dictionary<Int32, Utf8|Binary> keys are supported");
-  ds.value_format = d.format;
-  ds.value_kind = d.kind;
+  DevAllocPtr o, b;
+  BGPU_TRY(dev_alloc(ctx, (size_t)(n + 1) * 4, &o));
+  BGPU_TRY(dev_alloc(ctx, (size_t)ends[1], &b));
+  if (n) BGPU_CUDA(ctx, cudaMemcpyAsync(o->p, d.offsets, (size_t)(n + 1) * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+  else BGPU_CUDA(ctx, cudaMemsetAsync(o->p, 0, 4, ctx->stream));
+  if (ends[1]) BGPU_CUDA(ctx, cudaMemcpyAsync(b->p, d.values, (size_t)ends[1], cudaMemcpyDeviceToDevice, ctx->stream));
+  c->offsets = (int32_t*)o->p; c->values = b->p; c->data_bytes = ends[1];
+  c->owned.push_back(o); c->owned.push_back(b);
+  *out = c;
+  return BGPU_OK;
+}
+
+// Fold dictionary `d` into the host-side canonical index of group column state `ds`; map[j] = canonical id of value j
+// (-1 for a null value).
+static int index_dictionary(bgpu_agg* g, bgpu_agg::DictState& ds, const Column& d, std::vector<int32_t>* map, bool* identity) {
+  bgpu_ctx* ctx = g->ctx;
   const int64_t n = d.length;
   std::vector<int32_t> offs((size_t)n + 1, 0);
   std::vector<uint8_t> valid;
@@ -111,8 +163,8 @@ static int canonicalize_dictionary(bgpu_agg* g, int32_t i, const Column& c, cons
       BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
   }
-  std::vector<int32_t> map((size_t)n);
-  bool identity = true;
+  map->assign((size_t)n, -1);
+  *identity = true;
   for (int64_t j = 0; j < n; j++) {
     int32_t id = -1;
     if (valid.empty() || ((valid[(size_t)(j >> 3)] >> (j & 7)) & 1)) {
@@ -126,12 +178,56 @@ static int canonicalize_dictionary(bgpu_agg* g, int32_t i, const Column& c, cons
         id = it->second;
       }
     }
-    map[(size_t)j] = id;
-    identity &= id == (int32_t)j;
+    (*map)[(size_t)j] = id;
+    *identity &= id == (int32_t)j;
   }
+  return BGPU_OK;
+}
+
+// Map the batch's dictionary onto the aggregate's canonical dictionary of group column i (group keys are compared by
+// VALUE, as the reference does). *remap = device array or nullptr for the identity.
+//   fast path: the first dictionary an aggregate sees, when its values are pairwise distinct and non-null, IS the
+//              canonical dictionary (identity map, nothing leaves the device) — the common case of one dictionary
+//              shared by every batch of a scan (db-benchmark id3 has 1e5..1e7 values);
+//   exact path: a different dictionary arrives (or duplicates / nulls): dictionaries are folded into a host-side
+//              index by value (they are small next to the batches that reference them).
+static int canonicalize_dictionary(bgpu_agg* g, int32_t i, const Column& c, const int32_t** remap) {
+  bgpu_ctx* ctx = g->ctx;
+  bgpu_agg::DictState& ds = g->dicts[(size_t)i];
+  *remap = nullptr;
+  if (ds.last && ds.last == c.dict) {  // same Column object (kept alive by ds.last, so the identity cannot be recycled)
+    *remap = ds.last_remap ? (const int32_t*)ds.last_remap->p : nullptr;
+    return BGPU_OK;
+  }
+  const Column& d = *c.dict;
+  if (d.kind != K_UTF8 && d.kind != K_BINARY)
+    return ctx->fail(BGPU_EUNSUPPORTED, "group column " + c.name + ": only Dictionary<Int32, Utf8|Binary> keys are supported");
+  ds.value_format = d.format;
+  ds.value_kind = d.kind;
+  if (!ds.canon_dev && ds.values.empty()) {
+    bool unique = false;
+    BGPU_TRY(dict_values_unique(g, c.dict, &unique));
+    if (unique) {
+      ds.canon_dev = c.dict;
+      if (c.dict->owned.empty()) BGPU_TRY(own_dictionary(g, d, &ds.canon_dev));  // borrowed buffers may die with the batch
+      ds.last = c.dict;
+      ds.last_remap = nullptr;
+      return BGPU_OK;
+    }
+  }
+  std::vector<int32_t> map;
+  bool identity = true;
+  if (ds.canon_dev) {  // leave the fast path: the device-resident canonical dictionary becomes ids 0..n-1 of the index
+    std::shared_ptr<Column> first = ds.canon_dev;
+    ds.canon_dev = nullptr;
+    BGPU_TRY(index_dictionary(g, ds, *first, &map, &identity));
+    if (!identity) return ctx->fail(BGPU_EINVAL, "internal: canonical dictionary is not duplicate free");
+  }
+  BGPU_TRY(index_dictionary(g, ds, d, &map, &identity));
   ds.last = c.dict;
   ds.last_remap = nullptr;
   if (!identity) {
+    const int64_t n = d.length;
     BGPU_TRY(dev_alloc(ctx, (size_t)n * 4, &ds.last_remap));
     BGPU_CUDA(ctx, cudaMemcpyAsync(ds.last_remap->p, map.data(), (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
     BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // `map` dies here
@@ -144,6 +240,10 @@ static int canonicalize_dictionary(bgpu_agg* g, int32_t i, const Column& c, cons
 static int upload_canonical_dictionary(bgpu_agg* g, size_t i, std::shared_ptr<Column>* out) {
   bgpu_ctx* ctx = g->ctx;
   const bgpu_agg::DictState& ds = g->dicts[i];
+  if (ds.canon_dev) {  // fast path: the (only) dictionary seen is the canonical one and already lives on the device
+    *out = ds.canon_dev;
+    return BGPU_OK;
+  }
   auto d = std::make_shared<Column>();
   d->name = ""; d->format = ds.value_format; d->kind = ds.value_kind; d->flags = ARROW_FLAG_NULLABLE;
   d->length = (int64_t)ds.values.size(); d->null_count = 0;
@@ -317,11 +417,15 @@ static int check_common_flags(bgpu_agg* g, const uint32_t* h) {
   return BGPU_OK;
 }
 
-// Table overflowed during a pass: groups [0, max_groups) are intact; size for the distinct count observed, rebuild.
-static int grow_after_overflow(bgpu_agg* g, uint32_t counter) {
+// Table overflowed during a pass: groups [0, max_groups) are intact. Interning stops as soon as the overflow flag is
+// up, so `counter` barely exceeds the old capacity and says little about the true cardinality; every retry is a full
+// pass over the batch, so grow geometrically fast (x16, bounded by what this batch can still add) rather than x2.
+static int grow_after_overflow(bgpu_agg* g, uint32_t counter, int64_t batch_rows) {
   const uint32_t keep = g->max_groups;
   if (counter > 0x70000000u) return g->ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
-  const uint32_t new_max = next_pow2(std::max<uint64_t>((uint64_t)counter + counter / 4, (uint64_t)keep * 2));
+  const uint64_t bound = (uint64_t)keep + (uint64_t)batch_rows;  // no batch can create more groups than it has rows
+  const uint64_t want = std::max<uint64_t>((uint64_t)counter + counter / 4, std::min<uint64_t>((uint64_t)keep * 16, bound));
+  const uint32_t new_max = next_pow2(std::max<uint64_t>(want, (uint64_t)keep * 2));
   const uint32_t reset[8] = {keep, 0, 0, 0, 0, 0, 0, 0};
   BGPU_TRY(write_counters(g, reset));
   return agg_resize(g, new_max, keep);
@@ -383,8 +487,8 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
       if (cudaEventElapsedTime(&ms, g->ev[0], g->ev[1]) == cudaSuccess) g->hot_kernel_ms += ms;
       BGPU_TRY(check_common_flags(g, h));
       if (h[1]) {  // global table overflow: grow and run the same rung again
-        if (attempt >= 4) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
-        BGPU_TRY(grow_after_overflow(g, h[0]));
+        if (attempt >= 8) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
+        BGPU_TRY(grow_after_overflow(g, h[0], n_rows));
         continue;
       }
       if (h[4]) {  // some CTA met a group id >= G: nothing was committed; the groups interned so far stay
@@ -427,8 +531,8 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
       g->n_groups = h[0];
       break;
     }
-    if (attempt >= 4) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
-    BGPU_TRY(grow_after_overflow(g, h[0]));
+    if (attempt >= 8) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
+    BGPU_TRY(grow_after_overflow(g, h[0], n_rows));
   }
   refresh_pointers(g, b);
   if (b->ap.n == 0) { g->last_path = "intern"; return BGPU_OK; }

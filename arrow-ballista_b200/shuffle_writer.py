@@ -1,0 +1,183 @@
+"""Host mirror of Ballista's `ShuffleWriterExec` with the hash repartition on the GPU
+(/root/reference/ballista/core/src/execution_plans/shuffle_writer.rs).
+
+`GpuShuffleWriterExec` keeps the reference operator's contract:
+  * `try_new(job_id, stage_id, partitions, plan, work_dir, shuffle_output_partitioning)` (:165-190)
+  * `schema()` = the input's schema, `output_partitioning()` = the INPUT partitioning (:483-493)
+  * `execute_shuffle_write()` (:234-257, 328-449): drives the child, partitions every batch with
+    `BatchPartitioner` (here: libbgpu's create_hashes + histogram/scan/scatter kernels), lazily opens one Arrow IPC
+    stream writer (LZ4_FRAME) per non-empty output partition at `<work_dir>/<job_id>/<stage_id>/<p>/<uuid>.arrow`
+    (:351-385), counts batches/rows, and reports `num_bytes` = the file length taken BEFORE `finish()` (:396-399);
+    `None` partitioning writes one `data.arrow` (:258-326); anything else is
+    "Invalid shuffle partitioning scheme" (:451-453)
+  * `execute()` (:518-579) wraps the result as one batch with `result_schema()` (:590-597)
+  * metrics `write_time`, `repart_time`, `input_rows`, `output_rows` (:139-163)
+
+The IPC encoding itself stays on the host (pyarrow's writer stands in for arrow-ipc's `StreamWriter`; SURVEY.md §8f-1
+ranks a device-side encoder next). Inside one NVSwitch node the files are bypassed altogether: see `exchange.py`.
+"""
+import os
+import time
+import uuid
+from dataclasses import dataclass, field
+
+import pyarrow as pa
+
+from ._lib import BGPU_EINVAL, BgpuError
+from .partitioner import BatchPartitioner, Partitioning
+from .runtime import Context
+
+
+@dataclass
+class ShuffleWritePartition:
+    """ballista.proto ShuffleWritePartition (/root/reference/ballista/core/proto/ballista.proto:443-450)."""
+    partitions: list
+    output_partition: int
+    path: str
+    num_batches: int
+    num_rows: int
+    num_bytes: int
+
+
+@dataclass
+class ShuffleWriteMetrics:
+    write_time: float = 0.0
+    repart_time: list = field(default_factory=lambda: [0.0])  # shared with BatchPartitioner as its timer
+    input_rows: int = 0
+    output_rows: int = 0
+
+
+def result_schema():
+    """shuffle_writer.rs:590-597 + PartitionStats::arrow_struct_repr (serde/scheduler/mod.rs:132-146)."""
+    stats = pa.struct([pa.field("num_rows", pa.uint64(), False), pa.field("num_batches", pa.uint64(), False),
+                       pa.field("num_bytes", pa.uint64(), False)])
+    return pa.schema([pa.field("partition", pa.uint32(), False), pa.field("path", pa.string(), False),
+                      pa.field("partition_stats", stats, False)])
+
+
+class _WriteTracker:
+    def __init__(self, path, schema):
+        self.path, self.num_batches, self.num_rows = path, 0, 0
+        self._sink = open(path, "wb")
+        self._writer = pa.ipc.new_stream(self._sink, schema, options=pa.ipc.IpcWriteOptions(compression="lz4"))
+
+    def write(self, batch):
+        self._writer.write_batch(batch)
+        self.num_batches += 1
+        self.num_rows += batch.num_rows
+
+    def finish(self):
+        """Returns the file length as the reference takes it: before the end-of-stream marker is written."""
+        self._sink.flush()
+        num_bytes = os.path.getsize(self.path)
+        self._writer.close()
+        self._sink.close()
+        return num_bytes
+
+
+class GpuShuffleWriterExec:
+    """ShuffleWriterExec whose `Partitioning::Hash` arm runs on the B200.
+
+    `plan` is the child: any iterable (or zero-argument callable returning an iterable) of pyarrow RecordBatches with
+    a `.schema`; `input_partitioning` is what `output_partitioning()` reports, as the reference reports its input's.
+    """
+
+    def __init__(self, job_id, stage_id, partitions, plan, work_dir, shuffle_output_partitioning, ctx=None,
+                 input_schema=None, input_partitioning=None):
+        self.job_id, self.stage_id, self.partitions = str(job_id), int(stage_id), list(partitions)
+        self.plan, self.work_dir = plan, str(work_dir)
+        self.shuffle_output_partitioning = shuffle_output_partitioning
+        self._schema = input_schema if input_schema is not None else getattr(plan, "schema", None)
+        self._input_partitioning = input_partitioning or Partitioning.UnknownPartitioning(1)
+        self.ctx = ctx
+        self.metrics = ShuffleWriteMetrics()
+
+    @classmethod
+    def try_new(cls, job_id, stage_id, partitions, plan, work_dir, shuffle_output_partitioning, ctx=None, **kw):
+        return cls(job_id, stage_id, partitions, plan, work_dir, shuffle_output_partitioning, ctx, **kw)
+
+    # ---- ExecutionPlan answers -------------------------------------------------------------------------------
+    def schema(self):
+        return self._schema
+
+    def output_partitioning(self):
+        return self._input_partitioning
+
+    def shuffle_output_partitioning_(self):
+        return self.shuffle_output_partitioning
+
+    def children(self):
+        return [self.plan]
+
+    def __str__(self):
+        return f"GpuShuffleWriterExec: {self.shuffle_output_partitioning and self.shuffle_output_partitioning.kind}"
+
+    def _stream(self):
+        s = self.plan() if callable(self.plan) else self.plan
+        return iter(s)
+
+    # ---- execute_shuffle_write ---------------------------------------------------------------------------------
+    def execute_shuffle_write(self):
+        base = os.path.join(self.work_dir, self.job_id, str(self.stage_id))
+        shuffle_id = str(uuid.uuid4())
+        m = self.metrics
+        part = self.shuffle_output_partitioning
+        if part is None:
+            path = os.path.join(base, shuffle_id)
+            os.makedirs(path, exist_ok=True)
+            path = os.path.join(path, "data.arrow")
+            w = None
+            t0 = time.perf_counter()
+            for batch in self._stream():
+                if w is None:
+                    w = _WriteTracker(path, batch.schema)
+                w.write(batch)
+            if w is None:
+                w = _WriteTracker(path, self._schema)
+            num_bytes = w.finish()
+            m.write_time += time.perf_counter() - t0
+            m.input_rows += w.num_rows
+            m.output_rows += w.num_rows
+            return [ShuffleWritePartition([int(p) for p in self.partitions], 0, path, w.num_batches, w.num_rows, num_bytes)]
+        if part.kind != "hash":
+            raise BgpuError(BGPU_EINVAL, "Invalid shuffle partitioning scheme")
+        n = part.partition_count()
+        writers = [None] * n
+        if self.ctx is None:
+            self.ctx = Context(0)
+        partitioner = BatchPartitioner.try_new(Partitioning.Hash(part.exprs, n), self.ctx, m.repart_time)
+
+        def on_partition(output_partition, output_batch):
+            # the partitioner never hands over an empty batch (shuffle_writer.rs:349)
+            t0 = time.perf_counter()
+            w = writers[output_partition]
+            if w is None:
+                d = os.path.join(base, str(output_partition))
+                os.makedirs(d, exist_ok=True)
+                w = writers[output_partition] = _WriteTracker(os.path.join(d, f"{shuffle_id}.arrow"), output_batch.schema)
+            w.write(output_batch)
+            m.output_rows += output_batch.num_rows
+            m.write_time += time.perf_counter() - t0
+
+        for input_batch in self._stream():
+            m.input_rows += input_batch.num_rows
+            partitioner.partition(input_batch, on_partition)
+        part_locs = []
+        for i, w in enumerate(writers):
+            if w is not None:
+                num_bytes = w.finish()
+                part_locs.append(ShuffleWritePartition([int(p) for p in self.partitions], i, w.path, w.num_batches,
+                                                       w.num_rows, num_bytes))
+        return part_locs
+
+    # ---- execute: the metadata batch -------------------------------------------------------------------------------
+    def execute(self, _partition=0):
+        locs = self.execute_shuffle_write()
+        stats = pa.StructArray.from_arrays(
+            [pa.array([l.num_rows for l in locs], type=pa.uint64()), pa.array([l.num_batches for l in locs], type=pa.uint64()),
+             pa.array([l.num_bytes for l in locs], type=pa.uint64())],
+            fields=list(result_schema().field("partition_stats").type))
+        batch = pa.RecordBatch.from_arrays(
+            [pa.array([l.output_partition for l in locs], type=pa.uint32()), pa.array([l.path for l in locs], type=pa.string()),
+             stats], schema=result_schema())
+        return [batch]

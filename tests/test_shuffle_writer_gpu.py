@@ -1,0 +1,98 @@
+"""GpuShuffleWriterExec: the reference's own tests restated
+(/root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:611-710, `test` and `test_partitioned`, same
+input plan :712-737) plus bit-exact parity of the written partitions against the oracle.
+
+The reference's tests are #[ignore]d and assert a 4/4 (2/2) split of UInt32 {1, 2} over two partitions; with the
+ahash-0.8 fallback hasher and seeds (0,0,0,0) both keys hash to the same partition (oracle/evidence/README.md), so the
+row counts asserted here are the oracle's, and everything hash-independent is asserted as the reference does.
+"""
+import os
+
+import numpy as np
+import pyarrow as pa
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def create_input_batches(copies):
+    """create_input_plan(): batches of a = [1, 2] (UInt32), b = ["hello", "world"]."""
+    schema = pa.schema([pa.field("a", pa.uint32(), True), pa.field("b", pa.string(), True)])
+    batch = pa.RecordBatch.from_arrays([pa.array([1, 2], type=pa.uint32()), pa.array(["hello", "world"])], schema=schema)
+    return [batch] * copies, schema
+
+
+def read_ipc(path):
+    with pa.ipc.open_stream(path) as r:
+        return r.read_all()
+
+
+@pytest.mark.parametrize("copies,total", [(4, 8), (2, 4)])  # `test` coalesces 2 partitions x 2 batches; `test_partitioned` reads one
+def test_reference_shuffle_writer_tests(bb, ctx, oracle, tmp_path, copies, total):
+    from ballista_b200.shuffle_writer import GpuShuffleWriterExec, result_schema
+
+    batches, schema = create_input_batches(copies)
+    query_stage = GpuShuffleWriterExec.try_new("jobOne", 1, [0], batches, str(tmp_path), bb.Partitioning.Hash([0], 2), ctx,
+                                               input_schema=schema)
+    out = query_stage.execute(0)
+    assert len(out) == 1
+    batch = out[0]
+    assert batch.schema.equals(result_schema())
+    assert batch.num_columns == 3
+    # oracle: which partitions are non-empty and how many rows each gets
+    want = {}
+    for b in batches:
+        for p, pb in oracle.partition(b, [0], 2)[0]:
+            want[p] = want.get(p, 0) + pb.num_rows
+    assert batch.num_rows == len(want)
+    paths = batch.column(1).to_pylist()
+    parts = batch.column(0).to_pylist()
+    assert parts == sorted(want)
+    for p, path in zip(parts, paths):
+        head, name = os.path.split(path)
+        assert head.endswith(os.path.join("jobOne", "1", str(p))) and name.endswith(".arrow")
+    stats = batch.column(2)
+    num_rows = stats.field("num_rows").to_pylist()
+    assert num_rows == [want[p] for p in parts] and sum(num_rows) == total
+    assert stats.field("num_batches").to_pylist() == [copies if want[p] else 0 for p in parts]
+    for path, nbytes in zip(paths, stats.field("num_bytes").to_pylist()):
+        assert 0 < nbytes <= os.path.getsize(path)  # taken before finish(): the EOS marker is not counted
+    m = query_stage.metrics
+    assert m.input_rows == total and m.output_rows == total
+
+
+def test_written_partitions_match_oracle(bb, ctx, oracle, tmp_path):
+    from ballista_b200.shuffle_writer import GpuShuffleWriterExec
+    from helpers import random_batch
+
+    rng = np.random.default_rng(3)
+    batches = [random_batch(rng, n) for n in (5000, 1, 8192, 0, 777)]
+    keys, n = [0, 9], 7  # k64 + a Utf8 column with nulls
+    ex = GpuShuffleWriterExec.try_new("job", 3, [0, 1], batches, str(tmp_path), bb.Partitioning.Hash(keys, n), ctx,
+                                      input_schema=batches[0].schema)
+    locs = ex.execute_shuffle_write()
+    want = {}
+    for b in batches:
+        for p, pb in oracle.partition(b, keys, n)[0]:
+            want.setdefault(p, []).append(pb)
+    assert [l.output_partition for l in locs] == sorted(want)
+    for l in locs:
+        got = read_ipc(l.path)
+        exp = pa.Table.from_batches(want[l.output_partition])
+        assert l.num_batches == len(want[l.output_partition]) and l.num_rows == exp.num_rows
+        assert l.partitions == [0, 1]
+        assert got.equals(exp), f"partition {l.output_partition} differs from the oracle"
+
+
+def test_unpartitioned_and_invalid_scheme(bb, ctx, tmp_path):
+    from ballista_b200.shuffle_writer import GpuShuffleWriterExec
+
+    batches, schema = create_input_batches(3)
+    ex = GpuShuffleWriterExec.try_new("j", 2, [5], batches, str(tmp_path), None, ctx, input_schema=schema)
+    (loc,) = ex.execute_shuffle_write()
+    assert loc.output_partition == 0 and loc.path.endswith("data.arrow") and loc.num_rows == 6 and loc.num_batches == 3
+    assert read_ipc(loc.path).equals(pa.Table.from_batches(batches))
+    bad = GpuShuffleWriterExec.try_new("j", 2, [5], batches, str(tmp_path), bb.Partitioning.RoundRobinBatch(4), ctx,
+                                       input_schema=schema)
+    with pytest.raises(bb.BgpuError, match="Invalid shuffle partitioning scheme"):
+        bad.execute_shuffle_write()
