@@ -375,8 +375,8 @@ struct Gen {
         if (g->phys[ai].value != (int32_t)vi) continue;
         const int alias = sh.acc_alias[ai];
         const int word0 = alias >= 0 ? sh.acc_word0[(size_t)alias] : sh.acc_word0[ai];
-        if (alias >= 0) o.fmt("      if (!Sink::kSkipAliased) sink.template add<%d, %d, %zu>(a, %s);", g->phys[ai].op, word0, ai, as_val.c_str());
-        else o.fmt("      sink.template add<%d, %d, %zu>(a, %s);", g->phys[ai].op, word0, ai, as_val.c_str());
+        if (alias >= 0) o.fmt("      if (!Sink::kSkipAliased) sink.template add<%d, %d, %zu, %d>(a, %s);", g->phys[ai].op, word0, ai, g->phys[ai].out_off, as_val.c_str());
+        else o.fmt("      sink.template add<%d, %d, %zu, %d>(a, %s);", g->phys[ai].op, word0, ai, g->phys[ai].out_off, as_val.c_str());
         o.fmt("      seen |= %uu;", 1u << ai);
       }
       o.line("    }");
@@ -391,7 +391,7 @@ struct Gen {
     for (size_t ai = 0; ai < g->phys.size(); ai++) {
       const int alias = sh.acc_alias[ai];
       const int word0 = alias >= 0 ? sh.acc_word0[(size_t)alias] : sh.acc_word0[ai];
-      o.fmt("    f.template acc<%d, %d, %d, %zu, %s>();", g->phys[ai].op, word0, g->phys[ai].words, ai, alias >= 0 ? "true" : "false");
+      o.fmt("    f.template acc<%d, %d, %d, %zu, %s, %d>();", g->phys[ai].op, word0, g->phys[ai].words, ai, alias >= 0 ? "true" : "false", g->phys[ai].out_off);
     }
     o.line("  }");
   }
@@ -423,11 +423,14 @@ int agg_generate_source(const bgpu_agg* g, const JitShape& sh, std::string* out)
   o.line("}  // namespace bgpu");
   o.line("using namespace bgpu;");
   if (sh.kernels & 1)
-    o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T, Plan::MIN_CTAS) bgpu_fused(const __grid_constant__ JitArgs a) { fused_body<Plan>(a); }");
+    o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T, Plan::MIN_CTAS) bgpu_fused(const __grid_constant__ JitArgs a) { fused_body<Plan, 0>(a); }");
+  if (sh.kernels & 4)
+    o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T, Plan::MIN_CTAS) bgpu_fused_shared(const __grid_constant__ JitArgs a) { fused_body<Plan, 1>(a); }");
   if (sh.kernels & 2) {
     o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_intern(const __grid_constant__ JitArgs a) { intern_body<Plan>(a); }");
     o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_acc_shared(const __grid_constant__ JitArgs a) { accumulate_body<Plan, 1>(a); }");
     o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_acc_global(const __grid_constant__ JitArgs a) { accumulate_body<Plan, 2>(a); }");
+    o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_sketch(const __grid_constant__ JitArgs a) { sketch_body<Plan>(a); }");
   }
   *out = std::move(o.s);
   return BGPU_OK;

@@ -15,7 +15,7 @@ struct PhysAcc {
   int32_t op = 0;
   int32_t value = -1;  // index into bgpu_agg::values
   int32_t words = 1;
-  DevAllocPtr buf;  // words * max_groups u64
+  int32_t out_off = 0;  // first word inside a group's accumulator record
 };
 struct LogicalAgg {
   int32_t fn = 0;
@@ -26,7 +26,7 @@ struct LogicalAgg {
   int scale_up = 0;  // Avg(decimal): result scale - sum scale
 };
 
-constexpr int kFusedRungs = 3;
+constexpr int kFusedRungs = 4;  // private 512x2; shared-atomic 3 CTAs/SM, 1 CTA/SM, 1 CTA/SM without key cache
 
 struct bgpu_agg {
   bgpu_ctx* ctx = nullptr;
@@ -43,7 +43,9 @@ struct bgpu_agg {
   std::vector<LogicalAgg> aggs;
   // group table
   uint32_t max_groups = 0, n_groups = 0;
-  DevAllocPtr entries, key0, key1, kmeta, counters /* u32 [0]=n_groups, [1..4]=flags */, seen, scratch;
+  // slots: the table (key inline); acc: one record of acc_stride u64 per group
+  DevAllocPtr slots, acc, counters /* u32 [0]=n_groups, [1..4]=flags */, seen, scratch;
+  uint32_t acc_stride = 1;
   bool seen_tracking = false;
   int fused_rung = 0;  // first rung of the fused ladder still worth trying; kFusedRungs = two-pass only
   // dictionary-typed group columns are keyed by value: the aggregate keeps one canonical dictionary per column
@@ -62,7 +64,7 @@ struct bgpu_agg {
   // and launch geometry; the modules themselves live in jit.cu's process-wide cache)
   std::map<std::string, const bgpu::JitModule*> modules;
   bool emitted = false;
-  // introspection for tests / bench: which path the last update took ("fused512", "fused256", "fused128",
+  // introspection for tests / bench: which path the last update took ("fused512", "fused_shared2", "fused_shared1",
   // "shared", "global")
   std::string last_path;
   // device time of the fused kernel launches so far (CUDA events on the ctx stream): bench.py's roofline numerator
@@ -78,8 +80,8 @@ struct bgpu_agg {
   uint32_t* d_n_groups() { return (uint32_t*)counters->p; }
   int32_t* d_flags() { return (int32_t*)counters->p + 1; }
   bgpu::GroupTable table() {
-    return bgpu::GroupTable{(unsigned long long*)entries->p, max_groups * 2 - 1, max_groups, (uint64_t*)key0->p,
-                            key1 ? (uint64_t*)key1->p : nullptr, (uint32_t*)kmeta->p, d_n_groups(), d_flags()};
+    return bgpu::GroupTable{(uint64_t*)slots->p, max_groups * 2 - 1, max_groups, d_n_groups(), d_flags(),
+                            (uint64_t*)acc->p, acc_stride, key_words == 1 ? 2u : 4u};
   }
 };
 
@@ -103,7 +105,9 @@ struct JitShape {
   int32_t W = 0;                             // accumulator words per group
   bool has_seen = false;
   int32_t T = 256, R = 4, min_ctas = 1;
-  int32_t kernels = 3;  // which entry points to emit: bit 0 bgpu_fused, bit 1 bgpu_intern + bgpu_acc_shared + bgpu_acc_global
+  // which entry points to emit: bit 0 bgpu_fused, bit 1 bgpu_intern + bgpu_acc_shared + bgpu_acc_global,
+  // bit 2 bgpu_fused_shared
+  int32_t kernels = 3;
   bool any_validity = false;
 };
 // slot of batch column `batch_col` (created on first use); -1 when the table is full

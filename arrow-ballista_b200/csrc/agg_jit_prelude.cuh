@@ -30,16 +30,21 @@ constexpr uint32_t kGidOverflow = 0xfffffff0u;  // "no room": always >= max_grou
 constexpr int kJitSlots = 24;
 constexpr int kJitAcc = 24;
 
+// The global group table (host mirror: agg_plan.h, same layout): open addressing with the packed key stored INSIDE
+// the slot, so a probe is one 16-byte (one key word) or 32-byte (two key words) access — one DRAM sector.
+//   slot = [k0][k1 if KEY_WORDS == 2][sm][pad if KEY_WORDS == 2],  sm = (null bits << 32) | state,
+//   state: 0 empty, 1 busy (being published), >= 2: dense group id + 2.
+// Accumulators: one record of acc_stride u64 per group (array of structs).
 struct GroupTable {
-  unsigned long long* entries;  // (tag << 32) | state; state 0 empty, 1 busy, >= 2: gid + 2
-  uint32_t mask;                // capacity - 1 (capacity = 2 * max_groups, power of two)
+  uint64_t* slots;
+  uint32_t mask;        // capacity - 1 (capacity = 2 * max_groups, power of two)
   uint32_t max_groups;
-  uint64_t* key0;               // packed keys of group gid (dense)
-  uint64_t* key1;
-  uint32_t* kmeta;              // null bits of the key columns
-  uint32_t* n_groups;           // device counter
-  int32_t* flags;               // [0] capacity overflow, [1] string key too long, [2] arithmetic overflow,
-                                // [3] private tier abort (a group id beyond the private capacity)
+  uint32_t* n_groups;   // device counter
+  int32_t* flags;       // [0] capacity overflow, [1] string key too long, [2] arithmetic overflow,
+                        // [3] fused pass abort (a group id beyond the per-CTA capacity)
+  uint64_t* acc;        // max_groups * acc_stride u64
+  uint32_t acc_stride;
+  uint32_t slot_words;  // 2 or 4
 };
 
 // The single by-value kernel argument; the host mirror is agg_plan.h's JitArgs (same layout).
@@ -48,7 +53,6 @@ struct JitArgs {
   const int32_t* aux[kJitSlots];     // slot s: utf8 offsets, or the dictionary remap (nullptr = identity)
   const uint8_t* valid[kJitSlots];   // slot s: validity bitmap (only read when the plan marks the slot nullable)
   GroupTable t;
-  uint64_t* acc_out[kJitAcc];        // dense accumulator arrays (words * max_groups u64)
   uint32_t* seen;                    // per-group bitmask of accumulators that saw a non-null input
   uint64_t* scratch;                 // fused path: per-CTA slabs
   uint32_t* gids;                    // two-pass path: group id per row
@@ -79,35 +83,34 @@ __device__ __forceinline__ uint64_t key_hash(const PackedKey& k) {
 template <int WORDS>
 __device__ __noinline__ uint32_t intern_slow(const GroupTable& t, uint64_t k0, uint64_t k1, uint32_t meta) {
   const PackedKey k{k0, k1, meta};  // by value: a reference would force the caller's key into local memory
-  const uint64_t h = key_hash<WORDS>(k);
-  const unsigned long long tag = (h >> 32) << 32;
-  uint32_t i = (uint32_t)h & t.mask;
+  constexpr int SW = WORDS == 1 ? 2 : 4, SMW = WORDS == 1 ? 1 : 2;  // slot words, index of the state|meta word
+  uint32_t i = (uint32_t)key_hash<WORDS>(k) & t.mask;
   for (uint32_t probes = 0; probes <= t.mask; probes++) {
-    unsigned long long e = *(volatile unsigned long long*)&t.entries[i];
-    if (e == 0) {
+    uint64_t* slot = t.slots + (size_t)i * SW;
+    // one 16-byte access brings key word 0 and state|meta (WORDS == 1) or both key words (WORDS == 2); L2-coherent
+    const ulonglong2 a = __ldcg((const ulonglong2*)slot);
+    uint64_t sm = WORDS == 1 ? a.y : __ldcg(slot + SMW);
+    if ((uint32_t)sm == 0u) {
       if (*(volatile int32_t*)&t.flags[0]) return kGidOverflow;  // the pass is void already: do not fill the table
-      e = atomicCAS(&t.entries[i], 0ULL, tag | 1ULL);
-      if (e == 0) {  // we own the slot: allocate the dense id, publish the key, then the entry
+      const unsigned long long prev = atomicCAS((unsigned long long*)(slot + SMW), 0ULL, 1ULL);
+      if (prev == 0ULL) {  // we own the slot: write the key, allocate the dense id, then publish state|meta
+        slot[0] = k.k0;
+        if (WORDS > 1) slot[1] = k.k1;
         const uint32_t gid = atomicAdd(t.n_groups, 1u);
-        if (gid < t.max_groups) {
-          t.key0[gid] = k.k0;
-          if (WORDS > 1) t.key1[gid] = k.k1;
-          t.kmeta[gid] = k.meta;
-        } else {
-          atomicOr(&t.flags[0], 1);
-        }
+        if (gid >= t.max_groups) atomicOr(&t.flags[0], 1);
         __threadfence();
-        *(volatile unsigned long long*)&t.entries[i] = tag | (unsigned long long)(gid + 2u);
+        *(volatile uint64_t*)(slot + SMW) = ((uint64_t)k.meta << 32) | (uint64_t)(gid + 2u);
         return gid;
       }
+      sm = prev;
     }
-    if ((e & 0xffffffff00000000ULL) == tag) {
-      while ((uint32_t)e == 1u) e = *(volatile unsigned long long*)&t.entries[i];  // inserter is publishing
-      const uint32_t gid = (uint32_t)e - 2u;
-      if (gid >= t.max_groups) return gid;
-      // dense key arrays share cache lines between groups: read through L2 (L1 may hold a stale line)
-      if (__ldcg(&t.key0[gid]) == k.k0 && (WORDS == 1 || __ldcg(&t.key1[gid]) == k.k1) && __ldcg(&t.kmeta[gid]) == k.meta)
-        return gid;
+    while ((uint32_t)sm == 1u) sm = *(volatile uint64_t*)(slot + SMW);  // inserter is publishing
+    // published slots never change again. The key words above may predate the publication we just observed (or the
+    // 16-byte access may have been split): on a mismatch re-read them once before moving on.
+    if ((uint32_t)(sm >> 32) == k.meta) {
+      bool same = a.x == k.k0 && (WORDS == 1 || a.y == k.k1);
+      if (!same) same = *(volatile uint64_t*)slot == k.k0 && (WORDS == 1 || *(volatile uint64_t*)(slot + 1) == k.k1);
+      if (same) return (uint32_t)sm - 2u;
     }
     i = (i + 1) & t.mask;
   }
@@ -277,7 +280,7 @@ template <int T>
 struct PrivateSink {
   static constexpr bool kSkipAliased = true;
   uint64_t* base;  // &s_acc[g * W * T + threadIdx.x]
-  template <int OP, int WORD0, int IDX>
+  template <int OP, int WORD0, int IDX, int OUT>
   __device__ __forceinline__ void add(const JitArgs&, Val v) {
     uint64_t* p = base + WORD0 * T;
     if (OP == OP_ADD_F64) {
@@ -312,16 +315,83 @@ __device__ __forceinline__ void add_atomic(uint64_t* p, Val v) {
 struct SharedAtomicSink {  // one of `replicas` copies of [n_groups][W] in shared memory
   static constexpr bool kSkipAliased = true;
   uint64_t* base;  // &s_acc[(rep * n_groups + g) * W]
-  template <int OP, int WORD0, int IDX>
+  template <int OP, int WORD0, int IDX, int OUT>
   __device__ __forceinline__ void add(const JitArgs&, Val v) { add_atomic<OP>(base + WORD0, v); }
+};
+
+// 64-bit / 128-bit integer adds in SHARED memory as chains of native 32-bit atomics (ATOMS.ADD): the thread whose add
+// wraps a limb carries into the next one. (A 64-bit shared atomicAdd compiles to a compare-and-swap spin loop.)
+__device__ __forceinline__ void add_shared_limbs(uint32_t* q, const uint32_t* limb, int n) {
+  uint32_t carry = 0;
+#pragma unroll
+  for (int i = 0; i < n; i++) {
+    const uint32_t v = limb[i] + carry;
+    const uint32_t wrapped = (limb[i] + carry) < carry;  // limb[i] = 0xffffffff and carry = 1: passes the carry on
+    carry = wrapped;
+    if (v) {
+      const uint32_t old = atomicAdd(q + i, v);
+      carry += (old + v) < old;
+    }
+  }
+}
+struct SharedSplitSink {  // one of `replicas` copies of [g_cap][W] in shared memory
+  static constexpr bool kSkipAliased = true;
+  uint64_t* base;  // &s_acc[(rep * g_cap + g) * W]
+  template <int OP, int WORD0, int IDX, int OUT>
+  __device__ __forceinline__ void add(const JitArgs&, Val v) {
+    uint32_t* q = (uint32_t*)(base + WORD0);
+    if (OP == OP_ADD_F64) {
+      atomicAdd((double*)(base + WORD0), as_f64(v.lo));
+    } else if (OP == OP_COUNT) {
+      const uint32_t old = atomicAdd(q, 1u);
+      if (old == 0xffffffffu) atomicAdd(q + 1, 1u);
+    } else if (OP == OP_ADD_I128) {
+      const uint32_t limb[4] = {(uint32_t)v.lo, (uint32_t)(v.lo >> 32), (uint32_t)v.hi, (uint32_t)(v.hi >> 32)};
+      add_shared_limbs(q, limb, 4);
+    } else {
+      const uint32_t limb[2] = {(uint32_t)v.lo, (uint32_t)(v.lo >> 32)};
+      add_shared_limbs(q, limb, 2);
+    }
+  }
+};
+
+// fused MODE 1: fold the CTA's replicas of one accumulator into its slab (one thread per group)
+struct FlushReplicas {
+  const uint64_t* s_acc;
+  uint64_t* slab;
+  uint32_t G, replicas;
+  int W, T;
+  template <int OP, int WORD0, int WORDS, int IDX, bool ALIASED, int OUT>
+  __device__ __forceinline__ void acc() {
+    if (ALIASED) return;
+    for (uint32_t grp = threadIdx.x; grp < G; grp += T) {
+      uint64_t* o = slab + (size_t)grp * W + WORD0;
+      if (OP == OP_ADD_F64) {
+        double f = 0.0;
+        for (uint32_t t = 0; t < replicas; t++) f += as_f64(s_acc[((size_t)t * G + grp) * W + WORD0]);
+        o[0] = f64_bits(f);
+      } else {
+        Val s{0, 0};
+        for (uint32_t t = 0; t < replicas; t++) {
+          const uint64_t* p = &s_acc[((size_t)t * G + grp) * W + WORD0];
+          const uint64_t lo = p[0];
+          s.lo += lo;
+          s.hi += (s.lo < lo);
+          if (WORDS > 1) s.hi += p[1];
+        }
+        o[0] = s.lo;
+        if (WORDS > 1) o[1] = s.hi;
+      }
+    }
+  }
 };
 
 struct GlobalAtomicSink {
   static constexpr bool kSkipAliased = false;
   uint32_t g;
-  template <int OP, int WORD0, int IDX>
+  template <int OP, int WORD0, int IDX, int OUT>
   __device__ __forceinline__ void add(const JitArgs& a, Val v) {
-    add_atomic<OP>(a.acc_out[IDX] + (size_t)g * (OP == OP_ADD_I128 ? 2 : 1), v);
+    add_atomic<OP>(a.t.acc + (size_t)g * a.t.acc_stride + OUT, v);
   }
 };
 
@@ -354,7 +424,7 @@ struct FlushPrivate {
   uint64_t* slab;
   uint32_t G;
   int W;
-  template <int OP, int WORD0, int WORDS, int IDX, bool ALIASED>
+  template <int OP, int WORD0, int WORDS, int IDX, bool ALIASED, int OUT>
   __device__ __forceinline__ void acc() {
     if (ALIASED) return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -390,11 +460,11 @@ struct FlushShared {
   const JitArgs* a;
   uint32_t n_groups, replicas;
   int W, T;
-  template <int OP, int WORD0, int WORDS, int IDX, bool ALIASED>
+  template <int OP, int WORD0, int WORDS, int IDX, bool ALIASED, int OUT>
   __device__ __forceinline__ void acc() {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (uint32_t grp = warp; grp < n_groups; grp += T / 32) {
-      uint64_t* o = a->acc_out[IDX] + (size_t)grp * (OP == OP_ADD_I128 ? 2 : 1);
+      uint64_t* o = a->t.acc + (size_t)grp * a->t.acc_stride + OUT;
       if (OP == OP_ADD_F64) {
         double f = 0.0;
         for (uint32_t t = lane; t < replicas; t += 32) f += as_f64(s_acc[((size_t)t * n_groups + grp) * W + WORD0]);
@@ -433,13 +503,17 @@ constexpr int NEED_FILTER = 1, NEED_KEY = 2, NEED_VALUES = 4;
 
 // Shared memory: acc u64[g_cap * W * T] | seen u32[g_cap] | key cache (slots)
 // Scratch slab of CTA b: u64[g_cap * W] partial accumulators, then u32[g_cap] seen masks (padded to 8 bytes).
-template <class Plan>
+// MODE 0: thread-private accumulators (copies = T; best for a handful of groups).
+// MODE 1: `a.replicas` shared copies of [g_cap][W] updated with native 32-bit shared atomics (hundreds to thousands of
+//         groups: the accumulators no longer scale with the thread count, so the SM runs at full residency).
+template <class Plan, int MODE>
 __device__ __forceinline__ void fused_body(const JitArgs& a) {
   constexpr int T = Plan::T, R = Plan::R, W = Plan::W, KW = Plan::KEY_WORDS;
   extern __shared__ __align__(16) uint64_t smem[];
   const uint32_t G = a.g_cap;
+  const uint32_t copies = MODE == 0 ? (uint32_t)T : a.replicas;
   uint64_t* s_acc = smem;
-  uint32_t* s_seen = (uint32_t*)(s_acc + (size_t)G * W * T);
+  uint32_t* s_seen = (uint32_t*)(s_acc + (size_t)G * W * copies);
   KeyCache cache;
   {
     unsigned char* p = (unsigned char*)(s_seen + ((G + 1) & ~1u));
@@ -450,7 +524,7 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
     cache.mask = a.cache_slots - 1;
   }
   __shared__ int s_abort;
-  for (uint32_t i = threadIdx.x; i < G * W * T; i += T) s_acc[i] = 0;
+  for (uint32_t i = threadIdx.x; i < G * W * copies; i += T) s_acc[i] = 0;
   for (uint32_t i = threadIdx.x; i < G; i += T) s_seen[i] = 0;
   for (uint32_t i = threadIdx.x; i < a.cache_slots; i += T) cache.state[i] = 0;
   if (threadIdx.x == 0) s_abort = 0;
@@ -458,6 +532,7 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
 
   bool ovf = false;
   uint32_t tiles_done = 0;
+  const uint32_t rep = MODE == 0 ? 0u : (threadIdx.x >> 5) % a.replicas;  // one replica per warp while they last
   const int64_t tile = (int64_t)T * R, last = a.n_rows - 1, stride = (int64_t)gridDim.x * tile;
   // Software pipeline over this CTA's tiles (rows past the end re-read the last row):
   //   tile i+1: bulk L2 prefetch of every streamed buffer; its "early" loads (utf8 offsets, remapped dictionary keys)
@@ -495,10 +570,17 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
       const int64_t r = base + u * T + threadIdx.x;
       if (r > last || !Plan::filter(a, x[u])) continue;
       const PackedKey k = Plan::key(a, x[u]);
-      const uint32_t gid = cached_intern<KW>(cache, a.t, k);
+      // cache_slots == 0: no per-CTA key cache (all of shared memory holds accumulators; the table is L2 resident)
+      const uint32_t gid = (MODE != 0 && a.cache_slots == 0) ? intern<KW>(a.t, k) : cached_intern<KW>(cache, a.t, k);
       if (gid >= G) { s_abort = 1; continue; }  // beyond the private capacity (or the global table overflowed)
-      PrivateSink<T> sink{s_acc + (size_t)gid * W * T + threadIdx.x};
-      const uint32_t seen = Plan::accumulate(a, x[u], sink, &ovf);
+      uint32_t seen;
+      if (MODE == 0) {
+        PrivateSink<T> sink{s_acc + (size_t)gid * W * T + threadIdx.x};
+        seen = Plan::accumulate(a, x[u], sink, &ovf);
+      } else {
+        SharedSplitSink sink{s_acc + ((size_t)rep * G + gid) * W};
+        seen = Plan::accumulate(a, x[u], sink, &ovf);
+      }
       if (Plan::HAS_SEEN && seen) atomicOr(&s_seen[gid], seen);
     }
     // some CTA gave up: the pass is void (the global flag is polled every 16th tile: it only saves work)
@@ -511,10 +593,47 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
     return;
   }
   uint64_t* slab = a.scratch + (size_t)blockIdx.x * fused_slab_words(G, W);
-  FlushPrivate<T> fl{s_acc, slab, G, W};
-  Plan::for_each_acc(fl);
+  if (MODE == 0) {
+    FlushPrivate<T> fl{s_acc, slab, G, W};
+    Plan::for_each_acc(fl);
+  } else {
+    FlushReplicas fl{s_acc, slab, G, a.replicas, W, T};
+    Plan::for_each_acc(fl);
+  }
   uint32_t* slab_seen = (uint32_t*)(slab + (size_t)G * W);
   for (uint32_t i = threadIdx.x; i < G; i += T) slab_seen[i] = s_seen[i];
+}
+
+// two-pass path, pass 0 (only when the batch could overflow the table): linear-counting sketch of the batch's distinct
+// keys. Every surviving row sets one bit (chosen by its table hash) of a bitmap of `a.n_groups` 32-bit words
+// (a power of two) at `a.gids`; the host turns the fraction of zero bits into a cardinality estimate and sizes the
+// table once, instead of discovering the cardinality by overflowing and re-running the intern pass.
+template <class Plan>
+__device__ __forceinline__ void sketch_body(const JitArgs& a) {
+  constexpr int T = Plan::T, R = Plan::R;
+  const int64_t tile = (int64_t)T * R, last = a.n_rows - 1;
+  const uint32_t wmask = a.n_groups - 1;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < a.n_rows; base += (int64_t)gridDim.x * tile) {
+    typename Plan::Raw x[R];
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      Plan::template load0<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
+      Plan::template load1<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      Plan::template load2<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      if (r > last || !Plan::filter(a, x[u])) continue;
+      const uint64_t h = key_hash<Plan::KEY_WORDS>(Plan::key(a, x[u])) >> 16;  // bits the table index does not use first
+      atomicOr(&a.gids[(uint32_t)(h >> 5) & wmask], 1u << (h & 31));
+    }
+  }
 }
 
 // two-pass path, pass 1

@@ -7,16 +7,22 @@
 namespace bgpu {
 
 constexpr int kAggThreads = 256;
-constexpr uint32_t kNoGroup = 0xffffffffu;  // row dropped by the filter
 
-// Rebuild the entry table from the dense keys (after growing).
-__global__ void __launch_bounds__(kAggThreads) rehash_kernel(const __grid_constant__ GroupTable t, uint32_t n, int words) {
-  for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < n; g += gridDim.x * blockDim.x) {
-    PackedKey k{t.key0[g], words > 1 ? t.key1[g] : 0, t.kmeta[g]};
-    const uint64_t h = key_hash(k);
-    const unsigned long long tag = (h >> 32) << 32;
-    uint32_t i = (uint32_t)h & t.mask;
-    while (atomicCAS(&t.entries[i], 0ULL, tag | (unsigned long long)(g + 2u)) != 0ULL) i = (i + 1) & t.mask;
+// Re-insert every published slot of the old table with a group id < keep into the (empty) new one after growing;
+// group ids are kept (ids >= keep were handed out by the void pass that overflowed and are dropped).
+__global__ void __launch_bounds__(kAggThreads)
+    rehash_kernel(const uint64_t* __restrict__ old_slots, uint32_t old_capacity, uint32_t keep, const __grid_constant__ GroupTable t) {
+  const int W = (int)t.slot_words, smw = W == 2 ? 1 : 2;
+  for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < old_capacity; s += gridDim.x * blockDim.x) {
+    const uint64_t* o = old_slots + (size_t)s * W;
+    const uint64_t sm = o[smw];
+    if ((uint32_t)sm < 2u || (uint32_t)sm - 2u >= keep) continue;
+    const PackedKey k{o[0], W == 4 ? o[1] : 0ULL, (uint32_t)(sm >> 32)};
+    uint32_t i = (uint32_t)key_hash(k) & t.mask;
+    while (atomicCAS((unsigned long long*)(slot_ptr(t, i) + smw), 0ULL, (unsigned long long)sm) != 0ULL) i = (i + 1) & t.mask;
+    uint64_t* n = slot_ptr(t, i);
+    n[0] = k.k0;
+    if (W == 4) n[1] = k.k1;
   }
 }
 
@@ -25,8 +31,8 @@ __host__ __device__ __forceinline__ size_t fused_slab_words(uint32_t g_cap, int 
   return (size_t)g_cap * W + ((size_t)g_cap + 1) / 2;
 }
 
-// Fold the per-CTA slabs into the dense accumulator arrays: one WARP per (group, accumulator); lanes stride over the
-// slabs and the partials are combined by shuffles in a fixed order (Float64 sums are reproducible for a fixed grid).
+// Fold the per-CTA slabs into the group records: one WARP per (group, accumulator); lanes stride over the slabs and
+// the partials are combined by shuffles in a fixed order (Float64 sums are reproducible for a fixed grid).
 __global__ void __launch_bounds__(kAggThreads)
     commit_kernel(const __grid_constant__ AccPlan plan, const uint64_t* __restrict__ scratch, uint32_t n_ctas,
                   uint32_t g_cap, uint32_t n_groups) {
@@ -58,7 +64,7 @@ __global__ void __launch_bounds__(kAggThreads)
       hi += ohi + (lo < olo);
     }
     if (lane == 0) {
-      uint64_t* o = a.out + (size_t)grp * a.words;
+      uint64_t* o = plan.acc + (size_t)grp * plan.stride + a.out_off;
       if (a.op == OP_ADD_F64) {
         *(double*)o += fsum;
       } else {
@@ -85,6 +91,33 @@ __global__ void __launch_bounds__(kAggThreads)
 }
 
 // ---- emit kernels -----------------------------------------------------------------------------------------------
+// Dense key arrays (index = group id) from the table slots.
+__global__ void __launch_bounds__(kAggThreads)
+    densify_keys_kernel(const __grid_constant__ GroupTable t, uint64_t* __restrict__ key0, uint64_t* __restrict__ key1,
+                        uint32_t* __restrict__ kmeta) {
+  const int W = (int)t.slot_words, smw = W == 2 ? 1 : 2;
+  for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s <= t.mask; s += gridDim.x * blockDim.x) {
+    const uint64_t* o = t.slots + (size_t)s * W;
+    const uint64_t sm = o[smw];
+    if ((uint32_t)sm < 2u) continue;
+    const uint32_t gid = (uint32_t)sm - 2u;
+    if (gid >= t.max_groups) continue;
+    key0[gid] = o[0];
+    if (key1) key1[gid] = W == 4 ? o[1] : 0ULL;
+    kmeta[gid] = (uint32_t)(sm >> 32);
+  }
+}
+
+// One accumulator of every group record -> a dense Arrow values buffer (words = 1 or 2).
+__global__ void __launch_bounds__(kAggThreads)
+    extract_acc_kernel(const uint64_t* __restrict__ acc, uint32_t stride, int off, int words, uint32_t n, uint64_t* __restrict__ out) {
+  for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < n; g += gridDim.x * blockDim.x) {
+    const uint64_t* p = acc + (size_t)g * stride + off;
+    out[(size_t)g * words] = p[0];
+    if (words > 1) out[(size_t)g * words + 1] = p[1];
+  }
+}
+
 // Unpack one fixed-width / bool / dictionary key column of the dense key arrays into an Arrow column.
 __global__ void __launch_bounds__(kAggThreads)
     unpack_fixed_kernel(const uint64_t* __restrict__ key0, const uint64_t* __restrict__ key1,
@@ -158,23 +191,33 @@ __global__ void __launch_bounds__(kAggThreads)
   }
 }
 
+// set bits of the cardinality sketch's bitmap (run_two_pass)
+__global__ void __launch_bounds__(kAggThreads) popcount_kernel(const uint32_t* __restrict__ w, uint32_t n, unsigned long long* out) {
+  unsigned long long c = 0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) c += __popc(w[i]);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) c += __shfl_down_sync(0xffffffffu, c, d);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
 __global__ void __launch_bounds__(kAggThreads) fill_u32_kernel(uint32_t* p, uint32_t n, uint32_t v) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = v;
 }
 
-// AvgGroupsAccumulator::evaluate. Float64: sum / count. Decimal128: (sum * 10^scale_up) / count, truncating;
-// an overflowing scaled multiply is an error in the reference -> flags[2].
+// AvgGroupsAccumulator::evaluate from the group records. Float64: sum / count. Decimal128: (sum * 10^scale_up) / count,
+// truncating; an overflowing scaled multiply is an error in the reference -> flags[2].
 __global__ void __launch_bounds__(kAggThreads)
-    avg_evaluate_kernel(const uint64_t* __restrict__ sum, const uint64_t* __restrict__ count, uint32_t n, int is_decimal,
+    avg_evaluate_kernel(const uint64_t* __restrict__ acc, uint32_t stride, int sum_off, int count_off, uint32_t n, int is_decimal,
                         int scale_up, uint64_t* __restrict__ out, uint32_t* __restrict__ out_valid, int32_t* flags) {
   const uint32_t n_pad = (n + 31) & ~31u;
   for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < n_pad; g += gridDim.x * blockDim.x) {
     bool valid = false;
     if (g < n) {
-      const uint64_t c = count[g];
+      const uint64_t* rec = acc + (size_t)g * stride;
+      const uint64_t c = rec[count_off];
       valid = c != 0;
       if (is_decimal) {
-        __int128 s = (__int128)(((unsigned __int128)sum[2 * g + 1] << 64) | sum[2 * g]);
+        __int128 s = (__int128)(((unsigned __int128)rec[sum_off + 1] << 64) | rec[sum_off]);
         __int128 q = 0;
         if (valid) {
           bool ovf = false;
@@ -189,7 +232,7 @@ __global__ void __launch_bounds__(kAggThreads)
         out[2 * g] = (uint64_t)q;
         out[2 * g + 1] = (uint64_t)((unsigned __int128)q >> 64);
       } else {
-        const double s = __longlong_as_double((long long)sum[g]);
+        const double s = __longlong_as_double((long long)rec[sum_off]);
         out[g] = (uint64_t)__double_as_longlong(valid ? s / (double)c : 0.0);
       }
     }

@@ -43,16 +43,22 @@ struct KeyPlan {
   int32_t words;  // 1: packed key fits 8 bytes, 2: 16 bytes
 };
 
+// The global group table: open addressing with the packed key stored INSIDE the slot, so a probe is one 16-byte
+// (one key word) or 32-byte (two key words) access — one DRAM sector — instead of entry + key + null-bits accesses.
+//   slot = [k0][k1 if key_words == 2][sm][pad if key_words == 2],  sm = (null bits << 32) | state,
+//   state: 0 empty, 1 busy (being published), >= 2: dense group id + 2.
+// Accumulators are one record of `acc_stride` u64 per group (array of structs): all of a group's words share one or
+// two sectors. Dense key columns and Arrow accumulator columns are produced at emit.
 struct GroupTable {
-  unsigned long long* entries;  // (tag << 32) | state; state 0 empty, 1 busy, >= 2: gid + 2
-  uint32_t mask;                // capacity - 1 (capacity = 2 * max_groups, power of two)
+  uint64_t* slots;
+  uint32_t mask;        // capacity - 1 (capacity = 2 * max_groups, power of two)
   uint32_t max_groups;
-  uint64_t* key0;               // packed keys of group gid (dense)
-  uint64_t* key1;
-  uint32_t* kmeta;              // null bits of the key columns
-  uint32_t* n_groups;           // device counter
-  int32_t* flags;               // [0] capacity overflow, [1] string key too long, [2] arithmetic overflow,
-                                // [3] private tier abort (a group id beyond the private capacity)
+  uint32_t* n_groups;   // device counter
+  int32_t* flags;       // [0] capacity overflow, [1] string key too long, [2] arithmetic overflow,
+                        // [3] fused pass abort (a group id beyond the per-CTA capacity)
+  uint64_t* acc;        // max_groups * acc_stride u64
+  uint32_t acc_stride;
+  uint32_t slot_words;  // 2 or 4
 };
 
 // ---- value expressions: product of up to three factors, each `x`, `x + y` or `x - y` ------------------------------
@@ -99,20 +105,22 @@ struct FilterPlan {
 
 // ---- accumulators -------------------------------------------------------------------------------------------
 struct AccK {
-  uint64_t* out;     // dense accumulator array: words * max_groups u64
+  int32_t out_off;   // first word of this accumulator inside a group's record (GroupTable::acc)
   int32_t op;        // AccOp
   int32_t words;     // 1 or 2
-  int32_t word0;     // first word of this accumulator inside a group's private/shared state
+  int32_t word0;     // first word of this accumulator inside a group's per-CTA (private / replicated) state
   int32_t seen_bit;  // bit in seen[gid]
-  int32_t alias;     // >= 0: this batch it equals accumulator `alias` (counts over null-free values); skip in the
-                     // row loop and add the alias' partial at flush time. -1 otherwise
-  int32_t pad;
+  int32_t alias;     // >= 0: this batch it equals accumulator `alias` (counts over null-free values); skipped in the
+                     // row loop, the alias' partial is added at flush time. -1 otherwise
 };
 struct AccPlan {
   AccK a[kMaxAcc];
   int32_t n;
   int32_t total_words;
-  uint32_t* seen;  // per-group bitmask of accumulators that saw a non-null input; nullptr = not tracked yet
+  uint32_t* seen;   // per-group bitmask of accumulators that saw a non-null input; nullptr = not tracked yet
+  uint64_t* acc;    // GroupTable::acc
+  uint32_t stride;  // GroupTable::acc_stride
+  uint32_t pad;
 };
 
 // ---- host-side logical description (independent of any batch) -----------------------------------------------------
@@ -153,7 +161,6 @@ struct JitArgs {
   const int32_t* aux[kJitSlots];
   const uint8_t* valid[kJitSlots];
   GroupTable t;
-  uint64_t* acc_out[kJitAcc];
   uint32_t* seen;
   uint64_t* scratch;
   uint32_t* gids;

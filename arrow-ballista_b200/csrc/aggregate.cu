@@ -179,6 +179,14 @@ static int agg_create_impl(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema
       for (int k = 0; k < 2; k++)
         if (a.phys[k] >= 0) a.phys[k] = pnew[(size_t)a.phys[k]];
   }
+  {  // accumulator record layout (array of structs): i128 accumulators on 16-byte boundaries
+    int32_t off = 0;
+    for (PhysAcc& p : g->phys)
+      if (p.words == 2) { p.out_off = off; off += 2; }
+    for (PhysAcc& p : g->phys)
+      if (p.words == 1) { p.out_off = off; off += 1; }
+    g->acc_stride = (uint32_t)std::max(1, (off + 1) & ~1);
+  }
   if (!plan_only) {
     BGPU_TRY(dev_alloc(ctx, 32, &g->counters));
     BGPU_CUDA(ctx, cudaMemsetAsync(g->counters->p, 0, 32, ctx->stream));
@@ -276,7 +284,7 @@ extern "C" int bgpu_agg_debug_compile(bgpu_ctx* ctx, int32_t mode, const struct 
   }
   sh.W = w;
   sh.has_seen = flags & 4;
-  sh.T = threads; sh.R = rows_per_thread; sh.min_ctas = min_ctas; sh.kernels = 3;
+  sh.T = threads; sh.R = rows_per_thread; sh.min_ctas = min_ctas; sh.kernels = 7;
   std::string src, cubin;
   BGPU_TRY(agg_generate_source(g.get(), sh, &src));
   src = std::string(agg_jit_prelude()) + src;

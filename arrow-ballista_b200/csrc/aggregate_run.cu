@@ -11,6 +11,7 @@
 // star's 1e-9 tolerance (the fused path is reproducible run to run, the atomic path is not).
 #include <stdio.h>
 #include <stdlib.h>
+#include <math.h>
 #include <string.h>
 
 #include <algorithm>
@@ -44,36 +45,27 @@ bool same_shape(const Column& a, const Column& b) { return a.kind == b.kind && a
 
 int agg_resize(bgpu_agg* g, uint32_t new_max, uint32_t keep) {
   bgpu_ctx* ctx = g->ctx;
-  DevAllocPtr entries, key0, key1, kmeta, seen;
-  BGPU_TRY(dev_alloc(ctx, (size_t)new_max * 2 * 8, &entries));
-  BGPU_TRY(dev_alloc(ctx, (size_t)new_max * 8, &key0));
-  if (g->key_words > 1) BGPU_TRY(dev_alloc(ctx, (size_t)new_max * 8, &key1));
-  BGPU_TRY(dev_alloc(ctx, (size_t)new_max * 4, &kmeta));
-  BGPU_CUDA(ctx, cudaMemsetAsync(entries->p, 0, (size_t)new_max * 2 * 8, ctx->stream));
-  if (keep) {
-    BGPU_CUDA(ctx, cudaMemcpyAsync(key0->p, g->key0->p, (size_t)keep * 8, cudaMemcpyDeviceToDevice, ctx->stream));
-    if (key1) BGPU_CUDA(ctx, cudaMemcpyAsync(key1->p, g->key1->p, (size_t)keep * 8, cudaMemcpyDeviceToDevice, ctx->stream));
-    BGPU_CUDA(ctx, cudaMemcpyAsync(kmeta->p, g->kmeta->p, (size_t)keep * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-  }
-  for (PhysAcc& p : g->phys) {
-    DevAllocPtr nb;
-    const size_t bytes = (size_t)new_max * p.words * 8;
-    BGPU_TRY(dev_alloc(ctx, bytes, &nb));
-    const size_t keep_bytes = (size_t)keep * p.words * 8;
-    if (keep) BGPU_CUDA(ctx, cudaMemcpyAsync(nb->p, p.buf->p, keep_bytes, cudaMemcpyDeviceToDevice, ctx->stream));
-    BGPU_CUDA(ctx, cudaMemsetAsync((char*)nb->p + keep_bytes, 0, bytes - keep_bytes, ctx->stream));
-    p.buf = nb;
-  }
+  const size_t slot_bytes = g->key_words == 1 ? 16 : 32;
+  DevAllocPtr slots, acc, seen;
+  BGPU_TRY(dev_alloc(ctx, (size_t)new_max * 2 * slot_bytes, &slots));
+  BGPU_CUDA(ctx, cudaMemsetAsync(slots->p, 0, (size_t)new_max * 2 * slot_bytes, ctx->stream));
+  const size_t rec = (size_t)g->acc_stride * 8, keep_bytes = (size_t)keep * rec;
+  BGPU_TRY(dev_alloc(ctx, (size_t)new_max * rec, &acc));
+  if (keep) BGPU_CUDA(ctx, cudaMemcpyAsync(acc->p, g->acc->p, keep_bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+  BGPU_CUDA(ctx, cudaMemsetAsync((char*)acc->p + keep_bytes, 0, (size_t)new_max * rec - keep_bytes, ctx->stream));
   if (g->seen_tracking) {
     BGPU_TRY(dev_alloc(ctx, (size_t)new_max * 4, &seen));
     if (keep) BGPU_CUDA(ctx, cudaMemcpyAsync(seen->p, g->seen->p, (size_t)keep * 4, cudaMemcpyDeviceToDevice, ctx->stream));
     BGPU_CUDA(ctx, cudaMemsetAsync((char*)seen->p + (size_t)keep * 4, 0, (size_t)(new_max - keep) * 4, ctx->stream));
     g->seen = seen;
   }
-  g->entries = entries; g->key0 = key0; g->key1 = key1; g->kmeta = kmeta;
+  DevAllocPtr old_slots = g->slots;
+  const uint32_t old_capacity = g->max_groups * 2;
+  g->slots = slots; g->acc = acc;
   g->max_groups = new_max;
   if (keep) {
-    rehash_kernel<<<agg_launch_grid(ctx, keep, kAggThreads), kAggThreads, 0, ctx->stream>>>(g->table(), keep, g->key_words);
+    rehash_kernel<<<agg_launch_grid(ctx, old_capacity, kAggThreads), kAggThreads, 0, ctx->stream>>>(
+        (const uint64_t*)old_slots->p, old_capacity, keep, g->table());
     ctx->launches++;
     BGPU_CUDA(ctx, cudaGetLastError());
   }
@@ -274,7 +266,7 @@ struct Bound {
   AccPlan ap{};
   const JitModule* mod = nullptr;
 };
-enum JitKernel : int { JK_FUSED = 0, JK_INTERN = 0, JK_ACC_SHARED = 1, JK_ACC_GLOBAL = 2 };  // index into the module of its kind
+enum JitKernel : int { JK_FUSED = 0, JK_INTERN = 0, JK_ACC_SHARED = 1, JK_ACC_GLOBAL = 2, JK_SKETCH = 3 };  // index into the module of its kind
 
 static int bind_value_atom(bgpu_ctx* ctx, const bgpu_batch* batch, const HAtom& h, Bound* b, bool* nullable) {
   if (!h.is_col) return BGPU_OK;
@@ -348,7 +340,7 @@ static int bind_batch(bgpu_agg* g, const bgpu_batch* batch, Bound* b) {
   for (int32_t i = 0; i < b->ap.n; i++) {
     const PhysAcc& p = g->phys[(size_t)i];
     AccK& a = b->ap.a[i];
-    a = AccK{(uint64_t*)p.buf->p, p.op, p.words, 0, i, -1, 0};
+    a = AccK{p.out_off, p.op, p.words, 0, i, -1};
     if (p.op == OP_COUNT && !b->sh.value_nullable[(size_t)p.value]) {
       if (first_count < 0) first_count = i;
       else a.alias = first_count;
@@ -367,16 +359,14 @@ static int bind_batch(bgpu_agg* g, const bgpu_batch* batch, Bound* b) {
 
 // accumulator / seen arrays and the table move when the table grows
 static void refresh_pointers(bgpu_agg* g, Bound* b) {
-  for (int32_t i = 0; i < b->ap.n; i++) {
-    b->ap.a[i].out = (uint64_t*)g->phys[(size_t)i].buf->p;
-    b->args.acc_out[i] = b->ap.a[i].out;
-  }
   b->ap.seen = g->seen_tracking ? (uint32_t*)g->seen->p : nullptr;
+  b->ap.acc = (uint64_t*)g->acc->p;
+  b->ap.stride = g->acc_stride;
   b->args.seen = b->ap.seen;
   b->args.t = g->table();
 }
 
-// Generate + compile (cached) the fused kernel (kernels = 1) or the two-pass kernels (kernels = 2) for this batch
+// Generate + compile (cached) the fused kernel (kernels = 1 private, 4 shared-atomic) or the two-pass kernels (2) for this batch
 // shape at the given launch geometry. b->mod->fn is indexed by JitKernel.
 static int specialise(bgpu_agg* g, Bound* b, int kernels, int T, int R, int min_ctas) {
   b->sh.T = T; b->sh.R = R; b->sh.min_ctas = min_ctas; b->sh.kernels = kernels;
@@ -385,8 +375,9 @@ static int specialise(bgpu_agg* g, Bound* b, int kernels, int T, int R, int min_
   BGPU_TRY(agg_generate_source(g, b->sh, &src));
   auto it = g->modules.find(src);
   if (it != g->modules.end()) { b->mod = it->second; return BGPU_OK; }
-  static const std::vector<std::string> fused{"bgpu_fused"}, two_pass{"bgpu_intern", "bgpu_acc_shared", "bgpu_acc_global"};
-  BGPU_TRY(jit_compile(g->ctx, agg_jit_prelude(), src, kernels == 1 ? fused : two_pass, &b->mod));
+  static const std::vector<std::string> fused{"bgpu_fused"}, fused_shared{"bgpu_fused_shared"},
+      two_pass{"bgpu_intern", "bgpu_acc_shared", "bgpu_acc_global", "bgpu_sketch"};
+  BGPU_TRY(jit_compile(g->ctx, agg_jit_prelude(), src, kernels == 1 ? fused : kernels == 4 ? fused_shared : two_pass, &b->mod));
   g->modules.emplace(std::move(src), b->mod);
   return BGPU_OK;
 }
@@ -431,7 +422,9 @@ static int grow_after_overflow(bgpu_agg* g, uint32_t counter, int64_t batch_rows
   return agg_resize(g, new_max, keep);
 }
 
-struct Rung { int threads; int rows; int min_ctas; size_t smem_cap; const char* name; };
+// The single-pass ("fused") ladder. mode 0 = thread-private accumulators, mode 1 = replicated shared-memory
+// accumulators with 32-bit shared atomics.
+struct Rung { int mode; int threads; int rows; int min_ctas; const char* name; };
 
 // Try the fused ladder. *done = true when the batch has been committed.
 static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
@@ -440,27 +433,47 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
   const int W = b->sh.W;
   if (W == 0) { g->fused_rung = kFusedRungs; return BGPU_OK; }
   const size_t smem_max = ctx->smem_optin - 1024;
-  // Thread-private accumulators cost G * W * 8 bytes of shared memory per thread, so shared memory (not registers)
-  // bounds the threads per SM; one large CTA per SM with 2 rows per thread in flight measured best on B200 (Q1:
-  // 512x2 1.27 ms vs 256x4x2 1.59 ms per 60M rows). Lower rungs trade threads for private group capacity.
-  Rung rungs[kFusedRungs] = {{512, 2, 1, smem_max, "fused512"}, {256, 4, 1, smem_max, "fused256"}, {128, 8, 1, smem_max, "fused128"}};
+  // rung 0: thread-private accumulators cost G * W * 8 bytes of shared memory per THREAD, so shared memory (not
+  //   registers) bounds the threads per SM; one large CTA per SM with 2 rows per thread in flight measured best on
+  //   B200 (Q1: 512x2 1.27 ms vs 256x4x2 1.59 ms per 60M rows). Good for a handful of groups.
+  // rungs 1, 2: `replicas` copies of [G][W] per CTA (one per warp while they fit), native 32-bit shared atomics; the
+  //   accumulators no longer scale with the thread count, so hundreds to thousands of groups run at full residency.
+  // rung 3: as rung 2 without the per-CTA key cache (group ids straight from the global table, which is L2 resident at
+  //   this cardinality): all of shared memory holds accumulators, ~10^4 groups.
+  Rung rungs[kFusedRungs] = {{0, 512, 2, 1, "fused512"}, {1, 256, 4, 3, "fused_shared2"}, {1, 512, 2, 1, "fused_shared1"},
+                             {2, 512, 2, 1, "fused_shared0"}};
   if (const char* e = getenv("BGPU_FUSED_GEOMETRY")) {  // tuning knob: "threads,rows,ctas_per_sm" for the first rung
     int t = 0, r = 0, c = 0;
     if (sscanf(e, "%d,%d,%d", &t, &r, &c) == 3 && t >= 32 && t <= 1024 && t % 32 == 0 && r >= 1 && r <= 16 && c >= 1 && c <= 8)
-      rungs[0] = Rung{t, r, c, smem_max / (size_t)c - 1024, "fused512"};
+      rungs[0] = Rung{0, t, r, c, "fused512"};
   }
   while (g->fused_rung < kFusedRungs) {
     const Rung& rg = rungs[g->fused_rung];
     const int T = rg.threads;
-    // private capacity: largest G with G*W*T*8 + seen + key cache <= cap (cache = 2G slots rounded up, 24 B each)
-    uint32_t G = (uint32_t)(rg.smem_cap / ((size_t)W * T * 8 + 4 + 4 * 24));
-    if (G > 4096) G = 4096;
+    const size_t cap = smem_max / (size_t)rg.min_ctas - 1024;
+    // capacity G: largest with accumulators + seen + key cache (2G slots rounded up, 24 B each) <= cap
+    uint32_t G, replicas = 1;
+    if (rg.mode == 0) {
+      G = (uint32_t)(cap / ((size_t)W * T * 8 + 4 + 4 * 24));
+    } else if (rg.mode == 1) {
+      G = (uint32_t)(cap / ((size_t)W * 8 + 4 + 4 * 24));
+      if (rg.min_ctas > 1) G = std::min<uint32_t>(G, 1024);  // keep room for several replicas on the multi-CTA rung
+    } else {
+      G = (uint32_t)((cap - 64) / ((size_t)W * 8 + 4));
+    }
+    if (G > 32768) G = 32768;
     if (G < 1 || G < g->n_groups) { g->fused_rung++; continue; }
-    const uint32_t slots = std::max<uint32_t>(16, next_pow2((uint64_t)G * 2));
-    const size_t smem = (size_t)G * W * T * 8 + (size_t)((G + 1) & ~1u) * 4 + (size_t)slots * 24;
+    const uint32_t slots = rg.mode == 2 ? 0u : std::max<uint32_t>(16, next_pow2((uint64_t)G * 2));
+    const size_t fixed = (size_t)((G + 1) & ~1u) * 4 + (size_t)slots * 24;
+    if (rg.mode != 0) {
+      if (fixed + (size_t)G * W * 8 > cap) { g->fused_rung++; continue; }
+      replicas = (uint32_t)std::min<size_t>((size_t)T / 32, (cap - fixed) / ((size_t)G * W * 8));
+    }
+    const size_t smem = (size_t)G * W * 8 * (rg.mode == 0 ? (size_t)T : (size_t)replicas) + fixed;
     if (smem > smem_max) { g->fused_rung++; continue; }
-    BGPU_TRY(specialise(g, b, 1, T, rg.rows, rg.min_ctas));
+    BGPU_TRY(specialise(g, b, rg.mode == 0 ? 1 : 4, T, rg.rows, rg.min_ctas));
     const CUfunction fn = b->mod->fn[JK_FUSED];
+    b->args.replicas = replicas;
     BGPU_TRY(jit_set_max_smem(ctx, fn, smem));
     int occ = 1;
     BGPU_TRY(jit_occupancy(ctx, fn, T, smem, &occ));
@@ -516,10 +529,39 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
   bgpu_ctx* ctx = g->ctx;
   constexpr int T = 256, R = 4;
   BGPU_TRY(specialise(g, b, 2, T, R, 1));
+  const int64_t tiles = ceil_div64(n_rows, (int64_t)T * R);
+  // A batch with more rows than the table has room for may overflow it, and every overflow costs a full extra pass:
+  // estimate the batch's distinct keys first (linear counting over a bitmap, one cheap pass over the key columns)
+  // and size the table once.
+  if ((uint64_t)n_rows + g->n_groups > g->max_groups) {
+    const uint32_t words = next_pow2(std::max<uint64_t>(1024, std::min<uint64_t>((uint64_t)n_rows, 1ULL << 31) / 32));
+    DevAllocPtr bitmap, cnt;
+    BGPU_TRY(dev_alloc(ctx, (size_t)words * 4, &bitmap));
+    BGPU_TRY(dev_alloc(ctx, 16, &cnt));
+    BGPU_CUDA(ctx, cudaMemsetAsync(bitmap->p, 0, (size_t)words * 4, ctx->stream));
+    BGPU_CUDA(ctx, cudaMemsetAsync(cnt->p, 0, 16, ctx->stream));
+    refresh_pointers(g, b);
+    b->args.gids = (uint32_t*)bitmap->p;
+    b->args.n_groups = words;
+    BGPU_TRY(jit_launch(ctx, b->mod->fn[JK_SKETCH], (int)std::min<int64_t>(tiles, (int64_t)ctx->sm_count * 8), T, 0, &b->args));
+    popcount_kernel<<<agg_launch_grid(ctx, words, kAggThreads), kAggThreads, 0, ctx->stream>>>((const uint32_t*)bitmap->p, words,
+                                                                                         (unsigned long long*)cnt->p);
+    ctx->launches++;
+    unsigned long long* pin = (unsigned long long*)ctx->pinned + 8;
+    BGPU_CUDA(ctx, cudaMemcpyAsync(pin, cnt->p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const double m = (double)words * 32.0, set = (double)*pin;
+    // linear counting: distinct ~ -m ln(zero fraction); a saturated bitmap means "at least as many as rows"
+    const double est = set >= m ? (double)n_rows : std::min<double>((double)n_rows, -m * log(1.0 - set / m));
+    const uint64_t need = (uint64_t)g->n_groups + (uint64_t)(est * 1.10) + 1024;
+    if (need > g->max_groups) {
+      if (need > 0x70000000ULL) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
+      BGPU_TRY(agg_resize(g, next_pow2(need), g->n_groups));
+    }
+  }
   DevAllocPtr gids;
   BGPU_TRY(dev_alloc(ctx, (size_t)n_rows * 4, &gids));
   b->args.gids = (uint32_t*)gids->p;
-  const int64_t tiles = ceil_div64(n_rows, (int64_t)T * R);
   for (int attempt = 0;; attempt++) {
     refresh_pointers(g, b);
     const int grid = (int)std::min<int64_t>(tiles, (int64_t)ctx->sm_count * 8);
@@ -619,9 +661,22 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
   std::unique_ptr<bgpu_batch> out(new bgpu_batch(ctx));
   out->n_rows = n;
   const int grid = agg_launch_grid(ctx, std::max<uint32_t>(n, 1), kAggThreads);
-  const uint64_t* key0 = (const uint64_t*)g->key0->p;
-  const uint64_t* key1 = g->key1 ? (const uint64_t*)g->key1->p : nullptr;
-  const uint32_t* kmeta = (const uint32_t*)g->kmeta->p;
+  // dense key arrays (index = group id) out of the table slots
+  DevAllocPtr d_key0, d_key1, d_kmeta;
+  BGPU_TRY(dev_alloc(ctx, (size_t)std::max<uint32_t>(n, 1) * 8, &d_key0));
+  if (g->key_words > 1) BGPU_TRY(dev_alloc(ctx, (size_t)std::max<uint32_t>(n, 1) * 8, &d_key1));
+  BGPU_TRY(dev_alloc(ctx, (size_t)std::max<uint32_t>(n, 1) * 4, &d_kmeta));
+  const uint64_t* key0 = (const uint64_t*)d_key0->p;
+  const uint64_t* key1 = d_key1 ? (const uint64_t*)d_key1->p : nullptr;
+  const uint32_t* kmeta = (const uint32_t*)d_kmeta->p;
+  if (n) {
+    bgpu::GroupTable t = g->table();
+    t.max_groups = n;  // ids handed out by a void (overflowed) pass are not groups
+    densify_keys_kernel<<<agg_launch_grid(ctx, (int64_t)g->max_groups * 2, kAggThreads), kAggThreads, 0, ctx->stream>>>(
+        t, (uint64_t*)d_key0->p, d_key1 ? (uint64_t*)d_key1->p : nullptr, (uint32_t*)d_kmeta->p);
+    ctx->launches++;
+    BGPU_CUDA(ctx, cudaGetLastError());
+  }
   // group key columns
   for (size_t i = 0; i < g->group_cols.size(); i++) {
     const Column& f = g->fields[(size_t)g->group_cols[i]];
@@ -677,8 +732,17 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
                         Column* c) -> int {
     const PhysAcc& p = g->phys[(size_t)phys_idx];
     c->name = name; c->format = format; c->flags = ARROW_FLAG_NULLABLE; c->kind = K_FIXED; c->width = p.words * 8;
-    c->length = n; c->null_count = 0; c->values = p.buf->p;
-    c->owned.push_back(p.buf);  // accumulators are dense arrays: they are the Arrow buffer
+    c->length = n; c->null_count = 0;
+    DevAllocPtr vals;  // the accumulator's word(s) of every group record -> a dense Arrow values buffer
+    BGPU_TRY(dev_alloc(ctx, (size_t)std::max<uint32_t>(n, 1) * p.words * 8, &vals));
+    if (n) {
+      extract_acc_kernel<<<grid, kAggThreads, 0, ctx->stream>>>((const uint64_t*)g->acc->p, g->acc_stride, p.out_off, p.words, n,
+                                                                (uint64_t*)vals->p);
+      ctx->launches++;
+      BGPU_CUDA(ctx, cudaGetLastError());
+    }
+    c->values = vals->p;
+    c->owned.push_back(vals);
     if (nullable_by_seen) BGPU_TRY(emit_validity(g, phys_idx, n, c));
     return BGPU_OK;
   };
@@ -707,7 +771,7 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
       BGPU_TRY(dev_alloc(ctx, (size_t)ceil_div64(std::max<uint32_t>(n, 1), 32) * 4, &valid));
       if (n) {
         avg_evaluate_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(
-            (const uint64_t*)g->phys[(size_t)a.phys[1]].buf->p, (const uint64_t*)g->phys[(size_t)a.phys[0]].buf->p, n,
+            (const uint64_t*)g->acc->p, g->acc_stride, g->phys[(size_t)a.phys[1]].out_off, g->phys[(size_t)a.phys[0]].out_off, n,
             a.decimal ? 1 : 0, a.scale_up, (uint64_t*)vals->p, (uint32_t*)valid->p, g->d_flags());
         ctx->launches++;
         BGPU_CUDA(ctx, cudaGetLastError());
