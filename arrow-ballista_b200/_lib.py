@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbgpu.so")
+LIB_PATH = os.environ.get("BGPU_LIB") or os.path.join(_HERE, "libbgpu.so")  # BGPU_LIB: tuning builds only
 
 BGPU_OK, BGPU_EINVAL, BGPU_EUNSUPPORTED, BGPU_ECUDA, BGPU_ENODEVICE, BGPU_EOVERFLOW, BGPU_ENCCL = range(7)
 _ERR_NAMES = {1: "EINVAL", 2: "EUNSUPPORTED", 3: "ECUDA", 4: "ENODEVICE", 5: "EOVERFLOW", 6: "ENCCL"}

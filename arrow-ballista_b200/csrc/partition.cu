@@ -19,9 +19,14 @@
 
 namespace bgpu {
 
-constexpr int kThreads = 256;
+#ifndef BGPU_PART_THREADS
+#define BGPU_PART_THREADS 256
+#define BGPU_PART_ITEMS 16
+#define BGPU_PART_MIN_CTAS 3
+#endif
+constexpr int kThreads = BGPU_PART_THREADS;
 constexpr int kWarps = kThreads / 32;
-constexpr int kItems = 16;
+constexpr int kItems = BGPU_PART_ITEMS;
 constexpr int kTile = kThreads * kItems;  // 4096 rows
 constexpr uint32_t kMaxPartitions = 2048;
 
@@ -161,7 +166,7 @@ __device__ __forceinline__ void scatter_bits(const uint8_t* __restrict__ in, uin
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, BGPU_PART_MIN_CTAS)
     scatter_kernel(const __grid_constant__ KeySet ks, const __grid_constant__ Modulo mod,
                    const __grid_constant__ ScatterArgs args, int64_t n_rows, int64_t chunk_rows,
                    const uint64_t* __restrict__ base /* [n][gridDim.x] */) {
