@@ -264,6 +264,7 @@ struct Gen {
   void key() {
     o.line("  static __device__ __forceinline__ PackedKey key(const JitArgs& a, const Raw& x) {");
     o.line("    PackedKey k{0, 0, 0};");
+    o.line("    bool too_long = false;  // a string key beyond its packed width: the pass is void (flags[1])");
     for (size_t ki = 0; ki < sh.key_slot.size(); ki++) {
       const size_t s = (size_t)sh.key_slot[ki];
       const JitSlot& sl = sh.slots[s];
@@ -283,7 +284,7 @@ struct Gen {
                    word.c_str(), s, shift);
           break;
         default:
-          snprintf(buf, sizeof buf, "if (x.l%zu > %d) atomicOr(&a.t.flags[1], 1); str_field<%d, %d>(a.col[%zu], x.b%zu, x.l%zu, x.w%zu, k.k0, k.k1);",
+          snprintf(buf, sizeof buf, "too_long |= x.l%zu > %d; str_field<%d, %d>(a.col[%zu], x.b%zu, x.l%zu, x.w%zu, k.k0, k.k1);",
                    s, width, off, width, s, s, s, s);
           break;
       }
@@ -291,6 +292,7 @@ struct Gen {
       if (sl.nullable) o.fmt("    if (!x.v%zu) k.meta |= %uu; else { %s }", s, 1u << ki, body.c_str());
       else o.fmt("    { %s }", body.c_str());
     }
+    o.line("    if (too_long) atomicOr(&a.t.flags[1], 1);");
     o.line("    return k;");
     o.line("  }");
   }
@@ -408,6 +410,21 @@ int agg_generate_source(const bgpu_agg* g, const JitShape& sh, std::string* out)
   o.fmt("  static constexpr int T = %d, R = %d, W = %d, KEY_WORDS = %d, MIN_CTAS = %d;", sh.T, sh.R, sh.W, g->key_words, sh.min_ctas);
   o.fmt("  static constexpr bool HAS_SEEN = %s;", sh.has_seen ? "true" : "false");
   o.fmt("  static constexpr bool L2_PREFETCH = %s;", getenv("BGPU_L2_PREFETCH") ? "true" : "false");
+  // one row per thread and tile: run the three-stage load pipeline (fused_body)
+  const char* pipe = getenv("BGPU_FUSED_PIPE");
+  o.fmt("  static constexpr bool PIPE = %s;", (pipe ? atoi(pipe) != 0 : sh.R == 1) ? "true" : "false");
+  {  // thread-private layout of the fused kernel (PrivateSink): u64 slot and, for i128 sums, i32 high-word slot
+    std::string p8 = "0", p4 = "0";
+    int n8 = 0, n4 = 0;
+    for (size_t ai = 0; ai < g->phys.size(); ai++) {
+      if (sh.acc_alias[ai] >= 0) continue;
+      p8 = "w == " + std::to_string(sh.acc_word0[ai]) + " ? " + std::to_string(n8++) + " : " + p8;
+      if (g->phys[ai].words == 2) p4 = "w == " + std::to_string(sh.acc_word0[ai]) + " ? " + std::to_string(n4++) + " : " + p4;
+    }
+    o.fmt("  static constexpr int P8 = %d, P4 = %d, PRIV_WORDS = %d;", n8, n4, n8 + (n4 + 1) / 2);
+    o.fmt("  static __device__ constexpr int p8_of(int w) { return %s; }", p8.c_str());
+    o.fmt("  static __device__ constexpr int p4_of(int w) { return %s; }", p4.c_str());
+  }
   gen.raw_struct();
   gen.load0();
   gen.prefetch();

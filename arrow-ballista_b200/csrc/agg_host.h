@@ -48,6 +48,7 @@ struct bgpu_agg {
   uint32_t acc_stride = 1;
   bool seen_tracking = false;
   int fused_rung = 0;  // first rung of the fused ladder still worth trying; kFusedRungs = two-pass only
+  uint32_t private_gcap = 4;  // groups per thread the private rung starts with (doubles when a batch needs more)
   // dictionary-typed group columns are keyed by value: the aggregate keeps one canonical dictionary per column
   // (host copy; uploaded at emit) and maps every batch dictionary onto it
   struct DictState {
@@ -64,7 +65,7 @@ struct bgpu_agg {
   // and launch geometry; the modules themselves live in jit.cu's process-wide cache)
   std::map<std::string, const bgpu::JitModule*> modules;
   bool emitted = false;
-  // introspection for tests / bench: which path the last update took ("fused512", "fused_shared2", "fused_shared1",
+  // introspection for tests / bench: which path the last update took ("fused_private", "fused_shared2", "fused_shared1",
   // "shared", "global")
   std::string last_path;
   // device time of the fused kernel launches so far (CUDA events on the ctx stream): bench.py's roofline numerator

@@ -171,26 +171,28 @@ __device__ __forceinline__ Val zext(uint64_t v) { return Val{v, 0}; }
 __device__ __forceinline__ double as_f64(uint64_t b) { return __longlong_as_double((long long)b); }
 __device__ __forceinline__ uint64_t f64_bits(double d) { return (uint64_t)__double_as_longlong(d); }
 
-__device__ __forceinline__ Val i128_neg(Val a) {
+// 128-bit add / subtract as one carry chain (add.cc / addc): four 32-bit adds in SASS, no compare-and-select
+__device__ __forceinline__ Val add128(Val a, Val b) {
   Val r;
-  r.lo = ~a.lo + 1;
-  r.hi = ~a.hi + (r.lo == 0);
+  asm("add.cc.u64 %0, %2, %4;\n\taddc.u64 %1, %3, %5;" : "=l"(r.lo), "=l"(r.hi) : "l"(a.lo), "l"(a.hi), "l"(b.lo), "l"(b.hi));
   return r;
 }
+__device__ __forceinline__ Val sub128(Val a, Val b) {
+  Val r;
+  asm("sub.cc.u64 %0, %2, %4;\n\tsubc.u64 %1, %3, %5;" : "=l"(r.lo), "=l"(r.hi) : "l"(a.lo), "l"(a.hi), "l"(b.lo), "l"(b.hi));
+  return r;
+}
+__device__ __forceinline__ Val i128_neg(Val a) { return sub128(Val{0, 0}, a); }
 __device__ __forceinline__ bool i128_is_neg(Val a) { return (int64_t)a.hi < 0; }
 __device__ __forceinline__ bool fits_i64(Val a) { return a.hi == (uint64_t)((int64_t)a.lo >> 63); }
 // checked add/sub: *ovf is set on signed overflow (arrow-arith add_checked / sub_checked on i128)
 __device__ __forceinline__ Val i128_add_checked(Val a, Val b, bool* ovf) {
-  Val r;
-  r.lo = a.lo + b.lo;
-  r.hi = a.hi + b.hi + (r.lo < a.lo);
+  const Val r = add128(a, b);
   if ((~(a.hi ^ b.hi) & (a.hi ^ r.hi)) >> 63) *ovf = true;
   return r;
 }
 __device__ __forceinline__ Val i128_sub_checked(Val a, Val b, bool* ovf) {
-  Val r;
-  r.lo = a.lo - b.lo;
-  r.hi = a.hi - b.hi - (a.lo < b.lo);
+  const Val r = sub128(a, b);
   if (((a.hi ^ b.hi) & (a.hi ^ r.hi)) >> 63) *ovf = true;
   return r;
 }
@@ -218,9 +220,18 @@ __device__ __noinline__ ValOvf i128_mul_slow(Val a, Val b) {
   }
   return ValOvf{r, ok ? 0u : 1u};
 }
-// checked multiply with the common case inline: both operands fit i64 -> one signed 64x64->128 product, which
-// cannot overflow i128
+// checked multiply with the common cases inline: both operands fit i32, or both fit i64 (one signed 64x64->128
+// product, which cannot overflow i128)
 __device__ __forceinline__ Val i128_mul_checked(Val a, Val b, bool* ovf) {
+  {  // both operands fit i32 (prices x percentages): a single 32x32->64 multiply
+    const uint32_t sa = (uint32_t)((int32_t)(uint32_t)a.lo >> 31), sb = (uint32_t)((int32_t)(uint32_t)b.lo >> 31);
+    const uint32_t wide = (((uint32_t)(a.lo >> 32) ^ sa) | ((uint32_t)a.hi ^ sa) | ((uint32_t)(a.hi >> 32) ^ sa)) |
+                          (((uint32_t)(b.lo >> 32) ^ sb) | ((uint32_t)b.hi ^ sb) | ((uint32_t)(b.hi >> 32) ^ sb));
+    if (wide == 0) {
+      const int64_t p = (int64_t)(int32_t)(uint32_t)a.lo * (int64_t)(int32_t)(uint32_t)b.lo;
+      return Val{(uint64_t)p, (uint64_t)(p >> 63)};
+    }
+  }
   if (fits_i64(a) && fits_i64(b)) return Val{a.lo * b.lo, (uint64_t)__mul64hi((int64_t)a.lo, (int64_t)b.lo)};
   const ValOvf r = i128_mul_slow(a, b);
   if (r.ovf) *ovf = true;
@@ -275,20 +286,34 @@ __device__ __forceinline__ void str_field(const void* data, int32_t b, int32_t l
 }
 
 // ---- accumulator sinks: where Plan::accumulate sends each (accumulator, value) ---------------------------------------
-// thread-private slots in shared memory: word w of group g of thread t lives at s_acc[(g * W + w) * T + t]
-template <int T>
+// Thread-private accumulators in shared memory. Group g owns Plan::PRIV_WORDS * T u64 words:
+//   [P8][T] u64   one per live accumulator: the whole value of a one-word accumulator, the LOW word of an i128 sum
+//   [P4][T] i32   per i128 sum: the thread's running high-word contribution (value.hi + carry per row: 0 or -1 +- 1
+//                 for in-range decimals). A contribution beyond 16 bits goes to the CTA-wide u64 spill word instead, so
+//                 with at most 65535 rows per thread (the host sizes the grid for it) the i32 cannot wrap.
+// 12 instead of 16 bytes per i128 sum is what lets 640 threads x 5 groups of TPC-H Q1 fit one SM.
+template <class Plan>
 struct PrivateSink {
   static constexpr bool kSkipAliased = true;
-  uint64_t* base;  // &s_acc[g * W * T + threadIdx.x]
+  uint64_t* base;   // &s_acc[g * PRIV_WORDS * T]
+  uint64_t* spill;  // &s_spill[g * P4]
   template <int OP, int WORD0, int IDX, int OUT>
   __device__ __forceinline__ void add(const JitArgs&, Val v) {
-    uint64_t* p = base + WORD0 * T;
+    constexpr int T = Plan::T;
+    uint64_t* p = base + Plan::p8_of(WORD0) * T + threadIdx.x;
     if (OP == OP_ADD_F64) {
       *(double*)p += as_f64(v.lo);
     } else if (OP == OP_ADD_I128) {
-      const uint64_t old = p[0], lo = old + v.lo;
-      p[0] = lo;
-      p[T] += v.hi + (lo < old);
+      const Val sum = add128(Val{*p, 0}, v);  // sum.hi = v.hi + carry
+      *p = sum.lo;
+      if (sum.hi != 0) {
+        if (sum.hi + 0x8000ULL < 0x10000ULL) {
+          uint32_t* ph = (uint32_t*)(base + Plan::P8 * T) + Plan::p4_of(WORD0) * T + threadIdx.x;
+          *ph += (uint32_t)sum.hi;
+        } else {
+          atomicAdd((unsigned long long*)(spill + Plan::p4_of(WORD0)), (unsigned long long)sum.hi);
+        }
+      }
     } else if (OP == OP_COUNT) {
       p[0] += 1;
     } else {
@@ -401,9 +426,7 @@ __device__ __forceinline__ Val warp_sum_u128(Val v) {
   for (int d = 16; d > 0; d >>= 1) {
     const uint64_t lo = __shfl_down_sync(0xffffffffu, v.lo, d);
     const uint64_t hi = __shfl_down_sync(0xffffffffu, v.hi, d);
-    const uint64_t s = v.lo + lo;
-    v.hi += hi + (s < lo);
-    v.lo = s;
+    v = add128(v, Val{lo, hi});
   }
   return v;
 }
@@ -418,18 +441,19 @@ __host__ __device__ __forceinline__ size_t fused_slab_words(uint32_t g_cap, int 
 }
 
 // fused path: reduce the T private copies of one accumulator of every group into the CTA's slab (one warp per group)
-template <int T>
+template <class Plan>
 struct FlushPrivate {
   const uint64_t* s_acc;
+  const uint64_t* s_spill;
   uint64_t* slab;
   uint32_t G;
-  int W;
   template <int OP, int WORD0, int WORDS, int IDX, bool ALIASED, int OUT>
   __device__ __forceinline__ void acc() {
     if (ALIASED) return;
+    constexpr int T = Plan::T, W = Plan::W;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (uint32_t grp = warp; grp < G; grp += T / 32) {
-      const uint64_t* p = s_acc + ((size_t)grp * W + WORD0) * T;
+      const uint64_t* p = s_acc + ((size_t)grp * Plan::PRIV_WORDS + Plan::p8_of(WORD0)) * T;
       uint64_t* o = slab + (size_t)grp * W + WORD0;
       if (OP == OP_ADD_F64) {
         double f = 0.0;
@@ -437,17 +461,17 @@ struct FlushPrivate {
         f = warp_sum_f64(f);
         if (lane == 0) o[0] = f64_bits(f);
       } else {
+        const int32_t* ph = (const int32_t*)(s_acc + ((size_t)grp * Plan::PRIV_WORDS + Plan::P8) * T) + Plan::p4_of(WORD0) * T;
         Val s{0, 0};
         for (int th = lane; th < T; th += 32) {
-          const uint64_t lo = p[th];
-          s.lo += lo;
-          s.hi += (s.lo < lo);
-          if (WORDS > 1) s.hi += p[T + th];
+          Val x{p[th], 0};
+          if (WORDS > 1) x.hi = (uint64_t)(int64_t)ph[th];
+          s = add128(s, x);
         }
         s = warp_sum_u128(s);
         if (lane == 0) {
           o[0] = s.lo;
-          if (WORDS > 1) o[1] = s.hi;
+          if (WORDS > 1) o[1] = s.hi + s_spill[(size_t)grp * Plan::P4 + Plan::p4_of(WORD0)];
         }
       }
     }
@@ -513,7 +537,10 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
   const uint32_t G = a.g_cap;
   const uint32_t copies = MODE == 0 ? (uint32_t)T : a.replicas;
   uint64_t* s_acc = smem;
-  uint32_t* s_seen = (uint32_t*)(s_acc + (size_t)G * W * copies);
+  // MODE 0: [G][PRIV_WORDS][T] thread-private words, then the high-word spill u64[G][P4]
+  const uint32_t acc_words = MODE == 0 ? G * (uint32_t)(Plan::PRIV_WORDS * T + Plan::P4) : G * W * copies;
+  uint64_t* s_spill = s_acc + (size_t)G * Plan::PRIV_WORDS * T;
+  uint32_t* s_seen = (uint32_t*)(s_acc + acc_words);
   KeyCache cache;
   {
     unsigned char* p = (unsigned char*)(s_seen + ((G + 1) & ~1u));
@@ -524,7 +551,7 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
     cache.mask = a.cache_slots - 1;
   }
   __shared__ int s_abort;
-  for (uint32_t i = threadIdx.x; i < G * W * copies; i += T) s_acc[i] = 0;
+  for (uint32_t i = threadIdx.x; i < acc_words; i += T) s_acc[i] = 0;
   for (uint32_t i = threadIdx.x; i < G; i += T) s_seen[i] = 0;
   for (uint32_t i = threadIdx.x; i < a.cache_slots; i += T) cache.state[i] = 0;
   if (threadIdx.x == 0) s_abort = 0;
@@ -538,53 +565,87 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
   //   tile i+1: bulk L2 prefetch of every streamed buffer; its "early" loads (utf8 offsets, remapped dictionary keys)
   //             are issued into registers while tile i is processed
   //   tile i:   all remaining loads are issued back to back (phase 1), then consumed (phase 2)
-  typename Plan::Raw0 nx[R];
-  {
-    const int64_t base = (int64_t)blockIdx.x * tile;
-#pragma unroll
-    for (int u = 0; u < R; u++) {
-      const int64_t r = base + u * T + threadIdx.x;
-      Plan::template load0<7>(a, r < last ? r : last, nx[u]);
+  auto consume = [&](const typename Plan::Raw& xr, int64_t r) {
+    if (r > last || !Plan::filter(a, xr)) return;
+    const PackedKey k = Plan::key(a, xr);
+    // cache_slots == 0: no per-CTA key cache (all of shared memory holds accumulators; the table is L2 resident)
+    const uint32_t gid = (MODE != 0 && a.cache_slots == 0) ? intern<KW>(a.t, k) : cached_intern<KW>(cache, a.t, k);
+    if (gid >= G) { s_abort = 1; return; }  // beyond the private capacity (or the global table overflowed)
+    uint32_t seen;
+    if (MODE == 0) {
+      PrivateSink<Plan> sink{s_acc + (size_t)gid * Plan::PRIV_WORDS * T, s_spill + (size_t)gid * Plan::P4};
+      seen = Plan::accumulate(a, xr, sink, &ovf);
+    } else {
+      SharedSplitSink sink{s_acc + ((size_t)rep * G + gid) * W};
+      seen = Plan::accumulate(a, xr, sink, &ovf);
     }
-  }
-  for (int64_t base = (int64_t)blockIdx.x * tile; base < a.n_rows; base += stride) {
-    typename Plan::Raw x[R];
-    const int64_t next = base + stride;
-    if (Plan::L2_PREFETCH && next < a.n_rows)
-      Plan::template prefetch_l2<7>(a, next, next + tile <= a.n_rows ? tile : a.n_rows - next);
+    if (Plan::HAS_SEEN && seen) atomicOr(&s_seen[gid], seen);
+  };
+  const int64_t first = (int64_t)blockIdx.x * tile;
+  if (Plan::PIPE) {
+    // Three-stage pipeline: while tile i is consumed, every load of tile i+1 is in flight (issued from the early
+    // loads of tile i+1, which were requested one iteration ago) and the early loads of tile i+2 are requested.
+    typename Plan::Raw0 early[R];
+    typename Plan::Raw fly[R];
 #pragma unroll
     for (int u = 0; u < R; u++) {
-      const int64_t r = base + u * T + threadIdx.x;
-      static_cast<typename Plan::Raw0&>(x[u]) = nx[u];
-      Plan::template load1<7>(a, r < last ? r : last, x[u]);
-      Plan::template load2<7>(a, r < last ? r : last, x[u]);
+      const int64_t r = first + u * T + threadIdx.x;
+      Plan::template load0<7>(a, r < last ? r : last, early[u]);
     }
 #pragma unroll
     for (int u = 0; u < R; u++) {
-      const int64_t r = next + u * T + threadIdx.x;
-      Plan::template load0<7>(a, r < last ? r : last, nx[u]);
+      const int64_t r = first + u * T + threadIdx.x, rc = r < last ? r : last;
+      static_cast<typename Plan::Raw0&>(fly[u]) = early[u];
+      Plan::template load1<7>(a, rc, fly[u]);
+      Plan::template load2<7>(a, rc, fly[u]);
+      const int64_t r1 = r + stride;
+      Plan::template load0<7>(a, r1 < last ? r1 : last, early[u]);
     }
-    // phase 2
+    for (int64_t base = first; base < a.n_rows; base += stride) {
+      typename Plan::Raw x[R];
 #pragma unroll
-    for (int u = 0; u < R; u++) {
-      const int64_t r = base + u * T + threadIdx.x;
-      if (r > last || !Plan::filter(a, x[u])) continue;
-      const PackedKey k = Plan::key(a, x[u]);
-      // cache_slots == 0: no per-CTA key cache (all of shared memory holds accumulators; the table is L2 resident)
-      const uint32_t gid = (MODE != 0 && a.cache_slots == 0) ? intern<KW>(a.t, k) : cached_intern<KW>(cache, a.t, k);
-      if (gid >= G) { s_abort = 1; continue; }  // beyond the private capacity (or the global table overflowed)
-      uint32_t seen;
-      if (MODE == 0) {
-        PrivateSink<T> sink{s_acc + (size_t)gid * W * T + threadIdx.x};
-        seen = Plan::accumulate(a, x[u], sink, &ovf);
-      } else {
-        SharedSplitSink sink{s_acc + ((size_t)rep * G + gid) * W};
-        seen = Plan::accumulate(a, x[u], sink, &ovf);
+      for (int u = 0; u < R; u++) {
+        x[u] = fly[u];
+        const int64_t r1 = base + stride + u * T + threadIdx.x, rc = r1 < last ? r1 : last;
+        static_cast<typename Plan::Raw0&>(fly[u]) = early[u];
+        Plan::template load1<7>(a, rc, fly[u]);
+        Plan::template load2<7>(a, rc, fly[u]);
+        const int64_t r2 = r1 + stride;
+        Plan::template load0<7>(a, r2 < last ? r2 : last, early[u]);
       }
-      if (Plan::HAS_SEEN && seen) atomicOr(&s_seen[gid], seen);
+#pragma unroll
+      for (int u = 0; u < R; u++) consume(x[u], base + u * T + threadIdx.x);
+      if (*(volatile int*)&s_abort || ((++tiles_done & 15) == 0 && *(volatile int*)&a.t.flags[3])) break;
     }
-    // some CTA gave up: the pass is void (the global flag is polled every 16th tile: it only saves work)
-    if (*(volatile int*)&s_abort || ((++tiles_done & 15) == 0 && *(volatile int*)&a.t.flags[3])) break;
+  } else {
+    typename Plan::Raw0 nx[R];
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = first + u * T + threadIdx.x;
+      Plan::template load0<7>(a, r < last ? r : last, nx[u]);
+    }
+    for (int64_t base = first; base < a.n_rows; base += stride) {
+      typename Plan::Raw x[R];
+      const int64_t next = base + stride;
+      if (Plan::L2_PREFETCH && next < a.n_rows)
+        Plan::template prefetch_l2<7>(a, next, next + tile <= a.n_rows ? tile : a.n_rows - next);
+#pragma unroll
+      for (int u = 0; u < R; u++) {
+        const int64_t r = base + u * T + threadIdx.x;
+        static_cast<typename Plan::Raw0&>(x[u]) = nx[u];
+        Plan::template load1<7>(a, r < last ? r : last, x[u]);
+        Plan::template load2<7>(a, r < last ? r : last, x[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < R; u++) {
+        const int64_t r = next + u * T + threadIdx.x;
+        Plan::template load0<7>(a, r < last ? r : last, nx[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < R; u++) consume(x[u], base + u * T + threadIdx.x);
+      // some CTA gave up: the pass is void (the global flag is polled every 16th tile: it only saves work)
+      if (*(volatile int*)&s_abort || ((++tiles_done & 15) == 0 && *(volatile int*)&a.t.flags[3])) break;
+    }
   }
   if (ovf) atomicOr(&a.t.flags[2], 1);
   __syncthreads();
@@ -594,7 +655,7 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
   }
   uint64_t* slab = a.scratch + (size_t)blockIdx.x * fused_slab_words(G, W);
   if (MODE == 0) {
-    FlushPrivate<T> fl{s_acc, slab, G, W};
+    FlushPrivate<Plan> fl{s_acc, s_spill, slab, G};
     Plan::for_each_acc(fl);
   } else {
     FlushReplicas fl{s_acc, slab, G, a.replicas, W, T};

@@ -433,19 +433,20 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
   const int W = b->sh.W;
   if (W == 0) { g->fused_rung = kFusedRungs; return BGPU_OK; }
   const size_t smem_max = ctx->smem_optin - 1024;
-  // rung 0: thread-private accumulators cost G * W * 8 bytes of shared memory per THREAD, so shared memory (not
-  //   registers) bounds the threads per SM; one large CTA per SM with 2 rows per thread in flight measured best on
-  //   B200 (Q1: 512x2 1.27 ms vs 256x4x2 1.59 ms per 60M rows). Good for a handful of groups.
+  // rung 0: thread-private accumulators cost 8 bytes per live accumulator (+4 per i128 sum) per group and THREAD, so
+  //   shared memory and the register file together bound the threads per SM: 640 threads x 4 groups of Q1 fill one SM
+  //   at <= 96 registers. One row per thread and tile through the three-stage load pipeline measured best on B200
+  //   (Q1, 300M rows: 640x1 pipelined 4.76 ms, 640x2 4.96 ms, 512x2 6.6 ms, 768x2 (spills) 6.2 ms).
   // rungs 1, 2: `replicas` copies of [G][W] per CTA (one per warp while they fit), native 32-bit shared atomics; the
   //   accumulators no longer scale with the thread count, so hundreds to thousands of groups run at full residency.
   // rung 3: as rung 2 without the per-CTA key cache (group ids straight from the global table, which is L2 resident at
   //   this cardinality): all of shared memory holds accumulators, ~10^4 groups.
-  Rung rungs[kFusedRungs] = {{0, 512, 2, 1, "fused512"}, {1, 256, 4, 3, "fused_shared2"}, {1, 512, 2, 1, "fused_shared1"},
+  Rung rungs[kFusedRungs] = {{0, 640, 1, 1, "fused_private"}, {1, 256, 4, 3, "fused_shared2"}, {1, 512, 2, 1, "fused_shared1"},
                              {2, 512, 2, 1, "fused_shared0"}};
   if (const char* e = getenv("BGPU_FUSED_GEOMETRY")) {  // tuning knob: "threads,rows,ctas_per_sm" for the first rung
     int t = 0, r = 0, c = 0;
     if (sscanf(e, "%d,%d,%d", &t, &r, &c) == 3 && t >= 32 && t <= 1024 && t % 32 == 0 && r >= 1 && r <= 16 && c >= 1 && c <= 8)
-      rungs[0] = Rung{0, t, r, c, "fused512"};
+      rungs[0] = Rung{0, t, r, c, "fused_private"};
   }
   while (g->fused_rung < kFusedRungs) {
     const Rung& rg = rungs[g->fused_rung];
@@ -453,8 +454,19 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
     const size_t cap = smem_max / (size_t)rg.min_ctas - 1024;
     // capacity G: largest with accumulators + seen + key cache (2G slots rounded up, 24 B each) <= cap
     uint32_t G, replicas = 1;
+    // thread-private layout (PrivateSink): one u64 per live accumulator + one i32 per i128 sum, per thread; one u64
+    // spill word per i128 sum, per CTA
+    int n128 = 0;
+    for (int32_t i = 0; i < b->ap.n; i++) n128 += b->ap.a[i].alias < 0 && b->ap.a[i].words == 2;
+    const size_t priv_bytes = ((size_t)(W - n128) + (size_t)(n128 + 1) / 2) * 8 * T + (size_t)n128 * 8;
+    bool g_can_grow = false;
     if (rg.mode == 0) {
-      G = (uint32_t)(cap / ((size_t)W * T * 8 + 4 + 4 * 24));
+      // Shared memory not taken by accumulators stays L1 cache, which the overlapping utf8 window and offset loads
+      // live on (Q1: capacity 5 instead of 4 groups costs 30%): start small and grow on demand.
+      const uint32_t g_max = (uint32_t)(cap / (priv_bytes + 4 + 4 * 24));
+      G = std::min<uint32_t>(g_max, std::max<uint32_t>(g->private_gcap, g->n_groups));
+      if (const char* e = getenv("BGPU_FUSED_GCAP")) G = std::min<uint32_t>(g_max, std::max(1, atoi(e)));
+      g_can_grow = G < g_max;
     } else if (rg.mode == 1) {
       G = (uint32_t)(cap / ((size_t)W * 8 + 4 + 4 * 24));
       if (rg.min_ctas > 1) G = std::min<uint32_t>(G, 1024);  // keep room for several replicas on the multi-CTA rung
@@ -469,7 +481,7 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
       if (fixed + (size_t)G * W * 8 > cap) { g->fused_rung++; continue; }
       replicas = (uint32_t)std::min<size_t>((size_t)T / 32, (cap - fixed) / ((size_t)G * W * 8));
     }
-    const size_t smem = (size_t)G * W * 8 * (rg.mode == 0 ? (size_t)T : (size_t)replicas) + fixed;
+    const size_t smem = (rg.mode == 0 ? (size_t)G * priv_bytes : (size_t)G * W * 8 * replicas) + fixed;
     if (smem > smem_max) { g->fused_rung++; continue; }
     BGPU_TRY(specialise(g, b, rg.mode == 0 ? 1 : 4, T, rg.rows, rg.min_ctas));
     const CUfunction fn = b->mod->fn[JK_FUSED];
@@ -481,14 +493,17 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
     // several CTAs per SM slot: the hardware block scheduler then evens out the per-SM speed differences that a
     // one-wave persistent grid leaves as a 20% idle tail (ncu: SM active 77% of elapsed), at ~10 us of prologue +
     // flush per extra CTA
-    int waves = 4;
+    int waves = 8;
     if (const char* e = getenv("BGPU_FUSED_WAVES")) waves = std::max(1, atoi(e));
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ceil_div64(n_rows, (int64_t)T * rg.rows), (int64_t)ctx->sm_count * occ * waves));
+    // (the private i32 high words need at most 65535 rows per thread)
+    const int grid = (int)std::max<int64_t>(std::max<int64_t>(1, ceil_div64(n_rows, (int64_t)T * 65535)),
+                                            std::min<int64_t>(ceil_div64(n_rows, (int64_t)T * rg.rows), (int64_t)ctx->sm_count * occ * waves));
     const size_t scratch_bytes = (size_t)grid * fused_slab_words(G, W) * 8;
     if (!g->scratch || g->scratch->bytes < scratch_bytes) BGPU_TRY(dev_alloc(ctx, scratch_bytes, &g->scratch));
     b->args.scratch = (uint64_t*)g->scratch->p;
     b->args.g_cap = G;
     b->args.cache_slots = slots;
+    bool retry_rung = false;
     for (int attempt = 0;; attempt++) {
       refresh_pointers(g, b);
       BGPU_CUDA(ctx, cudaEventRecord(g->ev[0], ctx->stream));
@@ -508,6 +523,10 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
         h[4] = 0;
         BGPU_TRY(write_counters(g, h));
         g->n_groups = h[0];
+        if (g_can_grow) {  // same rung, more private groups
+          g->private_gcap = std::max<uint32_t>(2 * G, g->n_groups);
+          retry_rung = true;
+        }
         break;
       }
       g->n_groups = h[0];
@@ -520,7 +539,7 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
       *done = true;
       return BGPU_OK;
     }
-    g->fused_rung++;
+    if (!retry_rung) g->fused_rung++;
   }
   return BGPU_OK;
 }

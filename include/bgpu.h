@@ -166,7 +166,7 @@ int bgpu_agg_update(bgpu_agg* agg, const bgpu_batch* batch);
  * reference (GroupValues uses a randomly seeded table). The aggregate may not be updated afterwards. */
 int bgpu_agg_emit(bgpu_agg* agg, bgpu_batch** out);
 int64_t bgpu_agg_num_groups(bgpu_agg* agg); /* groups seen so far */
-/* which kernel path the last update took ("fused512", "fused_shared2", "fused_shared1", "shared", "global", "intern");
+/* which kernel path the last update took ("fused_private", "fused_shared2", "fused_shared1", "shared", "global", "intern");
  * introspection for tests and the bench, not part of the reference's interface */
 const char* bgpu_agg_last_path(const bgpu_agg* agg);
 /* device time (ms, CUDA events on the ctx stream) spent so far in this aggregate's single-pass fused kernel launches:

@@ -61,7 +61,7 @@ def test_q1_with_nulls(bb, ctx, oracle):
 
 def test_q1_one_large_batch(bb, ctx, oracle):
     rng = np.random.default_rng(5)
-    run_q1(bb, ctx, oracle, [lineitem_batch(rng, 200_000)], n_partials=1, expect_path="fused512")
+    run_q1(bb, ctx, oracle, [lineitem_batch(rng, 200_000)], n_partials=1, expect_path="fused_private")
 
 
 def test_filter_drops_everything(bb, ctx):
@@ -96,7 +96,7 @@ def test_unsupported_expression_shape(bb, ctx):
     assert e.value.code == 2  # BGPU_EUNSUPPORTED, no silent fallback
 
 
-@pytest.mark.parametrize("k,expect", [(4, "fused512"), (100, "fused_shared2"), (2000, "fused_shared1"), (200_000, "global")])
+@pytest.mark.parametrize("k,expect", [(4, "fused_private"), (100, "fused_shared2"), (2000, "fused_shared1"), (200_000, "global")])
 def test_ladder_by_cardinality(bb, ctx, oracle, k, expect):
     """db-benchmark q1 shape (sum(v1) by id4) at growing cardinality walks the ladder; results stay exact."""
     rng = np.random.default_rng(k)

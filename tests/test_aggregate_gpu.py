@@ -1,6 +1,8 @@
 """GPU parity: GpuAggregateExec (Partial, FinalPartitioned) against the oracle's GroupedHashAggregateStream
 restatement. Integer / Decimal128 sums, counts and decimal averages are bit-exact; Float64 within 1e-9 relative
 (the north star's tolerance — the reference's own float sum order is not deterministic)."""
+import decimal
+
 import numpy as np
 import pyarrow as pa
 import pyarrow.compute as pc
@@ -130,3 +132,22 @@ def test_empty_input(bb, ctx):
     agg.update(b)
     out = agg.emit().download()
     assert out.num_rows == 0 and out.schema.names == ["small", "s[sum]"]
+
+
+def test_wide_decimal_sums_few_groups(bb, ctx, oracle):
+    """i128 sums whose per-row high-word contribution is large, small-negative and zero, on the thread-private
+    single-pass kernel (the private high words are 32-bit with a 64-bit spill word per group)."""
+    rng = np.random.default_rng(23)
+    n = 50_000
+    mag = rng.choice([1, 10**9, 10**19, 10**25, 10**30], n)
+    vals = [int(m) * int(x) for m, x in zip(mag, rng.integers(-9999, 9999, n))]
+    b = pa.RecordBatch.from_arrays(
+        [pa.array(rng.integers(0, 3, n), type=pa.int64()),
+         pa.array([decimal.Decimal(v) for v in vals], type=pa.decimal128(38, 0)),
+         pa.array([decimal.Decimal(int(x)) for x in rng.integers(-5, 5, n)], type=pa.decimal128(10, 0))],
+        names=["k", "wide", "narrow"])
+    spec = [("sum", "wide", "sw"), ("sum", "narrow", "sn"), ("count", None, "c"), ("avg", "narrow", "an")]
+    out = run_both(bb, ctx, oracle, [b.slice(0, 30_000), b.slice(30_000)], ["k"], spec, 1)
+    got = dict(zip(out.column(0).to_pylist(), out.column(1).to_pylist()))
+    for k in range(3):
+        assert got[k] == decimal.Decimal(sum(v for v, kk in zip(vals, b.column(0).to_pylist()) if kk == k))
