@@ -157,7 +157,7 @@ struct Gen {
   }
 
   void load0() {
-    o.line("  template <int NEED> static __device__ __forceinline__ void load0(const JitArgs& a, int64_t r, Raw0& x) {");
+    o.line("  template <int NEED> static __device__ __forceinline__ void load0(const JitArgs& a, Row r, Raw0& x) {");
     for (size_t s = 0; s < sh.slots.size(); s++) {
       const JitSlot& sl = sh.slots[s];
       if (!early(sl)) continue;
@@ -191,7 +191,7 @@ struct Gen {
   }
 
   void load1() {
-    o.line("  template <int NEED> static __device__ __forceinline__ void load1(const JitArgs& a, int64_t r, Raw& x) {");
+    o.line("  template <int NEED> static __device__ __forceinline__ void load1(const JitArgs& a, Row r, Raw& x) {");
     for (size_t s = 0; s < sh.slots.size(); s++) {
       const JitSlot& sl = sh.slots[s];
       std::string any;
@@ -220,7 +220,7 @@ struct Gen {
   }
 
   void load2() {
-    o.line("  template <int NEED> static __device__ __forceinline__ void load2(const JitArgs& a, int64_t r, Raw& x) {");
+    o.line("  template <int NEED> static __device__ __forceinline__ void load2(const JitArgs& a, Row r, Raw& x) {");
     for (size_t ki = 0; ki < sh.key_slot.size(); ki++) {
       const size_t s = (size_t)sh.key_slot[ki];
       const JitSlot& sl = sh.slots[s];
@@ -409,6 +409,7 @@ int agg_generate_source(const bgpu_agg* g, const JitShape& sh, std::string* out)
   o.line("struct Plan {");
   o.fmt("  static constexpr int T = %d, R = %d, W = %d, KEY_WORDS = %d, MIN_CTAS = %d;", sh.T, sh.R, sh.W, g->key_words, sh.min_ctas);
   o.fmt("  static constexpr bool HAS_SEEN = %s;", sh.has_seen ? "true" : "false");
+  o.fmt("  typedef %s Row;  // row index type of the loads", sh.row32 ? "uint32_t" : "int64_t");
   o.fmt("  static constexpr bool L2_PREFETCH = %s;", getenv("BGPU_L2_PREFETCH") ? "true" : "false");
   // one row per thread and tile: run the three-stage load pipeline (fused_body)
   const char* pipe = getenv("BGPU_FUSED_PIPE");

@@ -110,6 +110,7 @@ struct JitShape {
   // bit 2 bgpu_fused_shared
   int32_t kernels = 3;
   bool any_validity = false;
+  bool row32 = false;                        // row indices fit 32 bits (with room for two grid strides past the end)
 };
 // slot of batch column `batch_col` (created on first use); -1 when the table is full
 int32_t jit_slot(JitShape* sh, int32_t batch_col);

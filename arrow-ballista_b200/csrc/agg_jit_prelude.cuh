@@ -125,34 +125,36 @@ __device__ __forceinline__ uint32_t intern(const GroupTable& t, const PackedKey&
 // Per-CTA cache of (key -> gid) in shared memory in front of the global table: low-cardinality inputs resolve
 // every row from shared memory after the first few rows of the CTA.
 struct KeyCache {
-  uint32_t* state;  // 0 empty, 1 busy, gid + 2
-  uint64_t* k0;
-  uint64_t* k1;
-  uint32_t* meta;
+  // entries of 16 (one key word) or 24 bytes: k0, [k1], state (0 empty, 1 busy, gid + 2), meta
+  unsigned char* base;
   uint32_t mask;  // slots - 1
 };
 
 template <int WORDS>
 __device__ __forceinline__ uint32_t cached_intern(const KeyCache& c, const GroupTable& t, const PackedKey& k) {
-  // cheap slot hash (one multiply): the cache holds a handful of keys, the strong hash is only needed behind it
-  uint32_t i = (uint32_t)(((k.k0 ^ (WORDS > 1 ? k.k1 * 0xc2b2ae3d27d4eb4fULL : 0ULL) ^ k.meta) * 0x9e3779b97f4a7c15ULL) >> 40) & c.mask;
+  constexpr uint32_t ENTRY = WORDS == 1 ? 16 : 24, STATE = ENTRY - 8;
+  // cheap slot hash in 32-bit multiplies: the cache holds a handful of keys, the strong hash is only needed behind it
+  uint32_t h = (uint32_t)k.k0 * 0x9e3779b1u ^ (uint32_t)(k.k0 >> 32) * 0x85ebca6bu ^ k.meta;
+  if (WORDS > 1) h ^= (uint32_t)k.k1 * 0xc2b2ae35u ^ (uint32_t)(k.k1 >> 32) * 0x27d4eb2fu;
+  uint32_t i = ((h * 0x165667b1u) >> 15) & c.mask;
 #pragma unroll 1
   for (uint32_t probe = 0; probe <= c.mask; probe++) {
-    const uint32_t s = *(volatile uint32_t*)&c.state[i];
+    unsigned char* e = c.base + i * ENTRY;
+    const uint32_t s = *(volatile uint32_t*)(e + STATE);
     if (s >= 2u) {
-      if (*(volatile uint64_t*)&c.k0[i] == k.k0 && (WORDS == 1 || *(volatile uint64_t*)&c.k1[i] == k.k1) &&
-          *(volatile uint32_t*)&c.meta[i] == k.meta)
+      if (*(volatile uint64_t*)e == k.k0 && (WORDS == 1 || *(volatile uint64_t*)(e + 8) == k.k1) &&
+          *(volatile uint32_t*)(e + STATE + 4) == k.meta)
         return s - 2u;
       i = (i + 1) & c.mask;
       continue;
     }
     const uint32_t gid = intern<WORDS>(t, k);
-    if (s == 0u && probe * 2 < c.mask && atomicCAS(&c.state[i], 0u, 1u) == 0u) {
-      c.k0[i] = k.k0;
-      if (WORDS > 1) c.k1[i] = k.k1;
-      c.meta[i] = k.meta;
+    if (s == 0u && probe * 2 < c.mask && atomicCAS((uint32_t*)(e + STATE), 0u, 1u) == 0u) {
+      *(uint64_t*)e = k.k0;
+      if (WORDS > 1) *(uint64_t*)(e + 8) = k.k1;
+      *(uint32_t*)(e + STATE + 4) = k.meta;
       __threadfence_block();
-      *(volatile uint32_t*)&c.state[i] = gid + 2u;
+      *(volatile uint32_t*)(e + STATE) = gid + 2u;
     }
     return gid;
   }
@@ -162,7 +164,8 @@ __device__ __forceinline__ uint32_t cached_intern(const KeyCache& c, const Group
 // ---- values ---------------------------------------------------------------------------------------------------
 struct Val { uint64_t lo, hi; };  // i128, or i64 in lo, or the bits of a double in lo
 
-__device__ __forceinline__ Val ld_i128(const void* col, int64_t r) {
+template <class I>
+__device__ __forceinline__ Val ld_i128(const void* col, I r) {
   const ulonglong2 x = __ldg((const ulonglong2*)col + r);
   return Val{x.x, x.y};
 }
@@ -541,21 +544,15 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
   const uint32_t acc_words = MODE == 0 ? G * (uint32_t)(Plan::PRIV_WORDS * T + Plan::P4) : G * W * copies;
   uint64_t* s_spill = s_acc + (size_t)G * Plan::PRIV_WORDS * T;
   uint32_t* s_seen = (uint32_t*)(s_acc + acc_words);
-  KeyCache cache;
-  {
-    unsigned char* p = (unsigned char*)(s_seen + ((G + 1) & ~1u));
-    cache.k0 = (uint64_t*)p;      p += (size_t)a.cache_slots * 8;
-    cache.k1 = (uint64_t*)p;      p += (size_t)a.cache_slots * 8;
-    cache.state = (uint32_t*)p;   p += (size_t)a.cache_slots * 4;
-    cache.meta = (uint32_t*)p;
-    cache.mask = a.cache_slots - 1;
-  }
+  KeyCache cache{(unsigned char*)(s_seen + ((G + 1) & ~1u)), a.cache_slots - 1};
+  constexpr uint32_t CACHE_ENTRY = KW == 1 ? 16 : 24;
   __shared__ int s_abort;
   for (uint32_t i = threadIdx.x; i < acc_words; i += T) s_acc[i] = 0;
   for (uint32_t i = threadIdx.x; i < G; i += T) s_seen[i] = 0;
-  for (uint32_t i = threadIdx.x; i < a.cache_slots; i += T) cache.state[i] = 0;
-  if (threadIdx.x == 0) s_abort = 0;
+  for (uint32_t i = threadIdx.x; i < a.cache_slots; i += T) *(uint32_t*)(cache.base + i * CACHE_ENTRY + CACHE_ENTRY - 8) = 0;
+  if (threadIdx.x == 0) s_abort = *(volatile int*)&a.t.flags[3];  // an earlier CTA gave up already: the pass is void
   __syncthreads();
+  if (s_abort) return;
 
   bool ovf = false;
   uint32_t tiles_done = 0;
@@ -585,37 +582,41 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
   if (Plan::PIPE) {
     // Three-stage pipeline: while tile i is consumed, every load of tile i+1 is in flight (issued from the early
     // loads of tile i+1, which were requested one iteration ago) and the early loads of tile i+2 are requested.
+    // Row indices are Plan::Row (32-bit when the batch allows: one IMAD.WIDE per address).
+    typedef typename Plan::Row Row;
+    const Row rlast = (Row)last, rstride = (Row)stride;
     typename Plan::Raw0 early[R];
-    typename Plan::Raw fly[R];
+    typename Plan::Raw fa[R], fb[R];  // in flight, being consumed
+    Row r0 = (Row)first + threadIdx.x;  // first row of this thread in the tile being consumed
 #pragma unroll
     for (int u = 0; u < R; u++) {
-      const int64_t r = first + u * T + threadIdx.x;
-      Plan::template load0<7>(a, r < last ? r : last, early[u]);
+      const Row r = r0 + u * T;
+      Plan::template load0<7>(a, r < rlast ? r : rlast, early[u]);
     }
-#pragma unroll
-    for (int u = 0; u < R; u++) {
-      const int64_t r = first + u * T + threadIdx.x, rc = r < last ? r : last;
-      static_cast<typename Plan::Raw0&>(fly[u]) = early[u];
-      Plan::template load1<7>(a, rc, fly[u]);
-      Plan::template load2<7>(a, rc, fly[u]);
-      const int64_t r1 = r + stride;
-      Plan::template load0<7>(a, r1 < last ? r1 : last, early[u]);
-    }
-    for (int64_t base = first; base < a.n_rows; base += stride) {
-      typename Plan::Raw x[R];
+    auto issue = [&](typename Plan::Raw (&dst)[R], Row rt) {  // all loads of the tile at rt, early loads of the one after
 #pragma unroll
       for (int u = 0; u < R; u++) {
-        x[u] = fly[u];
-        const int64_t r1 = base + stride + u * T + threadIdx.x, rc = r1 < last ? r1 : last;
-        static_cast<typename Plan::Raw0&>(fly[u]) = early[u];
-        Plan::template load1<7>(a, rc, fly[u]);
-        Plan::template load2<7>(a, rc, fly[u]);
-        const int64_t r2 = r1 + stride;
-        Plan::template load0<7>(a, r2 < last ? r2 : last, early[u]);
+        const Row r = rt + u * T, rc = r < rlast ? r : rlast;
+        static_cast<typename Plan::Raw0&>(dst[u]) = early[u];
+        Plan::template load1<7>(a, rc, dst[u]);
+        Plan::template load2<7>(a, rc, dst[u]);
+        const Row rn = r + rstride;
+        Plan::template load0<7>(a, rn < rlast ? rn : rlast, early[u]);
       }
+    };
+    auto stop = [&]() {  // some CTA gave up: the pass is void (polled every 16th tile: it only saves work)
+      return (++tiles_done & 15) == 0 && (*(volatile int*)&s_abort || *(volatile int*)&a.t.flags[3]);
+    };
+    issue(fa, r0);
+    for (;;) {  // (two tiles per trip with the register sets swapping roles spills at 96 registers: measured 30% slower)
+      if (r0 - threadIdx.x > rlast) break;
 #pragma unroll
-      for (int u = 0; u < R; u++) consume(x[u], base + u * T + threadIdx.x);
-      if (*(volatile int*)&s_abort || ((++tiles_done & 15) == 0 && *(volatile int*)&a.t.flags[3])) break;
+      for (int u = 0; u < R; u++) fb[u] = fa[u];
+      issue(fa, r0 + rstride);
+#pragma unroll
+      for (int u = 0; u < R; u++) consume(fb[u], (int64_t)(r0 + u * T));
+      r0 += rstride;
+      if (stop()) break;
     }
   } else {
     typename Plan::Raw0 nx[R];

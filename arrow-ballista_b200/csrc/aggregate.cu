@@ -285,6 +285,7 @@ extern "C" int bgpu_agg_debug_compile(bgpu_ctx* ctx, int32_t mode, const struct 
   sh.W = w;
   sh.has_seen = flags & 4;
   sh.T = threads; sh.R = rows_per_thread; sh.min_ctas = min_ctas; sh.kernels = 7;
+  sh.row32 = !(flags & 8);
   std::string src, cubin;
   BGPU_TRY(agg_generate_source(g.get(), sh, &src));
   src = std::string(agg_jit_prelude()) + src;

@@ -424,7 +424,8 @@ static int grow_after_overflow(bgpu_agg* g, uint32_t counter, int64_t batch_rows
 
 // The single-pass ("fused") ladder. mode 0 = thread-private accumulators, mode 1 = replicated shared-memory
 // accumulators with 32-bit shared atomics.
-struct Rung { int mode; int threads; int rows; int min_ctas; const char* name; };
+// (alt_*: the geometry to fall back to when the kernel spills registers at the first one)
+struct Rung { int mode; int threads; int rows; int min_ctas; const char* name; int alt_threads; int alt_rows; int alt_ctas; };
 
 // Try the fused ladder. *done = true when the batch has been committed.
 static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
@@ -441,15 +442,31 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
   //   accumulators no longer scale with the thread count, so hundreds to thousands of groups run at full residency.
   // rung 3: as rung 2 without the per-CTA key cache (group ids straight from the global table, which is L2 resident at
   //   this cardinality): all of shared memory holds accumulators, ~10^4 groups.
-  Rung rungs[kFusedRungs] = {{0, 640, 1, 1, "fused_private"}, {1, 256, 4, 3, "fused_shared2"}, {1, 512, 2, 1, "fused_shared1"},
-                             {2, 512, 2, 1, "fused_shared0"}};
-  if (const char* e = getenv("BGPU_FUSED_GEOMETRY")) {  // tuning knob: "threads,rows,ctas_per_sm" for the first rung
+  // Shared-atomic rungs: one row per thread through the load pipeline at the highest residency the registers allow
+  //   (db-benchmark q2, 5e8 rows: 1024x1 7.9 ms vs 512x2 11.2 ms).
+  Rung rungs[kFusedRungs] = {{0, 640, 1, 1, "fused_private", 512, 1, 1}, {1, 512, 1, 2, "fused_shared2", 256, 4, 3},
+                             {1, 1024, 1, 1, "fused_shared1", 512, 2, 1}, {2, 1024, 1, 1, "fused_shared0", 512, 2, 1}};
+  // tuning knobs: "threads,rows,ctas_per_sm" for the first rung (BGPU_FUSED_GEOMETRY) or rung i (BGPU_FUSED_RUNG<i>)
+  for (int i = 0; i < kFusedRungs; i++) {
+    const std::string name = "BGPU_FUSED_RUNG" + std::to_string(i);
+    const char* e = getenv(name.c_str());
+    if (!e && i == 0) e = getenv("BGPU_FUSED_GEOMETRY");
     int t = 0, r = 0, c = 0;
-    if (sscanf(e, "%d,%d,%d", &t, &r, &c) == 3 && t >= 32 && t <= 1024 && t % 32 == 0 && r >= 1 && r <= 16 && c >= 1 && c <= 8)
-      rungs[0] = Rung{0, t, r, c, "fused_private"};
+    if (e && sscanf(e, "%d,%d,%d", &t, &r, &c) == 3 && t >= 32 && t <= 1024 && t % 32 == 0 && r >= 1 && r <= 16 && c >= 1 && c <= 8) {
+      rungs[i].threads = t; rungs[i].rows = r; rungs[i].min_ctas = c; rungs[i].alt_threads = 0;
+    }
   }
   while (g->fused_rung < kFusedRungs) {
-    const Rung& rg = rungs[g->fused_rung];
+    Rung rg = rungs[g->fused_rung];
+    int waves = 8;
+    if (const char* e = getenv("BGPU_FUSED_WAVES")) waves = std::max(1, atoi(e));
+    b->sh.row32 = !getenv("BGPU_ROW64") && n_rows < (1LL << 31) && (int64_t)ctx->sm_count * 32 * waves * 1024 * 16 < (1LL << 31);
+    if (rg.alt_threads) {  // does the kernel fit the register budget of the preferred geometry?
+      BGPU_TRY(specialise(g, b, rg.mode == 0 ? 1 : 4, rg.threads, rg.rows, rg.min_ctas));
+      int local = 0;
+      BGPU_TRY(jit_local_bytes(ctx, b->mod->fn[JK_FUSED], &local));
+      if (local > 0) { rg.threads = rg.alt_threads; rg.rows = rg.alt_rows; rg.min_ctas = rg.alt_ctas; }
+    }
     const int T = rg.threads;
     const size_t cap = smem_max / (size_t)rg.min_ctas - 1024;
     // capacity G: largest with accumulators + seen + key cache (2G slots rounded up, 24 B each) <= cap
@@ -493,8 +510,6 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
     // several CTAs per SM slot: the hardware block scheduler then evens out the per-SM speed differences that a
     // one-wave persistent grid leaves as a 20% idle tail (ncu: SM active 77% of elapsed), at ~10 us of prologue +
     // flush per extra CTA
-    int waves = 8;
-    if (const char* e = getenv("BGPU_FUSED_WAVES")) waves = std::max(1, atoi(e));
     // (the private i32 high words need at most 65535 rows per thread)
     const int grid = (int)std::max<int64_t>(std::max<int64_t>(1, ceil_div64(n_rows, (int64_t)T * 65535)),
                                             std::min<int64_t>(ceil_div64(n_rows, (int64_t)T * rg.rows), (int64_t)ctx->sm_count * occ * waves));

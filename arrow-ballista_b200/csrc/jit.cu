@@ -27,6 +27,7 @@ struct Api {
   CUresult (*LaunchKernel)(CUfunction, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, CUstream,
                            void**, void**) = nullptr;
   CUresult (*FuncSetAttribute)(CUfunction, CUfunction_attribute, int) = nullptr;
+  CUresult (*FuncGetAttribute)(int*, CUfunction_attribute, CUfunction) = nullptr;
   CUresult (*Occupancy)(int*, CUfunction, int, size_t) = nullptr;
   CUresult (*GetErrorString)(CUresult, const char**) = nullptr;
 };
@@ -61,6 +62,7 @@ const Api& api() {
     *(void**)&a.ModuleGetFunction = sym(drv, "cuModuleGetFunction");
     *(void**)&a.LaunchKernel = sym(drv, "cuLaunchKernel");
     *(void**)&a.FuncSetAttribute = sym(drv, "cuFuncSetAttribute");
+    *(void**)&a.FuncGetAttribute = sym(drv, "cuFuncGetAttribute");
     *(void**)&a.Occupancy = sym(drv, "cuOccupancyMaxActiveBlocksPerMultiprocessor");
     *(void**)&a.GetErrorString = sym(drv, "cuGetErrorString");
     a.ok = ok;
@@ -163,6 +165,13 @@ int jit_set_max_smem(bgpu_ctx* ctx, CUfunction fn, size_t smem) {
   const Api& a = api();
   const CUresult r = a.FuncSetAttribute(fn, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)smem);
   if (r != CUDA_SUCCESS) return ctx->fail(BGPU_ECUDA, "cuFuncSetAttribute(max dynamic smem): " + cu_err(a, r));
+  return BGPU_OK;
+}
+
+int jit_local_bytes(bgpu_ctx* ctx, CUfunction fn, int* out) {
+  const Api& a = api();
+  const CUresult r = a.FuncGetAttribute(out, CU_FUNC_ATTRIBUTE_LOCAL_SIZE_BYTES, fn);
+  if (r != CUDA_SUCCESS) return ctx->fail(BGPU_ECUDA, "cuFuncGetAttribute(local size): " + cu_err(a, r));
   return BGPU_OK;
 }
 

@@ -30,6 +30,8 @@ int jit_compile_cubin(bgpu_ctx* ctx, const std::string& source, std::string* cub
 // cuLaunchKernel on ctx->stream with a single by-value argument struct.
 int jit_launch(bgpu_ctx* ctx, CUfunction fn, int grid, int block, size_t smem, const void* arg_struct);
 int jit_set_max_smem(bgpu_ctx* ctx, CUfunction fn, size_t smem);
+// bytes of local memory per thread (register spills / stack) of a compiled kernel
+int jit_local_bytes(bgpu_ctx* ctx, CUfunction fn, int* out);
 int jit_occupancy(bgpu_ctx* ctx, CUfunction fn, int block, size_t smem, int* out);
 
 }  // namespace bgpu
