@@ -176,6 +176,23 @@ def host_lineitem_batches(cols_host, n, chunk):
     return out
 
 
+def upload_bytes(batch):
+    """Bytes bgpu_batch_upload copies for a host batch: fixed-width buffers whole, utf8 as (rows + 1) offsets plus the
+    byte range the offsets reference (arrow_io.cu import_column)."""
+    import numpy as np
+    import pyarrow as pa
+
+    total = 0
+    for col in batch.columns:
+        bufs = col.buffers()
+        if pa.types.is_string(col.type) or pa.types.is_binary(col.type):
+            offs = np.frombuffer(bufs[1], dtype=np.int32, count=len(col) + 1, offset=col.offset * 4)
+            total += (len(col) + 1) * 4 + int(offs[-1] - offs[0]) + (bufs[0].size if bufs[0] is not None else 0)
+        else:
+            total += sum(b.size for b in bufs if b is not None)
+    return total
+
+
 # ---- the hot path through the host mirror of the reference operators ---------------------------------------------
 class HotPath:
     """Partial aggregate -> hash repartition -> (exchange) -> FinalPartitioned aggregate on one GPU/rank."""
@@ -274,7 +291,7 @@ def run_ours(args):
     host = {k: v[: (ne + 1 if k.endswith("offsets") else ne)].cpu().pin_memory() for k, v in cols.items()}
     chunk = 8_000_000
     hbatches = host_lineitem_batches(host, ne, chunk)
-    h2d = sum(sum(b.size for b in col.buffers() if b is not None) for hb in hbatches for col in hb.columns)
+    h2d = sum(upload_bytes(hb) for hb in hbatches)
 
     def e2e_step():
         up = (bb.DeviceBatch.upload(ctx, hb) for hb in hbatches)
