@@ -21,13 +21,9 @@ namespace bgpu {
 
 #ifndef BGPU_PART_THREADS
 #define BGPU_PART_THREADS 256
-#define BGPU_PART_ITEMS 16
-#define BGPU_PART_MIN_CTAS 3
 #endif
 constexpr int kThreads = BGPU_PART_THREADS;
 constexpr int kWarps = kThreads / 32;
-constexpr int kItems = BGPU_PART_ITEMS;
-constexpr int kTile = kThreads * kItems;  // 4096 rows
 constexpr uint32_t kMaxPartitions = 2048;
 
 // ---- K1: create_hashes -----------------------------------------------------------------------------------
@@ -38,24 +34,41 @@ __global__ void __launch_bounds__(kThreads) hash_kernel(const __grid_constant__ 
 }
 
 // ---- K2: partition ids + per-chunk histogram ----------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads)
+constexpr int kCountThreads = 1024;  // the chunk layout is the scatter's; the histogram pass just wants residency
+__global__ void __launch_bounds__(kCountThreads)
     count_kernel(const __grid_constant__ KeySet ks, const __grid_constant__ Modulo mod, int64_t n_rows,
                  int64_t chunk_rows, uint32_t* __restrict__ hist /* [n][gridDim.x] */,
                  uint64_t* __restrict__ out_hashes) {
   extern __shared__ uint32_t s_hist[];
   const uint32_t n = mod.n;
-  for (uint32_t p = threadIdx.x; p < n; p += kThreads) s_hist[p] = 0;
+  for (uint32_t p = threadIdx.x; p < n; p += kCountThreads) s_hist[p] = 0;
   __syncthreads();
   const int64_t begin = (int64_t)blockIdx.x * chunk_rows;
   int64_t end = begin + chunk_rows;
   if (end > n_rows) end = n_rows;
-  for (int64_t r = begin + threadIdx.x; r < end; r += kThreads) {
+  constexpr int U = 8;  // rows per thread in flight
+  int64_t r = begin + threadIdx.x;
+  if (ks.fast64) {  // single 8-byte key column: all U loads go out before the first hash
+    const uint64_t* keys = (const uint64_t*)ks.cols[0].values;
+    for (; r + (int64_t)(U - 1) * kCountThreads < end; r += (int64_t)U * kCountThreads) {
+      uint64_t k[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) k[u] = __ldg(keys + r + (int64_t)u * kCountThreads);
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const uint64_t h = hash_u64(k[u]);
+        if (out_hashes) out_hashes[r + (int64_t)u * kCountThreads] = h;
+        atomicAdd(&s_hist[partition_of(h, mod)], 1u);
+      }
+    }
+  }
+  for (; r < end; r += kCountThreads) {
     const uint64_t h = row_hash(ks, r);
     if (out_hashes) out_hashes[r] = h;
     atomicAdd(&s_hist[partition_of(h, mod)], 1u);
   }
   __syncthreads();
-  for (uint32_t p = threadIdx.x; p < n; p += kThreads) hist[(size_t)p * gridDim.x + blockIdx.x] = s_hist[p];
+  for (uint32_t p = threadIdx.x; p < n; p += kCountThreads) hist[(size_t)p * gridDim.x + blockIdx.x] = s_hist[p];
 }
 
 // ---- scan of hist[p][chunk] (single CTA; n*G <= ~1.2M entries) ---------------------------------------------
@@ -103,6 +116,11 @@ __global__ void __launch_bounds__(1024) scan_kernel(const uint32_t* __restrict__
 }
 
 // ---- K3: stable scatter ---------------------------------------------------------------------------------------
+// Per tile of THREADS x ITEMS rows: rank every row stably by partition, then move the columns through shared memory
+// in partition order and write them out in runs. Fixed-width columns of 4, 8 and 16 bytes are staged ALL AT ONCE with
+// cp.async (LDGSTS: global -> shared at the row's sorted position, no registers held), so a tile exposes one DRAM
+// latency for all of them instead of one per column; the remaining kinds (1/2-byte values, utf8 (length, start)
+// pairs) go one at a time through a small side buffer while the async copies are in flight, bitmaps with atomics.
 constexpr int kMaxCols = 32;
 struct ScatterCol {
   const void* in;           // fixed values / dict keys / bool bits
@@ -114,98 +132,165 @@ struct ScatterCol {
   int32_t* out_src;         // utf8: source byte start of output row d
   int32_t kind;
   int32_t width;
+  int32_t stage_off;        // byte offset of this column's async stage area for a tile of ONE row (x tile rows); -1 = side buffer
 };
+struct AsyncCol { const void* in; void* out; int32_t width; int32_t stage_off; };
 struct ScatterArgs {
   ScatterCol cols[kMaxCols];
-  int32_t n_cols;
-  int32_t stage_width;  // bytes per staged element: widest scattered value, multiple of 4, <= 16
+  AsyncCol async_cols[kMaxCols];  // the cp.async-staged columns, widest first
+  int8_t side_cols[kMaxCols];     // the columns step 4 has work for (bitmaps, utf8, side-buffer values)
+  int32_t n_cols, n_async, n_side;
+  int32_t async_width;  // sum of the widths of the async-staged columns
+  int32_t side_width;   // bytes per element of the side buffer (0 = none needed)
 };
 
 // peers of this lane's partition id within the warp
 __device__ __forceinline__ uint32_t match_peers(uint32_t pid) { return __match_any_sync(0xffffffffu, pid); }
 
-// Stage one column's values of this tile into shared memory in partition order, then write them out in runs.
-template <typename T, typename Load>
-__device__ __forceinline__ void scatter_staged(Load load, T* __restrict__ out, T* stage, const uint16_t* pid_sorted,
-                                               const int64_t* gdelta, int64_t tile_base, int tile_n,
-                                               const uint32_t (&pos)[kItems]) {
+template <int BYTES>
+__device__ __forceinline__ void cp_async(uint32_t smem_dst, const void* gsrc) {
+  if (BYTES == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+  else if (BYTES == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+  else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+
+// rows w*32*ITEMS + it*32 + lane of the tile: `in` points at the column's element of this thread's first row
+template <int THREADS, int ITEMS, typename T>
+__device__ __forceinline__ void stage_async(const T* __restrict__ in, uint32_t stage /* shared address */, int valid_items,
+                                            const uint32_t (&pos)[ITEMS]) {
+#pragma unroll
+  for (int it = 0; it < ITEMS; it++)
+    if (it < valid_items) cp_async<sizeof(T)>(stage + pos[it] * (uint32_t)sizeof(T), in + it * 32);
+}
+
+// write one staged column out: sorted position j = threadIdx.x + k * THREADS goes to output row d[k] (-1 = none)
+template <int THREADS, int ITEMS, typename T>
+__device__ __forceinline__ void write_runs(T* __restrict__ out, const T* stage, const int64_t (&d)[ITEMS]) {
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++)
+    if (d[k] >= 0) out[d[k]] = stage[threadIdx.x + k * THREADS];
+}
+// the same with the output row recomputed per element (side-buffer columns: keeps registers for the loads)
+template <int THREADS, int ITEMS, typename T>
+__device__ __forceinline__ void write_runs(T* __restrict__ out, const T* stage, const uint16_t* pid_sorted,
+                                           const int64_t* gdelta, int tile_n) {
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++) {
+    const int j = threadIdx.x + k * THREADS;
+    if (j < tile_n) out[(int64_t)j + gdelta[pid_sorted[j]]] = stage[j];
+  }
+}
+
+// one column through the side buffer: load -> stage in partition order -> sync -> write -> sync
+template <int THREADS, int ITEMS, typename T, typename Load>
+__device__ __forceinline__ void scatter_side(Load load, T* __restrict__ out, T* stage, int64_t tile_base, int tile_n,
+                                             const uint32_t (&pos)[ITEMS], const uint16_t* pid_sorted,
+                                             const int64_t* gdelta) {
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int kBatch = sizeof(T) >= 16 ? 4 : (sizeof(T) >= 8 ? 8 : 16);  // loads in flight per thread
+  constexpr int B = kBatch < ITEMS ? kBatch : ITEMS;
 #pragma unroll
-  for (int b0 = 0; b0 < kItems; b0 += kBatch) {
-    T v[kBatch];
+  for (int b0 = 0; b0 < ITEMS; b0 += B) {
+    T v[B];
 #pragma unroll
-    for (int k = 0; k < kBatch; k++) {
-      const int local = w * (32 * kItems) + (b0 + k) * 32 + lane;
+    for (int k = 0; k < B; k++) {
+      const int local = w * (32 * ITEMS) + (b0 + k) * 32 + lane;
       if (local < tile_n) v[k] = load(tile_base + local);
     }
 #pragma unroll
-    for (int k = 0; k < kBatch; k++) {
-      const int local = w * (32 * kItems) + (b0 + k) * 32 + lane;
+    for (int k = 0; k < B; k++) {
+      const int local = w * (32 * ITEMS) + (b0 + k) * 32 + lane;
       if (local < tile_n) stage[pos[b0 + k]] = v[k];
     }
   }
   __syncthreads();
-#pragma unroll 4
-  for (int j = threadIdx.x; j < tile_n; j += kThreads) out[j + gdelta[pid_sorted[j]]] = stage[j];
+  write_runs<THREADS, ITEMS, T>(out, stage, pid_sorted, gdelta, tile_n);
   __syncthreads();
 }
 
 // Scatter a bitmap (validity or boolean values): set bit d of the zero-initialised output for every set input bit.
+template <int THREADS, int ITEMS>
 __device__ __forceinline__ void scatter_bits(const uint8_t* __restrict__ in, uint32_t* __restrict__ out,
-                                             const int64_t* gdelta, const uint32_t (&pid)[kItems], int64_t tile_base,
-                                             int tile_n, const uint32_t (&pos)[kItems]) {
+                                             const int64_t* gdelta, const uint16_t* pid_sorted, int64_t tile_base,
+                                             int tile_n, const uint32_t (&pos)[ITEMS]) {
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #pragma unroll
-  for (int it = 0; it < kItems; it++) {
-    const int local = w * (32 * kItems) + it * 32 + lane;
+  for (int it = 0; it < ITEMS; it++) {
+    const int local = w * (32 * ITEMS) + it * 32 + lane;
     if (local < tile_n && bit_is_set(in, tile_base + local)) {
-      const int64_t d = (int64_t)pos[it] + gdelta[pid[it]];
+      const int64_t d = (int64_t)pos[it] + gdelta[pid_sorted[pos[it]]];
       atomicOr(&out[d >> 5], 1u << (d & 31));
     }
   }
 }
 
-__global__ void __launch_bounds__(kThreads, BGPU_PART_MIN_CTAS)
+// shared memory of one scatter CTA (tile = THREADS * items rows)
+static size_t scatter_smem_bytes(uint32_t n, int threads, int items, int async_width, int side_width) {
+  const size_t tile = (size_t)threads * items;
+  size_t b = tile * (size_t)(async_width + side_width);
+  b = (b + 15) & ~(size_t)15;
+  b += (size_t)n * 8 * 2 + (size_t)(threads / 32) * n * 4 + (size_t)n * 4 * 2 + tile * 2;
+  return b + 16;
+}
+
+template <int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2)
     scatter_kernel(const __grid_constant__ KeySet ks, const __grid_constant__ Modulo mod,
                    const __grid_constant__ ScatterArgs args, int64_t n_rows, int64_t chunk_rows,
                    const uint64_t* __restrict__ base /* [n][gridDim.x] */) {
+  constexpr int kTile = THREADS * ITEMS;
   extern __shared__ __align__(16) unsigned char smem[];
   const uint32_t n = mod.n;
-  // shared layout: stage (16 B aligned) | gdelta i64[n] | chunk_base u64[n] | warp_cnt u32[kWarps*n] |
-  //                tile_off u32[n] | tile_cnt u32[n] | pid_sorted u16[kTile]
+  // shared layout: async stage areas (column c at stage_off * kTile, 16 B aligned) | side buffer | gdelta i64[n] |
+  //                chunk_base u64[n] | warp_cnt u32[(THREADS / 32)*n] | tile_off u32[n] | tile_cnt u32[n] | pid_sorted u16[kTile]
   unsigned char* sp = smem;
-  void* stage = sp;                       sp += (size_t)kTile * args.stage_width;
+  unsigned char* stage = sp;              sp += (size_t)kTile * args.async_width;
+  void* side = sp;                        sp += (size_t)kTile * args.side_width;
+  sp = (unsigned char*)(((uintptr_t)sp + 15) & ~(uintptr_t)15);
   int64_t* gdelta = (int64_t*)sp;         sp += (size_t)n * 8;
   uint64_t* chunk_base = (uint64_t*)sp;   sp += (size_t)n * 8;
-  uint32_t* warp_cnt = (uint32_t*)sp;     sp += (size_t)kWarps * n * 4;
+  uint32_t* warp_cnt = (uint32_t*)sp;     sp += (size_t)(THREADS / 32) * n * 4;
   uint32_t* tile_off = (uint32_t*)sp;     sp += (size_t)n * 4;
   uint32_t* tile_cnt = (uint32_t*)sp;     sp += (size_t)n * 4;
   uint16_t* pid_sorted = (uint16_t*)sp;
-  __shared__ uint32_t s_scan[kWarps];
+  __shared__ uint32_t s_scan[(THREADS / 32)];
 
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1;
   const int64_t begin = (int64_t)blockIdx.x * chunk_rows;
   int64_t end = begin + chunk_rows;
   if (end > n_rows) end = n_rows;
-  for (uint32_t p = threadIdx.x; p < n; p += kThreads) chunk_base[p] = base[(size_t)p * gridDim.x + blockIdx.x];
+  for (uint32_t p = threadIdx.x; p < n; p += THREADS) chunk_base[p] = base[(size_t)p * gridDim.x + blockIdx.x];
+
+  // single 8-byte key column (ks.fast64): the next tile's keys are loaded into registers while this tile is moved,
+  // so the ranking never waits on DRAM
+  uint64_t next_key[ITEMS];
+  auto prefetch_keys = [&](int64_t tb) {
+    if (!ks.fast64) return;
+    const uint64_t* keys = (const uint64_t*)ks.cols[0].values;
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+      const int64_t r = tb + w * (32 * ITEMS) + it * 32 + lane;
+      next_key[it] = r < end ? __ldg(keys + r) : 0;
+    }
+  };
+  prefetch_keys(begin);
 
   for (int64_t tile_base = begin; tile_base < end; tile_base += kTile) {
     const int tile_n = (int)((end - tile_base) < kTile ? (end - tile_base) : kTile);
-    for (uint32_t i = threadIdx.x; i < kWarps * n; i += kThreads) warp_cnt[i] = 0;
+    for (uint32_t i = threadIdx.x; i < (THREADS / 32) * n; i += THREADS) warp_cnt[i] = 0;
     __syncthreads();
     // 1. partition id and stable rank within this warp's segment
-    uint32_t pid[kItems], pos[kItems];
+    uint32_t pid[ITEMS], pos[ITEMS];
     uint32_t* wc = warp_cnt + (size_t)w * n;
 #pragma unroll
-    for (int it = 0; it < kItems; it++) {
-      const int local = w * (32 * kItems) + it * 32 + lane;
+    for (int it = 0; it < ITEMS; it++) {
+      const int local = w * (32 * ITEMS) + it * 32 + lane;
       const bool valid = local < tile_n;
-      pid[it] = valid ? partition_of(row_hash(ks, tile_base + local), mod) : 0xffffffffu;
+      pid[it] = valid ? partition_of(ks.fast64 ? hash_u64(next_key[it]) : row_hash(ks, tile_base + local), mod) : 0xffffffffu;
     }
 #pragma unroll
-    for (int it = 0; it < kItems; it++) {
+    for (int it = 0; it < ITEMS; it++) {
       const uint32_t peers = match_peers(pid[it]);
       const int leader = __ffs(peers) - 1;
       uint32_t old = 0;
@@ -219,10 +304,10 @@ __global__ void __launch_bounds__(kThreads, BGPU_PART_MIN_CTAS)
     }
     __syncthreads();
     // 2. per partition: exclusive scan over warps, tile totals, then exclusive scan over partitions
-    for (uint32_t p = threadIdx.x; p < n; p += kThreads) {
+    for (uint32_t p = threadIdx.x; p < n; p += THREADS) {
       uint32_t run = 0;
 #pragma unroll
-      for (int ww = 0; ww < kWarps; ww++) {
+      for (int ww = 0; ww < (THREADS / 32); ww++) {
         const uint32_t c = warp_cnt[(size_t)ww * n + p];
         warp_cnt[(size_t)ww * n + p] = run;
         run += c;
@@ -231,7 +316,7 @@ __global__ void __launch_bounds__(kThreads, BGPU_PART_MIN_CTAS)
     }
     __syncthreads();
     {  // block exclusive scan of tile_cnt[0..n) into tile_off; each thread owns a contiguous slice
-      const uint32_t per = (n + kThreads - 1) / kThreads;
+      const uint32_t per = (n + THREADS - 1) / THREADS;
       const uint32_t p0 = threadIdx.x * per;
       uint32_t sum = 0;
       for (uint32_t k = 0; k < per; k++)
@@ -257,57 +342,91 @@ __global__ void __launch_bounds__(kThreads, BGPU_PART_MIN_CTAS)
         }
     }
     __syncthreads();
-    // 3. position of every row in the partition-ordered tile
+    // 3. position of every row in the partition-ordered tile; all async columns go in flight
 #pragma unroll
-    for (int it = 0; it < kItems; it++) {
+    for (int it = 0; it < ITEMS; it++) {
       if (pid[it] != 0xffffffffu) {
         pos[it] += tile_off[pid[it]] + wc[pid[it]];
         pid_sorted[pos[it]] = (uint16_t)pid[it];
       }
     }
+    {
+      const int first = w * (32 * ITEMS) + lane;  // this thread's rows: first + it * 32
+      const int valid_items = first < tile_n ? (tile_n - first + 31) / 32 : 0;
+      const int64_t r0 = tile_base + first;
+      const uint32_t stage_s = (uint32_t)__cvta_generic_to_shared(stage);
+      for (int c = 0; c < args.n_async; c++) {
+        const AsyncCol& ac = args.async_cols[c];
+        const uint32_t st = stage_s + (uint32_t)ac.stage_off * kTile;
+        if (ac.width == 8) stage_async<THREADS, ITEMS, uint64_t>((const uint64_t*)ac.in + r0, st, valid_items, pos);
+        else if (ac.width == 16) stage_async<THREADS, ITEMS, uint4>((const uint4*)ac.in + r0, st, valid_items, pos);
+        else stage_async<THREADS, ITEMS, uint32_t>((const uint32_t*)ac.in + r0, st, valid_items, pos);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    prefetch_keys(tile_base + kTile);
     __syncthreads();
-    // 4. columns
-    for (int c = 0; c < args.n_cols; c++) {
-      const ScatterCol& col = args.cols[c];
-      if (col.in_valid) scatter_bits(col.in_valid, col.out_valid, gdelta, pid, tile_base, tile_n, pos);
+    // 4. bitmaps and side-buffer columns while the async copies land
+    for (int sc = 0; sc < args.n_side; sc++) {
+      const ScatterCol& col = args.cols[args.side_cols[sc]];
+      if (col.in_valid) scatter_bits<THREADS, ITEMS>(col.in_valid, col.out_valid, gdelta, pid_sorted, tile_base, tile_n, pos);
       if (col.kind == K_BOOL) {
-        scatter_bits((const uint8_t*)col.in, (uint32_t*)col.out, gdelta, pid, tile_base, tile_n, pos);
+        scatter_bits<THREADS, ITEMS>((const uint8_t*)col.in, (uint32_t*)col.out, gdelta, pid_sorted, tile_base, tile_n, pos);
       } else if (col.kind == K_UTF8 || col.kind == K_BINARY) {
         const int32_t* offs = col.in_offsets;
-        scatter_staged<int32_t>([=](int64_t r) { return offs[r + 1] - offs[r]; }, col.out_len, (int32_t*)stage,
-                                pid_sorted, gdelta, tile_base, tile_n, pos);
-        scatter_staged<int32_t>([=](int64_t r) { return offs[r]; }, col.out_src, (int32_t*)stage, pid_sorted, gdelta,
-                                tile_base, tile_n, pos);
-      } else {
+        scatter_side<THREADS, ITEMS, int32_t>([=](int64_t r) { return offs[r + 1] - offs[r]; }, col.out_len, (int32_t*)side,
+                                     tile_base, tile_n, pos, pid_sorted, gdelta);
+        scatter_side<THREADS, ITEMS, int32_t>([=](int64_t r) { return offs[r]; }, col.out_src, (int32_t*)side, tile_base, tile_n,
+                                     pos, pid_sorted, gdelta);
+      } else if (col.stage_off < 0) {
         switch (col.width) {
-          case 8: {
-            const uint64_t* in = (const uint64_t*)col.in;
-            scatter_staged<uint64_t>([=](int64_t r) { return in[r]; }, (uint64_t*)col.out, (uint64_t*)stage,
-                                     pid_sorted, gdelta, tile_base, tile_n, pos);
-          } break;
           case 16: {
             const uint4* in = (const uint4*)col.in;
-            scatter_staged<uint4>([=](int64_t r) { return in[r]; }, (uint4*)col.out, (uint4*)stage, pid_sorted,
-                                  gdelta, tile_base, tile_n, pos);
+            scatter_side<THREADS, ITEMS, uint4>([=](int64_t r) { return in[r]; }, (uint4*)col.out, (uint4*)side, tile_base,
+                                       tile_n, pos, pid_sorted, gdelta);
+          } break;
+          case 8: {
+            const uint64_t* in = (const uint64_t*)col.in;
+            scatter_side<THREADS, ITEMS, uint64_t>([=](int64_t r) { return in[r]; }, (uint64_t*)col.out, (uint64_t*)side,
+                                          tile_base, tile_n, pos, pid_sorted, gdelta);
           } break;
           case 4: {
             const uint32_t* in = (const uint32_t*)col.in;
-            scatter_staged<uint32_t>([=](int64_t r) { return in[r]; }, (uint32_t*)col.out, (uint32_t*)stage,
-                                     pid_sorted, gdelta, tile_base, tile_n, pos);
+            scatter_side<THREADS, ITEMS, uint32_t>([=](int64_t r) { return in[r]; }, (uint32_t*)col.out, (uint32_t*)side,
+                                          tile_base, tile_n, pos, pid_sorted, gdelta);
           } break;
           case 2: {
             const uint16_t* in = (const uint16_t*)col.in;
-            scatter_staged<uint16_t>([=](int64_t r) { return in[r]; }, (uint16_t*)col.out, (uint16_t*)stage,
-                                     pid_sorted, gdelta, tile_base, tile_n, pos);
+            scatter_side<THREADS, ITEMS, uint16_t>([=](int64_t r) { return in[r]; }, (uint16_t*)col.out, (uint16_t*)side,
+                                          tile_base, tile_n, pos, pid_sorted, gdelta);
           } break;
           default: {
             const uint8_t* in = (const uint8_t*)col.in;
-            scatter_staged<uint8_t>([=](int64_t r) { return in[r]; }, (uint8_t*)col.out, (uint8_t*)stage,
-                                    pid_sorted, gdelta, tile_base, tile_n, pos);
+            scatter_side<THREADS, ITEMS, uint8_t>([=](int64_t r) { return in[r]; }, (uint8_t*)col.out, (uint8_t*)side, tile_base,
+                                         tile_n, pos, pid_sorted, gdelta);
           } break;
         }
       }
     }
+    // 5. the async-staged columns
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();
+    {  // sorted position j = threadIdx.x + k * THREADS -> output row d[k], once for all columns
+      int64_t d[ITEMS];
+#pragma unroll
+      for (int k = 0; k < ITEMS; k++) {
+        const int j = threadIdx.x + k * THREADS;
+        d[k] = j < tile_n ? (int64_t)j + gdelta[pid_sorted[j]] : -1;
+      }
+      for (int c = 0; c < args.n_async; c++) {
+        const AsyncCol& ac = args.async_cols[c];
+        const unsigned char* st = stage + (size_t)ac.stage_off * kTile;
+        if (ac.width == 8) write_runs<THREADS, ITEMS, uint64_t>((uint64_t*)ac.out, (const uint64_t*)st, d);
+        else if (ac.width == 16) write_runs<THREADS, ITEMS, uint4>((uint4*)ac.out, (const uint4*)st, d);
+        else write_runs<THREADS, ITEMS, uint32_t>((uint32_t*)ac.out, (const uint32_t*)st, d);
+      }
+    }
+    // (the next tile's first __syncthreads orders these reads before its cp.async writes)
   }
 }
 
@@ -385,8 +504,30 @@ extern "C" int bgpu_create_hashes(bgpu_ctx* ctx, const bgpu_batch* batch, const 
   return BGPU_OK;
 }
 
-static size_t scatter_smem_bytes(uint32_t n, int stage_width) {
-  return (size_t)kTile * stage_width + (size_t)n * 8 * 2 + (size_t)kWarps * n * 4 + (size_t)n * 4 * 2 + (size_t)kTile * 2;
+// scatter geometries (threads per CTA, rows per thread): tile = threads x items rows
+struct ScatterGeom { int threads, items; };
+constexpr ScatterGeom kGeomSmall{256, 4};    // 1024-row tiles, two CTAs per SM: few partitions (runs stay long)
+constexpr ScatterGeom kGeomMedium{256, 8};   // 2048-row tiles
+constexpr ScatterGeom kGeomLarge{1024, 4};   // 4096-row tiles, one CTA per SM: many partitions
+
+template <int THREADS, int ITEMS>
+static int scatter_run(bgpu_ctx* ctx, bool launch, int64_t g, size_t smem, const KeySet& ks, const Modulo& mod,
+                       const ScatterArgs& args, int64_t n_rows, int64_t chunk_rows, const uint64_t* base, int* occ) {
+  BGPU_CUDA(ctx, cudaFuncSetAttribute(scatter_kernel<THREADS, ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (!launch) {
+    BGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, scatter_kernel<THREADS, ITEMS>, THREADS, smem));
+    return BGPU_OK;
+  }
+  scatter_kernel<THREADS, ITEMS><<<(int)g, THREADS, smem, ctx->stream>>>(ks, mod, args, n_rows, chunk_rows, base);
+  return BGPU_OK;
+}
+static int scatter_dispatch(bgpu_ctx* ctx, ScatterGeom geom, bool launch, int64_t g, size_t smem, const KeySet& ks,
+                            const Modulo& mod, const ScatterArgs& args, int64_t n_rows, int64_t chunk_rows,
+                            const uint64_t* base, int* occ) {
+  if (geom.threads == 256 && geom.items == 4) return scatter_run<256, 4>(ctx, launch, g, smem, ks, mod, args, n_rows, chunk_rows, base, occ);
+  if (geom.threads == 256 && geom.items == 8) return scatter_run<256, 8>(ctx, launch, g, smem, ks, mod, args, n_rows, chunk_rows, base, occ);
+  if (geom.threads == 1024 && geom.items == 4) return scatter_run<1024, 4>(ctx, launch, g, smem, ks, mod, args, n_rows, chunk_rows, base, occ);
+  return ctx->fail(BGPU_EINVAL, "internal: unknown scatter geometry");
 }
 
 extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const int32_t* key_cols, int32_t n_keys,
@@ -410,7 +551,6 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
   // output columns + scatter descriptors
   ScatterArgs args{};
   args.n_cols = (int32_t)in->cols.size();
-  int stage_width = 4;
   struct Utf8Post { size_t col; DevAllocPtr len, src; };
   std::vector<Utf8Post> utf8;
   for (size_t i = 0; i < in->cols.size(); i++) {
@@ -449,11 +589,66 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
       BGPU_TRY(dev_alloc(ctx, (size_t)n_rows * c.width, &a));
       o.owned.push_back(a); o.values = a->p;
       sc.in = c.values; sc.out = a->p;
-      if (c.width > stage_width) stage_width = c.width;
       if (c.kind == K_DICT32) o.owned.insert(o.owned.end(), c.owned.begin(), c.owned.end());  // shares the dictionary
     }
   }
-  args.stage_width = stage_width;
+  // Stage plan: fixed 4/8/16-byte columns are staged together with cp.async (widest first, so every area is aligned to
+  // its element size); everything else shares a side buffer as wide as its widest element. Tile = 256 x items rows:
+  // the largest of 16/8/4 items per thread that leaves room for two CTAs per SM (one loads while the other writes);
+  // if the schema is too wide for that, columns are demoted to the side buffer (widest first) at 16 items.
+  std::vector<size_t> async_cols;
+  int side_width = 0;
+  for (size_t i = 0; i < in->cols.size(); i++) {
+    const Column& c = in->cols[i];
+    args.cols[i].stage_off = -1;
+    if (c.kind == K_UTF8 || c.kind == K_BINARY) side_width = std::max(side_width, 4);
+    else if (c.kind == K_BOOL) continue;
+    else if (c.width >= 4 && ((uintptr_t)c.values % (size_t)c.width) == 0) async_cols.push_back(i);
+    else side_width = std::max(side_width, (int)c.width);
+  }
+  std::stable_sort(async_cols.begin(), async_cols.end(), [&](size_t a, size_t b) { return in->cols[a].width > in->cols[b].width; });
+  // Geometry: long output runs need tile rows >> n_partitions; overlap of one CTA's loads with another's stores needs
+  // two CTAs per SM. Measured (config 3, 2e8 rows): n = 8 / 64: 256x4 4.1 / 5.1 ms, 256x8 5.4 / 6.3 ms; n = 512 wants the
+  // 4096-row tile. A schema too wide for the chosen tile demotes columns to the side buffer, widest first.
+  ScatterGeom geom = n <= 128 ? kGeomSmall : kGeomLarge;
+  if (const char* e = getenv("BGPU_PART_GEOMETRY")) {  // tuning knob: "threads,items"
+    int t = 0, it = 0;
+    if (sscanf(e, "%d,%d", &t, &it) == 2 && ((t == 256 && (it == 4 || it == 8)) || (t == 1024 && it == 4))) geom = ScatterGeom{t, it};
+  }
+  for (;;) {
+    int aw = 0;
+    for (size_t i : async_cols) aw += in->cols[i].width;
+    const size_t need = scatter_smem_bytes(n, geom.threads, geom.items, aw, side_width);
+    const size_t budget = geom.threads >= 1024 ? ctx->smem_optin : (ctx->smem_optin + 1024) / 2 - 1024 - 512;
+    if (need <= budget) break;
+    if (async_cols.empty()) {
+      if (geom.threads == 256 && geom.items == 4) {
+        if (need <= ctx->smem_optin) break;
+        return ctx->fail(BGPU_EUNSUPPORTED, "n_partitions too large for shared memory");
+      }
+      geom = kGeomSmall;  // the per-partition arrays alone overflow the larger tile
+      continue;
+    }
+    side_width = std::max(side_width, (int)in->cols[async_cols.front()].width);  // demote the widest async column
+    async_cols.erase(async_cols.begin());
+  }
+  {
+    int off = 0;
+    args.n_async = 0;
+    for (size_t i : async_cols) {
+      args.cols[i].stage_off = off;
+      args.async_cols[args.n_async++] = AsyncCol{args.cols[i].in, args.cols[i].out, in->cols[i].width, off};
+      off += in->cols[i].width;
+    }
+    args.async_width = off;
+    args.side_width = side_width;
+    args.n_side = 0;
+    for (size_t i = 0; i < in->cols.size(); i++) {
+      const Column& c = in->cols[i];
+      if (c.validity || c.kind == K_BOOL || c.kind == K_UTF8 || c.kind == K_BINARY || args.cols[i].stage_off < 0)
+        args.side_cols[args.n_side++] = (int8_t)i;
+    }
+  }
 
   if (n_rows == 0) {
     for (uint32_t p = 0; p <= n; p++) out_offsets[p] = 0;
@@ -468,11 +663,10 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
   const Modulo mod = make_modulo(n);
 
   // grid: one persistent CTA per resident slot, contiguous chunks of whole tiles
-  const size_t smem = scatter_smem_bytes(n, stage_width);
-  if (smem > ctx->smem_optin) return ctx->fail(BGPU_EUNSUPPORTED, "n_partitions too large for shared memory");
-  BGPU_CUDA(ctx, cudaFuncSetAttribute(scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const size_t smem = scatter_smem_bytes(n, geom.threads, geom.items, args.async_width, args.side_width);
+  const int64_t kTile = (int64_t)geom.threads * geom.items;
   int occ = 1;
-  BGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, scatter_kernel, kThreads, smem));
+  BGPU_TRY(scatter_dispatch(ctx, geom, false, 0, smem, ks, mod, args, n_rows, 0, nullptr, &occ));
   if (occ < 1) occ = 1;
   int64_t g = (int64_t)ctx->sm_count * occ;
   const int64_t tiles = ceil_div64(n_rows, kTile);
@@ -485,11 +679,11 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
   BGPU_TRY(dev_alloc(ctx, (size_t)n * g * 8, &base));
   BGPU_TRY(dev_alloc(ctx, (size_t)(n + 1) * 8, &offs));
 
-  count_kernel<<<(int)g, kThreads, n * 4, ctx->stream>>>(ks, mod, n_rows, chunk_rows, (uint32_t*)hist->p,
+  count_kernel<<<(int)g, kCountThreads, n * 4, ctx->stream>>>(ks, mod, n_rows, chunk_rows, (uint32_t*)hist->p,
                                                         out_hashes_device);
   scan_kernel<<<1, 1024, 0, ctx->stream>>>((const uint32_t*)hist->p, (uint64_t*)base->p, (uint64_t*)offs->p, n,
                                            (uint32_t)g, n_rows);
-  scatter_kernel<<<(int)g, kThreads, smem, ctx->stream>>>(ks, mod, args, n_rows, chunk_rows, (const uint64_t*)base->p);
+  BGPU_TRY(scatter_dispatch(ctx, geom, true, g, smem, ks, mod, args, n_rows, chunk_rows, (const uint64_t*)base->p, nullptr));
   ctx->launches += 3;
   BGPU_CUDA(ctx, cudaGetLastError());
 
