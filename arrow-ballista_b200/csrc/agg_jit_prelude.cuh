@@ -122,6 +122,111 @@ __device__ __forceinline__ uint32_t intern(const GroupTable& t, const PackedKey&
   return intern_slow<WORDS>(t, k.k0, WORDS > 1 ? k.k1 : 0ULL, k.meta);
 }
 
+// Warp-synchronous find-or-insert of R keys per lane (intern pass of the two-pass path; all 32 lanes call it).
+// Two things the one-key-at-a-time routine above cannot do at 10^7..10^8 groups:
+//   * the slot loads of all R rows of a lane are in flight together (a probe is a DRAM round trip), and
+//   * dense ids are allocated with ONE atomicAdd per warp and round for all lanes that claimed a slot in it - a
+//     single-address atomic per new group serialises in L2 (measured: 25 M inserts = 30 ms).
+// Rounds: load the slot of every unresolved row; match -> done, other key -> next slot, empty -> claim it (CAS), busy
+// -> look again next round. Claimed slots get their ids, keys and state|meta published before the next round, and
+// nobody ever waits inside a round, so lanes of one warp holding the same new key cannot deadlock.
+template <int WORDS, int R>
+__device__ __forceinline__ void warp_intern(const GroupTable& t, const PackedKey (&k)[R], const bool (&active)[R],
+                                            uint32_t (&gid)[R]) {
+  constexpr int SW = WORDS == 1 ? 2 : 4, SMW = WORDS == 1 ? 1 : 2;
+  const uint32_t lane = threadIdx.x & 31, lt_mask = (1u << lane) - 1;
+  uint32_t idx[R], probes[R];
+  bool pend[R];
+  bool any = false;
+  // read once per call, not per empty slot: every SM polling one address is an L2 hot spot (25 M reads = 10+ ms)
+  const bool overflowed = *(volatile int32_t*)&t.flags[0] != 0;
+#pragma unroll
+  for (int u = 0; u < R; u++) {
+    idx[u] = (uint32_t)key_hash<WORDS>(k[u]) & t.mask;
+    probes[u] = 0;
+    pend[u] = active[u];
+    gid[u] = kNoGroup;
+    any |= pend[u];
+  }
+  while (__any_sync(0xffffffffu, any)) {
+    ulonglong2 sa[R];
+    uint64_t sm[R];
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      if (!pend[u]) continue;
+      const uint64_t* slot = t.slots + (size_t)idx[u] * SW;
+      sa[u] = __ldcg((const ulonglong2*)slot);
+      sm[u] = WORDS == 1 ? sa[u].y : __ldcg(slot + SMW);
+    }
+    any = false;
+    bool won[R];
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      won[u] = false;
+      if (!pend[u]) continue;
+      uint64_t* slot = t.slots + (size_t)idx[u] * SW;
+      const uint32_t state = (uint32_t)sm[u];
+      if (state >= 2u) {
+        bool same = (uint32_t)(sm[u] >> 32) == k[u].meta;
+        if (same) {
+          same = sa[u].x == k[u].k0 && (WORDS == 1 || sa[u].y == k[u].k1);
+          // the key words may predate the publication just observed: re-read them once before moving on
+          if (!same) same = *(volatile uint64_t*)slot == k[u].k0 && (WORDS == 1 || *(volatile uint64_t*)(slot + 1) == k[u].k1);
+        }
+        if (same) {
+          gid[u] = state - 2u;
+          pend[u] = false;
+        } else if (++probes[u] > t.mask) {
+          atomicOr(&t.flags[0], 1);  // table full
+          gid[u] = kGidOverflow;
+          pend[u] = false;
+        } else {
+          idx[u] = (idx[u] + 1) & t.mask;
+        }
+      } else if (state == 0u) {
+        if (overflowed) {  // the pass is void already: do not fill the table
+          gid[u] = kGidOverflow;
+          pend[u] = false;
+        } else {
+          won[u] = atomicCAS((unsigned long long*)(slot + SMW), 0ULL, 1ULL) == 0ULL;
+        }
+      }  // state == 1: an inserter is publishing; look again next round
+    }
+    // one id allocation per warp and round for every slot claimed in it
+    uint32_t winners[R], before[R], total = 0;
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      winners[u] = __ballot_sync(0xffffffffu, won[u]);
+      before[u] = total;
+      total += __popc(winners[u]);
+    }
+    if (total) {
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(t.n_groups, total);
+      base = __shfl_sync(0xffffffffu, base, 0);
+#pragma unroll
+      for (int u = 0; u < R; u++) {
+        if (!won[u]) continue;
+        uint64_t* slot = t.slots + (size_t)idx[u] * SW;
+        gid[u] = base + before[u] + __popc(winners[u] & lt_mask);
+        slot[0] = k[u].k0;
+        if (WORDS > 1) slot[1] = k[u].k1;
+        if (gid[u] >= t.max_groups) atomicOr(&t.flags[0], 1);
+      }
+      __threadfence();
+#pragma unroll
+      for (int u = 0; u < R; u++) {
+        if (!won[u]) continue;
+        uint64_t* slot = t.slots + (size_t)idx[u] * SW;
+        *(volatile uint64_t*)(slot + SMW) = ((uint64_t)k[u].meta << 32) | (uint64_t)(gid[u] + 2u);
+        pend[u] = false;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < R; u++) any |= pend[u];
+  }
+}
+
 // Per-CTA cache of (key -> gid) in shared memory in front of the global table: low-cardinality inputs resolve
 // every row from shared memory after the first few rows of the CTA.
 struct KeyCache {
@@ -604,8 +709,8 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
         Plan::template load0<7>(a, rn < rlast ? rn : rlast, early[u]);
       }
     };
-    auto stop = [&]() {  // some CTA gave up: the pass is void (polled every 16th tile: it only saves work)
-      return (++tiles_done & 15) == 0 && (*(volatile int*)&s_abort || *(volatile int*)&a.t.flags[3]);
+    auto stop = [&]() {  // this CTA or (polled every 16th tile) another one gave up: the pass is void
+      return *(volatile int*)&s_abort || ((++tiles_done & 15) == 0 && *(volatile int*)&a.t.flags[3]);
     };
     issue(fa, r0);
     for (;;) {  // (two tiles per trip with the register sets swapping roles spills at 96 registers: measured 30% slower)
@@ -716,13 +821,20 @@ __device__ __forceinline__ void intern_body(const JitArgs& a) {
       const int64_t r = base + u * T + threadIdx.x;
       Plan::template load2<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
     }
+    PackedKey k[R];
+    bool active[R];
+    uint32_t gid[R];
 #pragma unroll
     for (int u = 0; u < R; u++) {
       const int64_t r = base + u * T + threadIdx.x;
-      if (r > last) continue;
-      uint32_t gid = kNoGroup;
-      if (Plan::filter(a, x[u])) gid = intern<Plan::KEY_WORDS>(a.t, Plan::key(a, x[u]));
-      a.gids[r] = gid;
+      active[u] = r <= last && Plan::filter(a, x[u]);
+      k[u] = active[u] ? Plan::key(a, x[u]) : PackedKey{0, 0, 0};  // (a dropped row must not raise "key too long")
+    }
+    warp_intern<Plan::KEY_WORDS, R>(a.t, k, active, gid);
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      if (r <= last) a.gids[r] = gid[u];
     }
   }
 }

@@ -15,6 +15,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -559,8 +560,26 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
   return BGPU_OK;
 }
 
+// BGPU_AGG_TRACE=1: per-phase wall times of the two-pass path and of emit on stderr (each phase synchronises)
+struct PhaseTrace {
+  bgpu_ctx* ctx;
+  bool on;
+  std::chrono::steady_clock::time_point t0;
+  explicit PhaseTrace(bgpu_ctx* c) : ctx(c), on(getenv("BGPU_AGG_TRACE") != nullptr) {
+    if (on) { cudaStreamSynchronize(ctx->stream); t0 = std::chrono::steady_clock::now(); }
+  }
+  void mark(const char* what) {
+    if (!on) return;
+    cudaStreamSynchronize(ctx->stream);
+    const auto t1 = std::chrono::steady_clock::now();
+    fprintf(stderr, "[bgpu agg] %-14s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+    t0 = t1;
+  }
+};
+
 static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
   bgpu_ctx* ctx = g->ctx;
+  PhaseTrace trace(ctx);
   constexpr int T = 256, R = 4;
   BGPU_TRY(specialise(g, b, 2, T, R, 1));
   const int64_t tiles = ceil_div64(n_rows, (int64_t)T * R);
@@ -590,7 +609,9 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
     const uint64_t need = (uint64_t)g->n_groups + (uint64_t)(est * 1.10) + 1024;
     if (need > g->max_groups) {
       if (need > 0x70000000ULL) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
+      trace.mark("sketch");
       BGPU_TRY(agg_resize(g, next_pow2(need), g->n_groups));
+      trace.mark("resize");
     }
   }
   DevAllocPtr gids;
@@ -610,6 +631,7 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
     if (attempt >= 8) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
     BGPU_TRY(grow_after_overflow(g, h[0], n_rows));
   }
+  trace.mark("intern");
   refresh_pointers(g, b);
   if (b->ap.n == 0) { g->last_path = "intern"; return BGPU_OK; }
   const uint32_t ng = g->n_groups;
@@ -634,6 +656,7 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
     BGPU_TRY(jit_launch(ctx, b->mod->fn[JK_ACC_GLOBAL], grid, T, 0, &b->args));
     g->last_path = "global";
   }
+  trace.mark("accumulate");
   return BGPU_OK;
 }
 
@@ -661,7 +684,9 @@ extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) {
   }
   b.args.n_rows = n_rows;
   bool done = false;
+  PhaseTrace trace(ctx);
   if (g->fused_rung < kFusedRungs) BGPU_TRY(try_fused(g, &b, n_rows, &done));
+  trace.mark(done ? "fused" : "fused (void)");
   if (!done) BGPU_TRY(run_two_pass(g, &b, n_rows));
   return BGPU_OK;
 }
@@ -694,6 +719,7 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
   const uint32_t n = g->n_groups;
   std::unique_ptr<bgpu_batch> out(new bgpu_batch(ctx));
   out->n_rows = n;
+  PhaseTrace trace(ctx);
   const int grid = agg_launch_grid(ctx, std::max<uint32_t>(n, 1), kAggThreads);
   // dense key arrays (index = group id) out of the table slots
   DevAllocPtr d_key0, d_key1, d_kmeta;
@@ -711,6 +737,7 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
     ctx->launches++;
     BGPU_CUDA(ctx, cudaGetLastError());
   }
+  trace.mark("emit densify");
   // group key columns
   for (size_t i = 0; i < g->group_cols.size(); i++) {
     const Column& f = g->fields[(size_t)g->group_cols[i]];
@@ -761,6 +788,7 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
     BGPU_CUDA(ctx, cudaGetLastError());
     out->cols.push_back(std::move(c));
   }
+  trace.mark("emit keys");
   // aggregate columns
   auto acc_column = [&](int phys_idx, const std::string& name, const std::string& format, bool nullable_by_seen,
                         Column* c) -> int {
@@ -818,6 +846,7 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
   uint32_t h[8];
   BGPU_TRY(read_counters(g, h));
   if (h[3]) return ctx->fail(BGPU_EOVERFLOW, "Arithmetic overflow in a Decimal128 aggregate argument or AVG");
+  trace.mark("emit accs");
   g->emitted = true;
   *out_batch = out.release();
   return BGPU_OK;

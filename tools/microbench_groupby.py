@@ -101,7 +101,14 @@ lines = torch.randint(1, 8, (N_OK // 3 + 8,), device="cuda", generator=g)
 order = torch.repeat_interleave(torch.arange(lines.numel(), device="cuda"), lines)[:N_OK]
 okey = (order // 8) * 32 + order % 8 + 1          # dbgen's sparse order keys
 perm = torch.randperm(N_OK, device="cuda", generator=g)
-okey = okey[perm].contiguous()                    # unsorted input = worst case for the partial aggregate
+if os.environ.get("OK_SORTED"):   # dbgen's own order (clustered): the best case
+    pass
+elif os.environ.get("OK_BUCKETED"):  # rows grouped into B hash buckets, unsorted inside
+    nb = int(os.environ["OK_BUCKETED"])
+    okey = okey[perm]
+    okey = okey[torch.argsort((okey * 0x9E3779B97F4A7C15) >> 40 & (nb - 1), stable=True)].contiguous()
+else:
+    okey = okey[perm].contiguous()                    # unsorted input = worst case for the partial aggregate
 n_groups = int(torch.unique(okey).numel())
 
 
