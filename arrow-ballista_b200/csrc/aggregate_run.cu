@@ -580,8 +580,14 @@ struct PhaseTrace {
 static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
   bgpu_ctx* ctx = g->ctx;
   PhaseTrace trace(ctx);
-  constexpr int T = 256, R = 4;
-  BGPU_TRY(specialise(g, b, 2, T, R, 1));
+  int T = 256, R = 8, min_ctas = 2;  // 8 rows per lane in flight: the probes are DRAM round trips (R = 4: 7.1 ms intern, R = 8: 5.8 ms per 1e8 rows)
+  if (const char* e = getenv("BGPU_TWOPASS_GEOMETRY")) {  // tuning knob: "threads,rows,ctas_per_sm"
+    int t = 0, r = 0, c = 0;
+    if (sscanf(e, "%d,%d,%d", &t, &r, &c) == 3 && t >= 32 && t <= 1024 && t % 32 == 0 && r >= 1 && r <= 16 && c >= 1 && c <= 8) {
+      T = t; R = r; min_ctas = c;
+    }
+  }
+  BGPU_TRY(specialise(g, b, 2, T, R, min_ctas));
   const int64_t tiles = ceil_div64(n_rows, (int64_t)T * R);
   // A batch with more rows than the table has room for may overflow it, and every overflow costs a full extra pass:
   // estimate the batch's distinct keys first (linear counting over a bitmap, one cheap pass over the key columns)
