@@ -12,3 +12,4 @@ from .expr import Column, Literal, BinaryExpr, col, lit  # noqa: F401
 from . import expr  # noqa: F401
 from .exchange import Exchange, exchange_plan, owner_of  # noqa: F401
 from .shuffle_writer import GpuShuffleWriterExec, ShuffleWritePartition, result_schema  # noqa: F401
+from . import ipc  # noqa: F401

@@ -13,8 +13,12 @@
   * `execute()` (:518-579) wraps the result as one batch with `result_schema()` (:590-597)
   * metrics `write_time`, `repart_time`, `input_rows`, `output_rows` (:139-163)
 
-The IPC encoding itself stays on the host (pyarrow's writer stands in for arrow-ipc's `StreamWriter`; SURVEY.md §8f-1
-ranks a device-side encoder next). Inside one NVSwitch node the files are bypassed altogether: see `exchange.py`.
+IPC framing: with `ipc="device"` (the default whenever the schema has no dictionary column) the
+RecordBatch messages are produced by libbgpu (`ipc.py`: bodies laid out by one kernel, one device-to-host copy,
+hand-built flatbuffer metadata) and appended to the partition files as they are - uncompressed Arrow IPC streams, which
+the reference's `StreamReader` reads like its own LZ4_FRAME ones. With `ipc="host"` (and for dictionary columns)
+pyarrow's writer stands in for arrow-ipc's `StreamWriter`, LZ4_FRAME as the reference writes. Inside one NVSwitch node
+the files are bypassed altogether: see `exchange.py`.
 """
 import os
 import time
@@ -23,9 +27,10 @@ from dataclasses import dataclass, field
 
 import pyarrow as pa
 
+from . import ipc
 from ._lib import BGPU_EINVAL, BgpuError
 from .partitioner import BatchPartitioner, Partitioning
-from .runtime import Context
+from .runtime import Context, DeviceBatch
 
 
 @dataclass
@@ -75,6 +80,28 @@ class _WriteTracker:
         return num_bytes
 
 
+class _IpcStreamFile:
+    """A partition file fed with ready-made IPC messages (ipc.encode_partitions)."""
+
+    def __init__(self, path, schema_msg):
+        self.path, self.num_batches, self.num_rows = path, 0, 0
+        self._sink = open(path, "wb")
+        self._sink.write(schema_msg)
+
+    def write_message(self, msg, rows):
+        self._sink.write(msg)
+        self.num_batches += 1
+        self.num_rows += rows
+
+    def finish(self):
+        """Returns the file length as the reference takes it: before the end-of-stream marker is written."""
+        self._sink.flush()
+        num_bytes = os.path.getsize(self.path)
+        self._sink.write(ipc.EOS)
+        self._sink.close()
+        return num_bytes
+
+
 class GpuShuffleWriterExec:
     """ShuffleWriterExec whose `Partitioning::Hash` arm runs on the B200.
 
@@ -83,7 +110,8 @@ class GpuShuffleWriterExec:
     """
 
     def __init__(self, job_id, stage_id, partitions, plan, work_dir, shuffle_output_partitioning, ctx=None,
-                 input_schema=None, input_partitioning=None):
+                 input_schema=None, input_partitioning=None, ipc=None):
+        self.ipc = ipc  # "device", "host" or None = device unless the schema has a dictionary column
         self.job_id, self.stage_id, self.partitions = str(job_id), int(stage_id), list(partitions)
         self.plan, self.work_dir = plan, str(work_dir)
         self.shuffle_output_partitioning = shuffle_output_partitioning
@@ -146,6 +174,12 @@ class GpuShuffleWriterExec:
         if self.ctx is None:
             self.ctx = Context(0)
         partitioner = BatchPartitioner.try_new(Partitioning.Hash(part.exprs, n), self.ctx, m.repart_time)
+        mode = self.ipc
+        if mode is None:
+            sch = self._schema
+            mode = "host" if sch is not None and any(pa.types.is_dictionary(f.type) for f in sch) else "device"
+        if mode == "device":
+            return self._write_device_ipc(base, shuffle_id, partitioner, n)
 
         def on_partition(output_partition, output_batch):
             # the partitioner never hands over an empty batch (shuffle_writer.rs:349)
@@ -162,6 +196,43 @@ class GpuShuffleWriterExec:
         for input_batch in self._stream():
             m.input_rows += input_batch.num_rows
             partitioner.partition(input_batch, on_partition)
+        part_locs = []
+        for i, w in enumerate(writers):
+            if w is not None:
+                num_bytes = w.finish()
+                part_locs.append(ShuffleWritePartition([int(p) for p in self.partitions], i, w.path, w.num_batches,
+                                                       w.num_rows, num_bytes))
+        return part_locs
+
+    def _write_device_ipc(self, base, shuffle_id, partitioner, n):
+        """Hash arm with the IPC messages framed by libbgpu: partition on the device, encode every non-empty partition
+        of the batch in one call, append the messages to the partition files."""
+        m = self.metrics
+        writers = [None] * n
+        schema_msg = None
+        for input_batch in self._stream():
+            m.input_rows += input_batch.num_rows
+            if input_batch.num_rows == 0:
+                continue
+            if schema_msg is None:
+                schema_msg = ipc.schema_message(self._schema if isinstance(input_batch, DeviceBatch) else input_batch.schema, self.ctx)
+            dbatch = input_batch if isinstance(input_batch, DeviceBatch) else DeviceBatch.upload(self.ctx, input_batch)
+            out, offs = partitioner.partition_device(dbatch)
+            t0 = time.perf_counter()
+            enc = ipc.encode_partitions(self.ctx, out, offs)
+            for p in range(n):
+                rows = offs[p + 1] - offs[p]
+                if rows == 0:
+                    continue  # the writer never sees an empty batch (shuffle_writer.rs:349)
+                w = writers[p]
+                if w is None:
+                    d = os.path.join(base, str(p))
+                    os.makedirs(d, exist_ok=True)
+                    w = writers[p] = _IpcStreamFile(os.path.join(d, f"{shuffle_id}.arrow"), schema_msg)
+                w.write_message(enc.message(p), rows)
+                m.output_rows += rows
+            enc.close()
+            m.write_time += time.perf_counter() - t0
         part_locs = []
         for i, w in enumerate(writers):
             if w is not None:

@@ -204,6 +204,29 @@ void bgpu_nccl_comm_destroy(void* comm);
 uint64_t bgpu_exchange_plan(const uint64_t* all_offsets, int32_t rank, int32_t world, uint32_t n_partitions,
                             uint64_t* recv_off, uint32_t* n_owned);
 
+/* ---- Arrow IPC stream framing of partitioned device batches --------------------------------------
+ * Replaces arrow-ipc's StreamWriter as ShuffleWriterExec drives it, one `write(batch)` per non-empty output partition
+ * (/root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:351-399; IPCWriter,
+ * /root/reference/ballista/core/src/utils.rs:63-141). A partition file is: schema message, the RecordBatch messages
+ * appended to it, then the end-of-stream marker (ff ff ff ff 00 00 00 00). Messages are uncompressed, metadata
+ * version V5, buffers 8-byte aligned. Dictionary columns: BGPU_EUNSUPPORTED.
+ *
+ * bgpu_ipc_schema_message: the encapsulated Schema message of a struct-typed ArrowSchema (host only; malloc'ed: free
+ *   with bgpu_ipc_free(p, 0)).
+ * bgpu_ipc_record_batch_metadata: the 8-byte prefix + RecordBatch metadata of one message, for callers that lay the
+ *   body out themselves (host only; nodes = (length, null_count) pairs, buffers = (offset, length) pairs; malloc'ed).
+ * bgpu_ipc_encode_partitions: one encapsulated RecordBatch message per non-empty partition p = rows
+ *   [offsets[p], offsets[p + 1]) of `batch`; bodies are laid out by one kernel on the device and arrive with one copy.
+ *   *out_bytes (pinned host memory; free with bgpu_ipc_free(p, 1); NULL when every partition is empty) holds the
+ *   messages back to back: message p = bytes [out_msg_off[p], out_msg_off[p + 1]) (empty range = empty partition).
+ *   out_msg_off has n + 1 entries. */
+int bgpu_ipc_schema_message(bgpu_ctx* ctx, const struct ArrowSchema* schema, uint8_t** out_bytes, uint64_t* out_len);
+int bgpu_ipc_record_batch_metadata(bgpu_ctx* ctx, int64_t rows, const int64_t* nodes, int32_t n_nodes, const int64_t* buffers,
+                                   int32_t n_buffers, int64_t body_len, uint8_t** out_bytes, uint64_t* out_len);
+int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch, const uint64_t* offsets, uint32_t n,
+                               uint8_t** out_bytes, uint64_t* out_msg_off);
+void bgpu_ipc_free(uint8_t* bytes, int pinned);
+
 #ifdef __cplusplus
 }
 #endif

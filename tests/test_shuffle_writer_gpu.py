@@ -27,13 +27,14 @@ def read_ipc(path):
         return r.read_all()
 
 
+@pytest.mark.parametrize("ipc", ["device", "host"])  # libbgpu's IPC framing / pyarrow's writer (LZ4_FRAME)
 @pytest.mark.parametrize("copies,total", [(4, 8), (2, 4)])  # `test` coalesces 2 partitions x 2 batches; `test_partitioned` reads one
-def test_reference_shuffle_writer_tests(bb, ctx, oracle, tmp_path, copies, total):
+def test_reference_shuffle_writer_tests(bb, ctx, oracle, tmp_path, copies, total, ipc):
     from ballista_b200.shuffle_writer import GpuShuffleWriterExec, result_schema
 
     batches, schema = create_input_batches(copies)
     query_stage = GpuShuffleWriterExec.try_new("jobOne", 1, [0], batches, str(tmp_path), bb.Partitioning.Hash([0], 2), ctx,
-                                               input_schema=schema)
+                                               input_schema=schema, ipc=ipc)
     out = query_stage.execute(0)
     assert len(out) == 1
     batch = out[0]
@@ -61,12 +62,13 @@ def test_reference_shuffle_writer_tests(bb, ctx, oracle, tmp_path, copies, total
     assert m.input_rows == total and m.output_rows == total
 
 
-def test_written_partitions_match_oracle(bb, ctx, oracle, tmp_path):
+@pytest.mark.parametrize("with_dict", [False, True])  # no dictionary column: device IPC framing; with one: host framing
+def test_written_partitions_match_oracle(bb, ctx, oracle, tmp_path, with_dict):
     from ballista_b200.shuffle_writer import GpuShuffleWriterExec
     from helpers import random_batch
 
     rng = np.random.default_rng(3)
-    batches = [random_batch(rng, n) for n in (5000, 1, 8192, 0, 777)]
+    batches = [random_batch(rng, n, with_dict=with_dict) for n in (5000, 1, 8192, 0, 777)]
     keys, n = [0, 9], 7  # k64 + a Utf8 column with nulls
     ex = GpuShuffleWriterExec.try_new("job", 3, [0, 1], batches, str(tmp_path), bb.Partitioning.Hash(keys, n), ctx,
                                       input_schema=batches[0].schema)
@@ -96,3 +98,34 @@ def test_unpartitioned_and_invalid_scheme(bb, ctx, tmp_path):
                                        input_schema=schema)
     with pytest.raises(bb.BgpuError, match="Invalid shuffle partitioning scheme"):
         bad.execute_shuffle_write()
+
+
+def test_device_ipc_messages_are_plain_arrow_streams(bb, ctx, oracle):
+    """ipc.encode_partitions directly: every partition's message, framed by the schema message and the end-of-stream
+    marker, reads back (pyarrow) as exactly the oracle's partition - nulls, empty strings, booleans, decimals, a
+    partition count that leaves some partitions empty, and null counts in the metadata."""
+    import io
+
+    from ballista_b200 import ipc
+    from helpers import random_batch
+
+    rng = np.random.default_rng(11)
+    for rows, n in ((3000, 5), (40, 64), (1, 3)):
+        batch = random_batch(rng, rows, null_frac=0.3, with_dict=False)
+        part, offs = bb.BatchPartitioner.try_new(bb.Partitioning.Hash([0, 1], n), ctx).partition_device(
+            bb.DeviceBatch.upload(ctx, batch))
+        enc = ipc.encode_partitions(ctx, part, offs)
+        want = dict(oracle.partition(batch, [0, 1], n)[0])
+        schema_msg = ipc.schema_message(batch.schema)
+        assert sum(1 for p in range(n) if len(enc.message(p))) == len(want)
+        for p in range(n):
+            msg = bytes(enc.message(p))
+            if p not in want:
+                assert msg == b""
+                continue
+            got = pa.ipc.open_stream(io.BytesIO(schema_msg + msg + ipc.EOS)).read_all()
+            assert got.num_rows == want[p].num_rows
+            assert got.equals(pa.Table.from_batches([want[p]])), f"partition {p} differs"
+            for a, b in zip(got.columns, want[p].columns):
+                assert a.null_count == b.null_count
+        enc.close()
