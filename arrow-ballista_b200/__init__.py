@@ -13,3 +13,5 @@ from . import expr  # noqa: F401
 from .exchange import Exchange, exchange_plan, owner_of  # noqa: F401
 from .shuffle_writer import GpuShuffleWriterExec, ShuffleWritePartition, result_schema  # noqa: F401
 from . import ipc  # noqa: F401
+from .shuffle_reader import (CoalesceBatchesExec, CoalesceTasksExec, ExecutorMetadata, FetchFailed, GpuShuffleReaderExec,  # noqa: F401
+                             PartitionLocation, PartitionStats)

@@ -97,6 +97,12 @@ SIGNATURES = {
     "bgpu_ipc_encode_partitions": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.c_uint32,
                                              C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
     "bgpu_ipc_free": (None, [C.c_void_p, C.c_int]),
+    "bgpu_ipc_reader_open": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]),
+    "bgpu_ipc_reader_schema": (C.c_int, [C.c_void_p, C.POINTER(ArrowSchema)]),
+    "bgpu_ipc_reader_next": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "bgpu_ipc_reader_close": (None, [C.c_void_p]),
+    "bgpu_debug_lz4_frame_decode_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]),
+    "bgpu_batch_concat": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int32, C.POINTER(C.c_void_p)]),
 }
 
 _lib = None

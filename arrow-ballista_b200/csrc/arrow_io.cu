@@ -323,6 +323,9 @@ void device_column(const Column& c, ArrowArray* a) {
 }
 }  // namespace
 
+// schema of a batch as an Arrow C schema (used by the IPC reader for streams without batches)
+void export_batch_schema(const bgpu_batch* b, struct ArrowSchema* out) { batch_schema(b, out); }
+
 extern "C" int bgpu_batch_download(bgpu_ctx* ctx, const bgpu_batch* b, int64_t row_offset, int64_t num_rows,
                                    struct ArrowArray* out, struct ArrowSchema* out_schema) {
   if (!ctx || !b || !out || !out_schema) return BGPU_EINVAL;

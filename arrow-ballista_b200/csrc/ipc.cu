@@ -118,7 +118,7 @@ class Fbb {
 };
 
 // Arrow's Schema.fbs / Message.fbs, the part this path needs
-enum FbType : uint8_t { T_Int = 2, T_FloatingPoint = 3, T_Binary = 4, T_Utf8 = 5, T_Bool = 6, T_Decimal = 7, T_Date = 8, T_Timestamp = 10 };
+enum FbType : uint8_t { T_Int = 2, T_FloatingPoint = 3, T_Binary = 4, T_Utf8 = 5, T_Bool = 6, T_Decimal = 7, T_Date = 8, T_Time = 9, T_Timestamp = 10 };
 enum FbHeader : uint8_t { H_Schema = 1, H_RecordBatch = 3 };
 constexpr int16_t kMetadataV5 = 4;
 
@@ -171,6 +171,17 @@ bool fb_type(Fbb& b, const std::string& f, uint8_t* type_type, uint32_t* type_of
     b.start_table(1);
     b.add<int16_t>(0, f == "tdD" ? 0 : 1);
     *type_type = T_Date;
+    *type_off = b.end_table();
+    return true;
+  }
+  if (f.size() == 3 && f.rfind("tt", 0) == 0) {
+    const char u = f[2];
+    const int unit = u == 's' ? 0 : u == 'm' ? 1 : u == 'u' ? 2 : u == 'n' ? 3 : -1;
+    if (unit < 0) return false;
+    b.start_table(2);
+    b.add<int16_t>(0, (int16_t)unit);
+    b.add<int32_t>(1, unit <= 1 ? 32 : 64);
+    *type_type = T_Time;
     *type_off = b.end_table();
     return true;
   }

@@ -94,3 +94,63 @@ def encode_partitions(ctx, device_batch, offsets):
     p = C.c_void_p()
     ctx.check(lib().bgpu_ipc_encode_partitions(ctx._h, device_batch._h, offs, n, C.byref(p), msg_off))
     return EncodedPartitions(p if p.value else None, list(msg_off))
+
+
+class StreamReader:
+    """Arrow IPC stream (bytes-like, host memory) -> DeviceBatches: the device-side `AsyncStreamReader`
+    (/root/reference/ballista/core/src/async_reader/mod.rs:108-258). Reads the reference's LZ4_FRAME partition files
+    (blocks decoded by a kernel) and the uncompressed ones `encode_partitions` writes. Iterable."""
+
+    def __init__(self, ctx, data):
+        import numpy as np
+
+        self.ctx = ctx
+        self._buf = np.frombuffer(data, dtype=np.uint8)  # zero-copy view; keeps `data` alive for the reader
+        self._h = C.c_void_p()
+        ctx.check(lib().bgpu_ipc_reader_open(ctx._h, C.c_void_p(self._buf.ctypes.data), self._buf.size, C.byref(self._h)))
+        self.num_batches = self.num_rows = 0
+
+    @property
+    def schema(self):
+        import pyarrow as pa
+
+        s = ArrowSchema()
+        self.ctx.check(lib().bgpu_ipc_reader_schema(self._h, C.byref(s)))
+        return pa.Schema._import_from_c(C.addressof(s))
+
+    def maybe_next(self):
+        """The next batch on the device, or None at the end of the stream (`maybe_next`, async_reader/mod.rs:168)."""
+        from .runtime import DeviceBatch
+
+        out = C.c_void_p()
+        self.ctx.check(lib().bgpu_ipc_reader_next(self._h, C.byref(out)))
+        if not out.value:
+            return None
+        b = DeviceBatch(self.ctx, out)
+        self.num_batches += 1
+        self.num_rows += b.num_rows
+        return b
+
+    def __iter__(self):
+        while True:
+            b = self.maybe_next()
+            if b is None:
+                return
+            yield b
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().bgpu_ipc_reader_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+
+def lz4_frame_decode_host(frame, out_len, ctx=None):
+    """TEST HOOK: the library's LZ4 frame walker + block decoder run on the host with one lane (the kernel's logic)."""
+    ctx = ctx or _HostContext()
+    out = (C.c_ubyte * max(1, out_len))()
+    src = (C.c_ubyte * max(1, len(frame))).from_buffer_copy(bytes(frame) or b"\0")
+    ctx.check(lib().bgpu_debug_lz4_frame_decode_host(ctx._h, src, len(frame), out, out_len))
+    return bytes(out[:out_len])

@@ -145,6 +145,15 @@ class DeviceBatch:
         self.ctx.check(lib().bgpu_batch_download(self.ctx._h, self._h, offset, length, C.byref(a), C.byref(s)))
         return pa.RecordBatch._import_from_c(C.addressof(a), C.addressof(s))
 
+    @classmethod
+    def concat(cls, ctx, batches):
+        """Rows of `batches` (one schema) in order as one DeviceBatch (bgpu_batch_concat; `concat_batches` of
+        CoalesceBatchesExec, planned at /root/reference/ballista/scheduler/src/planner.rs:386-387)."""
+        hs = (C.c_void_p * len(batches))(*[b._h for b in batches])
+        out = C.c_void_p()
+        ctx.check(lib().bgpu_batch_concat(ctx._h, hs, len(batches), C.byref(out)))
+        return cls(ctx, out)
+
     def close(self):
         if getattr(self, "_h", None):
             lib().bgpu_batch_destroy(self._h)

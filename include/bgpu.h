@@ -227,6 +227,35 @@ int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch, const uin
                                uint8_t** out_bytes, uint64_t* out_msg_off);
 void bgpu_ipc_free(uint8_t* bytes, int pinned);
 
+/* ---- Arrow IPC stream reader into device batches: the inverse of the above ----------------
+ * Replaces `AsyncStreamReader::{try_new, maybe_next}` (/root/reference/ballista/core/src/async_reader/mod.rs:108-258)
+ * as `fetch_partition_local_inner` drives it over one shuffle partition file
+ * (/root/reference/ballista/core/src/execution_plans/shuffle_reader.rs:771-785): the Schema message first, then one
+ * device batch per RecordBatch message until the end-of-stream marker, a zero length or plain EOF. Reads what the
+ * reference's ShuffleWriterExec writes (LZ4_FRAME buffer compression, shuffle_writer.rs:365-376: block-independent and
+ * block-linked frames, stored buffers with the -1 prefix) and what bgpu_ipc_encode_partitions writes (uncompressed).
+ * LZ4 blocks are decoded on the device, one decode chain per warp. `bytes` is borrowed host memory that must stay valid
+ * until bgpu_ipc_reader_close; each bgpu_ipc_reader_next returns with its copies out of it completed.
+ * Errors: BGPU_EINVAL for malformed streams (messages "Unable to read IPC message as schema", "Not expecting a schema
+ * when messages are read" as the reference's reader words them), BGPU_EUNSUPPORTED for dictionary batches, ZSTD,
+ * big-endian streams and types off the path. */
+typedef struct bgpu_ipc_reader bgpu_ipc_reader;
+int bgpu_ipc_reader_open(bgpu_ctx* ctx, const uint8_t* bytes, uint64_t len, bgpu_ipc_reader** out); /* host only */
+int bgpu_ipc_reader_schema(bgpu_ipc_reader* reader, struct ArrowSchema* out);                       /* host only */
+int bgpu_ipc_reader_next(bgpu_ipc_reader* reader, bgpu_batch** out); /* *out = NULL at the end of the stream */
+void bgpu_ipc_reader_close(bgpu_ipc_reader* reader);
+/* test hook (host, one lane): the LZ4 frame walker + block decoder the device kernel is built from; never called by
+ * the library itself */
+int bgpu_debug_lz4_frame_decode_host(bgpu_ctx* ctx, const uint8_t* frame, uint64_t len, uint8_t* out, uint64_t out_len);
+
+/* ---- concatenation of device batches ---------------------------------------------------------------
+ * Replaces `concat_batches` as CoalesceBatchesExec(target_batch_size) applies it above the shuffle reader
+ * (plan pinned at /root/reference/ballista/scheduler/src/planner.rs:386-387, 409-413): rows of batches[0..n) in order,
+ * all of one schema. One kernel moves every buffer (values copied, utf8 offsets rebased onto the running byte total,
+ * validity / boolean bitmaps re-aligned to the running row total; a column is nullable in the result when any input
+ * has nulls). Dictionary columns: BGPU_EUNSUPPORTED. */
+int bgpu_batch_concat(bgpu_ctx* ctx, const bgpu_batch* const* batches, int32_t n, bgpu_batch** out);
+
 #ifdef __cplusplus
 }
 #endif
