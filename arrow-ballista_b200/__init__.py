@@ -15,3 +15,4 @@ from .shuffle_writer import GpuShuffleWriterExec, ShuffleWritePartition, result_
 from . import ipc  # noqa: F401
 from .shuffle_reader import (CoalesceBatchesExec, CoalesceTasksExec, ExecutorMetadata, FetchFailed, GpuShuffleReaderExec,  # noqa: F401
                              PartitionLocation, PartitionStats)
+from .codec import GpuAggregateExecNode, GpuPhysicalCodec  # noqa: F401

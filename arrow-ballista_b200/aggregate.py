@@ -49,7 +49,7 @@ class GpuAggregateExec:
         from ._lib import ExprNode
         from .expr import Expr, col
 
-        self.ctx, self.mode, self.input_schema = ctx, mode, input_schema
+        self.ctx, self.mode, self.input_schema, self.filter = ctx, mode, input_schema, filter
         self.group_by = list(group_by)
         self.aggr_expr = []
         nodes, offsets = [], [0]
