@@ -91,6 +91,11 @@ SIGNATURES = {
                                         C.POINTER(C.c_uint32)]),
     "bgpu_all_to_all": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_uint64),
                                   C.c_uint32, C.POINTER(C.c_void_p)]),
+    "bgpu_peer_exchange_create": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_uint64, C.POINTER(C.c_void_p)]),
+    "bgpu_partition_exchange": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_uint32,
+                                          C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "bgpu_peer_exchange_window_bytes": (C.c_uint64, [C.c_void_p]),
+    "bgpu_peer_exchange_destroy": (None, [C.c_void_p]),
     "bgpu_ipc_schema_message": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
     "bgpu_ipc_record_batch_metadata": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_int32, C.POINTER(C.c_int64),
                                                  C.c_int32, C.c_int64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),

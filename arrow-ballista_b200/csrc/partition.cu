@@ -733,3 +733,5 @@ extern "C" int bgpu_hash_partition_host(bgpu_ctx* ctx, const struct ArrowArray* 
   bgpu_batch_destroy(in);
   return rc;
 }
+
+#include "peer_exchange.cuh"

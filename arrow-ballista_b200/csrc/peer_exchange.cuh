@@ -1,0 +1,480 @@
+// Fused hash repartition + exchange over NVLink peer memory (K3 + K6 in one kernel). Part of partition.cu's
+// translation unit (it reuses the count / scan kernels and the tile ranking of the scatter).
+//
+// Replaces, inside one NVSwitch node, BatchPartitioner::partition + shuffle file write + Flight do_get + reader fan-in
+// (/root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:336-391,
+// /root/reference/ballista/executor/src/flight_service.rs:124-166,
+// /root/reference/ballista/core/src/execution_plans/shuffle_reader.rs:539-624) for batches of fixed-width columns
+// (aggregate states): the scatter kernel ranks a tile by partition exactly as K3 does and then stores every run
+// STRAIGHT INTO THE OWNER RANK'S RECEIVE WINDOW (cudaIpc-mapped peer memory, plain 4/8/16-byte stores over NVLink), so
+// rows cross the link once, while the next tile is being ranked - no partitioned copy in local HBM, no send/recv staging.
+// The result is identical to bgpu_all_to_all(bgpu_hash_partition(batch)): rows grouped by (owned partition ascending,
+// source rank ascending), input order kept inside each group.
+//
+// Protocol (every rank, on its ctx stream; NCCL is used for the two tiny collectives only):
+//   1. count_kernel + scan_kernel: rows per partition of the local batch and base[p][chunk]
+//   2. ncclAllGather of the (n + 1) partition offsets + a "can fuse" flag -> every rank knows every count, so every rank
+//      computes every receive layout (bgpu_exchange_plan) and the same decisions (fallback, window growth)
+//      [this collective also orders the peers' stores after the owner's copy-out of the previous exchange]
+//   3. base[p][chunk] += (first row of (p, this rank) in the owner's window) - offsets[p]
+//   4. scatter_peer_kernel: out pointer of a run = window of owner(p) + column region + row * width
+//   5. ncclAllGather of one word: all ranks' stores have landed
+//   6. copy the window's column regions out into the result batch (local HBM copy; the window is reused)
+#include "nccl_dl.h"
+
+namespace bgpu {
+
+constexpr int kMaxPeers = 16;
+
+template <int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS, 2)
+    scatter_peer_kernel(const __grid_constant__ KeySet ks, const __grid_constant__ Modulo mod,
+                        const __grid_constant__ ScatterArgs args, int64_t n_rows, int64_t chunk_rows,
+                        const uint64_t* __restrict__ base /* [n][gridDim.x], window rows */,
+                        void* const* __restrict__ peer_out /* [n_async][world] column regions in the owners' windows */, int world) {
+  constexpr int kTile = THREADS * ITEMS;
+  extern __shared__ __align__(16) unsigned char smem[];
+  const uint32_t n = mod.n;
+  unsigned char* sp = smem;
+  unsigned char* stage = sp;              sp += (size_t)kTile * args.async_width;
+  sp = (unsigned char*)(((uintptr_t)sp + 15) & ~(uintptr_t)15);
+  int64_t* gdelta = (int64_t*)sp;         sp += (size_t)n * 8;
+  uint64_t* chunk_base = (uint64_t*)sp;   sp += (size_t)n * 8;
+  uint32_t* warp_cnt = (uint32_t*)sp;     sp += (size_t)(THREADS / 32) * n * 4;
+  uint32_t* tile_off = (uint32_t*)sp;     sp += (size_t)n * 4;
+  uint32_t* tile_cnt = (uint32_t*)sp;     sp += (size_t)n * 4;
+  uint16_t* pid_sorted = (uint16_t*)sp;   sp += (size_t)kTile * 2;
+  sp = (unsigned char*)(((uintptr_t)sp + 7) & ~(uintptr_t)7);
+  void** s_out = (void**)sp;              // [n_async][world]
+  __shared__ uint32_t s_scan[(THREADS / 32)];
+
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t lt_mask = (1u << lane) - 1;
+  const int64_t begin = (int64_t)blockIdx.x * chunk_rows;
+  int64_t end = begin + chunk_rows;
+  if (end > n_rows) end = n_rows;
+  for (uint32_t p = threadIdx.x; p < n; p += THREADS) chunk_base[p] = base[(size_t)p * gridDim.x + blockIdx.x];
+  for (int i = threadIdx.x; i < args.n_async * world; i += THREADS) s_out[i] = peer_out[i];
+
+  uint64_t next_key[ITEMS];
+  auto prefetch_keys = [&](int64_t tb) {
+    if (!ks.fast64) return;
+    const uint64_t* keys = (const uint64_t*)ks.cols[0].values;
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+      const int64_t r = tb + w * (32 * ITEMS) + it * 32 + lane;
+      next_key[it] = r < end ? __ldg(keys + r) : 0;
+    }
+  };
+  prefetch_keys(begin);
+
+  for (int64_t tile_base = begin; tile_base < end; tile_base += kTile) {
+    const int tile_n = (int)((end - tile_base) < kTile ? (end - tile_base) : kTile);
+    for (uint32_t i = threadIdx.x; i < (THREADS / 32) * n; i += THREADS) warp_cnt[i] = 0;
+    __syncthreads();
+    // 1. partition id and stable rank within this warp's segment (as scatter_kernel)
+    uint32_t pid[ITEMS], pos[ITEMS];
+    uint32_t* wc = warp_cnt + (size_t)w * n;
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+      const int local = w * (32 * ITEMS) + it * 32 + lane;
+      const bool valid = local < tile_n;
+      pid[it] = valid ? partition_of(ks.fast64 ? hash_u64(next_key[it]) : row_hash(ks, tile_base + local), mod) : 0xffffffffu;
+    }
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+      const uint32_t peers = match_peers(pid[it]);
+      const int leader = __ffs(peers) - 1;
+      uint32_t old = 0;
+      if (lane == leader && pid[it] != 0xffffffffu) {
+        old = wc[pid[it]];
+        wc[pid[it]] = old + __popc(peers);
+      }
+      old = __shfl_sync(0xffffffffu, old, leader);
+      pos[it] = old + __popc(peers & lt_mask);
+      __syncwarp();
+    }
+    __syncthreads();
+    // 2. per partition: exclusive scan over warps, tile totals, exclusive scan over partitions
+    for (uint32_t p = threadIdx.x; p < n; p += THREADS) {
+      uint32_t run = 0;
+#pragma unroll
+      for (int ww = 0; ww < (THREADS / 32); ww++) {
+        const uint32_t c = warp_cnt[(size_t)ww * n + p];
+        warp_cnt[(size_t)ww * n + p] = run;
+        run += c;
+      }
+      tile_cnt[p] = run;
+    }
+    __syncthreads();
+    {
+      const uint32_t per = (n + THREADS - 1) / THREADS;
+      const uint32_t p0 = threadIdx.x * per;
+      uint32_t sum = 0;
+      for (uint32_t k = 0; k < per; k++)
+        if (p0 + k < n) sum += tile_cnt[p0 + k];
+      uint32_t x = sum;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x += y;
+      }
+      if (lane == 31) s_scan[w] = x;
+      __syncthreads();
+      uint32_t wpre = 0;
+      for (int ww = 0; ww < w; ww++) wpre += s_scan[ww];
+      uint32_t run = wpre + x - sum;
+      for (uint32_t k = 0; k < per; k++)
+        if (p0 + k < n) {
+          const uint32_t p = p0 + k;
+          tile_off[p] = run;
+          gdelta[p] = (int64_t)chunk_base[p] - (int64_t)run;  // sorted position -> row in the owner's window
+          chunk_base[p] += tile_cnt[p];
+          run += tile_cnt[p];
+        }
+    }
+    __syncthreads();
+    // 3. position of every row in the partition-ordered tile; all columns go in flight
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) {
+      if (pid[it] != 0xffffffffu) {
+        pos[it] += tile_off[pid[it]] + wc[pid[it]];
+        pid_sorted[pos[it]] = (uint16_t)pid[it];
+      }
+    }
+    {
+      const int first = w * (32 * ITEMS) + lane;
+      const int valid_items = first < tile_n ? (tile_n - first + 31) / 32 : 0;
+      const int64_t r0 = tile_base + first;
+      const uint32_t stage_s = (uint32_t)__cvta_generic_to_shared(stage);
+      for (int c = 0; c < args.n_async; c++) {
+        const AsyncCol& ac = args.async_cols[c];
+        const uint32_t st = stage_s + (uint32_t)ac.stage_off * kTile;
+        if (ac.width == 8) stage_async<THREADS, ITEMS, uint64_t>((const uint64_t*)ac.in + r0, st, valid_items, pos);
+        else if (ac.width == 16) stage_async<THREADS, ITEMS, uint4>((const uint4*)ac.in + r0, st, valid_items, pos);
+        else stage_async<THREADS, ITEMS, uint32_t>((const uint32_t*)ac.in + r0, st, valid_items, pos);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    prefetch_keys(tile_base + kTile);
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();
+    // 4. runs go out: sorted position j -> (owner rank, row in its window), once for all columns; a run of one
+    //    partition is contiguous in the owner's window, so the stores of a warp coalesce into full NVLink packets
+    {
+      int64_t d[ITEMS];
+      int own[ITEMS];
+#pragma unroll
+      for (int k = 0; k < ITEMS; k++) {
+        const int j = threadIdx.x + k * THREADS;
+        if (j < tile_n) {
+          const uint32_t p = pid_sorted[j];
+          d[k] = (int64_t)j + gdelta[p];
+          own[k] = (int)(p % (uint32_t)world);
+        } else {
+          d[k] = -1;
+          own[k] = 0;
+        }
+      }
+      for (int c = 0; c < args.n_async; c++) {
+        const AsyncCol& ac = args.async_cols[c];
+        const unsigned char* st = stage + (size_t)ac.stage_off * kTile;
+        void* const* outs = s_out + c * world;
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+          if (d[k] < 0) continue;
+          const int j = threadIdx.x + k * THREADS;
+          if (ac.width == 8) ((uint64_t*)outs[own[k]])[d[k]] = ((const uint64_t*)st)[j];
+          else if (ac.width == 16) ((uint4*)outs[own[k]])[d[k]] = ((const uint4*)st)[j];
+          else ((uint32_t*)outs[own[k]])[d[k]] = ((const uint32_t*)st)[j];
+        }
+      }
+    }
+    // (the next tile's first __syncthreads orders these reads before its cp.async writes)
+  }
+}
+
+// base[p][chunk] += delta[p] (rows of partition p start at a different place in the owner's window)
+__global__ void add_delta_kernel(uint64_t* __restrict__ base, const int64_t* __restrict__ delta, uint32_t n, uint32_t g) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n * g) base[i] += (uint64_t)delta[i / g];
+}
+
+struct IpcHandle { char reserved[64]; };
+
+}  // namespace bgpu
+
+struct bgpu_peer_exchange {
+  bgpu_ctx* ctx = nullptr;
+  void* comm = nullptr;
+  int32_t rank = 0, world = 1;
+  void* window = nullptr;  // this rank's receive window (cudaMalloc: cudaIpc needs a non-pool allocation)
+  uint64_t window_bytes = 0;
+  void* peer[bgpu::kMaxPeers] = {};  // peer[d] = rank d's window mapped here (peer[rank] = window)
+  uint64_t exchanges = 0, fused = 0, bytes_sent = 0;
+};
+
+namespace bgpu {
+
+static int peer_close(bgpu_peer_exchange* x) {
+  for (int d = 0; d < x->world; d++) {
+    if (d != x->rank && x->peer[d]) cudaIpcCloseMemHandle(x->peer[d]);
+    x->peer[d] = nullptr;
+  }
+  return BGPU_OK;
+}
+
+// one word from every rank: a barrier on the stream (and the host, after the sync)
+static int peer_barrier(bgpu_peer_exchange* x) {
+  bgpu_ctx* ctx = x->ctx;
+  DevAllocPtr a, b;
+  BGPU_TRY(dev_alloc(ctx, 8, &a));
+  BGPU_TRY(dev_alloc(ctx, 8 * (size_t)x->world, &b));
+  BGPU_NCCL(ctx, nccl().AllGather(a->p, b->p, 8, kNcclUint8, x->comm, ctx->stream));
+  return BGPU_OK;
+}
+
+// (Re)allocate this rank's window and map every peer's. Collective: every rank calls it with the same `bytes`.
+static int peer_open(bgpu_peer_exchange* x, uint64_t bytes) {
+  bgpu_ctx* ctx = x->ctx;
+  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (x->window) {
+    // nobody may still hold a mapping of a window that is about to be freed
+    peer_close(x);
+    BGPU_TRY(peer_barrier(x));
+    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    BGPU_CUDA(ctx, cudaFree(x->window));
+    x->window = nullptr;
+  }
+  bytes = (bytes + (2u << 20) - 1) & ~(uint64_t)((2u << 20) - 1);
+  BGPU_CUDA(ctx, cudaMalloc(&x->window, bytes));
+  x->window_bytes = bytes;
+  x->peer[x->rank] = x->window;
+  if (x->world == 1) return BGPU_OK;
+  IpcHandle mine;
+  BGPU_CUDA(ctx, cudaIpcGetMemHandle((cudaIpcMemHandle_t*)&mine, x->window));
+  DevAllocPtr d_mine, d_all;
+  BGPU_TRY(dev_alloc(ctx, sizeof mine, &d_mine));
+  BGPU_TRY(dev_alloc(ctx, sizeof mine * (size_t)x->world, &d_all));
+  BGPU_CUDA(ctx, cudaMemcpyAsync(d_mine->p, &mine, sizeof mine, cudaMemcpyHostToDevice, ctx->stream));
+  BGPU_NCCL(ctx, nccl().AllGather(d_mine->p, d_all->p, sizeof mine, kNcclUint8, x->comm, ctx->stream));
+  std::vector<IpcHandle> all((size_t)x->world);
+  BGPU_CUDA(ctx, cudaMemcpyAsync(all.data(), d_all->p, sizeof mine * (size_t)x->world, cudaMemcpyDeviceToHost, ctx->stream));
+  BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int d = 0; d < x->world; d++) {
+    if (d == x->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, &all[(size_t)d], sizeof h);
+    const cudaError_t e = cudaIpcOpenMemHandle(&x->peer[d], h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      x->peer[d] = nullptr;
+      return ctx->fail(BGPU_ECUDA, std::string("cudaIpcOpenMemHandle(rank ") + std::to_string(d) + "): " + cudaGetErrorString(e));
+    }
+  }
+  return BGPU_OK;
+}
+
+}  // namespace bgpu
+
+extern "C" int bgpu_peer_exchange_create(bgpu_ctx* ctx, void* nccl_comm, int32_t rank, int32_t world, uint64_t window_bytes,
+                                         bgpu_peer_exchange** out) {
+  using namespace bgpu;
+  if (!ctx || !out || world < 1 || world > kMaxPeers || rank < 0 || rank >= world || (world > 1 && !nccl_comm)) return BGPU_EINVAL;
+  *out = nullptr;
+  if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
+  if (world > 1 && !nccl().ok) return ctx->fail(BGPU_ENCCL, "NCCL unavailable: " + nccl().why);
+  bgpu_peer_exchange* x = new bgpu_peer_exchange();
+  x->ctx = ctx;
+  x->comm = nccl_comm;
+  x->rank = rank;
+  x->world = world;
+  ctx_retain(ctx);
+  const int rc = peer_open(x, std::max<uint64_t>(window_bytes, 1u << 20));
+  if (rc != BGPU_OK) {
+    bgpu_peer_exchange_destroy(x);
+    return rc;
+  }
+  *out = x;
+  return BGPU_OK;
+}
+
+extern "C" void bgpu_peer_exchange_destroy(bgpu_peer_exchange* x) {
+  using namespace bgpu;
+  if (!x) return;
+  cudaSetDevice(x->ctx->device);
+  // not a collective (it also runs at interpreter shutdown): every exchange ends with all peers' stores landed, so no
+  // peer touches this window any more; the driver keeps the memory alive while a peer still has it mapped
+  peer_close(x);
+  cudaStreamSynchronize(x->ctx->stream);
+  if (x->window) cudaFree(x->window);
+  ctx_release(x->ctx);
+  delete x;
+}
+
+extern "C" uint64_t bgpu_peer_exchange_window_bytes(const bgpu_peer_exchange* x) { return x ? x->window_bytes : 0; }
+
+extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* in, const int32_t* key_cols, int32_t n_keys,
+                                       uint32_t n_partitions, bgpu_batch** out_received, uint64_t* out_recv_off,
+                                       uint64_t* out_sent_bytes) {
+  using namespace bgpu;
+  if (!x || !in || !key_cols || !out_received) return BGPU_EINVAL;
+  bgpu_ctx* ctx = x->ctx;
+  *out_received = nullptr;
+  if (out_sent_bytes) *out_sent_bytes = 0;
+  const uint32_t n = n_partitions;
+  const int world = x->world, me = x->rank;
+  if (n == 0 || n > kMaxPartitions) return ctx->fail(BGPU_EINVAL, "n_partitions out of range");
+  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int64_t n_rows = in->n_rows;
+  const size_t n_cols = in->cols.size();
+  x->exchanges++;
+
+  // can this rank's batch take the fused path? (every rank must agree: the flag travels with the counts)
+  const ScatterGeom geom = kGeomSmall;
+  const int64_t kTile = (int64_t)geom.threads * geom.items;
+  uint64_t can_fuse = n_cols > 0 && n_cols <= (size_t)kMaxCols && n <= 128;
+  int row_bytes = 0;
+  for (const Column& c : in->cols) {
+    if (c.kind != K_FIXED || (c.width != 4 && c.width != 8 && c.width != 16) || c.validity ||
+        (n_rows && ((uintptr_t)c.values % (size_t)c.width) != 0))
+      can_fuse = 0;
+    row_bytes += c.width;
+  }
+  const size_t smem = scatter_smem_bytes(n, geom.threads, geom.items, row_bytes, 0) + (size_t)kMaxCols * kMaxPeers * 8 + 16;
+  if (smem > (ctx->smem_optin + 1024) / 2 - 1024 - 512) can_fuse = 0;
+
+  // 1. local histogram + scan (grid fixed here: the scatter uses the same chunks)
+  KeySet ks{};
+  std::vector<DevAllocPtr> temps;
+  BGPU_TRY(make_keyset(ctx, in, key_cols, n_keys, &ks, &temps));
+  const Modulo mod = make_modulo(n);
+  int64_t g = (int64_t)ctx->sm_count * 2;
+  const int64_t tiles = std::max<int64_t>(1, ceil_div64(n_rows, kTile));
+  if (g > tiles) g = tiles;
+  const int64_t chunk_rows = ceil_div64(tiles, g) * kTile;
+  g = std::max<int64_t>(1, ceil_div64(n_rows, chunk_rows));
+  DevAllocPtr hist, base, hdr, all_hdr;
+  BGPU_TRY(dev_alloc(ctx, (size_t)n * g * 4, &hist));
+  BGPU_TRY(dev_alloc(ctx, (size_t)n * g * 8, &base));
+  const size_t hdr_words = (size_t)n + 2;  // offsets[n + 1], can_fuse
+  BGPU_TRY(dev_alloc(ctx, hdr_words * 8, &hdr));
+  BGPU_TRY(dev_alloc(ctx, hdr_words * 8 * (size_t)world, &all_hdr));
+  if (n_rows > 0) {
+    count_kernel<<<(int)g, kCountThreads, n * 4, ctx->stream>>>(ks, mod, n_rows, chunk_rows, (uint32_t*)hist->p, nullptr);
+    scan_kernel<<<1, 1024, 0, ctx->stream>>>((const uint32_t*)hist->p, (uint64_t*)base->p, (uint64_t*)hdr->p, n, (uint32_t)g, n_rows);
+    ctx->launches += 2;
+    BGPU_CUDA(ctx, cudaGetLastError());
+  } else {
+    BGPU_CUDA(ctx, cudaMemsetAsync(hdr->p, 0, hdr_words * 8, ctx->stream));
+  }
+  BGPU_CUDA(ctx, cudaMemcpyAsync((uint64_t*)hdr->p + n + 1, &can_fuse, 8, cudaMemcpyHostToDevice, ctx->stream));
+
+  // 2. everybody's counts
+  std::vector<uint64_t> all(hdr_words * (size_t)world);
+  if (world > 1) {
+    BGPU_NCCL(ctx, nccl().AllGather(hdr->p, all_hdr->p, hdr_words * 8, kNcclUint8, x->comm, ctx->stream));
+    BGPU_CUDA(ctx, cudaMemcpyAsync(all.data(), all_hdr->p, all.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  } else {
+    BGPU_CUDA(ctx, cudaMemcpyAsync(all.data(), hdr->p, hdr_words * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int s = 0; s < world; s++)
+    if (!all[(size_t)s * hdr_words + n + 1])
+      return ctx->fail(BGPU_EUNSUPPORTED, "fused exchange needs null-free 4/8/16-byte columns on every rank (rank " + std::to_string(s) +
+                                              " cannot): use bgpu_hash_partition + bgpu_all_to_all");
+
+  // receive layout of every rank: rows of (owned partition k, source s) start at recv[d][k * world + s]
+  std::vector<uint64_t> offs((size_t)world * (n + 1));
+  for (int s = 0; s < world; s++) memcpy(&offs[(size_t)s * (n + 1)], &all[(size_t)s * hdr_words], (size_t)(n + 1) * 8);
+  std::vector<std::vector<uint64_t>> recv((size_t)world);
+  std::vector<uint64_t> total((size_t)world);
+  uint64_t need = 0;
+  auto region = [&](uint64_t rows, int width) { return (rows * (uint64_t)width + 255) & ~255ULL; };
+  for (int d = 0; d < world; d++) {
+    const uint32_t owned = (n + (uint32_t)world - 1 - (uint32_t)d) / (uint32_t)world;
+    recv[(size_t)d].assign((size_t)owned * world + 1, 0);
+    uint32_t got = 0;
+    total[(size_t)d] = bgpu_exchange_plan(offs.data(), d, world, n, recv[(size_t)d].data(), &got);
+    uint64_t bytes = 0;
+    for (const Column& c : in->cols) bytes += region(total[(size_t)d], c.width);
+    need = std::max(need, bytes);
+  }
+  if (need > x->window_bytes) BGPU_TRY(peer_open(x, need + need / 4));  // collective: every rank sees the same `need`
+
+  // 3. window rows for this rank's partitions + the column regions in every owner's window
+  std::vector<int64_t> delta(n);
+  uint64_t sent_rows = 0;
+  for (uint32_t p = 0; p < n; p++) {
+    const int d = (int)(p % (uint32_t)world);
+    const uint32_t k = p / (uint32_t)world;
+    delta[p] = (int64_t)recv[(size_t)d][(size_t)k * world + me] - (int64_t)offs[(size_t)me * (n + 1) + p];
+    if (d != me) sent_rows += offs[(size_t)me * (n + 1) + p + 1] - offs[(size_t)me * (n + 1) + p];
+  }
+  ScatterArgs args{};
+  args.n_cols = (int32_t)n_cols;
+  std::vector<size_t> order(n_cols);
+  for (size_t i = 0; i < n_cols; i++) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return in->cols[a].width > in->cols[b].width; });
+  std::vector<void*> ptrs(n_cols * (size_t)world);
+  std::vector<uint64_t> my_region(n_cols);  // byte offset of column i in this rank's window
+  {
+    int off = 0;
+    for (size_t a = 0; a < n_cols; a++) {
+      const size_t i = order[a];
+      args.async_cols[a] = AsyncCol{in->cols[i].values, nullptr, in->cols[i].width, off};
+      off += in->cols[i].width;
+    }
+    args.n_async = (int32_t)n_cols;
+    args.async_width = off;
+    for (int d = 0; d < world; d++) {
+      uint64_t at = 0;
+      for (size_t i = 0; i < n_cols; i++) {  // regions in schema order
+        size_t a = 0;
+        while (order[a] != i) a++;
+        ptrs[a * (size_t)world + d] = (char*)x->peer[d] + at;
+        if (d == me) my_region[i] = at;
+        at += region(total[(size_t)d], in->cols[i].width);
+      }
+    }
+  }
+  if (n_rows > 0) {
+    DevAllocPtr d_delta, d_ptrs;
+    BGPU_TRY(dev_alloc(ctx, (size_t)n * 8, &d_delta));
+    BGPU_TRY(dev_alloc(ctx, ptrs.size() * 8, &d_ptrs));
+    BGPU_CUDA(ctx, cudaMemcpyAsync(d_delta->p, delta.data(), (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    BGPU_CUDA(ctx, cudaMemcpyAsync(d_ptrs->p, ptrs.data(), ptrs.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+    add_delta_kernel<<<(unsigned)((n * g + 255) / 256), 256, 0, ctx->stream>>>((uint64_t*)base->p, (const int64_t*)d_delta->p, n, (uint32_t)g);
+    BGPU_CUDA(ctx, cudaFuncSetAttribute(scatter_peer_kernel<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // 4. the fused scatter: runs go straight into the owners' windows
+    scatter_peer_kernel<256, 4><<<(int)g, 256, smem, ctx->stream>>>(ks, mod, args, n_rows, chunk_rows, (const uint64_t*)base->p,
+                                                                   (void* const*)d_ptrs->p, world);
+    ctx->launches += 2;
+    BGPU_CUDA(ctx, cudaGetLastError());
+    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // delta / ptrs are host temporaries of this call
+  }
+  // 5. everybody's stores have landed
+  if (world > 1) BGPU_TRY(peer_barrier(x));
+
+  // 6. copy out
+  std::unique_ptr<bgpu_batch> out(new bgpu_batch(ctx));
+  out->n_rows = (int64_t)total[(size_t)me];
+  out->cols.resize(n_cols);
+  for (size_t i = 0; i < n_cols; i++) {
+    const Column& c = in->cols[i];
+    Column& o = out->cols[i];
+    o.name = c.name; o.format = c.format; o.flags = c.flags; o.kind = c.kind; o.width = c.width;
+    o.length = out->n_rows; o.null_count = 0;
+    DevAllocPtr a;
+    BGPU_TRY(dev_alloc(ctx, (size_t)out->n_rows * c.width, &a));
+    o.owned.push_back(a);
+    o.values = a->p;
+    if (out->n_rows)
+      BGPU_CUDA(ctx, cudaMemcpyAsync(a->p, (char*)x->window + my_region[i], (size_t)out->n_rows * c.width, cudaMemcpyDeviceToDevice, ctx->stream));
+  }
+  if (out_recv_off) memcpy(out_recv_off, recv[(size_t)me].data(), recv[(size_t)me].size() * 8);
+  if (out_sent_bytes) *out_sent_bytes = sent_rows * (uint64_t)row_bytes;
+  x->fused++;
+  x->bytes_sent += sent_rows * (uint64_t)row_bytes;
+  *out_received = out.release();
+  return BGPU_OK;
+}

@@ -63,7 +63,33 @@ class Exchange:
                                              n_partitions, C.byref(out)))
         return DeviceBatch(self.ctx, out)
 
+    def partition_exchange(self, batch, key_cols, n_partitions, window_bytes=64 << 20):
+        """Fused hash repartition + exchange (bgpu_partition_exchange): == all_to_all(*partition_device(batch)), with the
+        scatter kernel storing straight into the owner ranks' receive windows over NVLink. COLLECTIVE. Batches the fused
+        kernel does not take (nulls, utf8, ...) go through hash partition + NCCL all-to-all on every rank alike.
+        Returns the received DeviceBatch; `last_sent_bytes` / `last_path` describe the call."""
+        from ._lib import BGPU_EUNSUPPORTED, BgpuError
+        from .partitioner import BatchPartitioner, Partitioning
+
+        if getattr(self, "_peer", None) is None:
+            self._peer = C.c_void_p()
+            self.ctx.check(lib().bgpu_peer_exchange_create(self.ctx._h, self._comm, self.rank, self.world, window_bytes,
+                                                           C.byref(self._peer)))
+        keys = (C.c_int32 * len(key_cols))(*key_cols)
+        out, sent = C.c_void_p(), C.c_uint64()
+        rc = lib().bgpu_partition_exchange(self._peer, batch._h, keys, len(keys), n_partitions, C.byref(out), None, C.byref(sent))
+        if rc == BGPU_EUNSUPPORTED:  # decided collectively inside the call: every rank lands here together
+            part, offsets = BatchPartitioner.try_new(Partitioning.Hash(list(key_cols), n_partitions), self.ctx).partition_device(batch)
+            self.last_path, self.last_sent_bytes = "nccl", None
+            return self.all_to_all(part, offsets, n_partitions) if self.world > 1 else part
+        self.ctx.check(rc)
+        self.last_path, self.last_sent_bytes = "fused_peer", int(sent.value)
+        return DeviceBatch(self.ctx, out)
+
     def close(self):
+        if getattr(self, "_peer", None):
+            lib().bgpu_peer_exchange_destroy(self._peer)
+            self._peer = None
         if getattr(self, "_comm", None):
             lib().bgpu_nccl_comm_destroy(self._comm)
             self._comm = None

@@ -204,6 +204,28 @@ void bgpu_nccl_comm_destroy(void* comm);
 uint64_t bgpu_exchange_plan(const uint64_t* all_offsets, int32_t rank, int32_t world, uint32_t n_partitions,
                             uint64_t* recv_off, uint32_t* n_owned);
 
+/* ---- fused hash repartition + exchange over NVLink peer memory (K3 + K6 in one kernel) ------------------------------
+ * bgpu_partition_exchange(batch) == bgpu_all_to_all(bgpu_hash_partition(batch)): replaces, inside one NVSwitch node,
+ * BatchPartitioner::partition + the shuffle file write + Flight do_get + the reader fan-in
+ * (/root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:336-391,
+ * /root/reference/ballista/executor/src/flight_service.rs:124-166,
+ * /root/reference/ballista/core/src/execution_plans/shuffle_reader.rs:539-624). The scatter kernel stores every run of a
+ * partition straight into the owner rank's receive window (cudaIpc-mapped peer memory), so rows cross NVLink once and no
+ * partitioned copy is made in local HBM; NCCL carries only the counts and a completion word.
+ * All three calls are COLLECTIVE over the ranks of `nccl_comm` (bgpu_peer_exchange_destroy is not).
+ * bgpu_partition_exchange accepts batches of null-free fixed-width columns of 4, 8 or 16 bytes (aggregate states),
+ * n_partitions <= 128; anything else returns BGPU_EUNSUPPORTED on EVERY rank (the ranks agree through the counts
+ * exchange) and the caller takes bgpu_hash_partition + bgpu_all_to_all. out_recv_off (optional, [n_owned * world + 1]):
+ * as bgpu_exchange_plan; out_sent_bytes (optional): bytes this rank stored into other ranks' windows. */
+typedef struct bgpu_peer_exchange bgpu_peer_exchange;
+int bgpu_peer_exchange_create(bgpu_ctx* ctx, void* nccl_comm, int32_t rank, int32_t world, uint64_t window_bytes,
+                              bgpu_peer_exchange** out);
+int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* batch, const int32_t* key_cols, int32_t n_keys,
+                            uint32_t n_partitions, bgpu_batch** out_received, uint64_t* out_recv_off,
+                            uint64_t* out_sent_bytes);
+uint64_t bgpu_peer_exchange_window_bytes(const bgpu_peer_exchange* x);
+void bgpu_peer_exchange_destroy(bgpu_peer_exchange* x);
+
 /* ---- Arrow IPC stream framing of partitioned device batches --------------------------------------
  * Replaces arrow-ipc's StreamWriter as ShuffleWriterExec drives it, one `write(batch)` per non-empty output partition
  * (/root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:351-399; IPCWriter,
