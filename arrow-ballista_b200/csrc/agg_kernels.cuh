@@ -200,6 +200,14 @@ __global__ void __launch_bounds__(kAggThreads) popcount_kernel(const uint32_t* _
   if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
 }
 
+// OR of all group key metas: bit c set = some group has a null in key column c (emit drops all-valid bitmaps)
+__global__ void __launch_bounds__(kAggThreads) or_kmeta_kernel(const uint32_t* __restrict__ kmeta, uint32_t n, uint32_t* __restrict__ out) {
+  uint32_t v = 0;
+  for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < n; g += gridDim.x * blockDim.x) v |= kmeta[g];
+  v = __reduce_or_sync(0xffffffffu, v);
+  if ((threadIdx.x & 31) == 0 && v) atomicOr(out, v);
+}
+
 __global__ void __launch_bounds__(kAggThreads) fill_u32_kernel(uint32_t* p, uint32_t n, uint32_t v) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = v;
 }

@@ -743,17 +743,37 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
     ctx->launches++;
     BGPU_CUDA(ctx, cudaGetLastError());
   }
+  // which key columns hold a null at all? (bit c of a group's meta = key column c is null.) Columns without one are
+  // emitted without a validity bitmap: the state batch of the common null-free case is then plain fixed-width data,
+  // which is what the fused repartition + exchange kernel takes.
+  uint32_t key_null_mask = 0;
+  if (n) {
+    DevAllocPtr d_mask;
+    BGPU_TRY(dev_alloc(ctx, 4, &d_mask));
+    BGPU_CUDA(ctx, cudaMemsetAsync(d_mask->p, 0, 4, ctx->stream));
+    or_kmeta_kernel<<<std::min(grid, ctx->sm_count * 4), kAggThreads, 0, ctx->stream>>>(kmeta, n, (uint32_t*)d_mask->p);
+    ctx->launches++;
+    uint32_t* pin = (uint32_t*)ctx->pinned + 32;
+    BGPU_CUDA(ctx, cudaMemcpyAsync(pin, d_mask->p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    key_null_mask = *pin;
+  }
   trace.mark("emit densify");
   // group key columns
   for (size_t i = 0; i < g->group_cols.size(); i++) {
     const Column& f = g->fields[(size_t)g->group_cols[i]];
     Column c;
     c.name = f.name; c.format = f.format; c.flags = f.flags | ARROW_FLAG_NULLABLE; c.kind = f.kind; c.width = f.width;
-    c.length = n; c.null_count = -1;
+    const bool has_nulls = (key_null_mask >> i) & 1;
+    c.length = n; c.null_count = has_nulls ? -1 : 0;
     DevAllocPtr valid;
-    BGPU_TRY(dev_alloc(ctx, (size_t)ceil_div64(std::max<uint32_t>(n, 1), 32) * 4, &valid));
-    c.owned.push_back(valid);
-    c.validity = (uint8_t*)valid->p;
+    uint32_t* valid_bits = nullptr;
+    if (has_nulls) {
+      BGPU_TRY(dev_alloc(ctx, (size_t)ceil_div64(std::max<uint32_t>(n, 1), 32) * 4, &valid));
+      c.owned.push_back(valid);
+      c.validity = (uint8_t*)valid->p;
+      valid_bits = (uint32_t*)valid->p;
+    }
     if (f.kind == K_UTF8 || f.kind == K_BINARY) {
       DevAllocPtr lens, offs, data;
       BGPU_TRY(dev_alloc(ctx, (size_t)(n + 1) * 4, &lens));
@@ -762,7 +782,7 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
       int32_t total = 0;
       if (n) {
         unpack_utf8_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(key0, key1, kmeta, n, (int)i, g->key_off[i], 0,
-                                                                 (int32_t*)lens->p, nullptr, (uint32_t*)valid->p);
+                                                                 (int32_t*)lens->p, nullptr, valid_bits);
         size_t tmp_bytes = 0;
         cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, (const int32_t*)lens->p, (int32_t*)offs->p + 1, (int)n, ctx->stream);
         DevAllocPtr tmp;
@@ -785,7 +805,7 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
       BGPU_TRY(dev_alloc(ctx, bytes, &vals));
       if (n)
         unpack_fixed_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(key0, key1, kmeta, n, (int)i, f.kind, f.width,
-                                                                  g->key_off[i], vals->p, (uint32_t*)valid->p);
+                                                                  g->key_off[i], vals->p, valid_bits);
       ctx->launches++;
       c.values = vals->p;
       c.owned.push_back(vals);

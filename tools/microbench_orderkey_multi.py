@@ -21,6 +21,8 @@ import ballista_b200 as bb
 
 N = int(float(sys.argv[1])) if len(sys.argv) > 1 else 100_000_000
 NP = 16
+FUSED = bool(int(os.environ.get("FUSED", "0")))  # 1: fused repartition + exchange over peer memory
+WINDOW = int(float(os.environ.get("WINDOW", 3e9)))
 world = int(os.environ.get("WORLD_SIZE", "1"))
 rank = int(os.environ.get("RANK", "0"))
 local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -76,11 +78,18 @@ def step():
     agg.update(batch)
     state = agg.emit()
     e[1].record(stream)
-    part, offsets = partitioner.partition_device(state)
-    e[2].record(stream)
-    sent_rows = sum(int(offsets[p + 1]) - int(offsets[p]) for p in range(NP) if p % world != rank)
-    if world > 1:
-        part = comm.all_to_all(part, offsets, NP)
+    if FUSED and world > 1:
+        # fused: the scatter kernel stores straight into the owners' windows (bgpu_partition_exchange)
+        e[2].record(stream)
+        part = comm.partition_exchange(state, [0], NP, window_bytes=WINDOW)
+        assert comm.last_path == "fused_peer"
+        sent_rows = comm.last_sent_bytes // 48
+    else:
+        part, offsets = partitioner.partition_device(state)
+        e[2].record(stream)
+        sent_rows = sum(int(offsets[p + 1]) - int(offsets[p]) for p in range(NP) if p % world != rank)
+        if world > 1:
+            part = comm.all_to_all(part, offsets, NP)
     e[3].record(stream)
     fin = bb.GpuAggregateExec(ctx, bb.AggregateMode.FinalPartitioned, [0], aggs, schema)
     fin.update(part)
@@ -110,6 +119,7 @@ if rank == 0:
     STATE = 48  # key 8 + 2 x i128 sum + i64 count
     line = {"config": "4b l_orderkey group-by, shuffled input", "n_gpus": world, "rows_per_gpu": N,
             "partial_groups_total": pg, "final_groups_total": fg, "path": path,
+            "exchange_path": "fused_peer (repartition inside the exchange time)" if FUSED and world > 1 else "hash partition + NCCL all-to-all",
             "ms": {"partial": best[0], "repartition": best[1], "exchange": best[2], "final": best[3], "step": best[4]},
             "rows_per_s": total / (best[4] * 1e-3),
             "nvlink": {"bytes_sent_per_gpu": sr * STATE / world, "GBps_per_gpu": (sr * STATE / world) / (best[2] * 1e-3) / 1e9
