@@ -16,6 +16,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -246,14 +247,23 @@ int schema_message(bgpu_ctx* ctx, const std::vector<Column>& cols, std::vector<u
 }
 
 void record_batch_message(int64_t rows, const std::vector<std::pair<int64_t, int64_t>>& nodes,
-                          const std::vector<std::pair<int64_t, int64_t>>& buffers, int64_t body_len, std::vector<uint8_t>* out) {
+                          const std::vector<std::pair<int64_t, int64_t>>& buffers, int64_t body_len, std::vector<uint8_t>* out,
+                          int compression = -1) {
   Fbb b;
+  uint32_t comp = 0;
+  if (compression >= 0) {  // BodyCompression{codec: LZ4_FRAME = 0 | ZSTD = 1, method: BUFFER = 0}
+    b.start_table(2);
+    b.add<int8_t>(0, (int8_t)compression);
+    b.add<int8_t>(1, 0);
+    comp = b.end_table();
+  }
   const uint32_t bv = b.struct_vector(buffers);
   const uint32_t nv = b.struct_vector(nodes);
   b.start_table(5);
   b.add<int64_t>(0, rows);
   b.add_ref(1, nv);
   b.add_ref(2, bv);
+  if (comp) b.add_ref(3, comp);
   const uint32_t rb = b.end_table();
   b.start_table(5);
   b.add<int16_t>(0, kMetadataV5);
@@ -337,6 +347,52 @@ __global__ void gather_i32_kernel(const int32_t* __restrict__ src, const uint64_
 
 inline uint64_t pad8(uint64_t x) { return (x + 7) & ~7ULL; }
 
+// Pinned host buffers for the encoded messages are recycled process-wide: cudaHostAlloc of a few hundred MB costs tens
+// of milliseconds, more than laying the bodies out and copying them. bgpu_ipc_free(p, 1) returns a buffer to the pool.
+struct PinnedPool {
+  std::mutex mu;
+  std::vector<std::pair<uint8_t*, size_t>> free_list;   // idle buffers
+  std::vector<std::pair<uint8_t*, size_t>> lent;        // handed out, by pointer
+  static constexpr size_t kKeepBytes = 1ULL << 30;
+  cudaError_t take(size_t bytes, uint8_t** out) {
+    std::lock_guard<std::mutex> lock(mu);
+    size_t best = free_list.size();
+    for (size_t i = 0; i < free_list.size(); i++)
+      if (free_list[i].second >= bytes && (best == free_list.size() || free_list[i].second < free_list[best].second)) best = i;
+    if (best != free_list.size() && free_list[best].second <= 4 * bytes + (1 << 20)) {
+      *out = free_list[best].first;
+      lent.push_back(free_list[best]);
+      free_list.erase(free_list.begin() + (long)best);
+      return cudaSuccess;
+    }
+    const size_t cap = (bytes + (1 << 20) - 1) & ~(size_t)((1 << 20) - 1);
+    const cudaError_t e = cudaHostAlloc((void**)out, cap, cudaHostAllocDefault);
+    if (e == cudaSuccess) lent.emplace_back(*out, cap);
+    return e;
+  }
+  void give(uint8_t* p) {
+    std::lock_guard<std::mutex> lock(mu);
+    for (size_t i = 0; i < lent.size(); i++)
+      if (lent[i].first == p) {
+        free_list.push_back(lent[i]);
+        lent.erase(lent.begin() + (long)i);
+        size_t total = 0;
+        for (auto& f : free_list) total += f.second;
+        while (total > kKeepBytes && !free_list.empty()) {  // keep at most 1 GiB idle: drop the oldest
+          total -= free_list.front().second;
+          cudaFreeHost(free_list.front().first);
+          free_list.erase(free_list.begin());
+        }
+        return;
+      }
+    cudaFreeHost(p);  // not ours (should not happen)
+  }
+};
+PinnedPool& pinned_pool() {
+  static PinnedPool* p = new PinnedPool();  // leaked on purpose: buffers may be returned during interpreter shutdown
+  return *p;
+}
+
 }  // namespace
 }  // namespace bgpu
 
@@ -361,13 +417,14 @@ extern "C" int bgpu_ipc_schema_message(bgpu_ctx* ctx, const struct ArrowSchema* 
 }
 
 extern "C" int bgpu_ipc_record_batch_metadata(bgpu_ctx* ctx, int64_t rows, const int64_t* nodes, int32_t n_nodes, const int64_t* buffers,
-                                              int32_t n_buffers, int64_t body_len, uint8_t** out_bytes, uint64_t* out_len) {
+                                              int32_t n_buffers, int64_t body_len, int32_t compression, uint8_t** out_bytes, uint64_t* out_len) {
   if (!ctx || !out_bytes || !out_len || n_nodes < 0 || n_buffers < 0 || (n_nodes && !nodes) || (n_buffers && !buffers)) return BGPU_EINVAL;
+  if (compression < -1 || compression > 0) return ctx->fail(BGPU_EUNSUPPORTED, "compression must be -1 (none) or 0 (LZ4_FRAME)");
   std::vector<std::pair<int64_t, int64_t>> nv, bv;
   for (int32_t i = 0; i < n_nodes; i++) nv.emplace_back(nodes[2 * i], nodes[2 * i + 1]);
   for (int32_t i = 0; i < n_buffers; i++) bv.emplace_back(buffers[2 * i], buffers[2 * i + 1]);
   std::vector<uint8_t> msg;
-  record_batch_message(rows, nv, bv, body_len, &msg);
+  record_batch_message(rows, nv, bv, body_len, &msg, compression);
   return to_malloc(ctx, msg, out_bytes, out_len);
 }
 
@@ -474,13 +531,13 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
   }
   BGPU_CUDA(ctx, cudaGetLastError());
   uint8_t* host = nullptr;
-  BGPU_CUDA(ctx, cudaHostAlloc((void**)&host, total, cudaHostAllocDefault));
+  BGPU_CUDA(ctx, pinned_pool().take(total, &host));
   std::vector<unsigned long long> set_bits((size_t)std::max(1, n_counters), 0);
   cudaError_t e = cudaMemcpyAsync(host, stage->p, total, cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(set_bits.data(), d_cnt->p, set_bits.size() * 8, cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
   if (e != cudaSuccess) {
-    cudaFreeHost(host);
+    pinned_pool().give(host);
     return ctx->fail(BGPU_ECUDA, std::string("IPC encode: ") + cudaGetErrorString(e));
   }
 
@@ -494,7 +551,7 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
       nodes.emplace_back((int64_t)rows, pt.counter[i] < 0 ? 0 : (int64_t)(rows - set_bits[(size_t)pt.counter[i]]));
     record_batch_message((int64_t)rows, nodes, pt.buffers, (int64_t)pt.body_len, &msg);
     if (msg.size() != meta_len) {
-      cudaFreeHost(host);
+      pinned_pool().give(host);
       return ctx->fail(BGPU_EINVAL, "internal: IPC metadata size is not constant");
     }
     memcpy(host + out_msg_off[p], msg.data(), msg.size());
@@ -505,6 +562,6 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
 
 extern "C" void bgpu_ipc_free(uint8_t* bytes, int pinned) {
   if (!bytes) return;
-  if (pinned) cudaFreeHost(bytes);
+  if (pinned) pinned_pool().give(bytes);
   else free(bytes);
 }

@@ -50,13 +50,14 @@ def schema_message(schema, ctx=None):
     return _take(p, n)
 
 
-def record_batch_metadata(rows, nodes, buffers, body_len, ctx=None):
-    """Prefix + RecordBatch metadata of one message: nodes = [(length, null_count)], buffers = [(offset, length)]. Host only."""
+def record_batch_metadata(rows, nodes, buffers, body_len, ctx=None, compression=-1):
+    """Prefix + RecordBatch metadata of one message: nodes = [(length, null_count)], buffers = [(offset, length)]; compression
+    0 marks the buffers as LZ4_FRAME-compressed. Host only."""
     ctx = ctx or _HostContext()
     nv = (C.c_int64 * max(1, 2 * len(nodes)))(*[int(x) for pair in nodes for x in pair])
     bv = (C.c_int64 * max(1, 2 * len(buffers)))(*[int(x) for pair in buffers for x in pair])
     p, n = C.c_void_p(), C.c_uint64()
-    ctx.check(lib().bgpu_ipc_record_batch_metadata(ctx._h, rows, nv, len(nodes), bv, len(buffers), body_len, C.byref(p), C.byref(n)))
+    ctx.check(lib().bgpu_ipc_record_batch_metadata(ctx._h, rows, nv, len(nodes), bv, len(buffers), body_len, compression, C.byref(p), C.byref(n)))
     return _take(p, n)
 
 

@@ -236,7 +236,8 @@ void bgpu_peer_exchange_destroy(bgpu_peer_exchange* x);
  * bgpu_ipc_schema_message: the encapsulated Schema message of a struct-typed ArrowSchema (host only; malloc'ed: free
  *   with bgpu_ipc_free(p, 0)).
  * bgpu_ipc_record_batch_metadata: the 8-byte prefix + RecordBatch metadata of one message, for callers that lay the
- *   body out themselves (host only; nodes = (length, null_count) pairs, buffers = (offset, length) pairs; malloc'ed).
+ *   body out themselves (host only; nodes = (length, null_count) pairs, buffers = (offset, length) pairs; malloc'ed);
+ *   compression = 0 marks the body's buffers as LZ4_FRAME-compressed (each: int64 uncompressed length, then the frame).
  * bgpu_ipc_encode_partitions: one encapsulated RecordBatch message per non-empty partition p = rows
  *   [offsets[p], offsets[p + 1]) of `batch`; bodies are laid out by one kernel on the device and arrive with one copy.
  *   *out_bytes (pinned host memory; free with bgpu_ipc_free(p, 1); NULL when every partition is empty) holds the
@@ -244,7 +245,8 @@ void bgpu_peer_exchange_destroy(bgpu_peer_exchange* x);
  *   out_msg_off has n + 1 entries. */
 int bgpu_ipc_schema_message(bgpu_ctx* ctx, const struct ArrowSchema* schema, uint8_t** out_bytes, uint64_t* out_len);
 int bgpu_ipc_record_batch_metadata(bgpu_ctx* ctx, int64_t rows, const int64_t* nodes, int32_t n_nodes, const int64_t* buffers,
-                                   int32_t n_buffers, int64_t body_len, uint8_t** out_bytes, uint64_t* out_len);
+                                   int32_t n_buffers, int64_t body_len, int32_t compression /* -1 none, 0 LZ4_FRAME */,
+                                   uint8_t** out_bytes, uint64_t* out_len);
 int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch, const uint64_t* offsets, uint32_t n,
                                uint8_t** out_bytes, uint64_t* out_msg_off);
 void bgpu_ipc_free(uint8_t* bytes, int pinned);

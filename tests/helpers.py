@@ -100,3 +100,100 @@ def q1_plan():
             ("avg", disc, "avg_disc"), ("count", None, "count_order")]
     filt = col(6) <= lit(10471, 3)  # l_shipdate <= date '1998-12-01' - interval '90' day = 1998-09-02
     return [4, 5], aggs, filt
+
+
+def _xxh32_short(data, seed=0):
+    """XXH32 of fewer than 16 bytes (the LZ4 frame descriptor): the header checksum byte is (xxh32 >> 8) & 0xff."""
+    P1, P2, P3, P4, P5, M = 2654435761, 2246822519, 3266489917, 668265263, 374761393, 0xFFFFFFFF
+    assert len(data) < 16
+
+    def rotl(x, r):
+        return ((x << r) | (x >> (32 - r))) & M
+    h = (seed + P5 + len(data)) & M
+    i = 0
+    while i + 4 <= len(data):
+        h = (h + int.from_bytes(data[i:i + 4], "little") * P3) & M
+        h = (rotl(h, 17) * P4) & M
+        i += 4
+    while i < len(data):
+        h = (h + data[i] * P5) & M
+        h = (rotl(h, 11) * P1) & M
+        i += 1
+    h ^= h >> 15
+    h = (h * P2) & M
+    h ^= h >> 13
+    h = (h * P3) & M
+    h ^= h >> 16
+    return h
+
+
+def independent_frame(data, block=65536, block_checksum=False, content_size=False):
+    """An LZ4 frame with block-independent 64 KB blocks, as lz4_flex's FrameEncoder (arrow-ipc's codec in the reference
+    build) writes by default; built from Arrow's raw LZ4 block codec. The header checksum is real; block checksums are placeholders."""
+    flg = 0x40 | 0x20 | (0x10 if block_checksum else 0) | (0x08 if content_size else 0)
+    out = bytearray(b"\x04\x22\x4d\x18" + bytes([flg, 0x40]))
+    if content_size:
+        out += len(data).to_bytes(8, "little")
+    out += bytes([(_xxh32_short(bytes(out[4:])) >> 8) & 0xFF])  # header checksum
+    for lo in range(0, len(data), block):
+        piece = data[lo:lo + block]
+        comp = pa.compress(piece, codec="lz4_raw", asbytes=True)
+        if len(comp) >= len(piece):
+            out += (len(piece) | 0x80000000).to_bytes(4, "little") + piece
+        else:
+            out += len(comp).to_bytes(4, "little") + comp
+        if block_checksum:
+            out += b"\0\0\0\0"
+    out += b"\0\0\0\0"
+    return bytes(out)
+
+
+def reference_style_lz4_stream(batches, block=65536):
+    """An Arrow IPC stream of `batches` (no dictionary columns) framed the way the reference's writer frames a shuffle file
+    (arrow-ipc StreamWriter with LZ4_FRAME, /root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:365-376):
+    every buffer = int64 uncompressed length + an LZ4 frame of block-independent 64 KB blocks (lz4_flex's FrameEncoder
+    default), or length -1 + the raw bytes when compression does not pay; buffers padded to 64 bytes. Metadata comes from
+    libbgpu's own flatbuffer builder (ballista_b200.ipc)."""
+    from ballista_b200 import ipc
+
+    def raw_buffers(col):
+        n = len(col)
+        bufs = col.buffers()
+        out = []
+        validity = bufs[0]
+        if validity is not None and col.null_count:
+            assert col.offset == 0
+            out.append(validity.to_pybytes()[: (n + 7) // 8])
+        else:
+            out.append(b"")
+        t = col.type
+        if pa.types.is_string(t) or pa.types.is_binary(t):
+            offs = np.frombuffer(bufs[1], dtype=np.int32, count=n + 1) if n else np.zeros(1, np.int32)
+            out.append(offs.tobytes())
+            out.append(bufs[2].to_pybytes()[: int(offs[-1])] if bufs[2] is not None else b"")
+        elif pa.types.is_boolean(t):
+            out.append(bufs[1].to_pybytes()[: (n + 7) // 8])
+        else:
+            out.append(bufs[1].to_pybytes()[: n * t.byte_width])
+        return out
+
+    schema = batches[0].schema
+    stream = bytearray(ipc.schema_message(schema))
+    for b in batches:
+        b = pa.RecordBatch.from_arrays([pa.concat_arrays([c]) for c in b.columns], schema=schema)  # offset 0, compact
+        body, buffers, nodes = bytearray(), [], []
+        for col in b.columns:
+            nodes.append((len(col), col.null_count))
+            for raw in raw_buffers(col):
+                if not raw:
+                    buffers.append((len(body), 0))
+                    continue
+                frame = independent_frame(raw, block)
+                enc = (len(raw).to_bytes(8, "little", signed=True) + frame) if len(frame) < len(raw) else \
+                    ((-1).to_bytes(8, "little", signed=True) + raw)
+                buffers.append((len(body), len(enc)))
+                body += enc
+                body += b"\0" * (-len(body) % 64)
+        stream += ipc.record_batch_metadata(b.num_rows, nodes, buffers, len(body), compression=0)
+        stream += body
+    return bytes(stream + ipc.EOS)

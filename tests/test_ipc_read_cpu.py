@@ -7,6 +7,8 @@ import numpy as np
 import pyarrow as pa
 import pytest
 
+from helpers import independent_frame, reference_style_lz4_stream
+
 
 def _stream(schema, batches=(), compression=None):
     sink = io.BytesIO()
@@ -108,27 +110,6 @@ def test_lz4_frame_decoder_rejects_corruption(bb):
         ipc.lz4_frame_decode_host(bytes(frame[: len(frame) // 2]), len(data))  # truncated
 
 
-def independent_frame(data, block=65536, block_checksum=False, content_size=False):
-    """An LZ4 frame with block-independent 64 KB blocks, as lz4_flex's FrameEncoder (arrow-ipc's codec in the reference
-    build) writes by default; built from Arrow's raw LZ4 block codec. Checksums are placeholders (not verified)."""
-    flg = 0x40 | 0x20 | (0x10 if block_checksum else 0) | (0x08 if content_size else 0)
-    out = bytearray(b"\x04\x22\x4d\x18" + bytes([flg, 0x40]))
-    if content_size:
-        out += len(data).to_bytes(8, "little")
-    out += b"\x00"  # header checksum
-    for lo in range(0, len(data), block):
-        piece = data[lo:lo + block]
-        comp = pa.compress(piece, codec="lz4_raw", asbytes=True)
-        if len(comp) >= len(piece):
-            out += (len(piece) | 0x80000000).to_bytes(4, "little") + piece
-        else:
-            out += len(comp).to_bytes(4, "little") + comp
-        if block_checksum:
-            out += b"\0\0\0\0"
-    out += b"\0\0\0\0"
-    return bytes(out)
-
-
 @pytest.mark.parametrize("block_checksum,content_size", [(False, False), (True, True)])
 def test_lz4_block_independent_frames(bb, block_checksum, content_size):
     from ballista_b200 import ipc
@@ -138,3 +119,17 @@ def test_lz4_block_independent_frames(bb, block_checksum, content_size):
             + b"xyz" * 33_333)
     frame = independent_frame(data, block_checksum=block_checksum, content_size=content_size)
     assert ipc.lz4_frame_decode_host(frame, len(data)) == data
+
+
+def test_reference_style_lz4_stream_is_valid_arrow_ipc(bb):
+    """The hand-framed stream the GPU reader tests use (buffers as block-independent LZ4 frames behind their int64 length
+    prefix, BodyCompression in libbgpu's RecordBatch metadata) is read by Arrow's own reader exactly as written."""
+    from helpers import random_batch
+
+    rng = np.random.default_rng(8)
+    batches = [random_batch(rng, n, with_dict=False) for n in (5, 0, 70_000)]
+    data = reference_style_lz4_stream(batches)
+    got = list(pa.ipc.open_stream(io.BytesIO(data)))
+    assert len(got) == 3
+    for g, w in zip(got, batches):
+        assert g.equals(w)

@@ -256,3 +256,19 @@ def test_two_stage_q1_job_through_shuffle_files(bb, ctx, oracle, tmp_path, ipc_m
     want = pa.Table.from_batches([of.emit()])
     keys = [(n_, "ascending") for n_ in got.schema.names[: len(gi)]]
     assert got.sort_by(keys).equals(want.sort_by(keys))
+
+
+@pytest.mark.parametrize("sizes", [[1], [7, 0, 1000], [200_000, 33_333]])
+def test_stream_reader_reads_reference_style_lz4_files(bb, ctx, sizes):
+    """Streams framed as the reference's writer frames them - block-independent 64 KB LZ4 blocks (lz4_flex) behind the int64
+    length prefix, stored buffers with -1: every block is one decode chain, decoded in shared memory by its own warp."""
+    from helpers import reference_style_lz4_stream
+    from ballista_b200 import ipc
+
+    rng = np.random.default_rng(77 + sum(sizes))
+    batches = [random_batch(rng, n, null_frac=0.1 if i % 2 == 0 else 0.0, with_dict=False) for i, n in enumerate(sizes)]
+    data = reference_style_lz4_stream(batches)
+    got = [b.download() for b in ipc.StreamReader(ctx, data)]
+    assert len(got) == len(batches)
+    for g, w in zip(got, batches):
+        _same(g, w)
