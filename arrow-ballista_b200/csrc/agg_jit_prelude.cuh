@@ -622,6 +622,35 @@ struct FlushShared {
   }
 };
 
+// two-pass TIER 2: fold the CTA's hot-group cache (slot -> group id in s_tag) into the global records, one thread per slot
+constexpr uint32_t kEmptyTag = 0xffffffffu;
+struct FlushCache {
+  const uint64_t* s_acc;
+  const uint32_t* s_tag;
+  const JitArgs* a;
+  uint32_t slots;
+  int W, T;
+  template <int OP, int WORD0, int WORDS, int IDX, bool ALIASED, int OUT>
+  __device__ __forceinline__ void acc() {
+    for (uint32_t slot = threadIdx.x; slot < slots; slot += T) {
+      const uint32_t grp = s_tag[slot];
+      if (grp == kEmptyTag) continue;
+      uint64_t* o = a->t.acc + (size_t)grp * a->t.acc_stride + OUT;
+      const uint64_t* p = s_acc + (size_t)slot * W + WORD0;
+      if (OP == OP_ADD_F64) {
+        const double f = as_f64(p[0]);
+        if (f != 0.0) atomicAdd((double*)o, f);
+      } else {
+        const Val v{p[0], WORDS > 1 ? p[1] : 0ULL};
+        if (v.lo | v.hi) {
+          if (OP == OP_ADD_I128) add_atomic<OP_ADD_I128>(o, v);
+          else add_atomic<OP_ADD_I64>(o, v);  // partial counts are sums by now; an aliased count adds its source's partial
+        }
+      }
+    }
+  }
+};
+
 // ---- kernel bodies ---------------------------------------------------------------------------------------------------
 // `Plan` (generated per aggregate and per batch shape by agg_codegen.cu) provides:
 //   constants  T (threads), R (rows per thread per tile), W (accumulator words per group), KEY_WORDS, HAS_SEEN
@@ -854,6 +883,25 @@ __device__ __forceinline__ void accumulate_body(const JitArgs& a) {
       for (uint32_t i = threadIdx.x; i < n_groups; i += T) s_seen[i] = 0;
     __syncthreads();
   }
+  // TIER 2 with skewed keys: a handful of groups take a large share of the rows, and their global atomics all land on
+  // the same L2 addresses (Zipf(1) over 1e7 groups: the hottest group gets 4 % of the rows; 5e8 rows: 166 ms instead of
+  // 43 ms uniform). Each CTA therefore keeps a small direct-mapped cache of groups in shared memory: the first group to
+  // arrive at a slot owns it for the launch (a hot group arrives first with high probability), its rows are added with
+  // native 32-bit shared atomics, everything else goes to the global records as before; the cache is folded into the
+  // global records once at the end.
+  uint32_t* s_tag = nullptr;
+  uint32_t* s_cseen = nullptr;
+  const uint32_t cslots = TIER == 2 ? a.cache_slots : 0;
+  if (TIER == 2 && cslots) {
+    for (uint32_t i = threadIdx.x; i < cslots * W; i += T) s_acc[i] = 0;
+    s_tag = (uint32_t*)(s_acc + (size_t)cslots * W);
+    s_cseen = s_tag + cslots;
+    for (uint32_t i = threadIdx.x; i < cslots; i += T) {
+      s_tag[i] = kEmptyTag;
+      if (Plan::HAS_SEEN) s_cseen[i] = 0;
+    }
+    __syncthreads();
+  }
   const uint32_t rep = TIER == 1 ? (threadIdx.x % a.replicas) : 0;
   bool ovf = false;
   const int64_t tile = (int64_t)T * R, last = a.n_rows - 1;
@@ -880,13 +928,38 @@ __device__ __forceinline__ void accumulate_body(const JitArgs& a) {
         seen = Plan::accumulate(a, x[u], sink, &ovf);
         if (Plan::HAS_SEEN && seen) atomicOr(&s_seen[g[u]], seen);
       } else {
-        GlobalAtomicSink sink{g[u]};
-        seen = Plan::accumulate(a, x[u], sink, &ovf);
-        if (Plan::HAS_SEEN && seen) atomicOr(&a.seen[g[u]], seen);
+        bool cached = false;
+        uint32_t slot = 0;
+        if (cslots) {
+          slot = (g[u] * 0x9E3779B1u) >> (32 - __popc(cslots - 1));
+          uint32_t tag = s_tag[slot];
+          if (tag == kEmptyTag) {
+            tag = atomicCAS(&s_tag[slot], kEmptyTag, g[u]);
+            if (tag == kEmptyTag) tag = g[u];
+          }
+          cached = tag == g[u];
+        }
+        if (cached) {
+          SharedSplitSink sink{s_acc + (size_t)slot * W};
+          seen = Plan::accumulate(a, x[u], sink, &ovf);
+          if (Plan::HAS_SEEN && seen) atomicOr(&s_cseen[slot], seen);
+        } else {
+          GlobalAtomicSink sink{g[u]};
+          seen = Plan::accumulate(a, x[u], sink, &ovf);
+          if (Plan::HAS_SEEN && seen) atomicOr(&a.seen[g[u]], seen);
+        }
       }
     }
   }
   if (ovf) atomicOr(&a.t.flags[2], 1);
+  if (TIER == 2 && cslots) {
+    __syncthreads();
+    FlushCache fc{s_acc, s_tag, &a, cslots, W, T};
+    Plan::for_each_acc(fc);
+    if (Plan::HAS_SEEN)
+      for (uint32_t i = threadIdx.x; i < cslots; i += T)
+        if (s_tag[i] != kEmptyTag && s_cseen[i]) atomicOr(&a.seen[s_tag[i]], s_cseen[i]);
+  }
   if (TIER != 1) return;
   __syncthreads();
   FlushShared fl{s_acc, &a, n_groups, a.replicas, W, T};

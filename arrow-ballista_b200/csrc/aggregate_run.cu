@@ -657,9 +657,18 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
     BGPU_TRY(jit_launch(ctx, fn, grid, T, smem, &b->args));
     g->last_path = "shared";
   } else {
+    // hot-group cache in shared memory (skewed keys): the largest power of two of slots that fits ~40 KB, so that the
+    // occupancy of the global tier stays what it was; BGPU_HOT_CACHE=0 switches it off (measurement)
+    uint32_t cslots = 1024;
+    const size_t slot_bytes = group_bytes + 8;
+    while (cslots > 64 && cslots * slot_bytes > 40 * 1024) cslots >>= 1;
+    if (const char* e = getenv("BGPU_HOT_CACHE")) cslots = (uint32_t)atoi(e);
+    if (cslots & (cslots - 1)) cslots = 0;
+    const size_t csmem = (size_t)cslots * slot_bytes;
     const int grid = (int)std::min<int64_t>(tiles, (int64_t)ctx->sm_count * 8);
     b->args.replicas = 1;
-    BGPU_TRY(jit_launch(ctx, b->mod->fn[JK_ACC_GLOBAL], grid, T, 0, &b->args));
+    b->args.cache_slots = cslots;
+    BGPU_TRY(jit_launch(ctx, b->mod->fn[JK_ACC_GLOBAL], grid, T, csmem, &b->args));
     g->last_path = "global";
   }
   trace.mark("accumulate");

@@ -151,3 +151,34 @@ def test_wide_decimal_sums_few_groups(bb, ctx, oracle):
     got = dict(zip(out.column(0).to_pylist(), out.column(1).to_pylist()))
     for k in range(3):
         assert got[k] == decimal.Decimal(sum(v for v, kk in zip(vals, b.column(0).to_pylist()) if kk == k))
+
+
+def zipf_keys(rng, n, domain):
+    """Zipf(1)-like keys over 1..domain: floor((domain + 1)^u) (tools/microbench_config5.py)."""
+    return np.clip(np.floor(np.exp(rng.random(n) * np.log(domain + 1.0))), 1, domain).astype(np.int64)
+
+
+@pytest.mark.parametrize("nulls", [False, True])
+def test_skewed_keys_global_tier_hot_group_cache(bb, ctx, oracle, nulls):
+    """BASELINE config 5 shape: Zipf-skewed Int64 keys over a domain large enough for the two-pass path's global-atomic
+    tier, where each CTA keeps hot groups in a shared-memory cache that is folded into the global records at the end:
+    sums / counts / decimal averages must stay bit-exact (Float64 within 1e-9), null tracking included."""
+    rng = np.random.default_rng(31 + nulls)
+    n = 300_000
+    batches = []
+    for _ in range(2):
+        k = zipf_keys(rng, n, 60_000)
+        mask = (rng.random(n) < 0.3) if nulls else None
+        dec = [decimal.Decimal(int(v)) / 100 for v in rng.integers(-10**9, 10**9, n)]
+        batches.append(pa.RecordBatch.from_arrays(
+            [pa.array(k), pa.array(rng.integers(1, 16, n), type=pa.int64(), mask=mask),
+             pa.array(np.round(rng.random(n) * 100, 6), mask=mask), pa.array(dec, type=pa.decimal128(15, 2), mask=mask)],
+            names=["id6", "v2", "v3", "d"]))
+    aggs = [("sum", "v2", "s2"), ("sum", "v3", "s3"), ("sum", "d", "sd"), ("avg", "d", "ad"), ("count", "v2", "c2"), ("count", None, "c")]
+    gp = bb.GpuAggregateExec(ctx, bb.AggregateMode.Partial, [0], [(f, None if c is None else batches[0].schema.names.index(c), nm)
+                                                                 for f, c, nm in aggs], batches[0].schema)
+    gp.update(batches[0])
+    assert gp.last_path == "global", gp.last_path  # the tier this test is about
+    out = run_both(bb, ctx, oracle, batches, ["id6"], aggs, n_partials=1)
+    hot = pa.Table.from_batches([out]).filter(pc.equal(pa.Table.from_batches([out]).column("id6"), 1))
+    assert hot.num_rows == 1 and hot.column("c")[0].as_py() > 0.04 * 2 * n  # the hottest group really is hot
