@@ -99,7 +99,7 @@ SIGNATURES = {
     "bgpu_ipc_schema_message": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
     "bgpu_ipc_record_batch_metadata": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_int32, C.POINTER(C.c_int64),
                                                  C.c_int32, C.c_int64, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
-    "bgpu_ipc_encode_partitions": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.c_uint32,
+    "bgpu_ipc_encode_partitions": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.c_uint32, C.c_int32,
                                              C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
     "bgpu_ipc_free": (None, [C.c_void_p, C.c_int]),
     "bgpu_ipc_reader_open": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]),

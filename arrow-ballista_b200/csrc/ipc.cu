@@ -340,6 +340,129 @@ __global__ void __launch_bounds__(kIpcThreads) ipc_body_kernel(const Job* __rest
   }
 }
 
+// ---- LZ4_FRAME compression of the message bodies (what the reference's writer applies per buffer,
+// /root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:365-376) -------------------------------------------
+// One warp compresses one block of at most 64 KB into an LZ4 block (block-independent frames, as lz4_flex writes them):
+// the 32 lanes test 32 consecutive positions at once against a 4096-entry hash table of earlier positions in shared
+// memory, the first lane with a >= 4-byte match wins, the match is extended 32 bytes per step, and the sequence (token,
+// literal run, offset, match length) is written out - header bytes by lane 0, literals strided over the lanes. Greedy,
+// no lazy matching: the ratio is a little below the CPU codec's, the format is the same.
+constexpr int kLzcWarps = 4;
+constexpr uint32_t kLzcBlock = 64 * 1024, kLzcHashBits = 12;
+constexpr uint32_t kLzcBound = kLzcBlock + kLzcBlock / 255 + 16;
+struct LzcJob {
+  const uint8_t* src;
+  uint8_t* dst;  // kLzcBound bytes
+  uint32_t n;
+  uint32_t pad;
+};
+__device__ __forceinline__ uint32_t lzc_load4(const uint8_t* p) {
+  return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+}
+// bytes a length of `v` adds after the token (v >= 15: 1 + (v - 15) / 255)
+__device__ __forceinline__ uint32_t lzc_len_bytes(uint32_t v) { return v >= 15 ? 1 + (v - 15) / 255 : 0; }
+__device__ __forceinline__ uint32_t lzc_put_len(uint8_t* dst, uint32_t op, uint32_t v) {  // one lane
+  if (v < 15) return op;
+  v -= 15;
+  while (v >= 255) { dst[op++] = 255; v -= 255; }
+  dst[op++] = (uint8_t)v;
+  return op;
+}
+__global__ void __launch_bounds__(kLzcWarps * 32) lz4_compress_kernel(const LzcJob* __restrict__ jobs, uint32_t n_jobs,
+                                                                     uint32_t* __restrict__ out_sizes) {
+  __shared__ uint16_t s_table[kLzcWarps][1u << kLzcHashBits];
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31, job = blockIdx.x * kLzcWarps + warp;
+  if (job >= n_jobs) return;
+  const LzcJob j = jobs[job];
+  const uint8_t* __restrict__ src = j.src;
+  uint8_t* dst = j.dst;
+  const uint32_t n = j.n;
+  uint16_t* table = s_table[warp];
+  for (uint32_t i = lane; i < (1u << kLzcHashBits); i += 32) table[i] = 0xffffu;
+  __syncwarp();
+  uint32_t op = 0, anchor = 0, pos = 0;
+  // a match must start at least 12 bytes before the end of the block and may not cover its last 5 bytes
+  const uint32_t match_start_limit = n >= 13 ? n - 12 : 0, match_end_limit = n >= 5 ? n - 5 : 0;
+  while (pos < match_start_limit) {
+    const uint32_t p = pos + lane;
+    const bool in_range = p < match_start_limit;
+    uint32_t v = 0, h = 0, cand = 0xffffu;
+    if (in_range) {
+      v = lzc_load4(src + p);
+      h = (v * 2654435761u) >> (32 - kLzcHashBits);
+      cand = table[h];
+    }
+    __syncwarp();
+    if (in_range) table[h] = (uint16_t)p;  // lanes with one hash: any winner will do
+    __syncwarp();
+    const bool hit = in_range && cand != 0xffffu && cand < p && lzc_load4(src + cand) == v;
+    const uint32_t hits = __ballot_sync(0xffffffffu, hit);
+    if (!hits) {
+      pos += 32;
+      continue;
+    }
+    const int first = __ffs(hits) - 1;
+    const uint32_t mp = pos + first, mc = __shfl_sync(0xffffffffu, cand, first);
+    // extend the match, 32 bytes per step
+    const uint32_t max_len = match_end_limit - mp;  // mp < n - 12, so max_len >= 8
+    uint32_t len = 4;
+    while (len < max_len) {
+      const uint32_t i = len + lane;
+      const bool same = i < max_len && src[mp + i] == src[mc + i];
+      const uint32_t ball = __ballot_sync(0xffffffffu, same);
+      if (ball == 0xffffffffu) {
+        len += 32;
+        continue;
+      }
+      len += (uint32_t)(__ffs(~ball) - 1);
+      break;
+    }
+    if (len > max_len) len = max_len;
+    // the sequence: token | literal length | literals | offset | match length
+    const uint32_t lit = mp - anchor, ml = len - 4;
+    const uint32_t lit_at = op + 1 + lzc_len_bytes(lit);
+    if (lane == 0) {
+      dst[op] = (uint8_t)(((lit < 15 ? lit : 15) << 4) | (ml < 15 ? ml : 15));
+      lzc_put_len(dst, op + 1, lit);
+      const uint32_t off_at = lit_at + lit, offset = mp - mc;
+      dst[off_at] = (uint8_t)offset;
+      dst[off_at + 1] = (uint8_t)(offset >> 8);
+      lzc_put_len(dst, off_at + 2, ml);
+    }
+    for (uint32_t i = lane; i < lit; i += 32) dst[lit_at + i] = src[anchor + i];
+    op = lit_at + lit + 2 + lzc_len_bytes(ml);
+    pos = mp + len;
+    anchor = pos;
+    __syncwarp();
+  }
+  {  // the last sequence: literals only
+    const uint32_t lit = n - anchor, lit_at = op + 1 + lzc_len_bytes(lit);
+    if (lane == 0) {
+      dst[op] = (uint8_t)((lit < 15 ? lit : 15) << 4);
+      lzc_put_len(dst, op + 1, lit);
+    }
+    for (uint32_t i = lane; i < lit; i += 32) dst[lit_at + i] = src[anchor + i];
+    op = lit_at + lit;
+  }
+  if (lane == 0) out_sizes[job] = op;
+}
+
+// byte ranges to byte positions (compressed blocks into their place in the frames)
+struct PackJob { const uint8_t* src; uint64_t dst; uint32_t n; uint32_t pad; };
+__global__ void __launch_bounds__(kIpcThreads) ipc_pack_kernel(const PackJob* __restrict__ jobs, uint8_t* __restrict__ out) {
+  const PackJob j = jobs[blockIdx.x];
+  uint8_t* dst = out + j.dst;
+  // destination-aligned 4-byte stores fed by bytes; ragged edges by bytes
+  const uint32_t head = min(j.n, (uint32_t)((4 - ((uint64_t)dst & 3)) & 3));
+  for (uint32_t i = threadIdx.x; i < head; i += kIpcThreads) dst[i] = j.src[i];
+  const uint32_t words = (j.n - head) >> 2;
+  for (uint32_t w = threadIdx.x; w < words; w += kIpcThreads) {
+    const uint8_t* s = j.src + head + 4 * w;
+    ((uint32_t*)(dst + head))[w] = (uint32_t)s[0] | ((uint32_t)s[1] << 8) | ((uint32_t)s[2] << 16) | ((uint32_t)s[3] << 24);
+  }
+  for (uint32_t i = head + 4 * words + threadIdx.x; i < j.n; i += kIpcThreads) dst[i] = j.src[i];
+}
+
 __global__ void gather_i32_kernel(const int32_t* __restrict__ src, const uint64_t* __restrict__ idx, int32_t* __restrict__ out, uint32_t n) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = src[idx[i]];
@@ -429,8 +552,9 @@ extern "C" int bgpu_ipc_record_batch_metadata(bgpu_ctx* ctx, int64_t rows, const
 }
 
 extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch, const uint64_t* offsets, uint32_t n,
-                                          uint8_t** out_bytes, uint64_t* out_msg_off) {
+                                          int32_t compression, uint8_t** out_bytes, uint64_t* out_msg_off) {
   if (!ctx || !batch || !offsets || !out_bytes || !out_msg_off || n == 0) return BGPU_EINVAL;
+  if (compression < -1 || compression > 0) return ctx->fail(BGPU_EUNSUPPORTED, "compression must be -1 (none) or 0 (LZ4_FRAME)");
   *out_bytes = nullptr;
   if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -462,9 +586,10 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
   size_t n_buffers = 0;
   for (const Column& c : batch->cols) n_buffers += (c.kind == K_UTF8 || c.kind == K_BINARY) ? 3 : 2;
   std::vector<uint8_t> msg;
-  record_batch_message(0, std::vector<std::pair<int64_t, int64_t>>(n_cols), std::vector<std::pair<int64_t, int64_t>>(n_buffers), 0, &msg);
+  record_batch_message(0, std::vector<std::pair<int64_t, int64_t>>(n_cols), std::vector<std::pair<int64_t, int64_t>>(n_buffers), 0, &msg,
+                       compression);
   const uint64_t meta_len = msg.size();
-  struct Part { std::vector<std::pair<int64_t, int64_t>> buffers; std::vector<int> counter; uint64_t body_len = 0; };
+  struct Part { std::vector<std::pair<int64_t, int64_t>> buffers; std::vector<int> counter; uint64_t body_len = 0, body0 = 0; };
   std::vector<Part> parts(n);
   std::vector<Job> jobs;
   uint64_t total = 0;
@@ -479,6 +604,7 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
     const uint64_t body0 = total + meta_len;
     uint64_t body = 0;
     auto buffer = [&](uint64_t len) { pt.buffers.emplace_back((int64_t)body, (int64_t)len); const uint64_t at = body0 + body; body += pad8(len); return at; };
+    pt.body0 = body0;
     size_t u = 0;
     for (size_t i = 0; i < n_cols; i++) {
       const Column& c = batch->cols[i];
@@ -530,6 +656,130 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
     ctx->launches++;
   }
   BGPU_CUDA(ctx, cudaGetLastError());
+  if (compression == 0) {
+    // ---- LZ4_FRAME: compress every buffer of every message on the device, then lay the compressed messages out ----------
+    // a. one job per <= 64 KB block of every non-empty buffer
+    struct Buf { uint32_t p; size_t idx; uint64_t at, len; size_t job0, n_jobs; };
+    std::vector<Buf> bufs;
+    std::vector<LzcJob> cjobs;
+    for (uint32_t p = 0; p < n; p++)
+      for (size_t i = 0; i < parts[p].buffers.size(); i++) {
+        const uint64_t len = (uint64_t)parts[p].buffers[i].second;
+        if (!len) continue;
+        Buf b{p, i, parts[p].body0 + (uint64_t)parts[p].buffers[i].first, len, cjobs.size(), (size_t)((len + kLzcBlock - 1) / kLzcBlock)};
+        for (size_t k = 0; k < b.n_jobs; k++)
+          cjobs.push_back(LzcJob{(const uint8_t*)stage->p + b.at + k * kLzcBlock, nullptr, (uint32_t)std::min<uint64_t>(kLzcBlock, len - k * kLzcBlock), 0});
+        bufs.push_back(b);
+      }
+    DevAllocPtr tmp, d_cjobs, d_sizes;
+    BGPU_TRY(dev_alloc(ctx, cjobs.size() * (size_t)kLzcBound, &tmp));
+    for (size_t k = 0; k < cjobs.size(); k++) cjobs[k].dst = (uint8_t*)tmp->p + k * (size_t)kLzcBound;
+    BGPU_TRY(dev_alloc(ctx, cjobs.size() * sizeof(LzcJob), &d_cjobs));
+    BGPU_TRY(dev_alloc(ctx, cjobs.size() * 4, &d_sizes));
+    BGPU_CUDA(ctx, cudaMemcpyAsync(d_cjobs->p, cjobs.data(), cjobs.size() * sizeof(LzcJob), cudaMemcpyHostToDevice, ctx->stream));
+    lz4_compress_kernel<<<(unsigned)((cjobs.size() + kLzcWarps - 1) / kLzcWarps), kLzcWarps * 32, 0, ctx->stream>>>(
+        (const LzcJob*)d_cjobs->p, (uint32_t)cjobs.size(), (uint32_t*)d_sizes->p);
+    ctx->launches++;
+    BGPU_CUDA(ctx, cudaGetLastError());
+    std::vector<uint32_t> sizes(cjobs.size());
+    std::vector<unsigned long long> set_bits((size_t)std::max(1, n_counters), 0);
+    BGPU_CUDA(ctx, cudaMemcpyAsync(sizes.data(), d_sizes->p, sizes.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BGPU_CUDA(ctx, cudaMemcpyAsync(set_bits.data(), d_cnt->p, set_bits.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    // b. compressed layout. A buffer becomes [int64 raw length][frame: magic FLG BD HC | (size, block)* | end mark], or
+    //    [-1][raw bytes] when the frame would not be smaller (as arrow-ipc does); a block that did not shrink is stored.
+    struct Word { uint64_t at; uint32_t v; };   // 4-byte words the host writes after the copy (sizes, marks)
+    std::vector<Word> words;
+    std::vector<std::pair<uint64_t, int64_t>> prefixes;  // (at, raw length or -1)
+    std::vector<PackJob> pjobs;
+    std::vector<std::vector<std::pair<int64_t, int64_t>>> cbuffers(n);
+    std::vector<uint64_t> cbody_len(n, 0), cmsg_off(n + 1, 0);
+    uint64_t ctotal = 0;
+    size_t bi = 0;
+    constexpr uint32_t kMagic = 0x184D2204u;
+    for (uint32_t p = 0; p < n; p++) {
+      cmsg_off[p] = ctotal;
+      if (offsets[p + 1] == offsets[p]) continue;
+      const uint64_t body0 = ctotal + meta_len;
+      uint64_t body = 0;
+      for (size_t i = 0; i < parts[p].buffers.size(); i++) {
+        if (!parts[p].buffers[i].second) {
+          cbuffers[p].emplace_back((int64_t)body, 0);
+          continue;
+        }
+        const Buf& b = bufs[bi++];
+        uint64_t frame = 7 + 4;  // header + end mark
+        for (size_t k = 0; k < b.n_jobs; k++) frame += 4 + std::min<uint32_t>(sizes[b.job0 + k], cjobs[b.job0 + k].n);
+        const uint64_t at = body0 + body;
+        uint64_t enc;
+        if (frame >= b.len) {  // stored
+          prefixes.emplace_back(at, -1);
+          for (size_t k = 0; k < b.n_jobs; k++)
+            pjobs.push_back(PackJob{cjobs[b.job0 + k].src, at + 8 + k * (uint64_t)kLzcBlock, cjobs[b.job0 + k].n, 0});
+          enc = 8 + b.len;
+        } else {
+          prefixes.emplace_back(at, (int64_t)b.len);
+          uint64_t q = at + 8;
+          words.push_back(Word{q, kMagic});
+          // FLG = version 01, block-independent; BD = 64 KB blocks; HC = (xxh32(FLG BD) >> 8) & 0xff = 0x82
+          words.push_back(Word{q + 4, 0x60u | (0x40u << 8) | (0x82u << 16)});  // the 4th byte is overwritten by the first block size
+          q += 7;
+          for (size_t k = 0; k < b.n_jobs; k++) {
+            const LzcJob& cj = cjobs[b.job0 + k];
+            const bool stored = sizes[b.job0 + k] >= cj.n;
+            const uint32_t sz = stored ? cj.n : sizes[b.job0 + k];
+            words.push_back(Word{q, sz | (stored ? 0x80000000u : 0u)});
+            pjobs.push_back(PackJob{stored ? cj.src : cj.dst, q + 4, sz, 0});
+            q += 4 + sz;
+          }
+          words.push_back(Word{q, 0});  // end mark
+          enc = 8 + frame;
+        }
+        cbuffers[p].emplace_back((int64_t)body, (int64_t)enc);
+        body += pad8(enc);
+      }
+      cbody_len[p] = body;
+      ctotal = body0 + body;
+    }
+    cmsg_off[n] = ctotal;
+    // c. pack on the device, one copy to the host, then the small words and the metadata
+    DevAllocPtr stage2, d_pjobs;
+    BGPU_TRY(dev_alloc(ctx, ctotal, &stage2));
+    BGPU_TRY(dev_alloc(ctx, pjobs.size() * sizeof(PackJob), &d_pjobs));
+    BGPU_CUDA(ctx, cudaMemsetAsync(stage2->p, 0, ctotal, ctx->stream));
+    BGPU_CUDA(ctx, cudaMemcpyAsync(d_pjobs->p, pjobs.data(), pjobs.size() * sizeof(PackJob), cudaMemcpyHostToDevice, ctx->stream));
+    ipc_pack_kernel<<<(unsigned)pjobs.size(), kIpcThreads, 0, ctx->stream>>>((const PackJob*)d_pjobs->p, (uint8_t*)stage2->p);
+    ctx->launches++;
+    BGPU_CUDA(ctx, cudaGetLastError());
+    uint8_t* chost = nullptr;
+    BGPU_CUDA(ctx, pinned_pool().take(ctotal, &chost));
+    cudaError_t ce = cudaMemcpyAsync(chost, stage2->p, ctotal, cudaMemcpyDeviceToHost, ctx->stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(ctx->stream);
+    if (ce != cudaSuccess) {
+      pinned_pool().give(chost);
+      return ctx->fail(BGPU_ECUDA, std::string("IPC encode: ") + cudaGetErrorString(ce));
+    }
+    for (const Word& w : words) {
+      memcpy(chost + w.at, &w.v, w.at + 4 <= ctotal ? 4 : ctotal - w.at);
+    }
+    for (auto& pr : prefixes) memcpy(chost + pr.first, &pr.second, 8);
+    for (uint32_t p = 0; p < n; p++) {
+      const uint64_t rows = offsets[p + 1] - offsets[p];
+      if (rows == 0) continue;
+      std::vector<std::pair<int64_t, int64_t>> nodes;
+      for (size_t i = 0; i < n_cols; i++)
+        nodes.emplace_back((int64_t)rows, parts[p].counter[i] < 0 ? 0 : (int64_t)(rows - set_bits[(size_t)parts[p].counter[i]]));
+      record_batch_message((int64_t)rows, nodes, cbuffers[p], (int64_t)cbody_len[p], &msg, 0);
+      if (msg.size() != meta_len) {
+        pinned_pool().give(chost);
+        return ctx->fail(BGPU_EINVAL, "internal: IPC metadata size is not constant");
+      }
+      memcpy(chost + cmsg_off[p], msg.data(), msg.size());
+    }
+    for (uint32_t p = 0; p <= n; p++) out_msg_off[p] = cmsg_off[p];
+    *out_bytes = chost;
+    return BGPU_OK;
+  }
   uint8_t* host = nullptr;
   BGPU_CUDA(ctx, pinned_pool().take(total, &host));
   std::vector<unsigned long long> set_bits((size_t)std::max(1, n_counters), 0);

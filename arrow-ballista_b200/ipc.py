@@ -87,13 +87,16 @@ class EncodedPartitions:
         self.close()
 
 
-def encode_partitions(ctx, device_batch, offsets):
-    """Rows [offsets[p], offsets[p + 1]) of `device_batch` for every p, each as one encapsulated RecordBatch message."""
+def encode_partitions(ctx, device_batch, offsets, compression=None):
+    """Rows [offsets[p], offsets[p + 1]) of `device_batch` for every p, each as one encapsulated RecordBatch message;
+    compression="lz4": buffers LZ4_FRAME-compressed on the device, as the reference's writer compresses them."""
     n = len(offsets) - 1
     offs = (C.c_uint64 * (n + 1))(*[int(o) for o in offsets])
     msg_off = (C.c_uint64 * (n + 1))()
     p = C.c_void_p()
-    ctx.check(lib().bgpu_ipc_encode_partitions(ctx._h, device_batch._h, offs, n, C.byref(p), msg_off))
+    if compression not in (None, "lz4"):
+        raise ValueError("compression must be None or 'lz4'")
+    ctx.check(lib().bgpu_ipc_encode_partitions(ctx._h, device_batch._h, offs, n, 0 if compression == "lz4" else -1, C.byref(p), msg_off))
     return EncodedPartitions(p if p.value else None, list(msg_off))
 
 

@@ -14,9 +14,10 @@
   * metrics `write_time`, `repart_time`, `input_rows`, `output_rows` (:139-163)
 
 IPC framing: with `ipc="device"` (the default whenever the schema has no dictionary column) the
-RecordBatch messages are produced by libbgpu (`ipc.py`: bodies laid out by one kernel, one device-to-host copy,
-hand-built flatbuffer metadata) and appended to the partition files as they are - uncompressed Arrow IPC streams, which
-the reference's `StreamReader` reads like its own LZ4_FRAME ones. With `ipc="host"` (and for dictionary columns)
+RecordBatch messages are produced by libbgpu (`ipc.py`: bodies laid out by one kernel, LZ4_FRAME-compressed per buffer
+by another as the reference's writer compresses them - `compression=None` leaves them uncompressed, which the
+reference's `StreamReader` reads just as well - one device-to-host copy, hand-built flatbuffer metadata) and appended
+to the partition files as they are. With `ipc="host"` (and for dictionary columns)
 pyarrow's writer stands in for arrow-ipc's `StreamWriter`, LZ4_FRAME as the reference writes. Inside one NVSwitch node
 the files are bypassed altogether: see `exchange.py`.
 """
@@ -110,8 +111,9 @@ class GpuShuffleWriterExec:
     """
 
     def __init__(self, job_id, stage_id, partitions, plan, work_dir, shuffle_output_partitioning, ctx=None,
-                 input_schema=None, input_partitioning=None, ipc=None):
+                 input_schema=None, input_partitioning=None, ipc=None, compression="lz4"):
         self.ipc = ipc  # "device", "host" or None = device unless the schema has a dictionary column
+        self.compression = compression  # device framing: "lz4" (LZ4_FRAME, as the reference writes) or None
         self.job_id, self.stage_id, self.partitions = str(job_id), int(stage_id), list(partitions)
         self.plan, self.work_dir = plan, str(work_dir)
         self.shuffle_output_partitioning = shuffle_output_partitioning
@@ -219,7 +221,7 @@ class GpuShuffleWriterExec:
             dbatch = input_batch if isinstance(input_batch, DeviceBatch) else DeviceBatch.upload(self.ctx, input_batch)
             out, offs = partitioner.partition_device(dbatch)
             t0 = time.perf_counter()
-            enc = ipc.encode_partitions(self.ctx, out, offs)
+            enc = ipc.encode_partitions(self.ctx, out, offs, self.compression)
             for p in range(n):
                 rows = offs[p + 1] - offs[p]
                 if rows == 0:

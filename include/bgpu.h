@@ -230,8 +230,8 @@ void bgpu_peer_exchange_destroy(bgpu_peer_exchange* x);
  * Replaces arrow-ipc's StreamWriter as ShuffleWriterExec drives it, one `write(batch)` per non-empty output partition
  * (/root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:351-399; IPCWriter,
  * /root/reference/ballista/core/src/utils.rs:63-141). A partition file is: schema message, the RecordBatch messages
- * appended to it, then the end-of-stream marker (ff ff ff ff 00 00 00 00). Messages are uncompressed, metadata
- * version V5, buffers 8-byte aligned. Dictionary columns: BGPU_EUNSUPPORTED.
+ * appended to it, then the end-of-stream marker (ff ff ff ff 00 00 00 00). Metadata version V5, buffers 8-byte aligned,
+ * bodies uncompressed or LZ4_FRAME. Dictionary columns: BGPU_EUNSUPPORTED.
  *
  * bgpu_ipc_schema_message: the encapsulated Schema message of a struct-typed ArrowSchema (host only; malloc'ed: free
  *   with bgpu_ipc_free(p, 0)).
@@ -242,13 +242,15 @@ void bgpu_peer_exchange_destroy(bgpu_peer_exchange* x);
  *   [offsets[p], offsets[p + 1]) of `batch`; bodies are laid out by one kernel on the device and arrive with one copy.
  *   *out_bytes (pinned host memory; free with bgpu_ipc_free(p, 1); NULL when every partition is empty) holds the
  *   messages back to back: message p = bytes [out_msg_off[p], out_msg_off[p + 1]) (empty range = empty partition).
- *   out_msg_off has n + 1 entries. */
+ *   out_msg_off has n + 1 entries. compression = 0: every buffer is LZ4_FRAME-compressed ON THE DEVICE as the reference's
+ *   writer does per buffer (shuffle_writer.rs:365-376; frames of block-independent 64 KB blocks like lz4_flex's, one warp
+ *   per block; a buffer that does not shrink is stored behind a -1 length) before the (smaller) copy to the host. */
 int bgpu_ipc_schema_message(bgpu_ctx* ctx, const struct ArrowSchema* schema, uint8_t** out_bytes, uint64_t* out_len);
 int bgpu_ipc_record_batch_metadata(bgpu_ctx* ctx, int64_t rows, const int64_t* nodes, int32_t n_nodes, const int64_t* buffers,
                                    int32_t n_buffers, int64_t body_len, int32_t compression /* -1 none, 0 LZ4_FRAME */,
                                    uint8_t** out_bytes, uint64_t* out_len);
 int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch, const uint64_t* offsets, uint32_t n,
-                               uint8_t** out_bytes, uint64_t* out_msg_off);
+                               int32_t compression /* -1 none, 0 LZ4_FRAME */, uint8_t** out_bytes, uint64_t* out_msg_off);
 void bgpu_ipc_free(uint8_t* bytes, int pinned);
 
 /* ---- Arrow IPC stream reader into device batches: the inverse of the above ----------------

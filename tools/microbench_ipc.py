@@ -66,6 +66,11 @@ sp, so = bb.BatchPartitioner.try_new(bb.Partitioning.Hash([0], 16), ctx).partiti
 t = timed(lambda: ipc.encode_partitions(ctx, sp, so))
 print(f"bgpu_ipc_encode_partitions {m} rows, 16 partitions: {t * 1e3:.3f} ms  {m * ROW / t / 1e9:.1f} GB/s (device layout + one D2H copy into pinned memory)")
 
+t = timed(lambda: ipc.encode_partitions(ctx, sp, so, compression="lz4"))
+enc = ipc.encode_partitions(ctx, sp, so, compression="lz4")
+print(f"bgpu_ipc_encode_partitions lz4, same batch: {t * 1e3:.3f} ms  {m * ROW / t / 1e9:.1f} GB/s of input, {enc.total_bytes / 1e6:.0f} MB out of {m * ROW / 1e6:.0f} MB")
+del enc
+
 # K8: reader. The stream is what Arrow's writer produces from the host copy of `small`.
 host = small.download()
 for comp in (None, "lz4"):
