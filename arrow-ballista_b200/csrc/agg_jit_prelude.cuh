@@ -822,13 +822,24 @@ __device__ __forceinline__ void sketch_body(const JitArgs& a) {
       const int64_t r = base + u * T + threadIdx.x;
       Plan::template load2<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
     }
+    // test before set: with repeated keys the bit is usually there already, and a plain L2 read does not serialise the
+    // way an atomic on a hot word does (Zipf(1) keys, 5e8 rows: 25.8 ms -> the uniform-key time)
+    uint32_t word[R], bit[R], cur[R];
 #pragma unroll
     for (int u = 0; u < R; u++) {
       const int64_t r = base + u * T + threadIdx.x;
+      bit[u] = 0;
+      word[u] = 0;
       if (r > last || !Plan::filter(a, x[u])) continue;
       const uint64_t h = key_hash<Plan::KEY_WORDS>(Plan::key(a, x[u])) >> 16;  // bits the table index does not use first
-      atomicOr(&a.gids[(uint32_t)(h >> 5) & wmask], 1u << (h & 31));
+      word[u] = (uint32_t)(h >> 5) & wmask;
+      bit[u] = 1u << (h & 31);
     }
+#pragma unroll
+    for (int u = 0; u < R; u++) cur[u] = bit[u] ? __ldcg(&a.gids[word[u]]) : 0u;
+#pragma unroll
+    for (int u = 0; u < R; u++)
+      if (bit[u] & ~cur[u]) atomicOr(&a.gids[word[u]], bit[u]);
   }
 }
 
