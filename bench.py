@@ -228,6 +228,30 @@ class HotPath:
         return self.shuffle_and_final(self.partial(device_batches))
 
 
+_ORIGINAL_AFFINITY = None
+
+
+def bind_to_gpu_numa_node(index):
+    """Run this rank on the CPUs next to its GPU (NVML's affinity mask), so that the pinned host buffers of the end-to-end
+    leg are first-touched on that NUMA node: with 8 ranks uploading at once, buffers that all sit on one socket share one
+    memory controller and one inter-socket link. Best effort (a rank that cannot be bound just stays where it is)."""
+    global _ORIGINAL_AFFINITY
+    try:
+        import pynvml
+
+        _ORIGINAL_AFFINITY = os.sched_getaffinity(0)
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (m >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -239,6 +263,7 @@ def run_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    bind_to_gpu_numa_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     stream = torch.cuda.Stream(device=dev)
@@ -332,6 +357,8 @@ def run_ours(args):
                      "bytes_per_row": Q1_BYTES_PER_ROW, "peak_source": peak_src},
     }
     if rank == 0 and not args.no_cpu:
+        if _ORIGINAL_AFFINITY:
+            os.sched_setaffinity(0, _ORIGINAL_AFFINITY)  # the CPU baseline gets every host core back
         line["cpu_baseline"] = cpu_baseline(args.cpu_rows)
     if rank == 0:
         print(json.dumps(line), flush=True)
