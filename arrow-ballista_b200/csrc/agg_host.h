@@ -49,6 +49,7 @@ struct bgpu_agg {
   bool seen_tracking = false;
   int fused_rung = 0;  // first rung of the fused ladder still worth trying; kFusedRungs = two-pass only
   uint32_t private_gcap = 4;  // groups per thread the private rung starts with (doubles when a batch needs more)
+  uint32_t shared_gcap = 128; // group capacity the multi-CTA shared rung starts with: few groups = one copy per warp
   // dictionary-typed group columns are keyed by value: the aggregate keeps one canonical dictionary per column
   // (host copy; uploaded at emit) and maps every batch dictionary onto it
   struct DictState {

@@ -488,6 +488,29 @@ struct SharedSplitSink {  // one of `replicas` copies of [g_cap][W] in shared me
   }
 };
 
+// A copy of [g_cap][W] that only ONE lane at a time touches for a given group (warp-private copies, equal group ids
+// inside the warp taken in turns): plain read-modify-write. LDS/STS move 128 B per cycle and SM; shared atomics retire
+// about one lane every two cycles, and the Float64 one is a compare-and-swap loop.
+struct PlainSharedSink {
+  static constexpr bool kSkipAliased = true;
+  uint64_t* base;  // &s_acc[(warp * g_cap + g) * W]
+  template <int OP, int WORD0, int IDX, int OUT>
+  __device__ __forceinline__ void add(const JitArgs&, Val v) {
+    uint64_t* p = base + WORD0;
+    if (OP == OP_ADD_F64) {
+      *(double*)p += as_f64(v.lo);
+    } else if (OP == OP_ADD_I128) {
+      const Val s = add128(Val{p[0], p[1]}, v);
+      p[0] = s.lo;
+      p[1] = s.hi;
+    } else if (OP == OP_COUNT) {
+      p[0] += 1;
+    } else {
+      p[0] += v.lo;
+    }
+  }
+};
+
 // fused MODE 1: fold the CTA's replicas of one accumulator into its slab (one thread per group)
 struct FlushReplicas {
   const uint64_t* s_acc;
@@ -696,7 +719,43 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
   //   tile i+1: bulk L2 prefetch of every streamed buffer; its "early" loads (utf8 offsets, remapped dictionary keys)
   //             are issued into registers while tile i is processed
   //   tile i:   all remaining loads are issued back to back (phase 1), then consumed (phase 2)
+  // MODE 1 with one copy per warp: no atomics at all. The lanes of a warp that hold the same group in this step take
+  // turns, everything else is a plain read-modify-write of the warp's own copy. Every lane runs the warp-synchronous
+  // part, whatever its row did.
+  const bool warp_private = MODE == 1 && a.replicas == (uint32_t)(T / 32);
+  unsigned char* s_claim = cache.base + (size_t)a.cache_slots * 24;  // u8[T / 32][G rounded up to 16] (host: fused smem)
   auto consume = [&](const typename Plan::Raw& xr, int64_t r) {
+    if (MODE == 1 && warp_private) {
+      const uint32_t lane = threadIdx.x & 31;
+      bool active = r <= last && Plan::filter(a, xr);
+      uint32_t gid = 0x80000000u | lane;  // rows that add nothing: a group id of their own
+      if (active) {
+        const PackedKey k = Plan::key(a, xr);
+        gid = a.cache_slots == 0 ? intern<KW>(a.t, k) : cached_intern<KW>(cache, a.t, k);
+        if (gid >= G) {
+          s_abort = 1;
+          active = false;
+          gid = 0x80000000u | lane;
+        }
+      }
+      // turns by claiming: every pending lane writes its lane id into the warp's claim byte of its group, the lane that
+      // reads its own id back owns the group for this turn. (match.any would give the peers directly, but its cost
+      // grows with the number of distinct values in the warp - ~27 of 32 here: measured 2.5 cycles per row and SM.)
+      unsigned char* claim = s_claim + (size_t)(threadIdx.x >> 5) * ((G + 15) & ~15u);
+      bool pending = active;
+      while (__any_sync(0xffffffffu, pending)) {
+        if (pending) claim[gid] = (unsigned char)lane;
+        __syncwarp();
+        if (pending && claim[gid] == (unsigned char)lane) {
+          PlainSharedSink sink{s_acc + ((size_t)rep * G + gid) * W};
+          const uint32_t seen = Plan::accumulate(a, xr, sink, &ovf);
+          if (Plan::HAS_SEEN && seen) atomicOr(&s_seen[gid], seen);
+          pending = false;
+        }
+        __syncwarp();
+      }
+      return;
+    }
     if (r > last || !Plan::filter(a, xr)) return;
     const PackedKey k = Plan::key(a, xr);
     // cache_slots == 0: no per-CTA key cache (all of shared memory holds accumulators; the table is L2 resident)
@@ -739,7 +798,8 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
       }
     };
     auto stop = [&]() {  // this CTA or (polled every 16th tile) another one gave up: the pass is void
-      return *(volatile int*)&s_abort || ((++tiles_done & 15) == 0 && *(volatile int*)&a.t.flags[3]);
+      const bool st = *(volatile int*)&s_abort || ((++tiles_done & 15) == 0 && *(volatile int*)&a.t.flags[3]);
+      return MODE == 1 ? (bool)__any_sync(0xffffffffu, st) : st;  // (the warp-private path needs whole warps in the loop)
     };
     issue(fa, r0);
     for (;;) {  // (two tiles per trip with the register sets swapping roles spills at 96 registers: measured 30% slower)
@@ -779,7 +839,8 @@ __device__ __forceinline__ void fused_body(const JitArgs& a) {
 #pragma unroll
       for (int u = 0; u < R; u++) consume(x[u], base + u * T + threadIdx.x);
       // some CTA gave up: the pass is void (the global flag is polled every 16th tile: it only saves work)
-      if (*(volatile int*)&s_abort || ((++tiles_done & 15) == 0 && *(volatile int*)&a.t.flags[3])) break;
+      const bool st = *(volatile int*)&s_abort || ((++tiles_done & 15) == 0 && *(volatile int*)&a.t.flags[3]);
+      if (MODE == 1 ? (bool)__any_sync(0xffffffffu, st) : st) break;
     }
   }
   if (ovf) atomicOr(&a.t.flags[2], 1);

@@ -356,8 +356,14 @@ struct LzcJob {
   uint32_t n;
   uint32_t pad;
 };
+// 4 bytes at any alignment: the two aligned words around them, funnel-shifted (reads up to 3 bytes before and 7 bytes
+// after p: the staging buffer is allocated with slack for that)
 __device__ __forceinline__ uint32_t lzc_load4(const uint8_t* p) {
-  return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+  const uintptr_t a = (uintptr_t)p;
+  const uint32_t* w = (const uint32_t*)(a & ~(uintptr_t)3);
+  const uint32_t sh = (uint32_t)(a & 3) * 8;
+  const uint32_t w0 = w[0];
+  return sh ? __funnelshift_r(w0, w[1], sh) : w0;
 }
 // bytes a length of `v` adds after the token (v >= 15: 1 + (v - 15) / 255)
 __device__ __forceinline__ uint32_t lzc_len_bytes(uint32_t v) { return v >= 15 ? 1 + (v - 15) / 255 : 0; }
@@ -406,15 +412,22 @@ __global__ void __launch_bounds__(kLzcWarps * 32) lz4_compress_kernel(const LzcJ
     // extend the match, 32 bytes per step
     const uint32_t max_len = match_end_limit - mp;  // mp < n - 12, so max_len >= 8
     uint32_t len = 4;
-    while (len < max_len) {
-      const uint32_t i = len + lane;
-      const bool same = i < max_len && src[mp + i] == src[mc + i];
-      const uint32_t ball = __ballot_sync(0xffffffffu, same);
-      if (ball == 0xffffffffu) {
-        len += 32;
+    while (len < max_len) {  // 4 bytes per lane, 128 per step
+      const uint32_t i = len + 4 * lane;
+      const uint32_t room = i < max_len ? (max_len - i < 4 ? max_len - i : 4) : 0;  // bytes of this lane's word that may match
+      uint32_t same = 0;
+      if (room) {
+        const uint32_t x = lzc_load4(src + mp + i) ^ lzc_load4(src + mc + i);
+        same = x ? (uint32_t)(__ffs(x) - 1) >> 3 : 4;
+        if (same > room) same = room;
+      }
+      const uint32_t full = __ballot_sync(0xffffffffu, same == 4);
+      if (full == 0xffffffffu) {
+        len += 128;
         continue;
       }
-      len += (uint32_t)(__ffs(~ball) - 1);
+      const int stop = __ffs(~full) - 1;  // first lane whose word did not match completely
+      len += 4 * (uint32_t)stop + __shfl_sync(0xffffffffu, same, stop);
       break;
     }
     if (len > max_len) len = max_len;
@@ -639,7 +652,7 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
 
   // 3. one kernel builds every body in a staging buffer that mirrors the final layout; one copy brings it to the host
   DevAllocPtr stage, d_jobs, d_cnt;
-  BGPU_TRY(dev_alloc(ctx, total, &stage));
+  BGPU_TRY(dev_alloc(ctx, total + 16, &stage));  // + 16: the LZ4 match search reads whole aligned words around a position
   BGPU_TRY(dev_alloc(ctx, jobs.size() * sizeof(Job), &d_jobs));
   BGPU_TRY(dev_alloc(ctx, (size_t)std::max(1, n_counters) * 8, &d_cnt));
   BGPU_CUDA(ctx, cudaMemsetAsync(stage->p, 0, total, ctx->stream));  // buffer padding is zero

@@ -182,3 +182,29 @@ def test_skewed_keys_global_tier_hot_group_cache(bb, ctx, oracle, nulls):
     out = run_both(bb, ctx, oracle, batches, ["id6"], aggs, n_partials=1)
     hot = pa.Table.from_batches([out]).filter(pc.equal(pa.Table.from_batches([out]).column("id6"), 1))
     assert hot.num_rows == 1 and hot.column("c")[0].as_py() > 0.04 * 2 * n  # the hottest group really is hot
+
+
+@pytest.mark.parametrize("domain,nulls,zipf", [(100, False, True), (100, True, True), (100, True, False), (700, True, True)])
+def test_shared_rung_warp_private_copies(bb, ctx, oracle, domain, nulls, zipf):
+    """db-benchmark q4 shape (k = 1e2, and 700 groups so that the capacity has to grow): the multi-CTA shared rung with one
+    accumulator copy per warp - equal group ids inside a warp take turns, everything else is a plain read-modify-write.
+    Zipf keys put the same group in a third of a warp's lanes. Bit-exact sums / counts, Float64 within 1e-9."""
+    rng = np.random.default_rng(domain + 2 * nulls + zipf)
+    n = 400_000
+    batches = []
+    for _ in range(2):
+        k = zipf_keys(rng, n, domain) if zipf else rng.integers(1, domain + 1, n)
+        mask = (rng.random(n) < 0.3) if nulls else None
+        dec = [decimal.Decimal(int(v)) / 100 for v in rng.integers(-10**9, 10**9, n)]
+        batches.append(pa.RecordBatch.from_arrays(
+            [pa.array(k, type=pa.int64()), pa.array(rng.integers(1, 6, n), type=pa.int64(), mask=mask),
+             pa.array(rng.integers(1, 16, n), type=pa.int64()), pa.array(np.round(rng.random(n) * 100, 6), mask=mask),
+             pa.array(dec, type=pa.decimal128(15, 2), mask=mask)],
+            names=["id4", "v1", "v2", "v3", "d"]))
+    aggs = [("avg", "v1", "a1"), ("avg", "v2", "a2"), ("avg", "v3", "a3"), ("sum", "d", "sd"), ("count", "v1", "c1"), ("count", None, "c")]
+    gp = bb.GpuAggregateExec(ctx, bb.AggregateMode.Partial, [0], [(f, None if c is None else batches[0].schema.names.index(c), nm)
+                                                                 for f, c, nm in aggs], batches[0].schema)
+    gp.update(batches[0])
+    # (700 groups of this many accumulators no longer fit two CTAs per SM: the one-CTA shared rung takes them)
+    assert gp.last_path == ("fused_shared2" if domain <= 128 else "fused_shared1"), gp.last_path
+    run_both(bb, ctx, oracle, batches, ["id4"], aggs, n_partials=1)
