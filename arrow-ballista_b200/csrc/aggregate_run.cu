@@ -774,8 +774,9 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
   // which key columns hold a null at all? (bit c of a group's meta = key column c is null.) Columns without one are
   // emitted without a validity bitmap: the state batch of the common null-free case is then plain fixed-width data,
   // which is what the fused repartition + exchange kernel takes.
-  uint32_t key_null_mask = 0;
-  if (n) {
+  // (only for states large enough for the exchange to matter: the answer costs a host round trip in the middle of emit)
+  uint32_t key_null_mask = n && n < 4096 ? 0xffffffffu : 0u;
+  if (n >= 4096) {
     DevAllocPtr d_mask;
     BGPU_TRY(dev_alloc(ctx, 4, &d_mask));
     BGPU_CUDA(ctx, cudaMemsetAsync(d_mask->p, 0, 4, ctx->stream));
