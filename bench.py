@@ -356,7 +356,7 @@ def run_ours(args):
                      "partial_stage_ms": partial_ms,
                      "bytes_per_row": Q1_BYTES_PER_ROW, "peak_source": peak_src},
     }
-    if rank == 0 and not args.no_cpu:
+    if rank == 0 and world == 1 and not args.no_cpu:  # the CPU baseline is reported at N = 1 only
         if _ORIGINAL_AFFINITY:
             os.sched_setaffinity(0, _ORIGINAL_AFFINITY)  # the CPU baseline gets every host core back
         line["cpu_baseline"] = cpu_baseline(args.cpu_rows)

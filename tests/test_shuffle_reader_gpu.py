@@ -272,3 +272,35 @@ def test_stream_reader_reads_reference_style_lz4_files(bb, ctx, sizes):
     assert len(got) == len(batches)
     for g, w in zip(got, batches):
         _same(g, w)
+
+
+def test_edge_cases_empty_inputs(bb, ctx):
+    """Empty streams, empty batches and empty partitions through the reader, the concat and the LZ4 encoder."""
+    from ballista_b200 import ipc
+
+    rng = np.random.default_rng(0)
+    proto = random_batch(rng, 10, with_dict=False)
+    empty = proto.slice(0, 0)
+    # a stream with a schema and no batch: nothing to iterate, the schema is there
+    r = ipc.StreamReader(ctx, _stream(proto.schema, [], None))
+    assert r.schema.equals(proto.schema) and list(r) == []
+    # zero-row batches (compressed and not) come back as zero-row batches
+    for comp in (None, "lz4"):
+        got = [b.download() for b in ipc.StreamReader(ctx, _stream(proto.schema, [empty, proto, empty], comp))]
+        assert [g.num_rows for g in got] == [0, 10, 0]
+        _same(got[1], proto)
+    # concat of nothing but empty batches, and of empty + one
+    e = bb.DeviceBatch.upload(ctx, empty)
+    out = bb.DeviceBatch.concat(ctx, [e, e]).download()
+    assert out.num_rows == 0 and out.schema.equals(proto.schema)
+    _same(bb.DeviceBatch.concat(ctx, [e, bb.DeviceBatch.upload(ctx, proto), e]).download(), proto)
+    # every partition empty: no message at all, with and without compression
+    part, offs = bb.BatchPartitioner.try_new(bb.Partitioning.Hash([0], 4), ctx).partition_device(e)
+    for comp in (None, "lz4"):
+        enc = ipc.encode_partitions(ctx, part, offs, compression=comp)
+        assert enc.total_bytes == 0 and all(len(enc.message(p)) == 0 for p in range(4))
+    # one row: three of four partitions are empty
+    one = bb.DeviceBatch.upload(ctx, proto.slice(0, 1))
+    part, offs = bb.BatchPartitioner.try_new(bb.Partitioning.Hash([0], 4), ctx).partition_device(one)
+    enc = ipc.encode_partitions(ctx, part, offs, compression="lz4")
+    assert sum(len(enc.message(p)) > 0 for p in range(4)) == 1
