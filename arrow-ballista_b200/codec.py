@@ -19,8 +19,8 @@ import struct
 from dataclasses import dataclass, field
 
 from . import ipc
-from ._lib import BGPU_EINVAL, BgpuError, ExprNode
-from .expr import BinaryExpr, Column, Expr, Literal, X_COLUMN, X_LITERAL, T_FLOAT64
+from ._lib import BGPU_EINVAL, BgpuError
+from .expr import BinaryExpr, Column, Literal, X_COLUMN, X_LITERAL, T_FLOAT64
 from .partitioner import Partitioning
 
 WT_VARINT, WT_FIXED64, WT_LEN = 0, 1, 2

@@ -68,7 +68,7 @@ class Exchange:
         scatter kernel storing straight into the owner ranks' receive windows over NVLink. COLLECTIVE. Batches the fused
         kernel does not take (nulls, utf8, ...) go through hash partition + NCCL all-to-all on every rank alike.
         Returns the received DeviceBatch; `last_sent_bytes` / `last_path` describe the call."""
-        from ._lib import BGPU_EUNSUPPORTED, BgpuError
+        from ._lib import BGPU_EUNSUPPORTED
         from .partitioner import BatchPartitioner, Partitioning
 
         if getattr(self, "_peer", None) is None:

@@ -13,7 +13,6 @@ the data staying on the B200:
     (:144-146), several are interleaved (the reference's mpsc channel gives an arbitrary interleave; this mirror takes
     one batch from each live partition in turn, which is one of them).
 """
-import os
 import random
 from dataclasses import dataclass, field
 
