@@ -197,3 +197,30 @@ def reference_style_lz4_stream(batches, block=65536):
         stream += ipc.record_batch_metadata(b.num_rows, nodes, buffers, len(body), compression=0)
         stream += body
     return bytes(stream + ipc.EOS)
+
+
+def q1_testdata():
+    """The reference's own two-partition lineitem test data as Q1 input batches + the expected answer
+    (tests/golden/q1_lineitem_testdata.json, written by tests/golden/make_q1_testdata.py with plain integer arithmetic)."""
+    d = json.load(open(os.path.join(GOLDEN, "q1_lineitem_testdata.json")))
+    dec = pa.decimal128(15, 2)
+    batches = []
+    for rows in d["partitions"]:
+        cols = [pa.array([decimal.Decimal(r[k]).scaleb(-2) for r in rows], type=dec)
+                for k in ("l_quantity", "l_extendedprice", "l_discount", "l_tax")]
+        cols += [pa.array([r[k] for r in rows], type=pa.string()) for k in ("l_returnflag", "l_linestatus")]
+        cols.append(pa.array(np.array([r["l_shipdate"] for r in rows], dtype="int32"), type=pa.date32()))
+        batches.append(pa.RecordBatch.from_arrays(cols, names=["l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_returnflag",
+                                                               "l_linestatus", "l_shipdate"]))
+    return batches, d["expected"]
+
+
+def q1_result_as_unscaled(table):
+    """A Q1 result (pyarrow Table / RecordBatch) as the golden file's rows: decimals as unscaled integers, sorted by key."""
+    out = []
+    for row in pa.Table.from_batches([table]).to_pylist() if isinstance(table, pa.RecordBatch) else table.to_pylist():
+        r = {}
+        for k, v in row.items():
+            r[k] = int(v.scaleb(-v.as_tuple().exponent)) if isinstance(v, decimal.Decimal) else v
+        out.append(r)
+    return sorted(out, key=lambda r: (r["l_returnflag"], r["l_linestatus"]))
