@@ -16,3 +16,5 @@ from . import ipc  # noqa: F401
 from .shuffle_reader import (CoalesceBatchesExec, CoalesceTasksExec, ExecutorMetadata, FetchFailed, GpuShuffleReaderExec,  # noqa: F401
                              PartitionLocation, PartitionStats)
 from .codec import GpuAggregateExecNode, GpuPhysicalCodec  # noqa: F401
+from .execution_engine import (DefaultExecutionEngine, DefaultQueryStageExec, GpuExecutionEngine, GpuQueryStageExec,  # noqa: F401
+                               QueryStageExecutor, match_partial_aggregate_stage)

@@ -180,6 +180,21 @@ class GpuAggregateExecNode:
     group_expr_name: list = field(default_factory=list)
     inputs: list = field(default_factory=list)
 
+    def children(self):
+        return list(self.inputs)
+
+    def execute(self, partition, ctx=None):
+        """AggregateExec::execute(partition): the input's partition through one aggregate; yields its output batch."""
+        from .runtime import Context
+
+        agg = self.instantiate(ctx if ctx is not None else Context(0))
+        try:
+            for b in self.inputs[0].execute(partition):
+                agg.update(b)
+            yield agg.emit()
+        finally:
+            agg.close()
+
     def instantiate(self, ctx):
         from .aggregate import GpuAggregateExec
 

@@ -137,6 +137,11 @@ class DeviceBatch:
     def num_columns(self):
         return int(lib().bgpu_batch_num_columns(self._h))
 
+    @property
+    def schema(self):
+        """The batch's Arrow schema (a zero-row download: no column data moves)."""
+        return self.download(0, 0).schema
+
     def download(self, offset=0, length=None):
         """Device -> host copy of rows [offset, offset+length) as a pyarrow RecordBatch."""
         if length is None:

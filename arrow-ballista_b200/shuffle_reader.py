@@ -141,11 +141,16 @@ class CoalesceBatchesExec:
 
 
 class CoalesceTasksExec:
-    """`execute_partition(p)` is the child's `execute(p)` (returns an iterable of batches); `partitions` the task
-    group's input partitions."""
+    """`input` is the child: a plan node with `execute(p)` (kept as `.input`, what `children()` returns), or just that
+    function (returns an iterable of batches); `partitions` the task group's input partitions."""
 
-    def __init__(self, execute_partition, partitions, schema=None):
-        self.execute_partition, self.partitions, self._schema = execute_partition, list(partitions), schema
+    def __init__(self, input, partitions, schema=None):
+        self.input = input if callable(getattr(input, "execute", None)) else None
+        self.execute_partition = input.execute if self.input is not None else input
+        self.partitions, self._schema = list(partitions), schema
+
+    def children(self):
+        return [self.input] if self.input is not None else []
 
     def schema(self):
         return self._schema

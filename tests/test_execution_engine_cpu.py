@@ -1,0 +1,115 @@
+"""Host logic of the stage-execution hook: which decoded stage plans `GpuExecutionEngine` takes to the
+device and which go to the fallback engine, mirroring /root/reference/ballista/executor/src/execution_engine.rs:63-97
+(the writer is re-created with the executor's work_dir; a plan whose root is no shuffle writer is an error). No GPU."""
+import os
+import sys
+
+import pyarrow as pa
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+class Scan:
+    """A leaf with three input partitions."""
+
+    def __init__(self, schema):
+        self._schema = schema
+
+    def schema(self):
+        return self._schema
+
+    def execute(self, partition):
+        return iter(())
+
+
+def q1_stage(bb, mode=None, coalesce=True, partitioning="hash", fns=None):
+    sys.path.insert(0, ROOT)
+    import bench
+
+    gi, aggs, filt = bench.q1_plan()
+    if fns:
+        aggs = [(fn, a, n) for fn, (_, a, n) in zip(fns, aggs)]
+    schema = bench.lineitem_schema()
+    node = bb.GpuAggregateExecNode(bb.AggregateMode.Partial if mode is None else mode, gi,
+                                   [(bb.AggregateFunction.parse(f), bb.expr.col(a) if isinstance(a, int) else a, n) for f, a, n in aggs],
+                                   schema, filt, inputs=[Scan(schema)])
+    child = bb.CoalesceTasksExec(node, [4, 5, 6]) if coalesce else node
+    part = {"hash": bb.Partitioning.Hash([0, 1], 16), "none": None}[partitioning]
+    return bb.GpuShuffleWriterExec.try_new("job", 1, [4, 5, 6], child, "", part, None), node
+
+
+def test_hot_path_map_stage_goes_to_the_device(bb, tmp_path):
+    plan, node = q1_stage(bb)
+    engine = bb.GpuExecutionEngine()
+    stage = engine.create_query_stage_exec("job7", 2, plan, str(tmp_path))
+    assert isinstance(stage, bb.GpuQueryStageExec) and engine.last_decision == "gpu"
+    # the writer is re-created with the executor's work_dir and the ids of the call (execution_engine.rs:77-87)
+    w = stage.shuffle_writer
+    assert (w.job_id, w.stage_id, w.work_dir, w.partitions) == ("job7", 2, str(tmp_path), [4, 5, 6])
+    assert w.shuffle_output_partitioning.partition_count() == 16 and w.shuffle_output_partitioning.exprs == [0, 1]
+    assert stage.aggregate is node and stage.partitions == [4, 5, 6]
+    assert "GpuAggregateExec(Partial" in str(stage) and "Hash([0, 1], 16)" in str(stage)
+    # without the CoalesceTasksExec the partitions come with execute_query_stage
+    plan, _ = q1_stage(bb, coalesce=False)
+    stage = engine.create_query_stage_exec("job7", 2, plan, str(tmp_path))
+    assert isinstance(stage, bb.GpuQueryStageExec) and stage.partitions is None
+
+
+@pytest.mark.parametrize("kw, why", [
+    (dict(partitioning="none"), "does not hash-repartition"),
+    (dict(mode=2), "not in Partial mode"),
+    (dict(fns=["min"]), "other than SUM / AVG / COUNT"),
+])
+def test_other_stages_go_to_the_fallback_engine(bb, tmp_path, kw, why):
+    plan, _ = q1_stage(bb, **kw)
+    engine = bb.GpuExecutionEngine()
+    stage = engine.create_query_stage_exec("j", 1, plan, str(tmp_path))
+    assert isinstance(stage, bb.DefaultQueryStageExec) and why in engine.last_decision
+    assert stage.shuffle_writer.work_dir == str(tmp_path) and stage.shuffle_writer.plan is plan.plan
+
+    class Theirs:
+        def create_query_stage_exec(self, *a):
+            return ("theirs",) + a
+    got = bb.GpuExecutionEngine(fallback=Theirs()).create_query_stage_exec("j", 1, plan, str(tmp_path))
+    assert got == ("theirs", "j", 1, plan, str(tmp_path), None)
+
+
+def test_child_that_is_a_plain_stream_and_partitioning_over_state_columns_fall_back(bb, tmp_path):
+    schema = pa.schema([("a", pa.int64())])
+    plan = bb.GpuShuffleWriterExec.try_new("j", 1, [0], [], "", bb.Partitioning.Hash([0], 4), None, input_schema=schema)
+    engine = bb.GpuExecutionEngine()
+    assert isinstance(engine.create_query_stage_exec("j", 1, plan, str(tmp_path)), bb.DefaultQueryStageExec)
+    assert "not an aggregate" in engine.last_decision
+    plan, _ = q1_stage(bb)
+    plan.shuffle_output_partitioning = bb.Partitioning.Hash([0, 2], 16)  # column 2 of the state batch is a sum, not a key
+    assert isinstance(engine.create_query_stage_exec("j", 1, plan, str(tmp_path)), bb.DefaultQueryStageExec)
+    assert "group columns" in engine.last_decision
+
+
+def test_root_that_is_no_shuffle_writer_is_an_error(bb, tmp_path):
+    _, node = q1_stage(bb)
+    for engine in (bb.GpuExecutionEngine(), bb.DefaultExecutionEngine()):
+        with pytest.raises(bb.BgpuError, match="Plan passed to new_query_stage_exec is not a ShuffleWriterExec"):
+            engine.create_query_stage_exec("j", 1, node, str(tmp_path))
+
+
+def test_stage_plan_survives_the_codec_and_still_matches(bb, tmp_path):
+    """scheduler -> executor: the optimized stage plan is encoded node by node (children ride as
+    PhysicalExtensionNode.inputs), decoded with work_dir "" and handed to the engine (executor_server.rs:383-397)."""
+    plan, node = q1_stage(bb, coalesce=False)
+    codec = bb.GpuPhysicalCodec()
+    scan = node.inputs[0]
+    agg = codec.try_decode(codec.try_encode(node), [scan])
+    writer = codec.try_decode(codec.try_encode(plan), [agg])
+    assert writer.work_dir == "" and writer.plan is agg and agg.inputs == [scan]
+    stage = bb.GpuExecutionEngine().create_query_stage_exec("job", 1, writer, str(tmp_path))
+    assert isinstance(stage, bb.GpuQueryStageExec) and stage.source is scan
+    assert stage.aggregate.group_by == node.group_by and stage.shuffle_writer.work_dir == str(tmp_path)
+
+
+def test_stage_with_no_input_partitions_writes_nothing(bb, tmp_path):
+    plan, _ = q1_stage(bb, coalesce=False)
+    stage = bb.GpuExecutionEngine(ctx=object()).create_query_stage_exec("job", 1, plan, str(tmp_path))
+    assert stage.execute_query_stage([]) == [] and not os.listdir(tmp_path)
+    assert stage.collect_plan_metrics()[0]["aggregate_input_rows"] == 0
