@@ -17,4 +17,4 @@ from .shuffle_reader import (CoalesceBatchesExec, CoalesceTasksExec, ExecutorMet
                              PartitionLocation, PartitionStats)
 from .codec import GpuAggregateExecNode, GpuPhysicalCodec  # noqa: F401
 from .execution_engine import (DefaultExecutionEngine, DefaultQueryStageExec, GpuExecutionEngine, GpuQueryStageExec,  # noqa: F401
-                               QueryStageExecutor, match_partial_aggregate_stage)
+                               QueryStageExecutor, match_aggregate_stage)

@@ -82,37 +82,51 @@ class DefaultExecutionEngine:
         return DefaultQueryStageExec(_recreate(plan, job_id, stage_id, work_dir))
 
 
-def match_partial_aggregate_stage(plan):
-    """(coalesce | None, aggregate node, source) when `plan` is a map stage of the hot path, else a string saying why
-    not. Purely structural: what the library cannot run (a key or argument type it has no kernel for) is reported by
+def match_aggregate_stage(plan):
+    """(coalesce | None, aggregate node, source) when `plan` is a stage of the hot path, else a string saying why not:
+
+        map stage     ShuffleWriterExec(Hash(group columns, n)) -> [CoalesceTasksExec] -> AggregateExec(Partial) -> source
+        reduce stage  ShuffleWriterExec(None | Hash)            -> [CoalesceTasksExec] -> AggregateExec(FinalPartitioned)
+                                                                   -> [CoalesceBatchesExec] -> ShuffleReaderExec
+
+    Purely structural: what the library cannot run (a key or argument type it has no kernel for) is reported by
     bgpu_agg_create_expr as BGPU_EUNSUPPORTED when the stage executes."""
     part = plan.shuffle_output_partitioning
-    if part is None or part.kind != "hash":
-        return "the stage does not hash-repartition its output"
+    if part is not None and part.kind != "hash":
+        return "the stage's output partitioning is neither hash nor none"
     node, coalesce = plan.plan, None
     if isinstance(node, CoalesceTasksExec):
         coalesce, node = node, node.input
     if not isinstance(node, GpuAggregateExecNode):
         return "the stage's child is not an aggregate"
-    if node.mode != AggregateMode.Partial:
-        return "the aggregate is not in Partial mode"
+    if node.mode not in (AggregateMode.Partial, AggregateMode.FinalPartitioned):
+        return "the aggregate is neither Partial nor FinalPartitioned"
     if not 1 <= len(node.group_by) <= 8:
         return "1..8 group columns"
     if any(f not in (AggregateFunction.Sum, AggregateFunction.Avg, AggregateFunction.Count) for f, _, _ in node.aggr_expr):
         return "an aggregate function other than SUM / AVG / COUNT"
     if len(node.inputs) != 1 or not callable(getattr(node.inputs[0], "execute", None)):
         return "the aggregate needs exactly one executable input"
-    if any(k >= len(node.group_by) for k in part.exprs):
-        # the state batch is (group columns ++ state columns): a stage planned by planner.rs:398-404 hashes group columns
-        return "the output partitioning is not over group columns"
+    if node.mode == AggregateMode.Partial:
+        if part is None:
+            return "a Partial aggregate whose stage does not hash-repartition its output"
+        if any(k >= len(node.group_by) for k in part.exprs):
+            # the state batch is (group columns ++ state columns): a stage planned by planner.rs:398-404 hashes group columns
+            return "the output partitioning is not over group columns"
     return coalesce, node, node.inputs[0]
 
 
+match_partial_aggregate_stage = match_aggregate_stage
+
+
 class GpuQueryStageExec(QueryStageExecutor):
-    """Map stage on the device. With `merge_partitions` (the default) the input partitions of the task group feed ONE
+    """A map (Partial) or reduce (FinalPartitioned) stage on the device. With `merge_partitions` (the default) the input partitions of the task group feed ONE
     Partial aggregate - the reference runs one per partition below its CoalesceTasksExec and interleaves their state
     batches; merging them earlier yields fewer state rows for the same FinalPartitioned result. `merge_partitions=False`
-    keeps one state batch per input partition, as the reference emits them."""
+    keeps one state batch per input partition, as the reference emits them. In a reduce stage the partitions hold
+    disjoint keys, so one merged FinalPartitioned table gives the union of the per-partition results. The reduce
+    stage's source (GpuShuffleReaderExec, CoalesceBatchesExec above it) hands over device batches; its output is
+    written from the device as well (`data.arrow` for an un-partitioned final stage, shuffle_writer.rs:258-326)."""
 
     def __init__(self, shuffle_writer, aggregate, source, partitions=None, ctx=None, merge_partitions=True):
         self.shuffle_writer, self.aggregate, self.source = shuffle_writer, aggregate, source
@@ -128,10 +142,14 @@ class GpuQueryStageExec(QueryStageExecutor):
             t0 = time.perf_counter()
             agg = self.aggregate.instantiate(ctx)
             try:
+                fed = 0
                 for p in group:
                     for b in self.source.execute(p):
                         m["aggregate_input_rows"] += b.num_rows
                         agg.update(b)
+                        fed += 1
+                if not fed:
+                    continue  # no batch at all (a reduce partition no map task wrote to): no output batch either
                 state = agg.emit()
                 m["hot_kernel_ms"] += agg.hot_kernel_ms
                 m["last_path"] = agg.last_path
@@ -167,13 +185,15 @@ class GpuQueryStageExec(QueryStageExecutor):
                                      "output_rows": m.output_rows}]
 
     def schema(self):
-        """The stage's output schema = the Partial state schema (known once the stage has run, or from the decoded plan)."""
+        """The stage's output schema = the aggregate's (known once the stage has run, or from the decoded plan)."""
         return self._schema if self._schema is not None else self.shuffle_writer.schema()
 
     def __str__(self):
         part = self.shuffle_writer.shuffle_output_partitioning
-        return (f"GpuQueryStageExec: GpuShuffleWriterExec(Hash({part.exprs}, {part.partition_count()})) <- "
-                f"GpuAggregateExec(Partial, group_by={self.aggregate.group_by}) <- partitions {self.partitions}")
+        out = "None" if part is None else f"Hash({part.exprs}, {part.partition_count()})"
+        mode = {AggregateMode.Partial: "Partial", AggregateMode.FinalPartitioned: "FinalPartitioned"}.get(self.aggregate.mode)
+        return (f"GpuQueryStageExec: GpuShuffleWriterExec({out}) <- "
+                f"GpuAggregateExec({mode}, group_by={self.aggregate.group_by}) <- partitions {self.partitions}")
 
 
 class GpuExecutionEngine:
@@ -187,7 +207,7 @@ class GpuExecutionEngine:
     def create_query_stage_exec(self, job_id, stage_id, plan, work_dir, sender=None):
         if not isinstance(plan, GpuShuffleWriterExec):
             raise BgpuError(BGPU_EINVAL, _NOT_A_WRITER)
-        m = match_partial_aggregate_stage(plan)
+        m = match_aggregate_stage(plan)
         if isinstance(m, str):
             self.last_decision = f"fallback: {m}"
             return self.fallback.create_query_stage_exec(job_id, stage_id, plan, work_dir, sender)

@@ -122,6 +122,16 @@ class CoalesceBatchesExec:
     def __init__(self, input_stream, ctx, target_batch_size=8192):
         self.input, self.ctx, self.target_batch_size = input_stream, ctx, int(target_batch_size)
 
+    def children(self):
+        return [self.input] if callable(getattr(self.input, "execute", None)) else []
+
+    def schema(self):
+        return self.input.schema() if callable(getattr(self.input, "schema", None)) else None
+
+    def execute(self, partition):
+        """As a plan node over a child with `execute(p)` (the reader): partition p's batches, coalesced."""
+        return iter(CoalesceBatchesExec(self.input.execute(partition), self.ctx, self.target_batch_size))
+
     def __iter__(self):
         buf, rows = [], 0
         for b in (self.input() if callable(self.input) else self.input):

@@ -143,8 +143,12 @@ class GpuShuffleWriterExec:
         return f"GpuShuffleWriterExec: {self.shuffle_output_partitioning and self.shuffle_output_partitioning.kind}"
 
     def _stream(self):
-        s = self.plan() if callable(self.plan) else self.plan
-        return iter(s)
+        # the reference executes partition 0 of its child (shuffle_writer.rs:253: below a task group's
+        # CoalesceTasksExec there is one); plain iterables and zero-argument callables stand in for a child stream
+        p = self.plan
+        if callable(getattr(p, "execute", None)):
+            return iter(p.execute(0))
+        return iter(p() if callable(p) else p)
 
     # ---- execute_shuffle_write ---------------------------------------------------------------------------------
     def execute_shuffle_write(self):
@@ -159,6 +163,20 @@ class GpuShuffleWriterExec:
             w = None
             t0 = time.perf_counter()
             for batch in self._stream():
+                if isinstance(batch, DeviceBatch):
+                    # a stage whose output is already on the device (a Final aggregate): framed by libbgpu like the hash
+                    # arm's partitions, as one "partition" holding every row; dictionary columns go through the host writer
+                    schema = self._schema if self._schema is not None else batch.schema
+                    if self.ipc == "host" or any(pa.types.is_dictionary(f.type) for f in schema):
+                        batch = batch.download()
+                    else:
+                        if w is None:
+                            w = _IpcStreamFile(path, ipc.schema_message(schema, self.ctx))
+                        if batch.num_rows:
+                            enc = ipc.encode_partitions(self.ctx, batch, [0, batch.num_rows], self.compression)
+                            w.write_message(enc.message(0), batch.num_rows)
+                            enc.close()
+                        continue
                 if w is None:
                     w = _WriteTracker(path, batch.schema)
                 w.write(batch)

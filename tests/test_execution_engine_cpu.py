@@ -58,7 +58,7 @@ def test_hot_path_map_stage_goes_to_the_device(bb, tmp_path):
 
 @pytest.mark.parametrize("kw, why", [
     (dict(partitioning="none"), "does not hash-repartition"),
-    (dict(mode=2), "not in Partial mode"),
+    (dict(mode=1), "neither Partial nor FinalPartitioned"),
     (dict(fns=["min"]), "other than SUM / AVG / COUNT"),
 ])
 def test_other_stages_go_to_the_fallback_engine(bb, tmp_path, kw, why):
@@ -113,3 +113,24 @@ def test_stage_with_no_input_partitions_writes_nothing(bb, tmp_path):
     stage = bb.GpuExecutionEngine(ctx=object()).create_query_stage_exec("job", 1, plan, str(tmp_path))
     assert stage.execute_query_stage([]) == [] and not os.listdir(tmp_path)
     assert stage.collect_plan_metrics()[0]["aggregate_input_rows"] == 0
+
+
+def test_reduce_stage_goes_to_the_device(bb, tmp_path):
+    """ShuffleWriterExec(None) -> CoalesceTasksExec -> AggregateExec(FinalPartitioned) -> CoalesceBatchesExec -> reader
+    (planner.rs:405-413 + task_group.rs:143-151: the coalesce sits above a Final aggregate)."""
+    sys.path.insert(0, ROOT)
+    import bench
+
+    gi, aggs, _ = bench.q1_plan()
+    schema = bench.lineitem_schema()
+    reader = bb.GpuShuffleReaderExec([[], [], []], None, None)
+    source = bb.CoalesceBatchesExec(reader, None)
+    assert source.children() == [reader]
+    node = bb.GpuAggregateExecNode(bb.AggregateMode.FinalPartitioned, gi, [(bb.AggregateFunction.parse(f), a, n) for f, a, n in aggs],
+                                   schema, None, inputs=[source])
+    plan = bb.GpuShuffleWriterExec.try_new("job", 2, [0, 1, 2], bb.CoalesceTasksExec(node, [0, 1, 2]), "", None, None)
+    engine = bb.GpuExecutionEngine(ctx=object())
+    stage = engine.create_query_stage_exec("job", 2, plan, str(tmp_path))
+    assert isinstance(stage, bb.GpuQueryStageExec) and engine.last_decision == "gpu"
+    assert stage.source is source and stage.partitions == [0, 1, 2] and "GpuShuffleWriterExec(None)" in str(stage)
+    assert "FinalPartitioned" in str(stage)
