@@ -134,3 +134,48 @@ def test_reduce_stage_goes_to_the_device(bb, tmp_path):
     assert isinstance(stage, bb.GpuQueryStageExec) and engine.last_decision == "gpu"
     assert stage.source is source and stage.partitions == [0, 1, 2] and "GpuShuffleWriterExec(None)" in str(stage)
     assert "FinalPartitioned" in str(stage)
+
+
+def test_reduce_stage_plumbing_with_a_stand_in_aggregate(bb, tmp_path, monkeypatch):
+    """execute_query_stage's host plumbing without a device: the aggregate is replaced by a stand-in that hands back
+    host batches, so that what is checked is the walk over the task group's partitions, the skipping of partitions
+    nobody wrote to, the writer re-creation with the stage's schema, the un-partitioned `data.arrow`
+    (shuffle_writer.rs:258-326) and the metrics."""
+    schema = pa.schema([("k", pa.int64()), ("v", pa.int64())])
+    parts = {0: [pa.record_batch({"k": [1, 2], "v": [10, 20]}, schema=schema)], 1: [],
+             2: [pa.record_batch({"k": [3], "v": [30]}, schema=schema), pa.record_batch({"k": [4], "v": [40]}, schema=schema)]}
+
+    class Source:
+        def execute(self, p):
+            return iter(parts[p])
+
+    class StandIn:
+        hot_kernel_ms, last_path = 0.0, "stand-in"
+
+        def __init__(self):
+            self.rows = []
+
+        def update(self, b):
+            self.rows.append(b)
+
+        def emit(self):
+            return pa.Table.from_batches(self.rows).combine_chunks().to_batches()[0]
+
+        def close(self):
+            pass
+    node = bb.GpuAggregateExecNode(bb.AggregateMode.FinalPartitioned, [0], [(bb.AggregateFunction.Sum, bb.expr.col(1), "v")], schema,
+                                   inputs=[Source()])
+    monkeypatch.setattr(bb.GpuAggregateExecNode, "instantiate", lambda self, ctx: StandIn())
+    for merge, n_batches in ((True, 1), (False, 2)):
+        plan = bb.GpuShuffleWriterExec.try_new("job", 2, [0, 1, 2], bb.CoalesceTasksExec(node, [0, 1, 2]), "", None, None)
+        stage = bb.GpuExecutionEngine(ctx=object(), merge_partitions=merge).create_query_stage_exec("job", 2, plan, str(tmp_path))
+        (w,) = stage.execute_query_stage([0, 1, 2])
+        assert (w.partitions, w.output_partition, w.num_rows, w.num_batches) == ([0, 1, 2], 0, 4, n_batches)
+        assert w.path.startswith(os.path.join(str(tmp_path), "job", "2")) and w.path.endswith("data.arrow")
+        with pa.ipc.open_stream(w.path) as r:
+            got = r.read_all()
+        assert got.sort_by("k").to_pydict() == {"k": [1, 2, 3, 4], "v": [10, 20, 30, 40]}
+        assert stage.schema().equals(schema)
+        m_agg, m_write = stage.collect_plan_metrics()
+        assert m_agg["aggregate_input_rows"] == 4 == m_agg["aggregate_output_rows"] and m_agg["last_path"] == "stand-in"
+        assert m_write["input_rows"] == 4 == m_write["output_rows"]
