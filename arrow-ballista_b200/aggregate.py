@@ -147,6 +147,6 @@ def debug_compile(mode, group_by, aggr_expr, input_schema, filter=None, flags=0,
         finally:
             _release(s)
         if rc != 0:
-            raise BgpuError(rc, L.bgpu_last_error(h).decode())
+            raise BgpuError(rc, L.bgpu_last_error(h).decode(errors="replace"))
     finally:
         L.bgpu_ctx_destroy(h)

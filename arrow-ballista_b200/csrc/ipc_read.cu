@@ -81,6 +81,12 @@ struct Table {
   size_t vec(int id, uint32_t* count) const {
     const size_t at = indirect(id);
     *count = at ? fb->rd<uint32_t>(at) : 0;
+    // the smallest element (an offset) is 4 bytes: a count the buffer cannot hold is a malformed message, and must not
+    // size an allocation
+    if (at && (!fb->ok || at + 4 > fb->n || (size_t)*count > (fb->n - at - 4) / 4)) {
+      fb->ok = false;
+      *count = 0;
+    }
     return at ? at + 4 : 0;
   }
 };
@@ -89,8 +95,37 @@ enum FbType : uint8_t { T_Int = 2, T_FloatingPoint = 3, T_Binary = 4, T_Utf8 = 5
 enum FbHeader : uint8_t { H_NONE = 0, H_Schema = 1, H_DictionaryBatch = 2, H_RecordBatch = 3 };
 
 // Field table -> Column descriptor (name, Arrow C format string, kind, width). Schema.fbs defaults apply to absent fields.
+// Arrow strings (field names, time zones) are UTF-8; a stream whose strings are not is malformed.
+bool valid_utf8(const std::string& s) {
+  const size_t n = s.size();
+  for (size_t i = 0; i < n;) {
+    const uint8_t b = (uint8_t)s[i];
+    int extra;
+    uint32_t cp;
+    if (b < 0x80) { i++; continue; }
+    if ((b & 0xe0) == 0xc0) { extra = 1; cp = b & 0x1f; }
+    else if ((b & 0xf0) == 0xe0) { extra = 2; cp = b & 0x0f; }
+    else if ((b & 0xf8) == 0xf0) { extra = 3; cp = b & 0x07; }
+    else return false;
+    if (i + (size_t)extra >= n) return false;  // truncated sequence
+    for (int k = 1; k <= extra; k++) {
+      const uint8_t cb = (uint8_t)s[i + (size_t)k];
+      if ((cb & 0xc0) != 0x80) return false;
+      cp = (cp << 6) | (cb & 0x3f);
+    }
+    static const uint32_t kMin[4] = {0, 0x80, 0x800, 0x10000};
+    if (cp < kMin[extra] || cp > 0x10ffff || (cp >= 0xd800 && cp <= 0xdfff)) return false;
+    i += (size_t)extra + 1;
+  }
+  return true;
+}
+
 int field_to_column(bgpu_ctx* ctx, Table f, Column* c) {
   c->name = f.str(0);
+  if (!valid_utf8(c->name)) {
+    c->name.clear();
+    return ctx->fail(BGPU_EINVAL, "IPC reader: field name is not UTF-8");
+  }
   c->flags = f.scalar<uint8_t>(1, 0) ? ARROW_FLAG_NULLABLE : 0;
   if (f.field(4)) return ctx->fail(BGPU_EUNSUPPORTED, "IPC reader: dictionary-encoded column " + c->name);
   const uint8_t tt = f.scalar<uint8_t>(2, 0);
@@ -127,6 +162,8 @@ int field_to_column(bgpu_ctx* ctx, Table f, Column* c) {
     case T_Decimal: {
       const int p = t.scalar<int32_t>(0, 0), s = t.scalar<int32_t>(1, 0), bits = t.scalar<int32_t>(2, 128);
       if (bits != 128) break;
+      if (p < 1 || p > 38 || s < -38 || s > 38)
+        return ctx->fail(BGPU_EINVAL, "IPC reader: Decimal128 precision / scale out of range for column " + c->name);
       return fixed("d:" + std::to_string(p) + "," + std::to_string(s), 16);
     }
     case T_Date: return t.scalar<int16_t>(0, 1) == 0 ? fixed("tdD", 4) : fixed("tdm", 8);
@@ -134,12 +171,15 @@ int field_to_column(bgpu_ctx* ctx, Table f, Column* c) {
       static const char* u = "smun";
       const int unit = t.scalar<int16_t>(0, 1), bits = t.scalar<int32_t>(1, 32);
       if (unit < 0 || unit > 3) break;
+      if (bits != (unit < 2 ? 32 : 64))  // Time32 is seconds / milliseconds, Time64 micro- / nanoseconds
+        return ctx->fail(BGPU_EINVAL, "IPC reader: Time unit does not match its bit width for column " + c->name);
       return fixed(std::string("tt") + u[unit], bits == 32 ? 4 : 8);
     }
     case T_Timestamp: {
       static const char* u = "smun";
       const int unit = t.scalar<int16_t>(0, 0);
       if (unit < 0 || unit > 3) break;
+      if (!valid_utf8(t.str(1))) return ctx->fail(BGPU_EINVAL, "IPC reader: time zone of column " + c->name + " is not UTF-8");
       return fixed(std::string("ts") + u[unit] + ":" + t.str(1), 8);
     }
     default: break;
@@ -339,7 +379,7 @@ static int next_message(bgpu_ipc_reader* r, const uint8_t** meta, uint32_t* meta
   return BGPU_OK;
 }
 
-extern "C" int bgpu_ipc_reader_open(bgpu_ctx* ctx, const uint8_t* bytes, uint64_t len, bgpu_ipc_reader** out) {
+static int reader_open_impl(bgpu_ctx* ctx, const uint8_t* bytes, uint64_t len, bgpu_ipc_reader** out) {
   if (!ctx || !out || (!bytes && len)) return BGPU_EINVAL;
   *out = nullptr;
   bgpu_ipc_reader tmp;
@@ -364,7 +404,9 @@ extern "C" int bgpu_ipc_reader_open(bgpu_ctx* ctx, const uint8_t* bytes, uint64_
     BGPU_TRY(field_to_column(ctx, f, &cols[i]));
   }
   if (!fb.ok) return ctx->fail(BGPU_EINVAL, "IPC reader: malformed schema message");
-  tmp.pos += (uint64_t)msg.scalar<int64_t>(3, 0);  // a schema message has no body; be exact anyway
+  const uint64_t schema_body = (uint64_t)msg.scalar<int64_t>(3, 0);  // a schema message has no body; be exact anyway
+  if (schema_body > tmp.len - tmp.pos) return ctx->fail(BGPU_EINVAL, "IPC reader: message body beyond the stream");
+  tmp.pos += schema_body;
   bgpu_ipc_reader* r = new bgpu_ipc_reader(tmp);
   ctx_retain(ctx);
   r->schema = new bgpu_batch(ctx);
@@ -391,7 +433,7 @@ struct PlacedBuffer {
   uint64_t arena_off = 0, bytes = 0;
 };
 
-extern "C" int bgpu_ipc_reader_next(bgpu_ipc_reader* r, bgpu_batch** out) {
+static int reader_next_impl(bgpu_ipc_reader* r, bgpu_batch** out) {
   if (!r || !out) return BGPU_EINVAL;
   *out = nullptr;
   bgpu_ctx* ctx = r->ctx;
@@ -408,7 +450,7 @@ extern "C" int bgpu_ipc_reader_next(bgpu_ipc_reader* r, bgpu_batch** out) {
   const Table msg{&fb, (size_t)fb.rd<uint32_t>(0)};
   const uint8_t header = msg.scalar<uint8_t>(1, 0);
   const uint64_t body_len = (uint64_t)msg.scalar<int64_t>(3, 0);
-  if (!fb.ok || r->pos + body_len > r->len) return ctx->fail(BGPU_EINVAL, "IPC reader: message body beyond the stream");
+  if (!fb.ok || body_len > r->len - r->pos) return ctx->fail(BGPU_EINVAL, "IPC reader: message body beyond the stream");
   const uint8_t* body = r->bytes + r->pos;
   r->pos += body_len;
   if (header == H_Schema) return ctx->fail(BGPU_EINVAL, "IPC reader: Not expecting a schema when messages are read");
@@ -432,6 +474,7 @@ extern "C" int bgpu_ipc_reader_next(bgpu_ipc_reader* r, bgpu_batch** out) {
   for (const Column& c : proto) want_buffers += (c.kind == K_UTF8 || c.kind == K_BINARY) ? 3 : 2;
   if (!fb.ok || rows < 0 || n_nodes != proto.size() || n_buffers != want_buffers)
     return ctx->fail(BGPU_EINVAL, "IPC reader: record batch does not match the schema");
+  if (rows > 0x7fffffffLL) return ctx->fail(BGPU_EUNSUPPORTED, "IPC reader: more than 2^31 rows in one batch");
 
   // 1. place every buffer in the arena (256-byte aligned); plan the LZ4 work for compressed ones
   std::vector<PlacedBuffer> placed(n_buffers);
@@ -452,6 +495,7 @@ extern "C" int bgpu_ipc_reader_next(bgpu_ipc_reader* r, bgpu_batch** out) {
       if (len < 8) return ctx->fail(BGPU_EINVAL, "IPC reader: compressed buffer without its length prefix");
       int64_t raw;
       memcpy(&raw, body + off, 8);
+      if (raw > (int64_t)1 << 40) return ctx->fail(BGPU_EINVAL, "IPC reader: implausible uncompressed length");
       if (raw == -1) {  // stored as is
         pb.bytes = len - 8;
         for (uint64_t done = 0; done < pb.bytes; done += 1u << 20) {  // 1 MB steps so that large buffers spread over warps
@@ -526,7 +570,7 @@ extern "C" int bgpu_ipc_reader_next(bgpu_ipc_reader* r, bgpu_batch** out) {
   for (size_t i = 0; i < proto.size(); i++) {
     Column& c = b->cols[i];
     const int64_t length = fb.rd<int64_t>(nodes + 16 * i), nulls = fb.rd<int64_t>(nodes + 16 * i + 8);
-    bool ok = length == rows;
+    bool ok = length == rows && nulls >= 0 && nulls <= rows;
     c.length = rows;
     c.null_count = nulls;
     c.owned = {arena};
@@ -558,7 +602,7 @@ extern "C" int bgpu_ipc_reader_next(bgpu_ipc_reader* r, bgpu_batch** out) {
 
 // Test hook: the LZ4 frame walker + block decoder run on the host with one lane. NOT a product path (nothing in the
 // library calls it); it lets the CPU test-suite pin the decoder logic against frames written by Arrow's own codec.
-extern "C" int bgpu_debug_lz4_frame_decode_host(bgpu_ctx* ctx, const uint8_t* frame, uint64_t len, uint8_t* out, uint64_t out_len) {
+static int lz4_frame_decode_host_impl(bgpu_ctx* ctx, const uint8_t* frame, uint64_t len, uint8_t* out, uint64_t out_len) {
   if (!ctx || !frame || (!out && out_len)) return BGPU_EINVAL;
   std::vector<Lz4Block> blocks;
   std::vector<Lz4Chain> chains;
@@ -576,4 +620,31 @@ extern "C" int bgpu_debug_lz4_frame_decode_host(bgpu_ctx* ctx, const uint8_t* fr
       if (got != k.dst_len) return ctx->fail(BGPU_EINVAL, "LZ4 block " + std::to_string(b) + " is malformed");
     }
   return BGPU_OK;
+}
+
+// Nothing is thrown across the C ABI: a malformed stream that drives an allocation out of memory is an error code.
+extern "C" int bgpu_ipc_reader_open(bgpu_ctx* ctx, const uint8_t* bytes, uint64_t len, bgpu_ipc_reader** out) {
+  try {
+    return reader_open_impl(ctx, bytes, len, out);
+  } catch (const std::exception& e) {
+    if (out) *out = nullptr;
+    return ctx ? ctx->fail(BGPU_EINVAL, std::string("IPC reader: ") + e.what()) : BGPU_EINVAL;
+  }
+}
+
+extern "C" int bgpu_ipc_reader_next(bgpu_ipc_reader* r, bgpu_batch** out) {
+  try {
+    return reader_next_impl(r, out);
+  } catch (const std::exception& e) {
+    if (out) *out = nullptr;
+    return r && r->ctx ? r->ctx->fail(BGPU_EINVAL, std::string("IPC reader: ") + e.what()) : BGPU_EINVAL;
+  }
+}
+
+extern "C" int bgpu_debug_lz4_frame_decode_host(bgpu_ctx* ctx, const uint8_t* frame, uint64_t len, uint8_t* out, uint64_t out_len) {
+  try {
+    return lz4_frame_decode_host_impl(ctx, frame, len, out, out_len);
+  } catch (const std::exception& e) {
+    return ctx ? ctx->fail(BGPU_EINVAL, std::string("LZ4 frame: ") + e.what()) : BGPU_EINVAL;
+  }
 }

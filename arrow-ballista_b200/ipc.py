@@ -21,7 +21,7 @@ class _HostContext:
 
     def check(self, rc):
         if rc != 0:
-            raise BgpuError(rc, lib().bgpu_last_error(self._h).decode())
+            raise BgpuError(rc, lib().bgpu_last_error(self._h).decode(errors="replace"))
 
     def __del__(self):
         if self._h:

@@ -18,14 +18,14 @@ class Context:
         else:
             rc = L.bgpu_ctx_create_on_stream(device, C.c_void_p(stream), C.byref(self._h))
         if rc != 0:
-            msg = L.bgpu_last_error(self._h).decode() if self._h else "allocation failed"
+            msg = L.bgpu_last_error(self._h).decode(errors="replace") if self._h else "allocation failed"
             L.bgpu_ctx_destroy(self._h)
             self._h = None
             raise BgpuError(rc, msg)
 
     def check(self, rc):
         if rc != 0:
-            raise BgpuError(rc, lib().bgpu_last_error(self._h).decode())
+            raise BgpuError(rc, lib().bgpu_last_error(self._h).decode(errors="replace"))
 
     def synchronize(self):
         self.check(lib().bgpu_ctx_synchronize(self._h))
