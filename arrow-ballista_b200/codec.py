@@ -18,6 +18,8 @@ google.protobuf's own runtime against the same schema.
 import struct
 from dataclasses import dataclass, field
 
+import pyarrow as pa
+
 from . import ipc
 from ._lib import BGPU_EINVAL, BgpuError
 from .expr import BinaryExpr, Column, Literal, X_COLUMN, X_LITERAL, T_FLOAT64
@@ -267,6 +269,17 @@ class GpuPhysicalCodec:
                 return self.inner.try_decode(buf, inputs)
             except Exception:
                 pass
+        try:
+            return self._decode_own(buf, inputs, ctx)
+        except BgpuError:
+            raise
+        except (AttributeError, TypeError, ValueError, LookupError, OverflowError, struct.error, pa.ArrowException) as e:
+            # a field with the wrong wire type, a string that is not UTF-8, a schema Arrow refuses ...
+            raise BgpuError(BGPU_EINVAL, f"GpuPhysicalCodec: malformed message ({type(e).__name__}: {e})") from e
+
+    def _decode_own(self, buf, inputs, ctx):
+        from .shuffle_writer import GpuShuffleWriterExec
+
         top = _fields(buf)
         if len(top) != 1 or top[0][1] != WT_LEN or top[0][0] not in (1, 2):
             raise BgpuError(BGPU_EINVAL, "GpuPhysicalCodec: not a GpuPhysicalPlanNode")

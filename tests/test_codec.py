@@ -155,3 +155,38 @@ def test_decoded_aggregate_runs_like_the_original(bb, ctx):
     a = pa.Table.from_batches([direct.execute([li])]).sort_by(keys)
     b = pa.Table.from_batches([decoded.execute([li])]).sort_by(keys)
     assert a.equals(b) and a.num_rows == 4
+
+
+def test_mutated_plan_bytes_decode_or_fail_with_the_codecs_own_error(bb):
+    """What arrives from the scheduler is bytes: flipped, truncated or spliced messages either decode or raise BgpuError
+    (a task failure the executor reports), never another exception type."""
+    import random
+
+    gi, aggs, filt, schema = q1(bb)
+
+    class Scan:
+        def schema(self):
+            return schema
+    node = bb.GpuAggregateExecNode(0, gi, [(bb.AggregateFunction.parse(f), a, n) for f, a, n in aggs], schema, filt, inputs=[Scan()])
+    writer = bb.GpuShuffleWriterExec.try_new("job", 1, [1, 2, 3], node, "", bb.Partitioning.Hash([0, 1], 16), None)
+    codec = bb.GpuPhysicalCodec()
+    goods = [codec.try_encode(node), codec.try_encode(writer)]
+    R = random.Random(5)
+    decoded = failed = 0
+    for _ in range(1500):
+        d = bytearray(R.choice(goods))
+        k = R.randrange(3)
+        if k == 0:
+            for _ in range(R.randrange(1, 6)):
+                d[R.randrange(len(d))] = R.randrange(256)
+        elif k == 1:
+            d = d[:R.randrange(len(d))]
+        else:
+            i = R.randrange(len(d))
+            d[i:i + R.randrange(1, 5)] = bytes(R.randrange(256) for _ in range(R.randrange(0, 6)))
+        try:
+            codec.try_decode(bytes(d), [Scan()])
+            decoded += 1
+        except bb.BgpuError:
+            failed += 1
+    assert decoded + failed == 1500 and failed > 1000
