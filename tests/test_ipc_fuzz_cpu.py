@@ -54,3 +54,15 @@ def test_schema_values_arrow_would_reject_are_rejected_here(bb):
             ipc.StreamReader(hc, bad).schema
         except bb.BgpuError:
             pass
+
+
+def test_fuzzed_aggregate_plans_are_errors_not_crashes():
+    """tools/fuzz_expr.py: random expression programs, column indices and modes against the aggregate planner's host side
+    (reached without a device through bgpu_agg_debug_compile); what passes validation is compiled by NVRTC."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "fuzz_expr.py"), "3", "250"], capture_output=True, text=True,
+                       timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    rows = [line.split(" ", 2) for line in r.stdout.splitlines()]
+    assert sum(int(n) for n, _, _ in rows) == 250
+    # 0 = compiled, 1 = BGPU_EINVAL, 2 = BGPU_EUNSUPPORTED; anything else (a CUDA / NVRTC failure) is a bug
+    assert {int(rc) for _, rc, _ in rows} <= {0, 1, 2}, r.stdout
