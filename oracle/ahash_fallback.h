@@ -8,7 +8,10 @@
  *
  * Structure pinned against compiled ahash-0.8.12 machine code (oracle/evidence/README.md):
  *   buffer = k1, pad = k0, extra_keys = [k2, k3], k_i = seed_i ^ PI2[i].
- * PARITY UNPINNED: no golden hash value from a reference build exists on this box (no Rust).
+ * and against known answers produced by EXECUTING compiled ahash-0.8.12 (tests/golden/ahash_0_8_12_kat.json:
+ * hash_one::<&[u8]> and from_keys, called by address in a Rust cdylib of this image; tests/test_oracle_ahash_kat.py).
+ * Still recalled, not executed: with_seeds' k_i = seed_i ^ PI2[i]. No golden value from a REFERENCE build exists on this
+ * box (no Rust), so DataFusion's glue around the hasher stays "parity unpinned".
  */
 #ifndef ORACLE_AHASH_FALLBACK_H
 #define ORACLE_AHASH_FALLBACK_H

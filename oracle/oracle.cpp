@@ -36,6 +36,30 @@ static inline uint64_t value_hash(const orc_col* c, int64_t r) {
   }
 }
 
+/* The hasher with explicit RandomState keys {k0,k1,k2,k3} (as stored, i.e. after with_seeds' xor): what the executed
+ * known-answer vectors of tests/golden/ahash_0_8_12_kat.json are checked against. */
+static ah_hasher ah_from_keys(const uint64_t* k) {
+  ah_hasher h;
+  h.buffer = k[1];
+  h.pad = k[0];
+  h.extra0 = k[2];
+  h.extra1 = k[3];
+  return h;
+}
+/* RandomState::hash_one::<&[u8]>: write_usize(len); write(bytes); finish() */
+extern "C" uint64_t orc_ahash_keyed_bytes(const uint64_t* keys, const uint8_t* d, uint64_t len) {
+  ah_hasher h = ah_from_keys(keys);
+  ah_update(&h, len);
+  ah_write(&h, d, len);
+  return ah_finish(&h);
+}
+/* write_u64(xs[0]); ...; write_u64(xs[n-1]); finish() */
+extern "C" uint64_t orc_ahash_keyed_u64s(const uint64_t* keys, const uint64_t* xs, int32_t n) {
+  ah_hasher h = ah_from_keys(keys);
+  for (int32_t i = 0; i < n; i++) ah_update(&h, xs[i]);
+  return ah_finish(&h);
+}
+
 extern "C" int orc_create_hashes(const orc_col* cols, int32_t n_cols, int64_t n_rows, uint64_t* hashes) {
   for (int32_t ci = 0; ci < n_cols; ci++) {
     const orc_col* c = &cols[ci];

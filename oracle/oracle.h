@@ -34,6 +34,10 @@ typedef struct orc_col {
   int64_t dict_len;
 } orc_col;
 
+/* the ahash fallback hasher with explicit RandomState keys {k0,k1,k2,k3}: hash_one(&[u8]) and a run of write_u64 */
+uint64_t orc_ahash_keyed_bytes(const uint64_t* keys, const uint8_t* d, uint64_t len);
+uint64_t orc_ahash_keyed_u64s(const uint64_t* keys, const uint64_t* xs, int32_t n);
+
 /* hash_utils.rs create_hashes: hashes[] must be zero-filled by the caller (as BatchPartitioner does). */
 int orc_create_hashes(const orc_col* cols, int32_t n_cols, int64_t n_rows, uint64_t* hashes);
 

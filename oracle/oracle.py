@@ -57,6 +57,8 @@ def lib():
         _lib.orc_groups_new.restype = C.c_void_p
         _lib.orc_groups_intern.restype = C.c_int64
         _lib.orc_avg_decimal_evaluate.restype = C.c_int64
+        _lib.orc_ahash_keyed_bytes.restype = C.c_uint64
+        _lib.orc_ahash_keyed_u64s.restype = C.c_uint64
     return _lib
 
 
@@ -123,6 +125,18 @@ def create_hashes(arrays):
     rc = lib().orc_create_hashes(_cols(arrays, keep), len(arrays), C.c_int64(n), out.ctypes.data_as(C.c_void_p))
     assert rc == 0
     return out
+
+
+def ahash_keyed_bytes(keys, data):
+    """RandomState{k0..k3}.hash_one(&[u8]) of the restated fallback hasher."""
+    ks = (C.c_uint64 * 4)(*keys)
+    return int(lib().orc_ahash_keyed_bytes(ks, bytes(data), C.c_uint64(len(data))))
+
+
+def ahash_keyed_u64s(keys, xs):
+    """from_random_state(RandomState{k0..k3}); write_u64(x) for x in xs; finish()."""
+    ks = (C.c_uint64 * 4)(*keys)
+    return int(lib().orc_ahash_keyed_u64s(ks, (C.c_uint64 * max(len(xs), 1))(*xs), len(xs)))
 
 
 def partition_indices(hashes, n_partitions):
