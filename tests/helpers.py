@@ -229,3 +229,37 @@ def q1_result_as_unscaled(table):
             r[k] = int(v.scaleb(-v.as_tuple().exponent)) if isinstance(v, decimal.Decimal) else v
         out.append(r)
     return sorted(out, key=lambda r: (r["l_returnflag"], r["l_linestatus"]))
+
+
+def record_batch_message_buffers(msg):
+    """The body buffers of ONE encapsulated RecordBatch message (bytes: continuation marker, metadata length, flatbuffer
+    metadata, body): returns (compressed?, [bytes of each buffer as it lies in the body]). A small flatbuffer walk over
+    Message{header_type@1, header@2, bodyLength@3} -> RecordBatch{length@0, nodes@1, buffers@2, compression@3}."""
+    import struct
+
+    msg = bytes(msg)
+    assert msg[:4] == b"\xff\xff\xff\xff"
+    meta_len = struct.unpack_from("<i", msg, 4)[0]
+    meta, body = msg[8:8 + meta_len], msg[8 + meta_len:]
+
+    def table(pos):
+        vt = pos - struct.unpack_from("<i", meta, pos)[0]
+        vsize = struct.unpack_from("<H", meta, vt)[0]
+
+        def field(i):
+            slot = 4 + 2 * i
+            if slot + 2 > vsize:
+                return 0
+            off = struct.unpack_from("<H", meta, vt + slot)[0]
+            return pos + off if off else 0
+        return field
+
+    def indirect(at):
+        return at + struct.unpack_from("<I", meta, at)[0]
+    message = table(indirect(0))
+    assert meta[message(1)] == 3, "not a RecordBatch message"
+    rb = table(indirect(message(2)))
+    vec = indirect(rb(2))
+    n = struct.unpack_from("<I", meta, vec)[0]
+    bufs = [struct.unpack_from("<qq", meta, vec + 4 + 16 * i) for i in range(n)]
+    return bool(rb(3)), [body[o:o + ln] for o, ln in bufs]
