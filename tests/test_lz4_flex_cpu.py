@@ -87,3 +87,33 @@ def test_reference_style_stream_buffers_decode_with_lz4_flex():
         assert len(got) == raw_len
         seen += 1
     assert seen >= 5
+
+
+def test_message_walk_on_arrow_written_messages():
+    """The same walk the GPU test does over the device's messages, here over Arrow C++'s: every compressed buffer of an
+    LZ4_FRAME RecordBatch message decodes with lz4_flex to the buffer of the uncompressed message."""
+    rng = np.random.default_rng(12)
+    batch = random_batch(rng, 20_000, with_dict=False)
+
+    def message(compression):
+        sink = io.BytesIO()
+        with pa.ipc.new_stream(sink, batch.schema, options=pa.ipc.IpcWriteOptions(compression=compression)) as w:
+            w.write_batch(batch)
+        reader = pa.ipc.MessageReader.open_stream(io.BytesIO(sink.getvalue()))
+        reader.read_next_message()
+        return reader.read_next_message().serialize().to_pybytes()
+    compressed, cbufs = record_batch_message_buffers(message("lz4"))
+    plain, rbufs = record_batch_message_buffers(message(None))
+    assert compressed and not plain and len(cbufs) == len(rbufs)
+    frames = 0
+    for cb, rb in zip(cbufs, rbufs):
+        if not cb:
+            continue
+        raw_len = int.from_bytes(cb[:8], "little", signed=True)
+        if raw_len == -1:
+            assert cb[8:8 + len(rb)] == rb[:len(cb) - 8]
+            continue
+        got = F.frame_decompress(cb[8:])
+        assert len(got) == raw_len and got == rb[:raw_len]
+        frames += 1
+    assert frames >= 5
