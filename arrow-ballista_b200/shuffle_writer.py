@@ -117,7 +117,11 @@ class GpuShuffleWriterExec:
         self.job_id, self.stage_id, self.partitions = str(job_id), int(stage_id), list(partitions)
         self.plan, self.work_dir = plan, str(work_dir)
         self.shuffle_output_partitioning = shuffle_output_partitioning
-        self._schema = input_schema if input_schema is not None else getattr(plan, "schema", None)
+        if input_schema is None:
+            input_schema = getattr(plan, "schema", None)  # a stream's attribute, or a plan node's schema() method
+            if callable(input_schema):
+                input_schema = input_schema()
+        self._schema = input_schema
         self._input_partitioning = input_partitioning or Partitioning.UnknownPartitioning(1)
         self.ctx = ctx
         self.metrics = ShuffleWriteMetrics()
@@ -235,7 +239,8 @@ class GpuShuffleWriterExec:
             if input_batch.num_rows == 0:
                 continue
             if schema_msg is None:
-                schema_msg = ipc.schema_message(self._schema if isinstance(input_batch, DeviceBatch) else input_batch.schema, self.ctx)
+                schema_msg = ipc.schema_message(self._schema if isinstance(input_batch, DeviceBatch) and self._schema is not None
+                                                else input_batch.schema, self.ctx)
             dbatch = input_batch if isinstance(input_batch, DeviceBatch) else DeviceBatch.upload(self.ctx, input_batch)
             out, offs = partitioner.partition_device(dbatch)
             t0 = time.perf_counter()
