@@ -263,3 +263,17 @@ def record_batch_message_buffers(msg):
     n = struct.unpack_from("<I", meta, vec)[0]
     bufs = [struct.unpack_from("<qq", meta, vec + 4 + 16 * i) for i in range(n)]
     return bool(rb(3)), [body[o:o + ln] for o, ln in bufs]
+
+
+def alltypes_plain():
+    """The reference's alltypes_plain test table as the aggregate input (tests/golden/alltypes_plain_aggregates.json) and
+    the answers the reference's own test asserts. Columns: g (constant Int64 key), id (Int64: the planner's coercion of the
+    Int32 column), bool_col, bigint_col, double_col, string_col."""
+    d = json.load(open(os.path.join(GOLDEN, "alltypes_plain_aggregates.json")))
+    c = d["columns"]
+    n = len(c["id"])
+    batch = pa.RecordBatch.from_arrays(
+        [pa.array([0] * n, type=pa.int64()), pa.array(c["id"], type=pa.int64()), pa.array(c["bool_col"]),
+         pa.array(c["bigint_col"], type=pa.int64()), pa.array(c["double_col"], type=pa.float64()), pa.array(c["string_col"])],
+        names=["g", "id", "bool_col", "bigint_col", "double_col", "string_col"])
+    return batch, d["reference_asserts"]
