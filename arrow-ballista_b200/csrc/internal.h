@@ -8,7 +8,26 @@
 #include <string>
 #include <vector>
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 #include "../../include/bgpu.h"
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize of a statically compiled kernel, only ever raised: the attribute belongs to
+// the kernel (per device), not to a launch, and tasks on different threads launch the same kernel with different
+// amounts - lowering it for one between another's set and launch would fail that launch. It is a cap, not a reservation.
+inline cudaError_t raise_max_dynamic_smem(const void* kernel, int device, size_t smem) {
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, size_t> current;
+  std::lock_guard<std::mutex> lk(mu);
+  auto key = std::make_pair(kernel, device);
+  auto it = current.find(key);
+  if (it != current.end() && it->second >= smem) return cudaSuccess;
+  const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e == cudaSuccess) current[key] = smem;
+  return e;
+}
 
 struct bgpu_ctx {
   int device = 0;

@@ -548,7 +548,7 @@ static int reader_next_impl(bgpu_ipc_reader* r, bgpu_batch** out) {
     if (!small.empty()) {
       BGPU_TRY(dev_alloc(ctx, small.size() * 4, &d_small));
       BGPU_CUDA(ctx, cudaMemcpyAsync(d_small->p, small.data(), small.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
-      cudaFuncSetAttribute(lz4_decode_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLz4SmemBlock);  // per device
+      BGPU_CUDA(ctx, raise_max_dynamic_smem((const void*)lz4_decode_smem_kernel, ctx->device, kLz4SmemBlock));
       lz4_decode_smem_kernel<<<(unsigned)small.size(), 32, kLz4SmemBlock, ctx->stream>>>(
           (const Lz4Block*)d_blocks->p, (const uint32_t*)d_small->p, (const uint8_t*)d_body->p, base, (unsigned int*)d_err->p);
       ctx->launches++;

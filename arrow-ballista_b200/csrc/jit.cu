@@ -161,10 +161,19 @@ int jit_launch(bgpu_ctx* ctx, CUfunction fn, int grid, int block, size_t smem, c
   return BGPU_OK;
 }
 
+// The limit is only ever raised: a CUfunction is shared by every task (thread) whose plan has the same shape, and their
+// launches want different amounts (capacity by demand) - lowering it for one task between another task's set and launch
+// would fail that launch. The attribute is a cap, not a reservation, so a larger value costs nothing.
 int jit_set_max_smem(bgpu_ctx* ctx, CUfunction fn, size_t smem) {
+  static std::mutex mu;
+  static std::map<CUfunction, size_t> current;
   const Api& a = api();
+  std::lock_guard<std::mutex> lk(mu);
+  auto it = current.find(fn);
+  if (it != current.end() && it->second >= smem) return BGPU_OK;
   const CUresult r = a.FuncSetAttribute(fn, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)smem);
   if (r != CUDA_SUCCESS) return ctx->fail(BGPU_ECUDA, "cuFuncSetAttribute(max dynamic smem): " + cu_err(a, r));
+  current[fn] = smem;
   return BGPU_OK;
 }
 

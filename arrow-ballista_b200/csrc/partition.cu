@@ -513,7 +513,7 @@ constexpr ScatterGeom kGeomLarge{1024, 4};   // 4096-row tiles, one CTA per SM: 
 template <int THREADS, int ITEMS>
 static int scatter_run(bgpu_ctx* ctx, bool launch, int64_t g, size_t smem, const KeySet& ks, const Modulo& mod,
                        const ScatterArgs& args, int64_t n_rows, int64_t chunk_rows, const uint64_t* base, int* occ) {
-  BGPU_CUDA(ctx, cudaFuncSetAttribute(scatter_kernel<THREADS, ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  BGPU_CUDA(ctx, raise_max_dynamic_smem((const void*)scatter_kernel<THREADS, ITEMS>, ctx->device, smem));
   if (!launch) {
     BGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, scatter_kernel<THREADS, ITEMS>, THREADS, smem));
     return BGPU_OK;

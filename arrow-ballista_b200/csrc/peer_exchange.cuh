@@ -444,7 +444,7 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
     BGPU_CUDA(ctx, cudaMemcpyAsync(d_delta->p, delta.data(), (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
     BGPU_CUDA(ctx, cudaMemcpyAsync(d_ptrs->p, ptrs.data(), ptrs.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
     add_delta_kernel<<<(unsigned)((n * g + 255) / 256), 256, 0, ctx->stream>>>((uint64_t*)base->p, (const int64_t*)d_delta->p, n, (uint32_t)g);
-    BGPU_CUDA(ctx, cudaFuncSetAttribute(scatter_peer_kernel<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    BGPU_CUDA(ctx, raise_max_dynamic_smem((const void*)scatter_peer_kernel<256, 4>, ctx->device, smem));
     // 4. the fused scatter: runs go straight into the owners' windows
     scatter_peer_kernel<256, 4><<<(int)g, 256, smem, ctx->stream>>>(ks, mod, args, n_rows, chunk_rows, (const uint64_t*)base->p,
                                                                    (void* const*)d_ptrs->p, world);
