@@ -78,7 +78,8 @@ for it in range(int(sys.argv[2])):
                 tree(R.randrange(0, 4), nodes)
             offs.append(len(nodes))
         filt = []
-        if R.randrange(2):
+        mode = R.choice([0, 0, 2, 3])
+        if mode != 2 and R.randrange(2):   # a filter applies to raw input rows only
             predicate(filt)
         groups = R.sample([0, 4, 5, 6, 7, 8], R.randrange(1, 4))
     else:
@@ -91,10 +92,10 @@ for it in range(int(sys.argv[2])):
         groups = [R.choice([0, 4, 5, 6, 7, 8, 2, 1, -1, 9]) for _ in range(R.choice([0, 1, 1, 2, 3, 9]))]
     s = ArrowSchema()
     schema._export_to_c(C.addressof(s))
-    rc = L.bgpu_agg_debug_compile(h, R.choice([0, 0, 3] if WELL_FORMED else [0, 0, 2, 1, 3, 5]), C.byref(s), (C.c_int32 * max(len(groups), 1))(*groups), len(groups),
+    rc = L.bgpu_agg_debug_compile(h, mode if WELL_FORMED else R.choice([0, 0, 2, 1, 3, 5]), C.byref(s), (C.c_int32 * max(len(groups), 1))(*groups), len(groups),
                                   (C.c_int32 * max(n_agg, 1))(*fns), (ExprNode * max(len(nodes), 1))(*nodes),
                                   (C.c_int32 * len(offs))(*offs), n_agg, (ExprNode * max(len(filt), 1))(*filt), len(filt),
-                                  R.randrange(8), 256, 4, 2, None)
+                                  R.randrange(16), R.choice([256, 256, 640, 1024]), R.choice([1, 4, 4, 8]), R.choice([1, 2, 2]), None)
     bb.runtime._release(s)
     msg = L.bgpu_last_error(h).decode(errors="replace") if rc else "compiled"
     out[(rc, msg[:70])] += 1
