@@ -202,15 +202,17 @@ extern "C" int bgpu_agg_create_expr(bgpu_ctx* ctx, int32_t mode, const struct Ar
                                     const int32_t* group_cols, int32_t n_group, const int32_t* agg_fns,
                                     const bgpu_expr_node* nodes, const int32_t* agg_expr_offsets,
                                     const char* const* agg_names, int32_t n_agg, const bgpu_expr_node* filter,
-                                    int32_t n_filter, bgpu_agg** out) {
+                                    int32_t n_filter, bgpu_agg** out) try {
   if (!group_cols || (n_agg > 0 && (!agg_fns || !agg_expr_offsets))) return BGPU_EINVAL;
   return agg_create_impl(ctx, mode, input_schema, group_cols, n_group, agg_fns, nodes, agg_expr_offsets, agg_names, n_agg,
                          filter, n_filter, false, out);
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 extern "C" int bgpu_agg_create(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema* input_schema,
                                const int32_t* group_cols, int32_t n_group, const int32_t* agg_fns,
-                               const int32_t* agg_cols, const char* const* agg_names, int32_t n_agg, bgpu_agg** out) {
+                               const int32_t* agg_cols, const char* const* agg_names, int32_t n_agg, bgpu_agg** out) try {
   if (!group_cols || n_agg < 0 || n_agg > 16 || (n_agg > 0 && (!agg_fns || !agg_cols))) return BGPU_EINVAL;
   std::vector<bgpu_expr_node> nodes;
   std::vector<int32_t> offs{0};
@@ -225,6 +227,8 @@ extern "C" int bgpu_agg_create(bgpu_ctx* ctx, int32_t mode, const struct ArrowSc
   }
   return agg_create_impl(ctx, mode, input_schema, group_cols, n_group, agg_fns, nodes.data(), offs.data(), agg_names, n_agg,
                          nullptr, 0, false, out);
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 // Introspection (no device needed): generate the kernels of this plan for a synthetic batch shape and compile them
@@ -234,7 +238,7 @@ extern "C" int bgpu_agg_debug_compile(bgpu_ctx* ctx, int32_t mode, const struct 
                                       const int32_t* group_cols, int32_t n_group, const int32_t* agg_fns,
                                       const bgpu_expr_node* nodes, const int32_t* agg_expr_offsets, int32_t n_agg,
                                       const bgpu_expr_node* filter, int32_t n_filter, int32_t flags, int32_t threads,
-                                      int32_t rows_per_thread, int32_t min_ctas, const char* out_prefix) {
+                                      int32_t rows_per_thread, int32_t min_ctas, const char* out_prefix) try {
   bgpu_agg* gp = nullptr;
   BGPU_TRY(agg_create_impl(ctx, mode, input_schema, group_cols, n_group, agg_fns, nodes, agg_expr_offsets, nullptr, n_agg,
                            filter, n_filter, true, &gp));
@@ -299,6 +303,8 @@ extern "C" int bgpu_agg_debug_compile(bgpu_ctx* ctx, int32_t mode, const struct 
     if (f) { fwrite(cubin.data(), 1, cubin.size(), f); fclose(f); }
   }
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 extern "C" void bgpu_agg_destroy(bgpu_agg* g) {

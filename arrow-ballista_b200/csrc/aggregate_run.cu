@@ -694,7 +694,7 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
   return BGPU_OK;
 }
 
-extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) {
+extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) try {
   if (!g || !batch) return BGPU_EINVAL;
   bgpu_ctx* ctx = g->ctx;
   if (g->emitted) return ctx->fail(BGPU_EINVAL, "aggregate already emitted");
@@ -723,6 +723,8 @@ extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) {
   trace.mark(done ? "fused" : "fused (void)");
   if (!done) BGPU_TRY(run_two_pass(g, &b, n_rows));
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(g ? g->ctx : nullptr, e);  // nothing is thrown across the C ABI
 }
 
 extern "C" const char* bgpu_agg_last_path(const bgpu_agg* g) { return g ? g->last_path.c_str() : ""; }
@@ -744,7 +746,7 @@ static int emit_validity(bgpu_agg* g, int phys_idx, uint32_t n, Column* col) {
   return BGPU_OK;
 }
 
-extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
+extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) try {
   if (!g || !out_batch) return BGPU_EINVAL;
   *out_batch = nullptr;
   bgpu_ctx* ctx = g->ctx;
@@ -905,4 +907,6 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) {
   g->emitted = true;
   *out_batch = out.release();
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(g ? g->ctx : nullptr, e);  // nothing is thrown across the C ABI
 }

@@ -154,12 +154,16 @@ static int import_batch(bgpu_ctx* ctx, const struct ArrowArray* a, const struct 
 }
 
 extern "C" int bgpu_batch_upload(bgpu_ctx* ctx, const struct ArrowArray* a, const struct ArrowSchema* s,
-                                 bgpu_batch** out) {
+                                 bgpu_batch** out) try {
   return import_batch(ctx, a, s, false, out);
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 extern "C" int bgpu_batch_wrap_device(bgpu_ctx* ctx, const struct ArrowArray* a, const struct ArrowSchema* s,
-                                      bgpu_batch** out) {
+                                      bgpu_batch** out) try {
   return import_batch(ctx, a, s, true, out);
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 extern "C" int64_t bgpu_batch_num_rows(const bgpu_batch* b) { return b ? b->n_rows : -1; }
 extern "C" int32_t bgpu_batch_num_columns(const bgpu_batch* b) { return b ? (int32_t)b->cols.size() : -1; }
@@ -327,7 +331,7 @@ void device_column(const Column& c, ArrowArray* a) {
 void export_batch_schema(const bgpu_batch* b, struct ArrowSchema* out) { batch_schema(b, out); }
 
 extern "C" int bgpu_batch_download(bgpu_ctx* ctx, const bgpu_batch* b, int64_t row_offset, int64_t num_rows,
-                                   struct ArrowArray* out, struct ArrowSchema* out_schema) {
+                                   struct ArrowArray* out, struct ArrowSchema* out_schema) try {
   if (!ctx || !b || !out || !out_schema) return BGPU_EINVAL;
   if (row_offset < 0 || num_rows < 0 || row_offset + num_rows > b->n_rows)
     return ctx->fail(BGPU_EINVAL, "row range out of bounds");
@@ -355,10 +359,12 @@ extern "C" int bgpu_batch_download(bgpu_ctx* ctx, const bgpu_batch* b, int64_t r
   }
   batch_schema(b, out_schema);
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 extern "C" int bgpu_batch_export_device(bgpu_ctx* ctx, const bgpu_batch* b, struct ArrowArray* out,
-                                        struct ArrowSchema* out_schema) {
+                                        struct ArrowSchema* out_schema) try {
   if (!ctx || !b || !out || !out_schema) return BGPU_EINVAL;
   ArrayPriv* p = fill_array(out, b->n_rows, 0, 0);
   p->buffers.push_back(nullptr);
@@ -370,4 +376,6 @@ extern "C" int bgpu_batch_export_device(bgpu_ctx* ctx, const bgpu_batch* b, stru
   finish_array(out);
   batch_schema(b, out_schema);
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }

@@ -89,7 +89,7 @@ __global__ void utf8_span_kernel(const SpanArg* __restrict__ a, int32_t* __restr
 
 using namespace bgpu;
 
-extern "C" int bgpu_batch_concat(bgpu_ctx* ctx, const bgpu_batch* const* batches, int32_t n, bgpu_batch** out) {
+extern "C" int bgpu_batch_concat(bgpu_ctx* ctx, const bgpu_batch* const* batches, int32_t n, bgpu_batch** out) try {
   if (!ctx || !out || n <= 0 || !batches) return BGPU_EINVAL;
   *out = nullptr;
   if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
@@ -245,4 +245,6 @@ extern "C" int bgpu_batch_concat(bgpu_ctx* ctx, const bgpu_batch* const* batches
   }
   *out = res;
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }

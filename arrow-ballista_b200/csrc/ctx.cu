@@ -92,3 +92,9 @@ int dev_alloc(bgpu_ctx* ctx, size_t bytes, DevAllocPtr* out) {
   *out = a;
   return BGPU_OK;
 }
+
+int bgpu::abi_guard(bgpu_ctx* ctx, const std::exception& e) {
+  const bool oom = dynamic_cast<const std::bad_alloc*>(&e) != nullptr;
+  if (!ctx) return BGPU_EINVAL;
+  return ctx->fail(oom ? BGPU_ECUDA : BGPU_EINVAL, std::string(oom ? "out of host memory: " : "internal error: ") + e.what());
+}

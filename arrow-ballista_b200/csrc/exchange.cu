@@ -62,7 +62,7 @@ extern "C" int bgpu_nccl_unique_id(bgpu_ctx* ctx, void* out_id128) {
   return BGPU_OK;
 }
 
-extern "C" int bgpu_nccl_comm_create(bgpu_ctx* ctx, const void* id128, int32_t rank, int32_t world, void** out_comm) {
+extern "C" int bgpu_nccl_comm_create(bgpu_ctx* ctx, const void* id128, int32_t rank, int32_t world, void** out_comm) try {
   if (!ctx || !id128 || !out_comm) return BGPU_EINVAL;
   *out_comm = nullptr;
   if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device");
@@ -73,6 +73,8 @@ extern "C" int bgpu_nccl_comm_create(bgpu_ctx* ctx, const void* id128, int32_t r
   memcpy(&id, id128, sizeof id);
   BGPU_NCCL(ctx, n.CommInitRank(out_comm, world, id, rank));
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 extern "C" void bgpu_nccl_comm_destroy(void* comm) {
@@ -99,7 +101,7 @@ extern "C" uint64_t bgpu_exchange_plan(const uint64_t* all_offsets, int32_t rank
 }
 
 extern "C" int bgpu_all_to_all(bgpu_ctx* ctx, void* comm, int32_t rank, int32_t world, const bgpu_batch* in,
-                               const uint64_t* offsets, uint32_t n_partitions, bgpu_batch** out) {
+                               const uint64_t* offsets, uint32_t n_partitions, bgpu_batch** out) try {
   if (!ctx || !out) return BGPU_EINVAL;
   *out = nullptr;
   if (!comm || !in || !offsets || world < 1 || rank < 0 || rank >= world || n_partitions == 0)
@@ -268,4 +270,6 @@ extern "C" int bgpu_all_to_all(bgpu_ctx* ctx, void* comm, int32_t rank, int32_t 
   BGPU_CUDA(ctx, cudaStreamSynchronize(st));
   *out = ob.release();
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }

@@ -14,6 +14,16 @@
 
 #include "../../include/bgpu.h"
 
+#include <exception>
+#include <new>
+
+struct bgpu_ctx;
+namespace bgpu {
+// What a C ABI entry point returns when its body threw (function-try-blocks around every compute entry point): an
+// allocation that failed or a container that refused a size is an error code with a message, never an abort.
+int abi_guard(bgpu_ctx* ctx, const std::exception& e);
+}  // namespace bgpu
+
 // cudaFuncAttributeMaxDynamicSharedMemorySize of a statically compiled kernel, only ever raised: the attribute belongs to
 // the kernel (per device), not to a launch, and tasks on different threads launch the same kernel with different
 // amounts - lowering it for one between another's set and launch would fail that launch. It is a cap, not a reservation.

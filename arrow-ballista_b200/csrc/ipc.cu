@@ -543,17 +543,19 @@ static int to_malloc(bgpu_ctx* ctx, const std::vector<uint8_t>& msg, uint8_t** o
   return BGPU_OK;
 }
 
-extern "C" int bgpu_ipc_schema_message(bgpu_ctx* ctx, const struct ArrowSchema* schema, uint8_t** out_bytes, uint64_t* out_len) {
+extern "C" int bgpu_ipc_schema_message(bgpu_ctx* ctx, const struct ArrowSchema* schema, uint8_t** out_bytes, uint64_t* out_len) try {
   if (!ctx || !schema || !out_bytes || !out_len) return BGPU_EINVAL;
   std::vector<Column> cols((size_t)schema->n_children);
   for (int64_t i = 0; i < schema->n_children; i++) BGPU_TRY(parse_field(ctx, schema->children[i], &cols[(size_t)i]));
   std::vector<uint8_t> msg;
   BGPU_TRY(schema_message(ctx, cols, &msg));
   return to_malloc(ctx, msg, out_bytes, out_len);
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 extern "C" int bgpu_ipc_record_batch_metadata(bgpu_ctx* ctx, int64_t rows, const int64_t* nodes, int32_t n_nodes, const int64_t* buffers,
-                                              int32_t n_buffers, int64_t body_len, int32_t compression, uint8_t** out_bytes, uint64_t* out_len) {
+                                              int32_t n_buffers, int64_t body_len, int32_t compression, uint8_t** out_bytes, uint64_t* out_len) try {
   if (!ctx || !out_bytes || !out_len || n_nodes < 0 || n_buffers < 0 || (n_nodes && !nodes) || (n_buffers && !buffers)) return BGPU_EINVAL;
   if (compression < -1 || compression > 0) return ctx->fail(BGPU_EUNSUPPORTED, "compression must be -1 (none) or 0 (LZ4_FRAME)");
   std::vector<std::pair<int64_t, int64_t>> nv, bv;
@@ -562,10 +564,12 @@ extern "C" int bgpu_ipc_record_batch_metadata(bgpu_ctx* ctx, int64_t rows, const
   std::vector<uint8_t> msg;
   record_batch_message(rows, nv, bv, body_len, &msg, compression);
   return to_malloc(ctx, msg, out_bytes, out_len);
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch, const uint64_t* offsets, uint32_t n,
-                                          int32_t compression, uint8_t** out_bytes, uint64_t* out_msg_off) {
+                                          int32_t compression, uint8_t** out_bytes, uint64_t* out_msg_off) try {
   if (!ctx || !batch || !offsets || !out_bytes || !out_msg_off || n == 0) return BGPU_EINVAL;
   if (compression < -1 || compression > 0) return ctx->fail(BGPU_EUNSUPPORTED, "compression must be -1 (none) or 0 (LZ4_FRAME)");
   *out_bytes = nullptr;
@@ -821,6 +825,8 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
   }
   *out_bytes = host;
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 extern "C" void bgpu_ipc_free(uint8_t* bytes, int pinned) {

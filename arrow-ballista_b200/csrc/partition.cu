@@ -489,7 +489,7 @@ static int make_keyset(bgpu_ctx* ctx, const bgpu_batch* b, const int32_t* key_co
 using namespace bgpu;
 
 extern "C" int bgpu_create_hashes(bgpu_ctx* ctx, const bgpu_batch* batch, const int32_t* key_cols, int32_t n_keys,
-                                  uint64_t* out_hashes_device) {
+                                  uint64_t* out_hashes_device) try {
   if (!ctx || !batch || !key_cols || !out_hashes_device) return BGPU_EINVAL;
   if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -502,6 +502,8 @@ extern "C" int bgpu_create_hashes(bgpu_ctx* ctx, const bgpu_batch* batch, const 
   ctx->launches++;
   BGPU_CUDA(ctx, cudaGetLastError());
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 // scatter geometries (threads per CTA, rows per thread): tile = threads x items rows
@@ -532,7 +534,7 @@ static int scatter_dispatch(bgpu_ctx* ctx, ScatterGeom geom, bool launch, int64_
 
 extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const int32_t* key_cols, int32_t n_keys,
                                    uint32_t n_partitions, bgpu_batch** out_partitioned, uint64_t* out_offsets,
-                                   uint64_t* out_hashes_device) {
+                                   uint64_t* out_hashes_device) try {
   if (!ctx || !in || !key_cols || !out_partitioned || !out_offsets) return BGPU_EINVAL;
   *out_partitioned = nullptr;
   if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
@@ -718,12 +720,14 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
   for (uint32_t p = 0; p <= n; p++) out_offsets[p] = h_offs[p];
   *out_partitioned = out.release();
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 extern "C" int bgpu_hash_partition_host(bgpu_ctx* ctx, const struct ArrowArray* batch, const struct ArrowSchema* schema,
                                         const int32_t* key_cols, int32_t n_keys, uint32_t n_partitions,
                                         struct ArrowArray* out_partitioned, struct ArrowSchema* out_schema,
-                                        uint64_t* out_offsets) {
+                                        uint64_t* out_offsets) try {
   if (!ctx) return BGPU_EINVAL;
   bgpu_batch *in = nullptr, *out = nullptr;
   int rc = bgpu_batch_upload(ctx, batch, schema, &in);
@@ -732,6 +736,8 @@ extern "C" int bgpu_hash_partition_host(bgpu_ctx* ctx, const struct ArrowArray* 
   bgpu_batch_destroy(out);
   bgpu_batch_destroy(in);
   return rc;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 #include "peer_exchange.cuh"

@@ -277,7 +277,7 @@ static int peer_open(bgpu_peer_exchange* x, uint64_t bytes) {
 }  // namespace bgpu
 
 extern "C" int bgpu_peer_exchange_create(bgpu_ctx* ctx, void* nccl_comm, int32_t rank, int32_t world, uint64_t window_bytes,
-                                         bgpu_peer_exchange** out) {
+                                         bgpu_peer_exchange** out) try {
   using namespace bgpu;
   if (!ctx || !out || world < 1 || world > kMaxPeers || rank < 0 || rank >= world || (world > 1 && !nccl_comm)) return BGPU_EINVAL;
   *out = nullptr;
@@ -296,6 +296,8 @@ extern "C" int bgpu_peer_exchange_create(bgpu_ctx* ctx, void* nccl_comm, int32_t
   }
   *out = x;
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
 extern "C" void bgpu_peer_exchange_destroy(bgpu_peer_exchange* x) {
@@ -315,7 +317,7 @@ extern "C" uint64_t bgpu_peer_exchange_window_bytes(const bgpu_peer_exchange* x)
 
 extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* in, const int32_t* key_cols, int32_t n_keys,
                                        uint32_t n_partitions, bgpu_batch** out_received, uint64_t* out_recv_off,
-                                       uint64_t* out_sent_bytes) {
+                                       uint64_t* out_sent_bytes) try {
   using namespace bgpu;
   if (!x || !in || !key_cols || !out_received) return BGPU_EINVAL;
   bgpu_ctx* ctx = x->ctx;
@@ -477,4 +479,6 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
   x->bytes_sent += sent_rows * (uint64_t)row_bytes;
   *out_received = out.release();
   return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(x ? x->ctx : nullptr, e);  // nothing is thrown across the C ABI
 }
