@@ -185,6 +185,16 @@ class GpuAggregateExecNode:
     def children(self):
         return list(self.inputs)
 
+    def with_new_children(self, children):
+        import dataclasses
+
+        return dataclasses.replace(self, inputs=list(children))
+
+    def output_partitioning(self):
+        # AggregateExec reports its input's partitioning (Partial) - hash-partitioned outputs are the exchange's business
+        child = getattr(self.inputs[0], "output_partitioning", None) if self.inputs else None
+        return child() if callable(child) else Partitioning.UnknownPartitioning(1)
+
     def execute(self, partition, ctx=None):
         """AggregateExec::execute(partition): the input's partition through one aggregate; yields its output batch."""
         from .runtime import Context

@@ -17,7 +17,7 @@ import random
 from dataclasses import dataclass, field
 
 from . import ipc
-from ._lib import BgpuError
+from ._lib import BGPU_EINVAL, BgpuError
 from .partitioner import Partitioning
 from .runtime import DeviceBatch
 
@@ -82,6 +82,13 @@ class GpuShuffleReaderExec:
     def children(self):
         return []
 
+    def output_ordering(self):
+        return None
+
+    def with_new_children(self, _children):
+        # shuffle_reader.rs:217-224
+        raise BgpuError(BGPU_EINVAL, "Ballista ShuffleReaderExec does not support with_new_children()")
+
     def __str__(self):
         return f"GpuShuffleReaderExec: partitions={len(self.partition)}"
 
@@ -125,6 +132,13 @@ class CoalesceBatchesExec:
     def children(self):
         return [self.input] if callable(getattr(self.input, "execute", None)) else []
 
+    def with_new_children(self, children):
+        return CoalesceBatchesExec(children[0], self.ctx, self.target_batch_size)
+
+    def output_partitioning(self):
+        child = getattr(self.input, "output_partitioning", None)
+        return child() if callable(child) else Partitioning.UnknownPartitioning(1)
+
     def schema(self):
         return self.input.schema() if callable(getattr(self.input, "schema", None)) else None
 
@@ -161,6 +175,13 @@ class CoalesceTasksExec:
 
     def children(self):
         return [self.input] if self.input is not None else []
+
+    def with_new_children(self, children):
+        # coalesce_tasks.rs:118-128: same partitions, new input
+        return CoalesceTasksExec(children[0], self.partitions, self._schema)
+
+    def output_ordering(self):
+        return None  # the unordered fan-in; streaming_merge over ordered children is not built
 
     def schema(self):
         return self._schema

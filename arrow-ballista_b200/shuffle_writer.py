@@ -135,7 +135,12 @@ class GpuShuffleWriterExec:
         return self._schema
 
     def output_partitioning(self):
-        return self._input_partitioning
+        # the INPUT's partitioning (shuffle_writer.rs:483-493): the child's own answer when the child is a plan node
+        child = getattr(self.plan, "output_partitioning", None)
+        return child() if callable(child) else self._input_partitioning
+
+    def output_ordering(self):
+        return None  # shuffle_writer.rs:495-497
 
     def shuffle_output_partitioning_(self):
         return self.shuffle_output_partitioning
@@ -143,8 +148,29 @@ class GpuShuffleWriterExec:
     def children(self):
         return [self.plan]
 
+    def _copy(self, **changes):
+        kw = dict(job_id=self.job_id, stage_id=self.stage_id, partitions=list(self.partitions), plan=self.plan,
+                  work_dir=self.work_dir, shuffle_output_partitioning=self.shuffle_output_partitioning, ctx=self.ctx,
+                  input_partitioning=self._input_partitioning, ipc=self.ipc, compression=self.compression)
+        if "plan" not in changes:
+            kw["input_schema"] = self._schema
+        kw.update(changes)
+        return GpuShuffleWriterExec.try_new(**kw)
+
+    def with_new_children(self, children):
+        """shuffle_writer.rs:503-516: the same writer over children[0]."""
+        return self._copy(plan=children[0])
+
+    def with_partitions(self, partitions):
+        """shuffle_writer.rs:205-223 (used by the task-group optimizer): the same writer for another set of stage partitions."""
+        return self._copy(partitions=[int(p) for p in partitions])
+
     def __str__(self):
-        return f"GpuShuffleWriterExec: {self.shuffle_output_partitioning and self.shuffle_output_partitioning.kind}"
+        # DisplayAs (shuffle_writer.rs:459-476): "ShuffleWriterExec: <partitioning>" or just the name
+        part = self.shuffle_output_partitioning
+        if part is None:
+            return "GpuShuffleWriterExec"
+        return f"GpuShuffleWriterExec: {part.kind.capitalize()}({part.exprs}, {part.partition_count()})"
 
     def _stream(self):
         # the reference executes partition 0 of its child (shuffle_writer.rs:253: below a task group's
