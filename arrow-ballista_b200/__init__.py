@@ -18,3 +18,4 @@ from .shuffle_reader import (CoalesceBatchesExec, CoalesceTasksExec, ExecutorMet
 from .codec import GpuAggregateExecNode, GpuPhysicalCodec  # noqa: F401
 from .execution_engine import (DefaultExecutionEngine, DefaultQueryStageExec, GpuExecutionEngine, GpuQueryStageExec,  # noqa: F401
                                QueryStageExecutor, match_aggregate_stage)
+from .task_group import OptimizeTaskGroup  # noqa: F401
