@@ -14,7 +14,7 @@ from .exchange import Exchange, exchange_plan, owner_of  # noqa: F401
 from .shuffle_writer import GpuShuffleWriterExec, ShuffleWritePartition, result_schema  # noqa: F401
 from . import ipc  # noqa: F401
 from .shuffle_reader import (CoalesceBatchesExec, CoalesceTasksExec, ExecutorMetadata, FetchFailed, GpuShuffleReaderExec,  # noqa: F401
-                             PartitionLocation, PartitionStats)
+                             PartitionLocation, PartitionStats, stats_for_partitions)
 from .codec import GpuAggregateExecNode, GpuPhysicalCodec  # noqa: F401
 from .execution_engine import (DefaultExecutionEngine, DefaultQueryStageExec, GpuExecutionEngine, GpuQueryStageExec,  # noqa: F401
                                QueryStageExecutor, match_aggregate_stage)

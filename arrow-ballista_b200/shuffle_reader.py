@@ -65,6 +65,16 @@ class FetchFailed(Exception):
         self.executor_id, self.map_stage_id, self.map_partitions, self.message = executor_id, map_stage_id, map_partitions, message
 
 
+def stats_for_partitions(num_fields, partition_stats):
+    """shuffle_reader.rs:315-337: exact row and byte totals of the partitions to read; one unknown statistic makes the
+    total unknown (None = Precision::Absent); no column statistics."""
+    num_rows, total_byte_size = 0, 0
+    for part in partition_stats:
+        num_rows = None if num_rows is None or part.num_rows is None else num_rows + part.num_rows
+        total_byte_size = None if total_byte_size is None or part.num_bytes is None else total_byte_size + part.num_bytes
+    return {"num_rows": num_rows, "total_byte_size": total_byte_size, "column_statistics": [None] * num_fields}
+
+
 class GpuShuffleReaderExec:
     """`partition[p]` = the PartitionLocations reduce partition p reads; `execute(p)` yields DeviceBatches."""
 
@@ -84,6 +94,11 @@ class GpuShuffleReaderExec:
 
     def output_ordering(self):
         return None
+
+    def statistics(self):
+        # shuffle_reader.rs:304-312
+        n = len(self._schema) if self._schema is not None else 0
+        return stats_for_partitions(n, (loc.partition_stats for locs in self.partition for loc in locs))
 
     def with_new_children(self, _children):
         # shuffle_reader.rs:217-224

@@ -65,3 +65,20 @@ def test_reader_answers_and_fetch_failed_without_a_device(bb, tmp_path):
     # locations whose statistics say "no rows" are never fetched (:248-252)
     empty = bb.PartitionLocation([0], "job", 2, 0, str(tmp_path / "missing.arrow"), meta, bb.PartitionStats(0, 0, 0))
     assert list(bb.GpuShuffleReaderExec([[empty]], schema, None).execute(0)) == []
+
+
+def test_stats_for_partitions_as_the_reference_tests_them(bb):
+    """test_stats_for_partitions_{empty,full,missing}
+    (/root/reference/ballista/core/src/execution_plans/shuffle_reader.rs:876-940)."""
+    S = bb.PartitionStats
+    assert bb.stats_for_partitions(0, []) == {"num_rows": 0, "total_byte_size": 0, "column_statistics": []}
+    full = [S(num_rows=10, num_batches=1, num_bytes=84), S(num_rows=4, num_batches=None, num_bytes=65)]
+    assert bb.stats_for_partitions(0, full) == {"num_rows": 14, "total_byte_size": 149, "column_statistics": []}
+    missing = [S(num_rows=10, num_batches=1, num_bytes=84), S(None, None, None)]
+    assert bb.stats_for_partitions(0, missing) == {"num_rows": None, "total_byte_size": None, "column_statistics": []}
+    # through the operator: every location of every reduce partition counts (shuffle_reader.rs:304-312)
+    schema = pa.schema([("a", pa.int64()), ("b", pa.string())])
+    locs = [[bb.PartitionLocation([0], "j", 1, 0, "p0", partition_stats=full[0])],
+            [bb.PartitionLocation([0], "j", 1, 1, "p1", partition_stats=full[1])]]
+    assert bb.GpuShuffleReaderExec(locs, schema, None).statistics() == {"num_rows": 14, "total_byte_size": 149,
+                                                                       "column_statistics": [None, None]}
