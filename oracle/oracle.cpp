@@ -1,6 +1,6 @@
 /* ORACLE (test infrastructure only — never linked into or called by the product path).
  * CPU restatement of DataFusion v34 create_hashes / BatchPartitioner / take / GroupsAccumulators.
- * See oracle.h for provenance. PARITY UNPINNED (no reference build on this box). */
+ * See oracle.h for provenance and parity status (no reference build on this box). */
 #include "oracle.h"
 
 #include <string>

@@ -6,7 +6,11 @@
  * arrow 49.0.0 (/root/reference/Cargo.toml:25), ahash "0.8" (/root/reference/ballista/core/Cargo.toml:47).
  * Anchors in the reference: shuffle_writer.rs:336-346 (BatchPartitioner call sites),
  * scheduler/src/planner.rs:376-427 (Partial / FinalPartitioned plan shape).
- * PARITY UNPINNED: the reference's own tests hold no hash value, partition id (n>2) or grouped result.
+ * PARITY STATUS: the reference's own tests hold no hash value, partition id (n > 2) or grouped result, so DataFusion's glue
+ * (seed derivation, combine_hashes, null handling, group order) stays "parity unpinned". Pinned: the ahash hasher against
+ * known answers produced by executing compiled upstream ahash-0.8.12 (tests/golden/ahash_0_8_12_kat.json), the Partial ->
+ * Final arithmetic against the only aggregate values the reference's tests assert (SUM = 28, AVG = 3.5, COUNT = 8 over its
+ * alltypes_plain table, ballista/client/src/context.rs:784-815) and against TPC-H Q1 over its own lineitem test data.
  */
 #ifndef ORACLE_H
 #define ORACLE_H

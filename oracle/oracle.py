@@ -3,7 +3,7 @@
 ctypes + pyarrow glue over oracle/_build/liboracle.so, the CPU restatement of the reference's hot path
 (DataFusion v34 create_hashes / BatchPartitioner / take / GroupedHashAggregateStream; SURVEY.md
 Appendix A; reference call sites /root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:336-346
-and /root/reference/ballista/scheduler/src/planner.rs:376-427).  PARITY UNPINNED — see oracle.h.
+and /root/reference/ballista/scheduler/src/planner.rs:376-427).  Parity status (what is pinned by execution and by the reference's fixtures, what is not): see oracle.h.
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
 """
