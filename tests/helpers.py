@@ -132,7 +132,7 @@ def _xxh32_short(data, seed=0):
     return h
 
 
-def independent_frame(data, block=65536, block_checksum=False, content_size=False):
+def independent_frame(data, block=65536, block_checksum=False, content_size=False, block_compress=None):
     """An LZ4 frame with block-independent 64 KB blocks, as lz4_flex's FrameEncoder (arrow-ipc's codec in the reference
     build) writes by default; built from Arrow's raw LZ4 block codec. The header checksum is real; block checksums are placeholders."""
     flg = 0x40 | 0x20 | (0x10 if block_checksum else 0) | (0x08 if content_size else 0)
@@ -142,7 +142,8 @@ def independent_frame(data, block=65536, block_checksum=False, content_size=Fals
     out += bytes([(_xxh32_short(bytes(out[4:])) >> 8) & 0xFF])  # header checksum
     for lo in range(0, len(data), block):
         piece = data[lo:lo + block]
-        comp = pa.compress(piece, codec="lz4_raw", asbytes=True)
+        # blocks from Arrow's raw LZ4 codec (liblz4), or from `block_compress` (tests/lz4_flex_ffi.py: lz4_flex itself)
+        comp = block_compress(piece) if block_compress else pa.compress(piece, codec="lz4_raw", asbytes=True)
         if len(comp) >= len(piece):
             out += (len(piece) | 0x80000000).to_bytes(4, "little") + piece
         else:
@@ -153,7 +154,7 @@ def independent_frame(data, block=65536, block_checksum=False, content_size=Fals
     return bytes(out)
 
 
-def reference_style_lz4_stream(batches, block=65536):
+def reference_style_lz4_stream(batches, block=65536, block_compress=None):
     """An Arrow IPC stream of `batches` (no dictionary columns) framed the way the reference's writer frames a shuffle file
     (arrow-ipc StreamWriter with LZ4_FRAME, /root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:365-376):
     every buffer = int64 uncompressed length + an LZ4 frame of block-independent 64 KB blocks (lz4_flex's FrameEncoder
@@ -193,7 +194,7 @@ def reference_style_lz4_stream(batches, block=65536):
                 if not raw:
                     buffers.append((len(body), 0))
                     continue
-                frame = independent_frame(raw, block)
+                frame = independent_frame(raw, block, block_compress=block_compress)
                 enc = (len(raw).to_bytes(8, "little", signed=True) + frame) if len(frame) < len(raw) else \
                     ((-1).to_bytes(8, "little", signed=True) + raw)
                 buffers.append((len(body), len(enc)))

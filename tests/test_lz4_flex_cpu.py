@@ -117,3 +117,13 @@ def test_message_walk_on_arrow_written_messages():
         assert len(got) == raw_len and got == rb[:raw_len]
         frames += 1
     assert frames >= 5
+
+
+def test_stream_with_lz4_flex_blocks_is_valid_arrow_ipc():
+    """The stand-in shuffle file with its blocks compressed by lz4_flex itself (what the GPU reader test feeds the device
+    decoder) is a stream Arrow's own reader accepts and reads back exactly."""
+    rng = np.random.default_rng(21)
+    batches = [random_batch(rng, n, with_dict=False) for n in (1, 3000, 40_000)]
+    stream = reference_style_lz4_stream(batches, block_compress=F.block_compress)
+    got = pa.ipc.open_stream(io.BytesIO(stream)).read_all().to_batches()
+    assert len(got) == 3 and all(g.equals(b) for g, b in zip(got, batches))
