@@ -31,3 +31,16 @@ def test_reference_arm_prints_the_contract_line():
 
 def test_reference_arm_other_ranks_stay_silent():
     assert run({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}) == []
+
+
+def test_our_arm_fails_loudly_without_a_gpu():
+    """No CPU fallback: on a box without a CUDA device the product arm exits non-zero and prints no benchmark line."""
+    import pytest
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "0"], capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode != 0
+    assert not any(line.lstrip().startswith("{") for line in r.stdout.splitlines())
