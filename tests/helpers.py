@@ -24,11 +24,6 @@ def golden_hash_cases():
                                           type=pa.decimal128(38, 0))], [h for _, h in v["decimal128"]]))
     cases.append(("i64_utf8", [pa.array([a for a, _, _ in v["i64_utf8"]], type=pa.int64()),
                                pa.array([s for _, s, _ in v["i64_utf8"]])], [h for _, _, h in v["i64_utf8"]]))
-    # Binary values hashed by EXECUTED upstream ahash-0.8.12 code (ahash_0_8_12_kat.json, oracle/evidence/make_ahash_kat.py):
-    # the vectors taken with the keys seeds (0,0,0,0) store
-    kat = json.load(open(os.path.join(GOLDEN, "ahash_0_8_12_kat.json")))["hash_one_bytes"]
-    kat = [(bytes.fromhex(x["data"]), int(x["hash"], 16)) for x in kat if x["keys"][0] == "452821e638d01377"]
-    cases.append(("binary_executed_ahash", [pa.array([d for d, _ in kat], type=pa.binary())], [h for _, h in kat]))
     # dictionary-encoded strings hash like plain strings
     cases.append(("dict_utf8", [pa.array([x for x, _ in v["utf8"]]).dictionary_encode()], [h for _, h in v["utf8"]]))
     return cases

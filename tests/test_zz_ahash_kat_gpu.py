@@ -28,3 +28,15 @@ def test_gpu_partitioning_follows_the_executed_hashes(bb, ctx, n):
         seg = rows[offs[p]:offs[p + 1]]
         assert seg == sorted(seg) and all(hashes[r] % n == p for r in seg), p
     assert got.column("k").to_pylist() == [keys[r] for r in rows]
+
+
+def test_gpu_create_hashes_equal_the_executed_hasher(bb, ctx):
+    """create_hashes over a Binary column (DataFusion hashes `&[u8]` values with hash_one) = what the compiled upstream
+    hasher gave for the same bytes with the keys seeds (0,0,0,0) store; a leading null keeps the zero the buffer starts with."""
+    vs = [v for v in json.load(open(GOLDEN))["hash_one_bytes"] if v["keys"][0] == "452821e638d01377"]
+    keys = [bytes.fromhex(v["data"]) for v in vs]
+    want = [int(v["hash"], 16) for v in vs]
+    batch = pa.RecordBatch.from_arrays([pa.array(keys, type=pa.binary())], names=["k"])
+    assert bb.create_hashes(ctx, bb.DeviceBatch.upload(ctx, batch), [0]).tolist() == want
+    with_null = pa.RecordBatch.from_arrays([pa.array([None] + keys, type=pa.binary())], names=["k"])
+    assert bb.create_hashes(ctx, bb.DeviceBatch.upload(ctx, with_null), [0]).tolist() == [0] + want
