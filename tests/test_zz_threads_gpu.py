@@ -41,6 +41,7 @@ def group_by(bb, ctx, batch):
     return pa.Table.from_batches([fin.emit().download()]).sort_by("k")
 
 
+@pytest.mark.timeout(900)
 def test_concurrent_tasks_each_on_their_own_context(bb):
     rng = np.random.default_rng(31)
     work = []
@@ -62,11 +63,13 @@ def test_concurrent_tasks_each_on_their_own_context(bb):
                     got[i] = (q1(bb, ctx, work[i][0]), group_by(bb, ctx, work[i][1]))
         except Exception as e:  # noqa: BLE001 - collected and reported below
             errors.append((i, repr(e)))
-    threads = [threading.Thread(target=task, args=(i,)) for i in range(len(work))]
+    # daemon threads + bounded joins: a deadlock must fail this test, not hang the suite
+    threads = [threading.Thread(target=task, args=(i,), daemon=True) for i in range(len(work))]
     for t in threads:
         t.start()
     for t in threads:
-        t.join()
+        t.join(timeout=300)
+    assert not any(t.is_alive() for t in threads), "a task is still running after 300 s"
     assert errors == []
     for i, ((wq, wg), (gq, gg)) in enumerate(zip(want, got)):
         assert gq.equals(wq), f"task {i}: Q1 result differs under concurrency"
