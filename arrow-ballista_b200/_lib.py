@@ -66,6 +66,7 @@ SIGNATURES = {
     "bgpu_create_hashes": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_void_p]),
     "bgpu_hash_partition": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_uint32,
                                       C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_void_p]),
+    "bgpu_partition_offsets_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_uint32, C.c_void_p]),
     "bgpu_hash_partition_host": (C.c_int, [C.c_void_p, C.POINTER(ArrowArray), C.POINTER(ArrowSchema),
                                            C.POINTER(C.c_int32), C.c_int32, C.c_uint32, C.POINTER(ArrowArray),
                                            C.POINTER(ArrowSchema), C.POINTER(C.c_uint64)]),

@@ -120,7 +120,7 @@ struct KeySet {
 };
 
 // create_hashes for row r over all key columns: column 0 sets, columns >= 1 combine; null rows are skipped.
-__device__ __noinline__ uint64_t row_hash_generic(const KeySet& ks, int64_t r) {
+static __device__ __noinline__ uint64_t row_hash_generic(const KeySet& ks, int64_t r) {
   uint64_t h = 0;
 #pragma unroll 1
   for (int c = 0; c < ks.n; c++) {

@@ -86,6 +86,18 @@ int bgpu_create_hashes(bgpu_ctx* ctx, const bgpu_batch* batch, const int32_t* ke
 int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* batch, const int32_t* key_cols, int32_t n_keys,
                         uint32_t n_partitions, bgpu_batch** out_partitioned, uint64_t* out_offsets,
                         uint64_t* out_hashes_device);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it). The partition offsets of the hash arm
+ * above - out_offsets_device[p] = first row of partition p in the partitioned order, out_offsets_device[n_partitions] =
+ * n_rows; exactly bgpu_hash_partition's out_offsets - for ONE non-null 8-byte key column (Int64 / UInt64 / Timestamp /
+ * Float64 bits) given as a plain device pointer. keys_device (n_rows x 8 bytes) and out_offsets_device
+ * ((n_partitions + 1) x 8 bytes) are the caller's device memory. The call allocates nothing (no cudaMalloc / cudaFree /
+ * cudaMallocAsync, no allocating library routine): its per-chunk histograms live in a file-scope __device__ array of
+ * 2 MiB + 256 B that every GPU which loads the library holds until exit. LIMIT: n_partitions <= 512 (more: BGPU_EINVAL
+ * with a message). Every call on a device shares that array: calls that overlap on the GPU race - serialise them. Work is
+ * ordered on the ctx stream; the result is ready after bgpu_ctx_synchronize (or later work on that stream). */
+int bgpu_partition_offsets_noalloc(bgpu_ctx* ctx, const int64_t* keys_device, int64_t n_rows, uint32_t n_partitions,
+                                   uint64_t* out_offsets_device);
 /* Host-buffer convenience used by the operator layer: upload + partition + download in one call. */
 int bgpu_hash_partition_host(bgpu_ctx* ctx, const struct ArrowArray* batch, const struct ArrowSchema* schema,
                              const int32_t* key_cols, int32_t n_keys, uint32_t n_partitions,
