@@ -10,7 +10,13 @@ import ctypes as C
 import pyarrow as pa
 
 from ._lib import ArrowSchema, lib
-from .runtime import DeviceBatch, _release
+from .runtime import DeviceBatch, _export, _release
+
+
+def export_batch(batch):
+    """(ArrowArray, ArrowSchema) C-Data structs of a host RecordBatch; the caller releases them (`_release`) or keeps
+    them for `GpuAggregateExec.push`."""
+    return _export(batch)
 
 
 class AggregateMode:
@@ -91,6 +97,34 @@ class GpuAggregateExec:
         if not isinstance(batch, DeviceBatch):
             batch = DeviceBatch.upload(self.ctx, batch)
         self.ctx.check(lib().bgpu_agg_update(self._h, batch._h))
+
+    def push(self, batch):
+        """One HOST RecordBatch of the child stream through the streamed input (bgpu_agg_push_host): packed into pinned
+        staging by the calling thread (thread-safe: one thread per input partition may push at once), uploaded and
+        aggregated chunk-wise. `batch` is a pyarrow RecordBatch or an (ArrowArray, ArrowSchema | None) pair already
+        exported with `export_batch` (what a Rust caller holds: FFI structs cost nothing to make)."""
+        if isinstance(batch, tuple):
+            a, s = batch
+            rc = lib().bgpu_agg_push_host(self._h, C.byref(a), C.byref(s) if s is not None else None)
+            self.ctx.check(rc)
+            return
+        a, s = export_batch(batch)
+        try:
+            self.ctx.check(lib().bgpu_agg_push_host(self._h, C.byref(a), C.byref(s)))
+        finally:
+            _release(a)
+            _release(s)
+
+    def flush(self):
+        """Submit the partly filled staging chunk and wait for every launch's outcome (bgpu_agg_flush)."""
+        self.ctx.check(lib().bgpu_agg_flush(self._h))
+
+    @property
+    def ingest_stats(self):
+        out = (C.c_uint64 * 8)()
+        self.ctx.check(lib().bgpu_agg_ingest_stats(self._h, out))
+        keys = ("rows", "batches", "wire_bytes", "arrow_bytes", "chunks", "async_launches", "replays")
+        return dict(zip(keys, [int(x) for x in out]))
 
     def emit(self):
         """End of input: the state batch (Partial) or the final values. Returns a DeviceBatch."""

@@ -47,6 +47,7 @@ struct bgpu_agg {
   DevAllocPtr slots, acc, counters /* u32 [0]=n_groups, [1..4]=flags */, seen, scratch;
   uint32_t acc_stride = 1;
   bool seen_tracking = false;
+  bool async_ready = false;  // the current fused rung has committed a batch: updates may be launched without reading back
   int fused_rung = 0;  // first rung of the fused ladder still worth trying; kFusedRungs = two-pass only
   uint32_t private_gcap = 4;  // groups per thread the private rung starts with (doubles when a batch needs more)
   uint32_t shared_gcap = 128; // group capacity the multi-CTA shared rung starts with: few groups = one copy per warp
@@ -72,6 +73,10 @@ struct bgpu_agg {
   // device time of the fused kernel launches so far (CUDA events on the ctx stream): bench.py's roofline numerator
   cudaEvent_t ev[2] = {nullptr, nullptr};
   double hot_kernel_ms = 0.0;
+
+  // streamed host input (ingest.cu): staging ring, device buffers, launches the host has not looked at yet
+  std::shared_ptr<void> ingest;
+  int (*ingest_drain)(bgpu_agg*) = nullptr;  // seal + submit + poll everything pending (set by ingest.cu)
 
   explicit bgpu_agg(bgpu_ctx* c) : ctx(c) { ctx_retain(c); }
   ~bgpu_agg() {
@@ -121,5 +126,19 @@ int agg_generate_source(const bgpu_agg* g, const JitShape& sh, std::string* out)
 const char* agg_jit_prelude();
 
 int agg_launch_grid(bgpu_ctx* ctx, int64_t n, int per_block);
+// One update whose outcome is read later (streamed input): the fused launch is followed by a device-side conditional
+// commit, the status words arrive in pinned memory once `done` has completed.
+struct AggAsyncReq {
+  uint32_t* d_status = nullptr;        // device, 8 words
+  volatile uint32_t* h_status = nullptr;  // pinned host, 8 words: {committed, n_groups, counters[1..6]}
+  cudaEvent_t k0 = nullptr, k1 = nullptr, done = nullptr;
+  bool launched = false;               // false: the update ran synchronously (two-pass path, first batch of a shape)
+};
+// update_batch / merge_batch; req != nullptr asks for the asynchronous form where the current path allows it
+int agg_update_impl(bgpu_agg* g, const bgpu_batch* batch, AggAsyncReq* req);
+// After req->done: take the launch's outcome. *replay = true: nothing was committed, run the batch again synchronously
+// (agg_update_replay).
+int agg_async_result(bgpu_agg* g, AggAsyncReq* req, bool* replay);
+int agg_update_replay(bgpu_agg* g, const bgpu_batch* batch);
 // (Re)allocate the table and accumulators for `new_max` groups, keeping the first `keep` groups.
 int agg_resize(bgpu_agg* g, uint32_t new_max, uint32_t keep);

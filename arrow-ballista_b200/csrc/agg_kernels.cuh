@@ -33,9 +33,8 @@ __host__ __device__ __forceinline__ size_t fused_slab_words(uint32_t g_cap, int 
 
 // Fold the per-CTA slabs into the group records: one WARP per (group, accumulator); lanes stride over the slabs and
 // the partials are combined by shuffles in a fixed order (Float64 sums are reproducible for a fixed grid).
-__global__ void __launch_bounds__(kAggThreads)
-    commit_kernel(const __grid_constant__ AccPlan plan, const uint64_t* __restrict__ scratch, uint32_t n_ctas,
-                  uint32_t g_cap, uint32_t n_groups) {
+__device__ __forceinline__ void commit_body(const AccPlan& plan, const uint64_t* __restrict__ scratch, uint32_t n_ctas,
+                                            uint32_t g_cap, uint32_t n_groups) {
   const int W = plan.total_words;
   const size_t slab = fused_slab_words(g_cap, W);
   const uint32_t items = n_groups * (uint32_t)plan.n;
@@ -88,6 +87,26 @@ __global__ void __launch_bounds__(kAggThreads)
       }
     }
   }
+}
+
+__global__ void __launch_bounds__(kAggThreads)
+    commit_kernel(const __grid_constant__ AccPlan plan, const uint64_t* __restrict__ scratch, uint32_t n_ctas,
+                  uint32_t g_cap, uint32_t n_groups) {
+  commit_body(plan, scratch, n_ctas, g_cap, n_groups);
+}
+
+// The same for a launch whose outcome the host has not looked at (streamed input, ingest.cu): the device decides. The
+// slabs are folded only when the fused launch neither overflowed the table (counters[1]) nor met a group beyond its
+// capacity (counters[4]) - both flags are sticky until the host clears them, so every later launch is skipped as well
+// and the host replays the skipped chunks in order. status = {committed, n_groups, counters[1..6]}.
+__global__ void __launch_bounds__(kAggThreads)
+    commit_cond_kernel(const __grid_constant__ AccPlan plan, const uint64_t* __restrict__ scratch, uint32_t n_ctas,
+                       uint32_t g_cap, const uint32_t* __restrict__ counters, uint32_t* __restrict__ status) {
+  const uint32_t n_groups = counters[0];
+  const bool ok = counters[1] == 0 && counters[4] == 0 && n_groups <= g_cap;
+  if (blockIdx.x == 0 && threadIdx.x < 8)
+    status[threadIdx.x] = threadIdx.x == 0 ? (ok ? 1u : 0u) : threadIdx.x == 1 ? n_groups : counters[threadIdx.x - 1];
+  if (ok) commit_body(plan, scratch, n_ctas, g_cap, n_groups);
 }
 
 // ---- emit kernels -----------------------------------------------------------------------------------------------

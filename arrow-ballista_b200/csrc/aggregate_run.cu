@@ -429,7 +429,7 @@ static int grow_after_overflow(bgpu_agg* g, uint32_t counter, int64_t batch_rows
 struct Rung { int mode; int threads; int rows; int min_ctas; const char* name; int alt_threads; int alt_rows; int alt_ctas; };
 
 // Try the fused ladder. *done = true when the batch has been committed.
-static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
+static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done, AggAsyncReq* req) {
   bgpu_ctx* ctx = g->ctx;
   *done = false;
   const int W = b->sh.W;
@@ -540,6 +540,24 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
     bool retry_rung = false;
     for (int attempt = 0;; attempt++) {
       refresh_pointers(g, b);
+      if (req && g->async_ready) {
+        // streamed input: launch, let the device decide whether to commit, look at the outcome later
+        if (b->sh.any_validity && !g->seen_tracking) return ctx->fail(BGPU_EINVAL, "internal: seen tracking not set up");
+        BGPU_CUDA(ctx, cudaEventRecord(req->k0, ctx->stream));
+        BGPU_TRY(jit_launch(ctx, fn, grid, T, smem, &b->args));
+        BGPU_CUDA(ctx, cudaEventRecord(req->k1, ctx->stream));
+        commit_cond_kernel<<<agg_launch_grid(ctx, (int64_t)std::max<uint32_t>(1, G * (uint32_t)b->ap.n) * 32, kAggThreads), kAggThreads, 0,
+                             ctx->stream>>>(b->ap, (const uint64_t*)g->scratch->p, (uint32_t)grid, G, (const uint32_t*)g->counters->p,
+                                            req->d_status);
+        ctx->launches++;
+        BGPU_CUDA(ctx, cudaGetLastError());
+        BGPU_CUDA(ctx, cudaMemcpyAsync((void*)req->h_status, req->d_status, 32, cudaMemcpyDeviceToHost, ctx->stream));
+        BGPU_CUDA(ctx, cudaEventRecord(req->done, ctx->stream));
+        req->launched = true;
+        g->last_path = rg.name;
+        *done = true;
+        return BGPU_OK;
+      }
       BGPU_CUDA(ctx, cudaEventRecord(g->ev[0], ctx->stream));
       BGPU_TRY(jit_launch(ctx, fn, grid, T, smem, &b->args));
       BGPU_CUDA(ctx, cudaEventRecord(g->ev[1], ctx->stream));
@@ -571,6 +589,7 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done) {
       ctx->launches++;
       BGPU_CUDA(ctx, cudaGetLastError());
       g->last_path = rg.name;
+      g->async_ready = true;  // this rung has just committed a batch: the next one may run without a host round trip
       *done = true;
       return BGPU_OK;
     }
@@ -694,11 +713,9 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
   return BGPU_OK;
 }
 
-extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) try {
-  if (!g || !batch) return BGPU_EINVAL;
+int agg_update_impl(bgpu_agg* g, const bgpu_batch* batch, AggAsyncReq* req) {
   bgpu_ctx* ctx = g->ctx;
-  if (g->emitted) return ctx->fail(BGPU_EINVAL, "aggregate already emitted");
-  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (req) req->launched = false;
   const int64_t n_rows = batch->n_rows;
   if (n_rows > 0xfffffff0LL) return ctx->fail(BGPU_EUNSUPPORTED, "more than 2^32 rows in one batch");
   Bound b;
@@ -719,10 +736,56 @@ extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) try {
   b.args.n_rows = n_rows;
   bool done = false;
   PhaseTrace trace(ctx);
-  if (g->fused_rung < kFusedRungs) BGPU_TRY(try_fused(g, &b, n_rows, &done));
+  if (g->fused_rung < kFusedRungs) BGPU_TRY(try_fused(g, &b, n_rows, &done, req));
   trace.mark(done ? "fused" : "fused (void)");
-  if (!done) BGPU_TRY(run_two_pass(g, &b, n_rows));
+  if (!done) {
+    g->async_ready = false;
+    BGPU_TRY(run_two_pass(g, &b, n_rows));
+  }
   return BGPU_OK;
+}
+
+int agg_async_result(bgpu_agg* g, AggAsyncReq* req, bool* replay) {
+  bgpu_ctx* ctx = g->ctx;
+  *replay = false;
+  if (!req->launched) return BGPU_OK;
+  BGPU_CUDA(ctx, cudaEventSynchronize(req->done));
+  uint32_t h[8];
+  for (int i = 0; i < 8; i++) h[i] = req->h_status[i];
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, req->k0, req->k1) == cudaSuccess) g->hot_kernel_ms += ms;
+  req->launched = false;
+  // h = {committed, n_groups, counters[1..6]}: counters[2] string key too long, counters[3] arithmetic overflow
+  const uint32_t c[8] = {h[1], h[2], h[3], h[4], h[5], h[6], h[7], 0};
+  BGPU_TRY(check_common_flags(g, c));
+  if (h[0]) {
+    g->n_groups = h[1];
+    return BGPU_OK;
+  }
+  *replay = true;
+  return BGPU_OK;
+}
+
+int agg_update_replay(bgpu_agg* g, const bgpu_batch* batch) {
+  // the skipped launch left its abort flag up (sticky, so that later launches skip too): clear it, then take the
+  // synchronous path, which grows the capacity / the table or changes rung as the batch needs
+  uint32_t h[8];
+  BGPU_TRY(read_counters(g, h));
+  if (h[4]) {
+    h[4] = 0;
+    BGPU_TRY(write_counters(g, h));
+  }
+  g->async_ready = false;
+  return agg_update_impl(g, batch, nullptr);
+}
+
+extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) try {
+  if (!g || !batch) return BGPU_EINVAL;
+  bgpu_ctx* ctx = g->ctx;
+  if (g->emitted) return ctx->fail(BGPU_EINVAL, "aggregate already emitted");
+  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (g->ingest_drain) BGPU_TRY(g->ingest_drain(g));  // streamed input still in flight goes first
+  return agg_update_impl(g, batch, nullptr);
 } catch (const std::exception& e) {
   return bgpu::abi_guard(g ? g->ctx : nullptr, e);  // nothing is thrown across the C ABI
 }
@@ -752,6 +815,7 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) try {
   bgpu_ctx* ctx = g->ctx;
   if (g->emitted) return ctx->fail(BGPU_EINVAL, "aggregate already emitted");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (g->ingest_drain) BGPU_TRY(g->ingest_drain(g));  // end of input: everything pushed so far is aggregated first
   const uint32_t n = g->n_groups;
   std::unique_ptr<bgpu_batch> out(new bgpu_batch(ctx));
   out->n_rows = n;

@@ -149,6 +149,9 @@ static int import_batch(bgpu_ctx* ctx, const struct ArrowArray* a, const struct 
     if (a->children[i]->length != a->length) return ctx->fail(BGPU_EINVAL, "column length mismatch");
     BGPU_TRY(import_column(ctx, a->children[i], s->children[i], device, &b->cols[(size_t)i]));
   }
+  // Host buffers are borrowed "for the call" (include/bgpu.h): every copy out of them must have completed before the
+  // caller may release or reuse them. Pageable memory is staged synchronously by the driver, pinned memory is not.
+  if (!device) BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   *out = b.release();
   return BGPU_OK;
 }

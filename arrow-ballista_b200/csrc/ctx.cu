@@ -54,7 +54,26 @@ static void ctx_teardown(bgpu_ctx* ctx) {
     if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);
   }
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  for (auto& b : ctx->pinned_pool) cudaFreeHost(b.first);
   delete ctx;
+}
+
+int ctx_pinned_get(bgpu_ctx* ctx, size_t bytes, void** out) {
+  {
+    std::lock_guard<std::mutex> lk(ctx->pinned_pool_mu);
+    for (size_t i = 0; i < ctx->pinned_pool.size(); i++)
+      if (ctx->pinned_pool[i].second >= bytes && ctx->pinned_pool[i].second <= bytes * 2) {
+        *out = ctx->pinned_pool[i].first;
+        ctx->pinned_pool.erase(ctx->pinned_pool.begin() + (long)i);
+        return BGPU_OK;
+      }
+  }
+  BGPU_CUDA(ctx, cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+  return BGPU_OK;
+}
+void ctx_pinned_put(bgpu_ctx* ctx, void* p, size_t bytes) {
+  std::lock_guard<std::mutex> lk(ctx->pinned_pool_mu);
+  ctx->pinned_pool.emplace_back(p, bytes);
 }
 
 void ctx_release(bgpu_ctx* ctx) {

@@ -54,6 +54,10 @@ struct bgpu_ctx {
   // small pinned scratch for device->host scalars (partition offsets, group counts)
   void* pinned = nullptr;
   size_t pinned_bytes = 0;
+  // pinned staging blocks of the streamed input (ingest.cu), kept for the life of the context: pinning memory costs
+  // milliseconds per block, an aggregate per stage must not pay it again
+  std::mutex pinned_pool_mu;
+  std::vector<std::pair<void*, size_t>> pinned_pool;
 
   int fail(int code, const std::string& msg) {
     err = msg;
@@ -75,6 +79,9 @@ struct bgpu_ctx {
     if (_rc != BGPU_OK) return _rc; \
   } while (0)
 
+// a pinned host block of at least `bytes` from the context's pool (cudaHostAlloc on a miss) / back into it
+int ctx_pinned_get(bgpu_ctx* ctx, size_t bytes, void** out);
+void ctx_pinned_put(bgpu_ctx* ctx, void* p, size_t bytes);
 void ctx_retain(bgpu_ctx* ctx);
 void ctx_release(bgpu_ctx* ctx);  // tears the context down when the last reference goes
 

@@ -174,6 +174,29 @@ int bgpu_agg_create_expr(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema* 
                          int32_t n_filter, bgpu_agg** out);
 /* update_batch (Partial/Single) or merge_batch (Final*) with one device-resident batch */
 int bgpu_agg_update(bgpu_agg* agg, const bgpu_batch* batch);
+/* The operator's input side as the reference drives it: one call per HOST RecordBatch of the child stream, 8192 rows by
+ * default (/root/reference/ballista/core/src/config.rs:180-182; the stream loop of
+ * /root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:342-346), from as many threads at once as the task
+ * has input partitions (/root/reference/ballista/core/src/execution_plans/coalesce_tasks.rs:183-216). Partial / Single
+ * modes. The call is THREAD-SAFE and returns once the batch's buffers have been read (borrowed for the call): the
+ * calling thread packs the columns the aggregate reads into a pinned staging chunk in a narrow wire form
+ * (frame-of-reference integers of 0/1/2/4/8 bytes - Decimal128 values that fit 64 bits included -, utf8 as narrow
+ * lengths + bytes); full chunks are uploaded on a copy stream, widened back to Arrow buffers on the device and
+ * aggregated by one kernel launch per chunk without a host round trip; results are bit-identical to bgpu_batch_upload +
+ * bgpu_agg_update per batch. `schema` may be NULL (the batch is then trusted to match input_schema). bgpu_agg_emit and
+ * bgpu_agg_update first complete everything pushed so far (callers join their pushing threads before); errors found
+ * late (a launch that reports overflow) surface from the next push / flush / emit. Dictionary columns:
+ * BGPU_EUNSUPPORTED (take bgpu_batch_upload + bgpu_agg_update).
+ * bgpu_agg_flush: submit the partly filled chunk and wait for every launch's outcome.
+ * bgpu_agg_ingest_stats (introspection): out8 = {rows, batches, wire bytes copied host->device, Arrow bytes they stand
+ * for, chunks, launches not read back, launches replayed, 0}. */
+int bgpu_agg_push_host(bgpu_agg* agg, const struct ArrowArray* batch, const struct ArrowSchema* schema);
+int bgpu_agg_flush(bgpu_agg* agg);
+int bgpu_agg_ingest_stats(const bgpu_agg* agg, uint64_t* out8);
+/* test hook (host only): the wire form of one fixed-width column segment as bgpu_agg_push_host packs it (which = 0: the
+ * AVX2 build of the packer, 1: the plain build); out_packed has room for n * 16 bytes */
+int bgpu_debug_pack_fixed_host(const char* format, const void* values, int64_t n, int32_t which, int64_t* out_base,
+                               uint32_t* out_code, uint8_t* out_packed);
 /* end of input: state() (Partial) or evaluate() (Final modes and Single). Group order is unspecified, as in the
  * reference (GroupValues uses a randomly seeded table). The aggregate may not be updated afterwards. */
 int bgpu_agg_emit(bgpu_agg* agg, bgpu_batch** out);
