@@ -126,6 +126,10 @@ class GpuAggregateExec:
         keys = ("rows", "batches", "wire_bytes", "arrow_bytes", "chunks", "async_launches", "replays")
         return dict(zip(keys, [int(x) for x in out]))
 
+    def reset(self):
+        """A new input stream over the same plan (`execute` of the next partition): bgpu_agg_reset."""
+        self.ctx.check(lib().bgpu_agg_reset(self._h))
+
     def emit(self):
         """End of input: the state batch (Partial) or the final values. Returns a DeviceBatch."""
         out = C.c_void_p()

@@ -63,9 +63,9 @@ struct bgpu_agg {
     DevAllocPtr last_remap;        // nullptr = identity
   };
   std::vector<DictState> dicts;
-  // runtime-specialised kernel modules of this aggregate, keyed by the generated plan source (one per batch shape
-  // and launch geometry; the modules themselves live in jit.cu's process-wide cache)
-  std::map<std::string, const bgpu::JitModule*> modules;
+  // what bgpu_agg_create_expr was given, byte for byte: with a batch shape, the key of the process-wide cache of
+  // run-time specialised kernels (aggregate_run.cu specialise)
+  std::string plan_key;
   bool emitted = false;
   // introspection for tests / bench: which path the last update took ("fused_private", "fused_shared2", "fused_shared1",
   // "shared", "global")
@@ -77,6 +77,7 @@ struct bgpu_agg {
   // streamed host input (ingest.cu): staging ring, device buffers, launches the host has not looked at yet
   std::shared_ptr<void> ingest;
   int (*ingest_drain)(bgpu_agg*) = nullptr;  // seal + submit + poll everything pending (set by ingest.cu)
+  void (*ingest_reset)(bgpu_agg*) = nullptr; // forget errors and statistics of the last stream
 
   explicit bgpu_agg(bgpu_ctx* c) : ctx(c) { ctx_retain(c); }
   ~bgpu_agg() {

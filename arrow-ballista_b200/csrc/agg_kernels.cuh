@@ -200,6 +200,157 @@ __global__ void __launch_bounds__(kAggThreads)
   }
 }
 
+// ---- emit in one launch ---------------------------------------------------------------------------------------------
+// Every output column of the state / result batch from the dense key arrays and the group records: key columns
+// (fixed-width, bool, dictionary indices, utf8 lengths), accumulator columns (1 or 2 words per group), AVG evaluation and
+// all validity bitmaps (ballots: thread = group id). SINGLE = one CTA covers all groups and also scans the utf8 lengths
+// into offsets and writes the string bytes; otherwise the host runs a device scan + unpack_utf8_kernel for utf8 keys.
+constexpr int kEmitThreads = 1024;
+constexpr int kMaxEmitAcc = 40;
+struct EmitKeyCol {
+  void* values;       // fixed / bool / dictionary indices
+  int32_t* offsets;   // utf8: n + 1 entries
+  int32_t* lens;      // utf8 (not SINGLE): n entries
+  uint8_t* data;      // utf8 bytes
+  uint32_t* valid;    // always present; the host drops it when no group has a null in this column
+  int32_t kind, width, byte_off, pad;
+};
+struct EmitAccCol {
+  uint64_t* out;
+  uint32_t* valid;    // nullptr: never null
+  int32_t type;       // 0: copy `words` words at `off`; 1: AVG Float64 (sum at off, count at count_off); 2: AVG Decimal128
+  int32_t words, off, count_off, scale_up, seen_bit;
+};
+struct EmitArgs {
+  EmitKeyCol k[kMaxGroupCols];
+  EmitAccCol a[kMaxEmitAcc];
+  const uint64_t* key0;
+  const uint64_t* key1;
+  const uint32_t* kmeta;
+  const uint64_t* acc;
+  const uint32_t* seen;
+  int32_t* flags;          // the aggregate's counters + 1
+  uint32_t* key_null_or;   // OR of all key metas (bit c = some group has a null in key column c)
+  uint32_t stride;
+  int32_t n_key, n_acc;
+};
+
+template <bool SINGLE>
+__global__ void __launch_bounds__(kEmitThreads) emit_all_kernel(const __grid_constant__ EmitArgs a, uint32_t n) {
+  const uint32_t n_pad = (n + 31) & ~31u;
+  const bool lane0 = (threadIdx.x & 31) == 0;
+  uint32_t null_or = 0;
+  for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < n_pad; g += gridDim.x * blockDim.x) {
+    const bool in = g < n;
+    uint64_t k0 = 0, k1 = 0;
+    uint32_t meta = 0;
+    if (in) {
+      k0 = a.key0[g];
+      k1 = a.key1 ? a.key1[g] : 0;
+      meta = a.kmeta[g];
+      null_or |= meta;
+    }
+    for (int c = 0; c < a.n_key; c++) {
+      const EmitKeyCol& kc = a.k[c];
+      const bool valid = in && !((meta >> c) & 1);
+      const uint64_t word = kc.byte_off < 8 ? (k0 >> (8 * kc.byte_off)) : (k1 >> (8 * (kc.byte_off - 8)));
+      if (kc.kind == K_UTF8 || kc.kind == K_BINARY) {
+        if (in) (SINGLE ? kc.offsets + 1 : kc.lens)[g] = valid ? (int32_t)(word & 0xff) : 0;
+      } else if (kc.kind == K_BOOL) {
+        const uint32_t bits = __ballot_sync(0xffffffffu, in && (word & 1));
+        if (lane0) ((uint32_t*)kc.values)[g >> 5] = bits;
+      } else if (in) {
+        if (kc.width == 16) ((ulonglong2*)kc.values)[g] = make_ulonglong2(k0, k1);
+        else if (kc.width == 8) ((uint64_t*)kc.values)[g] = word;
+        else if (kc.width == 4) ((uint32_t*)kc.values)[g] = (uint32_t)word;
+        else if (kc.width == 2) ((uint16_t*)kc.values)[g] = (uint16_t)word;
+        else ((uint8_t*)kc.values)[g] = (uint8_t)word;
+      }
+      const uint32_t vb = __ballot_sync(0xffffffffu, valid);
+      if (lane0) kc.valid[g >> 5] = vb;
+    }
+    const uint64_t* rec = a.acc + (size_t)(in ? g : 0) * a.stride;
+    const uint32_t seen = (a.seen && in) ? a.seen[g] : 0xffffffffu;
+    for (int j = 0; j < a.n_acc; j++) {
+      const EmitAccCol& ac = a.a[j];
+      bool valid = in;
+      if (ac.type == 0) {
+        if (in) {
+          ac.out[(size_t)g * ac.words] = rec[ac.off];
+          if (ac.words > 1) ac.out[(size_t)g * ac.words + 1] = rec[ac.off + 1];
+        }
+        valid = in && ((seen >> ac.seen_bit) & 1);
+      } else {
+        const uint64_t cnt = in ? rec[ac.count_off] : 0;
+        valid = in && cnt != 0;
+        if (in && ac.type == 2) {
+          __int128 s = (__int128)(((unsigned __int128)rec[ac.off + 1] << 64) | rec[ac.off]);
+          __int128 q = 0;
+          if (valid) {
+            bool ovf = false;
+            for (int i = 0; i < ac.scale_up; i++) {
+              const __int128 lim = (((__int128)1 << 126) - 1 + ((__int128)1 << 126)) / 10;  // i128::MAX / 10
+              if (s > lim || s < -lim) ovf = true;
+              s *= 10;
+            }
+            if (ovf) atomicOr(&a.flags[2], 1);
+            q = s / (__int128)cnt;
+          }
+          ac.out[2 * (size_t)g] = (uint64_t)q;
+          ac.out[2 * (size_t)g + 1] = (uint64_t)((unsigned __int128)q >> 64);
+        } else if (in) {
+          const double s = __longlong_as_double((long long)rec[ac.off]);
+          ac.out[g] = (uint64_t)__double_as_longlong(valid ? s / (double)cnt : 0.0);
+        }
+      }
+      if (ac.valid) {
+        const uint32_t vb = __ballot_sync(0xffffffffu, valid);
+        if (lane0) ac.valid[g >> 5] = vb;
+      }
+    }
+  }
+  null_or = __reduce_or_sync(0xffffffffu, null_or);
+  if (lane0 && null_or) atomicOr(a.key_null_or, null_or);
+  if (!SINGLE) return;
+  // one CTA: lengths (parked in offsets[1..n]) -> offsets, then the bytes
+  __shared__ int32_t s_warp[kEmitThreads / 32];
+  __shared__ int32_t s_carry;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int c = 0; c < a.n_key; c++) {
+    const EmitKeyCol& kc = a.k[c];
+    if (kc.kind != K_UTF8 && kc.kind != K_BINARY) continue;
+    __syncthreads();
+    if (threadIdx.x == 0) { s_carry = 0; kc.offsets[0] = 0; }
+    __syncthreads();
+    for (uint32_t g0 = 0; g0 < n; g0 += kEmitThreads) {
+      const uint32_t g = g0 + threadIdx.x;
+      const int32_t len = g < n ? kc.offsets[g + 1] : 0;
+      int32_t x = len;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int32_t y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x += y;
+      }
+      if (lane == 31) s_warp[warp] = x;
+      __syncthreads();
+      int32_t pre = s_carry;
+      for (int w = 0; w < warp; w++) pre += s_warp[w];
+      const int32_t end = pre + x;
+      if (g < n) {
+        kc.offsets[g + 1] = end;
+        const uint64_t k0 = a.key0[g], k1 = a.key1 ? a.key1[g] : 0;
+        for (int i = 0; i < len; i++) {
+          const int off = kc.byte_off + 1 + i;
+          kc.data[end - len + i] = (uint8_t)((off < 8 ? (k0 >> (8 * off)) : (k1 >> (8 * (off - 8)))) & 0xff);
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x == kEmitThreads - 1) s_carry = end;
+      __syncthreads();
+    }
+  }
+}
+
 // validity bitmap of an accumulator from the seen masks
 __global__ void __launch_bounds__(kAggThreads)
     seen_bitmap_kernel(const uint32_t* __restrict__ seen, uint32_t n, int bit, uint32_t* __restrict__ out_valid) {

@@ -43,6 +43,25 @@ static int agg_create_impl(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema
   for (int64_t i = 0; i < input_schema->n_children; i++)
     BGPU_TRY(parse_field(ctx, input_schema->children[i], &g->fields[(size_t)i]));
   if (n_filter && g->final_mode) return ctx->fail(BGPU_EINVAL, "a filter applies to raw input rows (Partial/Single modes)");
+  {  // the plan as given: key of the specialised-kernel cache
+    std::string& k = g->plan_key;
+    auto put = [&](const void* p, size_t n) { k.append((const char*)p, n); };
+    put(&mode, 4); put(&n_group, 4); put(&n_agg, 4); put(&n_filter, 4);
+    for (const Column& f : g->fields) { k += f.format; k += f.kind == K_DICT32 ? "|D" + f.dict->format : std::string(); k += ';'; }
+    put(group_cols, (size_t)n_group * 4);
+    if (n_agg) {
+      put(agg_fns, (size_t)n_agg * 4);
+      put(agg_expr_offsets, ((size_t)n_agg + 1) * 4);
+      for (int32_t i = 0; i < agg_expr_offsets[n_agg]; i++) {  // field by field: the struct has padding
+        const bgpu_expr_node& e = nodes[i];
+        put(&e.op, 4); put(&e.a, 4); put(&e.precision, 4); put(&e.scale, 4); put(&e.lo, 8); put(&e.hi, 8);
+      }
+    }
+    for (int32_t i = 0; i < n_filter; i++) {
+      const bgpu_expr_node& e = filter[i];
+      put(&e.op, 4); put(&e.a, 4); put(&e.precision, 4); put(&e.scale, 4); put(&e.lo, 8); put(&e.hi, 8);
+    }
+  }
   BGPU_TRY(compile_filter(ctx, g->fields, filter, n_filter, &g->filter));
   // packed key layout: fields in order, never straddling the 8-byte boundary; utf8 shares what is left
   int fixed_bytes = 0, n_var = 0;
@@ -305,6 +324,31 @@ extern "C" int bgpu_agg_debug_compile(bgpu_ctx* ctx, int32_t mode, const struct 
   return BGPU_OK;
 } catch (const std::exception& e) {
   return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
+}
+
+// A new input stream over the same plan (the reference's AggregateExec is created once per task and `execute`d per
+// partition, /root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:234-257): the table, the accumulators
+// and the counters are cleared; the plan, the compiled kernels, the learned rung / capacities and the staging buffers of
+// the streamed input stay.
+extern "C" int bgpu_agg_reset(bgpu_agg* g) try {
+  if (!g) return BGPU_EINVAL;
+  bgpu_ctx* ctx = g->ctx;
+  if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
+  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (g->ingest_drain && !g->emitted) (void)g->ingest_drain(g);  // nothing may still be writing the table
+  if (g->ingest_reset) g->ingest_reset(g);
+  const size_t slot_bytes = g->key_words == 1 ? 16 : 32;
+  BGPU_CUDA(ctx, cudaMemsetAsync(g->counters->p, 0, 32, ctx->stream));
+  BGPU_CUDA(ctx, cudaMemsetAsync(g->slots->p, 0, (size_t)g->max_groups * 2 * slot_bytes, ctx->stream));
+  BGPU_CUDA(ctx, cudaMemsetAsync(g->acc->p, 0, (size_t)g->max_groups * g->acc_stride * 8, ctx->stream));
+  if (g->seen_tracking) BGPU_CUDA(ctx, cudaMemsetAsync(g->seen->p, 0, (size_t)g->max_groups * 4, ctx->stream));
+  g->n_groups = 0;
+  g->emitted = false;
+  g->hot_kernel_ms = 0.0;
+  for (auto& d : g->dicts) d = bgpu_agg::DictState();
+  return BGPU_OK;
+} catch (const std::exception& e) {
+  return bgpu::abi_guard(g ? g->ctx : nullptr, e);  // nothing is thrown across the C ABI
 }
 
 extern "C" void bgpu_agg_destroy(bgpu_agg* g) {

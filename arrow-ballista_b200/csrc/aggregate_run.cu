@@ -16,6 +16,9 @@
 
 #include <algorithm>
 #include <chrono>
+#include <mutex>
+#include <tuple>
+#include <unordered_map>
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -367,19 +370,82 @@ static void refresh_pointers(bgpu_agg* g, Bound* b) {
   b->args.t = g->table();
 }
 
+// Everything of a JitShape the generated source depends on, as a compact key.
+static void shape_key(const JitShape& sh, std::string* k) {
+  auto put = [&](int32_t v) { k->append((const char*)&v, 4); };
+  put((int32_t)sh.slots.size());
+  for (const JitSlot& sl : sh.slots) {
+    put(sl.batch_col); put(sl.kind); put(sl.width); put(sl.vk);
+    put((sl.nullable ? 1 : 0) | (sl.remap ? 2 : 0) | (sl.key_use ? 4 : 0) | (sl.value_use ? 8 : 0) | (sl.filter_use ? 16 : 0));
+  }
+  put((int32_t)sh.key_slot.size());
+  for (int32_t v : sh.key_slot) put(v);
+  put((int32_t)sh.filter_slot.size());
+  for (int32_t v : sh.filter_slot) put(v);
+  put((int32_t)sh.value_nullable.size());
+  for (bool v : sh.value_nullable) put(v ? 1 : 0);
+  put((int32_t)sh.acc_alias.size());
+  for (int32_t v : sh.acc_alias) put(v);
+  for (int32_t v : sh.acc_word0) put(v);
+  put(sh.W); put(sh.has_seen ? 1 : 0); put(sh.T); put(sh.R); put(sh.min_ctas); put(sh.kernels);
+  put((sh.any_validity ? 1 : 0) | (sh.row32 ? 2 : 0));
+}
+
 // Generate + compile (cached) the fused kernel (kernels = 1 private, 4 shared-atomic) or the two-pass kernels (2) for this batch
-// shape at the given launch geometry. b->mod->fn is indexed by JitKernel.
+// shape at the given launch geometry. b->mod->fn is indexed by JitKernel. The process-wide cache is keyed by the plan (the
+// arguments bgpu_agg_create_expr was given, bgpu_agg::plan_key) and the shape, so that a stage that runs the same plan
+// again - a new aggregate per task - neither generates the source nor looks a multi-kilobyte string up.
 static int specialise(bgpu_agg* g, Bound* b, int kernels, int T, int R, int min_ctas) {
   b->sh.T = T; b->sh.R = R; b->sh.min_ctas = min_ctas; b->sh.kernels = kernels;
   b->sh.has_seen = g->seen_tracking;
+  static std::mutex mu;
+  static std::unordered_map<std::string, const JitModule*> cache;
+  std::string key;
+  key.reserve(g->plan_key.size() + 256);
+  key.append((const char*)&g->ctx->device, sizeof(int));
+  key += g->plan_key;
+  shape_key(b->sh, &key);
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { b->mod = it->second; return BGPU_OK; }
+  }
   std::string src;
   BGPU_TRY(agg_generate_source(g, b->sh, &src));
-  auto it = g->modules.find(src);
-  if (it != g->modules.end()) { b->mod = it->second; return BGPU_OK; }
   static const std::vector<std::string> fused{"bgpu_fused"}, fused_shared{"bgpu_fused_shared"},
       two_pass{"bgpu_intern", "bgpu_acc_shared", "bgpu_acc_global", "bgpu_sketch"};
   BGPU_TRY(jit_compile(g->ctx, agg_jit_prelude(), src, kernels == 1 ? fused : kernels == 4 ? fused_shared : two_pass, &b->mod));
-  g->modules.emplace(std::move(src), b->mod);
+  std::lock_guard<std::mutex> lk(mu);
+  cache.emplace(std::move(key), b->mod);
+  return BGPU_OK;
+}
+
+// attributes of a compiled kernel that never change: asked once
+static int cached_local_bytes(bgpu_ctx* ctx, CUfunction fn, int* out) {
+  static std::mutex mu;
+  static std::map<CUfunction, int> cache;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find(fn);
+    if (it != cache.end()) { *out = it->second; return BGPU_OK; }
+  }
+  BGPU_TRY(jit_local_bytes(ctx, fn, out));
+  std::lock_guard<std::mutex> lk(mu);
+  cache[fn] = *out;
+  return BGPU_OK;
+}
+static int cached_occupancy(bgpu_ctx* ctx, CUfunction fn, int block, size_t smem, int* out) {
+  static std::mutex mu;
+  static std::map<std::tuple<CUfunction, int, size_t>, int> cache;
+  const auto key = std::make_tuple(fn, block, smem);
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { *out = it->second; return BGPU_OK; }
+  }
+  BGPU_TRY(jit_occupancy(ctx, fn, block, smem, out));
+  std::lock_guard<std::mutex> lk(mu);
+  cache[key] = *out;
   return BGPU_OK;
 }
 
@@ -465,7 +531,7 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done, AggAsync
     if (rg.alt_threads) {  // does the kernel fit the register budget of the preferred geometry?
       BGPU_TRY(specialise(g, b, rg.mode == 0 ? 1 : 4, rg.threads, rg.rows, rg.min_ctas));
       int local = 0;
-      BGPU_TRY(jit_local_bytes(ctx, b->mod->fn[JK_FUSED], &local));
+      BGPU_TRY(cached_local_bytes(ctx, b->mod->fn[JK_FUSED], &local));
       if (local > 0) { rg.threads = rg.alt_threads; rg.rows = rg.alt_rows; rg.min_ctas = rg.alt_ctas; }
     }
     const int T = rg.threads;
@@ -524,7 +590,7 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done, AggAsync
     b->args.replicas = replicas;
     BGPU_TRY(jit_set_max_smem(ctx, fn, smem));
     int occ = 1;
-    BGPU_TRY(jit_occupancy(ctx, fn, T, smem, &occ));
+    BGPU_TRY(cached_occupancy(ctx, fn, T, smem, &occ));
     occ = std::max(1, occ);
     // several CTAs per SM slot: the hardware block scheduler then evens out the per-SM speed differences that a
     // one-wave persistent grid leaves as a 20% idle tail (ncu: SM active 77% of elapsed), at ~10 us of prologue +
@@ -689,7 +755,7 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
     const CUfunction fn = b->mod->fn[JK_ACC_SHARED];
     BGPU_TRY(jit_set_max_smem(ctx, fn, smem));
     int occ = 1;
-    BGPU_TRY(jit_occupancy(ctx, fn, T, smem, &occ));
+    BGPU_TRY(cached_occupancy(ctx, fn, T, smem, &occ));
     const int grid = (int)std::min<int64_t>(tiles, (int64_t)ctx->sm_count * std::max(1, occ));
     b->args.replicas = (uint32_t)replicas;
     BGPU_TRY(jit_launch(ctx, fn, grid, T, smem, &b->args));
@@ -794,21 +860,10 @@ extern "C" const char* bgpu_agg_last_path(const bgpu_agg* g) { return g ? g->las
 extern "C" double bgpu_agg_hot_kernel_ms(const bgpu_agg* g) { return g ? g->hot_kernel_ms : 0.0; }
 
 // ---- emit ---------------------------------------------------------------------------------------------------------
-static int emit_validity(bgpu_agg* g, int phys_idx, uint32_t n, Column* col) {
-  bgpu_ctx* ctx = g->ctx;
-  if (!g->seen_tracking || n == 0) return BGPU_OK;
-  DevAllocPtr v;
-  BGPU_TRY(dev_alloc(ctx, (size_t)ceil_div64(n, 32) * 4, &v));
-  seen_bitmap_kernel<<<agg_launch_grid(ctx, n, kAggThreads), kAggThreads, 0, ctx->stream>>>(
-      (const uint32_t*)g->seen->p, n, phys_idx, (uint32_t*)v->p);
-  ctx->launches++;
-  BGPU_CUDA(ctx, cudaGetLastError());
-  col->validity = (uint8_t*)v->p;
-  col->null_count = -1;
-  col->owned.push_back(v);
-  return BGPU_OK;
-}
-
+// Two launches and one host round trip whatever the plan: densify_keys_kernel (table slots -> dense key arrays) and
+// emit_all_kernel (every key column, accumulator column, AVG evaluation and validity bitmap); the counters and the OR of
+// the key null masks come back together at the end. utf8 key columns of more groups than one CTA covers add a device scan
+// and one unpack kernel, still without a round trip: their data buffer is sized by the packed key's width.
 extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) try {
   if (!g || !out_batch) return BGPU_EINVAL;
   *out_batch = nullptr;
@@ -816,19 +871,17 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) try {
   if (g->emitted) return ctx->fail(BGPU_EINVAL, "aggregate already emitted");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
   if (g->ingest_drain) BGPU_TRY(g->ingest_drain(g));  // end of input: everything pushed so far is aggregated first
-  const uint32_t n = g->n_groups;
+  const uint32_t n = g->n_groups, n1 = std::max<uint32_t>(n, 1);
   std::unique_ptr<bgpu_batch> out(new bgpu_batch(ctx));
   out->n_rows = n;
   PhaseTrace trace(ctx);
-  const int grid = agg_launch_grid(ctx, std::max<uint32_t>(n, 1), kAggThreads);
-  // dense key arrays (index = group id) out of the table slots
+  const size_t bitmap_bytes = (size_t)ceil_div64(n1, 32) * 4;
+  // one allocation for everything that is scratch or small: dense keys, metas, bitmaps come out of `pool`
+  EmitArgs ea{};
   DevAllocPtr d_key0, d_key1, d_kmeta;
-  BGPU_TRY(dev_alloc(ctx, (size_t)std::max<uint32_t>(n, 1) * 8, &d_key0));
-  if (g->key_words > 1) BGPU_TRY(dev_alloc(ctx, (size_t)std::max<uint32_t>(n, 1) * 8, &d_key1));
-  BGPU_TRY(dev_alloc(ctx, (size_t)std::max<uint32_t>(n, 1) * 4, &d_kmeta));
-  const uint64_t* key0 = (const uint64_t*)d_key0->p;
-  const uint64_t* key1 = d_key1 ? (const uint64_t*)d_key1->p : nullptr;
-  const uint32_t* kmeta = (const uint32_t*)d_kmeta->p;
+  BGPU_TRY(dev_alloc(ctx, (size_t)n1 * 8, &d_key0));
+  if (g->key_words > 1) BGPU_TRY(dev_alloc(ctx, (size_t)n1 * 8, &d_key1));
+  BGPU_TRY(dev_alloc(ctx, (size_t)n1 * 4, &d_kmeta));
   if (n) {
     bgpu::GroupTable t = g->table();
     t.max_groups = n;  // ids handed out by a void (overflowed) pass are not groups
@@ -837,137 +890,137 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) try {
     ctx->launches++;
     BGPU_CUDA(ctx, cudaGetLastError());
   }
-  // which key columns hold a null at all? (bit c of a group's meta = key column c is null.) Columns without one are
-  // emitted without a validity bitmap: the state batch of the common null-free case is then plain fixed-width data,
-  // which is what the fused repartition + exchange kernel takes.
-  // (only for states large enough for the exchange to matter: the answer costs a host round trip in the middle of emit)
-  uint32_t key_null_mask = n && n < 4096 ? 0xffffffffu : 0u;
-  if (n >= 4096) {
-    DevAllocPtr d_mask;
-    BGPU_TRY(dev_alloc(ctx, 4, &d_mask));
-    BGPU_CUDA(ctx, cudaMemsetAsync(d_mask->p, 0, 4, ctx->stream));
-    or_kmeta_kernel<<<std::min(grid, ctx->sm_count * 4), kAggThreads, 0, ctx->stream>>>(kmeta, n, (uint32_t*)d_mask->p);
-    ctx->launches++;
-    uint32_t* pin = (uint32_t*)ctx->pinned + 32;
-    BGPU_CUDA(ctx, cudaMemcpyAsync(pin, d_mask->p, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    key_null_mask = *pin;
-  }
-  trace.mark("emit densify");
+  ea.key0 = (const uint64_t*)d_key0->p;
+  ea.key1 = d_key1 ? (const uint64_t*)d_key1->p : nullptr;
+  ea.kmeta = (const uint32_t*)d_kmeta->p;
+  ea.acc = (const uint64_t*)g->acc->p;
+  ea.seen = g->seen_tracking ? (const uint32_t*)g->seen->p : nullptr;
+  ea.flags = g->d_flags();
+  ea.key_null_or = (uint32_t*)g->counters->p + 5;
+  ea.stride = g->acc_stride;
+  const bool single = n <= 4 * kEmitThreads;
   // group key columns
+  struct Utf8Post { size_t col; DevAllocPtr lens; };
+  std::vector<Utf8Post> utf8;
   for (size_t i = 0; i < g->group_cols.size(); i++) {
     const Column& f = g->fields[(size_t)g->group_cols[i]];
     Column c;
     c.name = f.name; c.format = f.format; c.flags = f.flags | ARROW_FLAG_NULLABLE; c.kind = f.kind; c.width = f.width;
-    const bool has_nulls = (key_null_mask >> i) & 1;
-    c.length = n; c.null_count = has_nulls ? -1 : 0;
+    c.length = n; c.null_count = -1;
+    EmitKeyCol& kc = ea.k[i];
+    kc.kind = f.kind; kc.width = f.width; kc.byte_off = g->key_off[i];
     DevAllocPtr valid;
-    uint32_t* valid_bits = nullptr;
-    if (has_nulls) {
-      BGPU_TRY(dev_alloc(ctx, (size_t)ceil_div64(std::max<uint32_t>(n, 1), 32) * 4, &valid));
-      c.owned.push_back(valid);
-      c.validity = (uint8_t*)valid->p;
-      valid_bits = (uint32_t*)valid->p;
-    }
+    BGPU_TRY(dev_alloc(ctx, bitmap_bytes, &valid));
+    c.owned.push_back(valid);
+    c.validity = (uint8_t*)valid->p;
+    kc.valid = (uint32_t*)valid->p;
     if (f.kind == K_UTF8 || f.kind == K_BINARY) {
-      DevAllocPtr lens, offs, data;
-      BGPU_TRY(dev_alloc(ctx, (size_t)(n + 1) * 4, &lens));
+      DevAllocPtr offs, data;
+      const size_t cap = (size_t)n1 * (size_t)std::max(1, g->key_width[i]) + 16;  // the packed key bounds every string
       BGPU_TRY(dev_alloc(ctx, (size_t)(n + 1) * 4, &offs));
-      BGPU_CUDA(ctx, cudaMemsetAsync(offs->p, 0, 4, ctx->stream));
-      int32_t total = 0;
-      if (n) {
-        unpack_utf8_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(key0, key1, kmeta, n, (int)i, g->key_off[i], 0,
-                                                                 (int32_t*)lens->p, nullptr, valid_bits);
-        size_t tmp_bytes = 0;
-        cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, (const int32_t*)lens->p, (int32_t*)offs->p + 1, (int)n, ctx->stream);
-        DevAllocPtr tmp;
-        BGPU_TRY(dev_alloc(ctx, tmp_bytes, &tmp));
-        BGPU_CUDA(ctx, cub::DeviceScan::InclusiveSum(tmp->p, tmp_bytes, (const int32_t*)lens->p, (int32_t*)offs->p + 1, (int)n, ctx->stream));
-        BGPU_CUDA(ctx, cudaMemcpyAsync(&total, (int32_t*)offs->p + n, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+      BGPU_TRY(dev_alloc(ctx, cap, &data));
+      kc.offsets = (int32_t*)offs->p; kc.data = (uint8_t*)data->p;
+      if (!single) {
+        Utf8Post up; up.col = i;
+        BGPU_TRY(dev_alloc(ctx, (size_t)n1 * 4, &up.lens));
+        kc.lens = (int32_t*)up.lens->p;
+        utf8.push_back(up);
+      } else if (!n) {
+        BGPU_CUDA(ctx, cudaMemsetAsync(offs->p, 0, 4, ctx->stream));
       }
-      BGPU_TRY(dev_alloc(ctx, (size_t)total, &data));
-      if (n)
-        unpack_utf8_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(key0, key1, kmeta, n, (int)i, g->key_off[i], 1,
-                                                                 (int32_t*)offs->p, (uint8_t*)data->p, nullptr);
-      ctx->launches += 3;
-      c.offsets = (int32_t*)offs->p; c.values = data->p; c.data_bytes = total;
+      c.offsets = (int32_t*)offs->p; c.values = data->p; c.data_bytes = (int64_t)cap - 16;
       c.owned.push_back(offs); c.owned.push_back(data);
     } else {
       DevAllocPtr vals;
-      const size_t bytes = f.kind == K_BOOL ? (size_t)ceil_div64(std::max<uint32_t>(n, 1), 32) * 4
-                                            : (size_t)std::max<uint32_t>(n, 1) * f.width;
-      BGPU_TRY(dev_alloc(ctx, bytes, &vals));
-      if (n)
-        unpack_fixed_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(key0, key1, kmeta, n, (int)i, f.kind, f.width,
-                                                                  g->key_off[i], vals->p, valid_bits);
-      ctx->launches++;
+      BGPU_TRY(dev_alloc(ctx, f.kind == K_BOOL ? bitmap_bytes : (size_t)n1 * f.width, &vals));
+      kc.values = vals->p;
       c.values = vals->p;
       c.owned.push_back(vals);
       if (f.kind == K_DICT32) BGPU_TRY(upload_canonical_dictionary(g, i, &c.dict));
     }
-    BGPU_CUDA(ctx, cudaGetLastError());
     out->cols.push_back(std::move(c));
   }
-  trace.mark("emit keys");
+  ea.n_key = (int32_t)g->group_cols.size();
   // aggregate columns
-  auto acc_column = [&](int phys_idx, const std::string& name, const std::string& format, bool nullable_by_seen,
-                        Column* c) -> int {
+  int n_acc = 0;
+  auto acc_column = [&](int type, int phys_idx, int count_phys, const LogicalAgg* la, const std::string& name,
+                        const std::string& format, bool nullable_by_seen) -> int {
+    if (n_acc >= kMaxEmitAcc) return ctx->fail(BGPU_EUNSUPPORTED, "too many output columns");
     const PhysAcc& p = g->phys[(size_t)phys_idx];
-    c->name = name; c->format = format; c->flags = ARROW_FLAG_NULLABLE; c->kind = K_FIXED; c->width = p.words * 8;
-    c->length = n; c->null_count = 0;
-    DevAllocPtr vals;  // the accumulator's word(s) of every group record -> a dense Arrow values buffer
-    BGPU_TRY(dev_alloc(ctx, (size_t)std::max<uint32_t>(n, 1) * p.words * 8, &vals));
-    if (n) {
-      extract_acc_kernel<<<grid, kAggThreads, 0, ctx->stream>>>((const uint64_t*)g->acc->p, g->acc_stride, p.out_off, p.words, n,
-                                                                (uint64_t*)vals->p);
-      ctx->launches++;
-      BGPU_CUDA(ctx, cudaGetLastError());
+    Column c;
+    c.name = name; c.format = format; c.flags = ARROW_FLAG_NULLABLE; c.kind = K_FIXED; c.length = n; c.null_count = 0;
+    EmitAccCol& ac = ea.a[n_acc++];
+    ac.type = type; ac.words = p.words; ac.off = p.out_off; ac.seen_bit = phys_idx;
+    c.width = type == 0 ? p.words * 8 : (type == 2 ? 16 : 8);
+    DevAllocPtr vals;
+    BGPU_TRY(dev_alloc(ctx, (size_t)n1 * c.width, &vals));
+    ac.out = (uint64_t*)vals->p;
+    c.values = vals->p;
+    c.owned.push_back(vals);
+    if (type != 0) {
+      ac.count_off = g->phys[(size_t)count_phys].out_off;
+      ac.scale_up = la->scale_up;
     }
-    c->values = vals->p;
-    c->owned.push_back(vals);
-    if (nullable_by_seen) BGPU_TRY(emit_validity(g, phys_idx, n, c));
+    if (type != 0 || (nullable_by_seen && g->seen_tracking)) {
+      DevAllocPtr valid;
+      BGPU_TRY(dev_alloc(ctx, bitmap_bytes, &valid));
+      ac.valid = (uint32_t*)valid->p;
+      c.validity = (uint8_t*)valid->p;
+      c.null_count = -1;
+      c.owned.push_back(valid);
+    }
+    out->cols.push_back(std::move(c));
     return BGPU_OK;
   };
   for (const LogicalAgg& a : g->aggs) {
     if (!g->final_mode && g->mode != BGPU_AGG_MODE_SINGLE) {  // Partial: state columns
       if (a.fn == BGPU_AGG_COUNT) {
-        Column c; BGPU_TRY(acc_column(a.phys[0], a.name + "[count]", "l", false, &c)); out->cols.push_back(std::move(c));
+        BGPU_TRY(acc_column(0, a.phys[0], -1, &a, a.name + "[count]", "l", false));
       } else if (a.fn == BGPU_AGG_SUM) {
-        Column c; BGPU_TRY(acc_column(a.phys[0], a.name + "[sum]", a.sum_format, true, &c)); out->cols.push_back(std::move(c));
+        BGPU_TRY(acc_column(0, a.phys[0], -1, &a, a.name + "[sum]", a.sum_format, true));
       } else {
-        Column c0; BGPU_TRY(acc_column(a.phys[0], a.name + "[count]", "L", false, &c0)); out->cols.push_back(std::move(c0));
-        Column c1; BGPU_TRY(acc_column(a.phys[1], a.name + "[sum]", a.sum_format, true, &c1)); out->cols.push_back(std::move(c1));
+        BGPU_TRY(acc_column(0, a.phys[0], -1, &a, a.name + "[count]", "L", false));
+        BGPU_TRY(acc_column(0, a.phys[1], -1, &a, a.name + "[sum]", a.sum_format, true));
       }
       continue;
     }
-    if (a.fn == BGPU_AGG_COUNT) {
-      Column c; BGPU_TRY(acc_column(a.phys[0], a.name, "l", false, &c)); out->cols.push_back(std::move(c));
-    } else if (a.fn == BGPU_AGG_SUM) {
-      Column c; BGPU_TRY(acc_column(a.phys[0], a.name, a.result_format, true, &c)); out->cols.push_back(std::move(c));
-    } else {  // Avg: evaluate
-      Column c;
-      c.name = a.name; c.format = a.result_format; c.flags = ARROW_FLAG_NULLABLE; c.kind = K_FIXED;
-      c.width = a.decimal ? 16 : 8; c.length = n; c.null_count = -1;
-      DevAllocPtr vals, valid;
-      BGPU_TRY(dev_alloc(ctx, (size_t)std::max<uint32_t>(n, 1) * c.width, &vals));
-      BGPU_TRY(dev_alloc(ctx, (size_t)ceil_div64(std::max<uint32_t>(n, 1), 32) * 4, &valid));
-      if (n) {
-        avg_evaluate_kernel<<<grid, kAggThreads, 0, ctx->stream>>>(
-            (const uint64_t*)g->acc->p, g->acc_stride, g->phys[(size_t)a.phys[1]].out_off, g->phys[(size_t)a.phys[0]].out_off, n,
-            a.decimal ? 1 : 0, a.scale_up, (uint64_t*)vals->p, (uint32_t*)valid->p, g->d_flags());
-        ctx->launches++;
-        BGPU_CUDA(ctx, cudaGetLastError());
-      }
-      c.values = vals->p; c.validity = (uint8_t*)valid->p;
-      c.owned.push_back(vals); c.owned.push_back(valid);
-      out->cols.push_back(std::move(c));
+    if (a.fn == BGPU_AGG_COUNT) BGPU_TRY(acc_column(0, a.phys[0], -1, &a, a.name, "l", false));
+    else if (a.fn == BGPU_AGG_SUM) BGPU_TRY(acc_column(0, a.phys[0], -1, &a, a.name, a.result_format, true));
+    else BGPU_TRY(acc_column(a.decimal ? 2 : 1, a.phys[1], a.phys[0], &a, a.name, a.result_format, false));  // Avg: evaluate
+  }
+  ea.n_acc = n_acc;
+  if (n) {
+    if (single) emit_all_kernel<true><<<1, kEmitThreads, 0, ctx->stream>>>(ea, n);
+    else emit_all_kernel<false><<<agg_launch_grid(ctx, n, kEmitThreads), kEmitThreads, 0, ctx->stream>>>(ea, n);
+    ctx->launches++;
+    BGPU_CUDA(ctx, cudaGetLastError());
+    for (const Utf8Post& up : utf8) {  // lengths -> offsets -> bytes, all on the stream
+      Column& c = out->cols[up.col];
+      BGPU_CUDA(ctx, cudaMemsetAsync(c.offsets, 0, 4, ctx->stream));
+      size_t tmp_bytes = 0;
+      cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, (const int32_t*)up.lens->p, c.offsets + 1, (int)n, ctx->stream);
+      DevAllocPtr tmp;
+      BGPU_TRY(dev_alloc(ctx, tmp_bytes, &tmp));
+      BGPU_CUDA(ctx, cub::DeviceScan::InclusiveSum(tmp->p, tmp_bytes, (const int32_t*)up.lens->p, c.offsets + 1, (int)n, ctx->stream));
+      unpack_utf8_kernel<<<agg_launch_grid(ctx, n, kAggThreads), kAggThreads, 0, ctx->stream>>>(
+          ea.key0, ea.key1, ea.kmeta, n, (int)up.col, g->key_off[up.col], 1, c.offsets, (uint8_t*)c.values, nullptr);
+      ctx->launches += 2;
+      BGPU_CUDA(ctx, cudaGetLastError());
     }
   }
+  trace.mark("emit kernels");
   uint32_t h[8];
-  BGPU_TRY(read_counters(g, h));
+  BGPU_TRY(read_counters(g, h));  // the one host round trip of emit
   if (h[3]) return ctx->fail(BGPU_EOVERFLOW, "Arithmetic overflow in a Decimal128 aggregate argument or AVG");
-  trace.mark("emit accs");
+  // key columns no group has a null in are emitted without a validity bitmap: the state batch of the common null-free
+  // case is then plain fixed-width data, which is what the fused repartition + exchange kernel takes
+  const uint32_t key_null_mask = n ? h[5] : 0;
+  for (size_t i = 0; i < g->group_cols.size(); i++)
+    if (!((key_null_mask >> i) & 1)) {
+      out->cols[i].validity = nullptr;
+      out->cols[i].null_count = 0;
+    }
+  trace.mark("emit readback");
   g->emitted = true;
   *out_batch = out.release();
   return BGPU_OK;

@@ -117,6 +117,7 @@ static int import_column(bgpu_ctx* ctx, const struct ArrowArray* a, const struct
       BGPU_TRY(h2d(ctx, (const uint8_t*)a->buffers[2] + first, (size_t)(last - first), c, &data));
       c->values = (uint8_t*)data - first;
       c->data_bytes = last;
+      c->data_first = first;
     } else if (c->kind == K_BOOL) {
       temps.push_back(realign_bits((const uint8_t*)a->buffers[1], off, n));
       BGPU_TRY(h2d(ctx, temps.back().data(), temps.back().size(), c, &c->values));
@@ -235,6 +236,10 @@ struct ArrayPriv {
   std::vector<DevAllocPtr> keep; // device buffers kept alive (device export)
   std::vector<ArrowArray*> children;
   ArrowArray* dict = nullptr;
+  // fast download: every buffer of the batch lives in one pinned block of the context's pool (top-level array only)
+  bgpu_ctx* pool_ctx = nullptr;
+  void* pool_block = nullptr;
+  size_t pool_bytes = 0;
 };
 void release_array(ArrowArray* a) {
   if (!a || !a->release) return;
@@ -248,6 +253,10 @@ void release_array(ArrowArray* a) {
     delete p->dict;
   }
   for (void* h : p->pinned) cudaFreeHost(h);
+  if (p->pool_ctx) {
+    ctx_pinned_put(p->pool_ctx, p->pool_block, p->pool_bytes);
+    ctx_release(p->pool_ctx);
+  }
   delete p;
   a->release = nullptr;
 }
@@ -333,12 +342,129 @@ void device_column(const Column& c, ArrowArray* a) {
 // schema of a batch as an Arrow C schema (used by the IPC reader for streams without batches)
 void export_batch_schema(const bgpu_batch* b, struct ArrowSchema* out) { batch_schema(b, out); }
 
+// ---- fast download of small batches --------------------------------------------------------------------------------------
+// Results and aggregate states are a few rows by a dozen columns: pinning a host buffer per Arrow buffer and one copy per
+// buffer cost more than the data. Here every buffer of the batch goes into ONE pinned block of the context's pool:
+// a gather kernel packs them into a device staging buffer, one copy brings them over, one synchronise.
+namespace {
+constexpr int kMaxGatherJobs = 96;
+constexpr size_t kFastDownloadBytes = 1u << 20;
+struct GatherJobs {
+  const uint8_t* src[kMaxGatherJobs];
+  uint32_t dst[kMaxGatherJobs], bytes[kMaxGatherJobs];
+};
+__global__ void __launch_bounds__(256) gather_kernel(const __grid_constant__ GatherJobs j, uint8_t* __restrict__ out) {
+  const uint8_t* s = j.src[blockIdx.x];
+  uint8_t* d = out + j.dst[blockIdx.x];
+  for (uint32_t i = threadIdx.x; i < j.bytes[blockIdx.x]; i += 256) d[i] = s[i];
+}
+struct FastPlan {
+  GatherJobs jobs;
+  int n = 0;
+  size_t total = 0;
+  // returns the offset of the buffer inside the block, or -1 when the plan is full
+  int64_t add(const void* src, size_t bytes) {
+    if (n >= kMaxGatherJobs || total + bytes > kFastDownloadBytes) return -1;
+    jobs.src[n] = (const uint8_t*)src;
+    jobs.dst[n] = (uint32_t)total;
+    jobs.bytes[n] = (uint32_t)bytes;
+    n++;
+    const int64_t off = (int64_t)total;
+    total = (total + bytes + 63) & ~(size_t)63;
+    return off;
+  }
+};
+// Plan column c (whole column: rows [0, c.length)); buffer offsets into `offs` in Arrow buffer order (-1 = absent).
+bool plan_column(const Column& c, FastPlan* fp, std::vector<int64_t>* offs) {
+  const int64_t n = c.length;
+  int64_t o = -1;
+  if (c.validity && (o = fp->add(c.validity, (size_t)((n + 7) / 8))) < 0) return false;
+  offs->push_back(c.validity ? o : -1);
+  if (c.kind == K_UTF8 || c.kind == K_BINARY) {
+    if (c.data_bytes < 0 || c.data_first != 0) return false;  // unknown extent (borrowed device buffers): the general path reads the offsets first
+    if ((o = fp->add(c.offsets, (size_t)(n + 1) * 4)) < 0) return false;
+    offs->push_back(o);
+    if ((o = fp->add(c.values, (size_t)c.data_bytes)) < 0) return false;
+    offs->push_back(o);
+  } else {
+    const size_t bytes = c.kind == K_BOOL ? (size_t)((n + 7) / 8) : (size_t)n * c.width;
+    if ((o = fp->add(c.values, bytes)) < 0) return false;
+    offs->push_back(o);
+  }
+  if (c.kind == K_DICT32) return plan_column(*c.dict, fp, offs);
+  return true;
+}
+void build_column(const Column& c, const uint8_t* block, const std::vector<int64_t>& offs, size_t* k, ArrowArray* a) {
+  ArrayPriv* p = fill_array(a, c.length, c.validity ? -1 : 0, 0);
+  const int n_buf = (c.kind == K_UTF8 || c.kind == K_BINARY) ? 3 : 2;
+  for (int i = 0; i < n_buf; i++) {
+    const int64_t o = offs[(*k)++];
+    p->buffers.push_back(o < 0 ? nullptr : block + o);
+  }
+  if (c.kind == K_DICT32) {
+    p->dict = new ArrowArray();
+    build_column(*c.dict, block, offs, k, p->dict);
+  }
+  finish_array(a);
+}
+// *done = false: not eligible (too large, sliced, unknown utf8 extents) - take the general path
+int download_fast(bgpu_ctx* ctx, const bgpu_batch* b, struct ArrowArray* out, bool* done) {
+  *done = false;
+  FastPlan fp;
+  std::vector<int64_t> offs;
+  for (const Column& c : b->cols)
+    if (!plan_column(c, &fp, &offs)) return BGPU_OK;
+  size_t block_bytes = 64 << 10;
+  while (block_bytes < fp.total) block_bytes <<= 1;
+  void* block = nullptr;
+  BGPU_TRY(ctx_pinned_get(ctx, block_bytes, &block));
+  int rc = BGPU_OK;
+  if (fp.n) {
+    DevAllocPtr stage;
+    rc = dev_alloc(ctx, fp.total, &stage);
+    if (rc == BGPU_OK) {
+      gather_kernel<<<fp.n, 256, 0, ctx->stream>>>(fp.jobs, (uint8_t*)stage->p);
+      ctx->launches++;
+      cudaError_t e = cudaGetLastError();
+      if (e == cudaSuccess) e = cudaMemcpyAsync(block, stage->p, fp.total, cudaMemcpyDeviceToHost, ctx->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+      if (e != cudaSuccess) rc = ctx->fail(BGPU_ECUDA, std::string("download: ") + cudaGetErrorString(e));
+    }
+  }
+  if (rc != BGPU_OK) {
+    ctx_pinned_put(ctx, block, block_bytes);
+    return rc;
+  }
+  ArrayPriv* p = fill_array(out, b->n_rows, 0, 0);
+  p->buffers.push_back(nullptr);
+  p->pool_ctx = ctx; p->pool_block = block; p->pool_bytes = block_bytes;
+  ctx_retain(ctx);
+  size_t k = 0;
+  for (const Column& c : b->cols) {
+    ArrowArray* ca = new ArrowArray();
+    build_column(c, (const uint8_t*)block, offs, &k, ca);
+    p->children.push_back(ca);
+  }
+  finish_array(out);
+  *done = true;
+  return BGPU_OK;
+}
+}  // namespace
+
 extern "C" int bgpu_batch_download(bgpu_ctx* ctx, const bgpu_batch* b, int64_t row_offset, int64_t num_rows,
                                    struct ArrowArray* out, struct ArrowSchema* out_schema) try {
   if (!ctx || !b || !out || !out_schema) return BGPU_EINVAL;
   if (row_offset < 0 || num_rows < 0 || row_offset + num_rows > b->n_rows)
     return ctx->fail(BGPU_EINVAL, "row range out of bounds");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (row_offset == 0 && num_rows == b->n_rows && !getenv("BGPU_NO_FAST_DOWNLOAD")) {
+    bool done = false;
+    BGPU_TRY(download_fast(ctx, b, out, &done));
+    if (done) {
+      batch_schema(b, out_schema);
+      return BGPU_OK;
+    }
+  }
   ArrayPriv* p = fill_array(out, num_rows, 0, row_offset & 7);
   p->buffers.push_back(nullptr);
   int rc = BGPU_OK;

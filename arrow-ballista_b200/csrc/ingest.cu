@@ -467,6 +467,16 @@ int ingest_drain(bgpu_agg* g) {
   return BGPU_OK;
 }
 
+void ingest_reset(bgpu_agg* g) {
+  Ingest* in = (Ingest*)g->ingest.get();
+  if (!in) return;
+  std::lock_guard<std::mutex> lk(in->mu);
+  in->sticky_error = BGPU_OK;
+  in->sticky_msg.clear();
+  for (DeviceSet& s : in->sets) s.pending = false;
+  in->st_rows = in->st_batches = in->st_wire_bytes = in->st_raw_bytes = in->st_chunks = in->st_replays = in->st_async = 0;
+}
+
 struct SegPlan {  // what pass 1 found for one column of one segment
   bgpu_pack::FixedStats fs{0, 0};
   size_t bytes = 0, bytes2 = 0, valid_bytes = 0;  // wire bytes: packed values / lengths, string bytes, validity bits
@@ -645,6 +655,7 @@ extern "C" int bgpu_agg_push_host(bgpu_agg* g, const struct ArrowArray* batch, c
     if (!g->ingest) {
       BGPU_TRY(ingest_create(g));
       g->ingest_drain = ingest_drain;
+      g->ingest_reset = ingest_reset;
     }
   }
   Ingest* in = (Ingest*)g->ingest.get();

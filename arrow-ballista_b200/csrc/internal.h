@@ -117,7 +117,9 @@ struct Column {
   uint8_t* validity = nullptr; // nullptr = all valid
   int64_t length = 0;
   int64_t null_count = 0;      // -1 = unknown
-  int64_t data_bytes = 0;      // utf8/binary: bytes addressable behind `values`
+  int64_t data_bytes = 0;      // utf8/binary: upper bound of the offsets, i.e. bytes addressable behind `values`; -1 = unknown
+  int64_t data_first = 0;      // utf8/binary: first byte behind `values` that is really allocated (uploads of sliced arrays
+                               // keep their offsets and point `values` before the copied range)
   std::shared_ptr<Column> dict;  // K_DICT32: dictionary values column
   std::vector<DevAllocPtr> owned;  // keeps buffers alive (shared with other batches when passed through)
 };

@@ -692,9 +692,15 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
   for (auto& up : utf8) {  // lengths -> offsets, then copy the bytes
     const Column& c = in->cols[up.col];
     Column& o = out->cols[up.col];
+    // the partitioned column holds exactly the bytes the input rows reference: when the input knows an upper bound of
+    // that (data_bytes) the output is sized by it and nothing is read back; borrowed device buffers of unknown extent
+    // cost one round trip for their first and last offset
     int32_t first_last[2] = {0, 0};
-    BGPU_CUDA(ctx, cudaMemcpyAsync(&first_last[0], c.offsets, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    BGPU_CUDA(ctx, cudaMemcpyAsync(&first_last[1], c.offsets + n_rows, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    const bool bounded = c.data_bytes >= 0;
+    if (!bounded) {
+      BGPU_CUDA(ctx, cudaMemcpyAsync(&first_last[0], c.offsets, 4, cudaMemcpyDeviceToHost, ctx->stream));
+      BGPU_CUDA(ctx, cudaMemcpyAsync(&first_last[1], c.offsets + n_rows, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    }
     BGPU_CUDA(ctx, cudaMemsetAsync(o.offsets, 0, 4, ctx->stream));
     size_t tmp_bytes = 0;
     cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, (const int32_t*)up.len->p, o.offsets + 1, n_rows, ctx->stream);
@@ -702,8 +708,8 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
     BGPU_TRY(dev_alloc(ctx, tmp_bytes, &tmp));
     BGPU_CUDA(ctx, cub::DeviceScan::InclusiveSum(tmp->p, tmp_bytes, (const int32_t*)up.len->p, o.offsets + 1, n_rows,
                                                  ctx->stream));
-    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    const int64_t data_bytes = (int64_t)first_last[1] - first_last[0];
+    if (!bounded) BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int64_t data_bytes = bounded ? c.data_bytes : (int64_t)first_last[1] - first_last[0];
     DevAllocPtr data;
     BGPU_TRY(dev_alloc(ctx, (size_t)data_bytes, &data));
     o.owned.push_back(data); o.values = data->p; o.data_bytes = data_bytes;

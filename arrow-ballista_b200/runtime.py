@@ -150,6 +150,34 @@ class DeviceBatch:
         self.ctx.check(lib().bgpu_batch_download(self.ctx._h, self._h, offset, length, C.byref(a), C.byref(s)))
         return pa.RecordBatch._import_from_c(C.addressof(a), C.addressof(s))
 
+    def column_tensor(self, i):
+        """A torch int64 tensor [rows, width / 8] holding a COPY of fixed-width column i's values (width 8 or 16), made
+        on the ctx stream. Plumbing for the bench's and the tests' device-side verification, not part of the reference's
+        interface."""
+        import torch
+        from cuda.bindings import runtime as cudart
+
+        a, s = ArrowArray(), ArrowSchema()
+        self.ctx.check(lib().bgpu_batch_export_device(self.ctx._h, self._h, C.byref(a), C.byref(s)))
+        try:
+            fmt = s.children[i].contents.format.decode()
+            width = 16 if fmt.startswith("d:") else 8
+            if not (fmt.startswith("d:") or fmt in ("l", "L", "g")):
+                raise TypeError(f"column_tensor: 8- or 16-byte columns only, got {fmt}")
+            child = a.children[i].contents
+            n = int(child.length)
+            out = torch.empty((n, width // 8), dtype=torch.int64, device=torch.device("cuda", torch.cuda.current_device()))
+            if n:
+                err, = cudart.cudaMemcpyAsync(out.data_ptr(), child.buffers[1], n * width,
+                                              cudart.cudaMemcpyKind.cudaMemcpyDeviceToDevice, self.ctx.stream or 0)
+                if int(err) != 0:
+                    raise RuntimeError(f"cudaMemcpyAsync: {err}")
+                self.ctx.synchronize()
+            return out
+        finally:
+            _release(a)
+            _release(s)
+
     @classmethod
     def concat(cls, ctx, batches):
         """Rows of `batches` (one schema) in order as one DeviceBatch (bgpu_batch_concat; `concat_batches` of

@@ -200,6 +200,11 @@ int bgpu_debug_pack_fixed_host(const char* format, const void* values, int64_t n
 /* end of input: state() (Partial) or evaluate() (Final modes and Single). Group order is unspecified, as in the
  * reference (GroupValues uses a randomly seeded table). The aggregate may not be updated afterwards. */
 int bgpu_agg_emit(bgpu_agg* agg, bgpu_batch** out);
+/* A new input stream over the same plan: the reference creates its AggregateExec once per task and `execute`s it per
+ * partition (/root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:234-257). Clears the groups and the
+ * accumulators; the plan, its compiled kernels, the kernel path and capacities the last stream settled on and the staging
+ * buffers of bgpu_agg_push_host stay. Allowed before or after bgpu_agg_emit. */
+int bgpu_agg_reset(bgpu_agg* agg);
 int64_t bgpu_agg_num_groups(bgpu_agg* agg); /* groups seen so far */
 /* which kernel path the last update took ("fused_private", "fused_shared2", "fused_shared1", "shared", "global", "intern");
  * introspection for tests and the bench, not part of the reference's interface */
