@@ -88,6 +88,7 @@ SIGNATURES = {
     "bgpu_debug_pack_fixed_host": (C.c_int, [C.c_char_p, C.c_void_p, C.c_int64, C.c_int32, C.POINTER(C.c_int64),
                                              C.POINTER(C.c_uint32), C.c_void_p]),
     "bgpu_agg_emit": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "bgpu_jit_stats": (None, [C.POINTER(C.c_uint64)]),
     "bgpu_agg_reset": (C.c_int, [C.c_void_p]),
     "bgpu_agg_num_groups": (C.c_int64, [C.c_void_p]),
     "bgpu_agg_destroy": (None, [C.c_void_p]),
@@ -98,6 +99,8 @@ SIGNATURES = {
                                         C.POINTER(C.c_uint32)]),
     "bgpu_all_to_all": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_uint64),
                                   C.c_uint32, C.POINTER(C.c_void_p)]),
+    "bgpu_small_exchange": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_int32), C.c_int32,
+                                      C.c_uint32, C.POINTER(C.c_void_p)]),
     "bgpu_peer_exchange_create": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_uint64, C.POINTER(C.c_void_p)]),
     "bgpu_partition_exchange": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_uint32,
                                           C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),

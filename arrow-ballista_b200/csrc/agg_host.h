@@ -74,6 +74,14 @@ struct bgpu_agg {
   cudaEvent_t ev[2] = {nullptr, nullptr};
   double hot_kernel_ms = 0.0;
 
+  // Pass-through mode of a Partial aggregate (aggregate_run.cu): when the first batch's distinct-key estimate says the
+  // pass would barely reduce (most rows are their own group), input rows are emitted as state rows - key, sum = the
+  // argument, count = 1 - and the FinalPartitioned side does the only aggregation, after the exchange. What DataFusion
+  // later added as skip_partial_aggregation; results are identical (a Partial aggregate never promised full reduction).
+  bool passthrough = false;
+  bool any_committed = false;  // some batch of this stream has been aggregated into the table
+  std::vector<std::unique_ptr<bgpu_batch>> pass_chunks;
+
   // streamed host input (ingest.cu): staging ring, device buffers, launches the host has not looked at yet
   std::shared_ptr<void> ingest;
   int (*ingest_drain)(bgpu_agg*) = nullptr;  // seal + submit + poll everything pending (set by ingest.cu)

@@ -378,6 +378,9 @@ __global__ void __launch_bounds__(kAggThreads) or_kmeta_kernel(const uint32_t* _
   if ((threadIdx.x & 31) == 0 && v) atomicOr(out, v);
 }
 
+__global__ void __launch_bounds__(kAggThreads) fill_u64_kernel(uint64_t* p, int64_t n, uint64_t v) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
 __global__ void __launch_bounds__(kAggThreads) fill_u32_kernel(uint32_t* p, uint32_t n, uint32_t v) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = v;
 }

@@ -343,12 +343,19 @@ extern "C" int bgpu_agg_reset(bgpu_agg* g) try {
   BGPU_CUDA(ctx, cudaMemsetAsync(g->acc->p, 0, (size_t)g->max_groups * g->acc_stride * 8, ctx->stream));
   if (g->seen_tracking) BGPU_CUDA(ctx, cudaMemsetAsync(g->seen->p, 0, (size_t)g->max_groups * 4, ctx->stream));
   g->n_groups = 0;
+  g->passthrough = false;
+  g->any_committed = false;
+  g->pass_chunks.clear();
   g->emitted = false;
   g->hot_kernel_ms = 0.0;
   for (auto& d : g->dicts) d = bgpu_agg::DictState();
   return BGPU_OK;
 } catch (const std::exception& e) {
   return bgpu::abi_guard(g ? g->ctx : nullptr, e);  // nothing is thrown across the C ABI
+}
+
+extern "C" void bgpu_jit_stats(uint64_t* out4) {
+  if (out4) bgpu::jit_stats(out4);
 }
 
 extern "C" void bgpu_agg_destroy(bgpu_agg* g) {

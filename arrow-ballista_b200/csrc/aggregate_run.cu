@@ -655,6 +655,7 @@ static int try_fused(bgpu_agg* g, Bound* b, int64_t n_rows, bool* done, AggAsync
       ctx->launches++;
       BGPU_CUDA(ctx, cudaGetLastError());
       g->last_path = rg.name;
+      g->any_committed = true;
       g->async_ready = true;  // this rung has just committed a batch: the next one may run without a host round trip
       *done = true;
       return BGPU_OK;
@@ -681,7 +682,103 @@ struct PhaseTrace {
   }
 };
 
-static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
+// ---- pass-through (skip a Partial aggregation that does not reduce) ---------------------------------------------------------
+// Eligible: Partial mode, no filter, non-null fixed-width group columns, every aggregate argument a plain non-null column
+// whose bits ARE its state (Decimal128 -> Decimal128 sum, Int64 -> Int64 sum, Float64 -> Float64 sum) or COUNT.
+static bool passthrough_eligible(const bgpu_agg* g, const bgpu_batch* batch) {
+  if (g->mode != BGPU_AGG_MODE_PARTIAL || !g->filter.empty() || getenv("BGPU_NO_PASSTHROUGH")) return false;
+  for (int32_t c : g->group_cols) {
+    const Column& col = batch->cols[(size_t)c];
+    if (col.kind != K_FIXED || col.validity) return false;
+  }
+  for (const PhysAcc& p : g->phys) {
+    const HValue& v = g->values[(size_t)p.value];
+    if (p.op == OP_COUNT) {
+      if (v.f.empty()) continue;  // COUNT(*)
+      if (!v.plain_column() || batch->cols[(size_t)v.f[0].x.col].validity) return false;
+      continue;
+    }
+    if (!v.plain_column()) return false;
+    const Column& col = batch->cols[(size_t)v.f[0].x.col];
+    if (col.validity || col.kind != K_FIXED) return false;
+    const int32_t vk = v.f[0].x.vk;
+    const bool same_bits = (p.op == OP_ADD_I128 && vk == V_I128) || (p.op == OP_ADD_I64 && (vk == V_I64 || vk == V_U64)) ||
+                           (p.op == OP_ADD_F64 && vk == V_F64);
+    if (!same_bits) return false;
+  }
+  return true;
+}
+
+// a column of the chunk that holds the values of input column `src`: shared when the batch owns its buffers, copied
+// when they are borrowed (they are only promised for the call)
+static int pass_column(bgpu_ctx* ctx, const Column& src, int64_t n, Column* out) {
+  out->kind = K_FIXED; out->width = src.width; out->length = n; out->null_count = 0; out->flags = ARROW_FLAG_NULLABLE;
+  if (!src.owned.empty()) {
+    out->values = src.values;
+    out->owned = src.owned;
+    return BGPU_OK;
+  }
+  DevAllocPtr a;
+  BGPU_TRY(dev_alloc(ctx, (size_t)n * src.width, &a));
+  if (n) BGPU_CUDA(ctx, cudaMemcpyAsync(a->p, src.values, (size_t)n * src.width, cudaMemcpyDeviceToDevice, ctx->stream));
+  out->values = a->p;
+  out->owned.push_back(a);
+  return BGPU_OK;
+}
+
+static int passthrough_update(bgpu_agg* g, const bgpu_batch* batch) {
+  bgpu_ctx* ctx = g->ctx;
+  const int64_t n = batch->n_rows;
+  std::unique_ptr<bgpu_batch> out(new bgpu_batch(ctx));
+  out->n_rows = n;
+  for (int32_t c : g->group_cols) {
+    const Column& f = g->fields[(size_t)c];
+    Column col;
+    BGPU_TRY(pass_column(ctx, batch->cols[(size_t)c], n, &col));
+    col.name = f.name; col.format = f.format; col.flags = f.flags | ARROW_FLAG_NULLABLE;
+    out->cols.push_back(std::move(col));
+  }
+  DevAllocPtr ones;  // one buffer of 1s behind every count column
+  auto count_column = [&](const std::string& name, const char* format) -> int {
+    if (!ones) {
+      BGPU_TRY(dev_alloc(ctx, (size_t)std::max<int64_t>(n, 1) * 8, &ones));
+      if (n) {
+        fill_u64_kernel<<<agg_launch_grid(ctx, n, kAggThreads), kAggThreads, 0, ctx->stream>>>((uint64_t*)ones->p, n, 1ULL);
+        ctx->launches++;
+        BGPU_CUDA(ctx, cudaGetLastError());
+      }
+    }
+    Column col;
+    col.name = name; col.format = format; col.flags = ARROW_FLAG_NULLABLE; col.kind = K_FIXED; col.width = 8;
+    col.length = n; col.null_count = 0; col.values = ones->p;
+    col.owned.push_back(ones);
+    out->cols.push_back(std::move(col));
+    return BGPU_OK;
+  };
+  auto sum_column = [&](int phys_idx, const std::string& name, const std::string& format) -> int {
+    const HValue& v = g->values[(size_t)g->phys[(size_t)phys_idx].value];
+    Column col;
+    BGPU_TRY(pass_column(ctx, batch->cols[(size_t)v.f[0].x.col], n, &col));
+    col.name = name; col.format = format;
+    out->cols.push_back(std::move(col));
+    return BGPU_OK;
+  };
+  for (const LogicalAgg& a : g->aggs) {
+    if (a.fn == BGPU_AGG_COUNT) {
+      BGPU_TRY(count_column(a.name + "[count]", "l"));
+    } else if (a.fn == BGPU_AGG_SUM) {
+      BGPU_TRY(sum_column(a.phys[0], a.name + "[sum]", a.sum_format));
+    } else {
+      BGPU_TRY(count_column(a.name + "[count]", "L"));
+      BGPU_TRY(sum_column(a.phys[1], a.name + "[sum]", a.sum_format));
+    }
+  }
+  g->pass_chunks.push_back(std::move(out));
+  g->last_path = "passthrough";
+  return BGPU_OK;
+}
+
+static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows, const bgpu_batch* batch) {
   bgpu_ctx* ctx = g->ctx;
   PhaseTrace trace(ctx);
   int T = 256, R = 8, min_ctas = 2;  // 8 rows per lane in flight: the probes are DRAM round trips (R = 4: 7.1 ms intern, R = 8: 5.8 ms per 1e8 rows)
@@ -716,6 +813,14 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
     const double m = (double)words * 32.0, set = (double)*pin;
     // linear counting: distinct ~ -m ln(zero fraction); a saturated bitmap means "at least as many as rows"
     const double est = set >= m ? (double)n_rows : std::min<double>((double)n_rows, -m * log(1.0 - set / m));
+    // a first batch that is mostly distinct keys: the Partial pass would be all cost and no reduction
+    double ratio = 0.6;
+    if (const char* e = getenv("BGPU_PASSTHROUGH_RATIO")) ratio = atof(e);
+    if (!g->any_committed && g->pass_chunks.empty() && n_rows >= (1 << 20) && est > ratio * (double)n_rows &&
+        passthrough_eligible(g, batch)) {
+      g->passthrough = true;
+      return passthrough_update(g, batch);
+    }
     const uint64_t need = (uint64_t)g->n_groups + (uint64_t)(est * 1.10) + 1024;
     if (need > g->max_groups) {
       if (need > 0x70000000ULL) return ctx->fail(BGPU_EUNSUPPORTED, "too many groups");
@@ -742,6 +847,7 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows) {
     BGPU_TRY(grow_after_overflow(g, h[0], n_rows));
   }
   trace.mark("intern");
+  g->any_committed = true;
   refresh_pointers(g, b);
   if (b->ap.n == 0) { g->last_path = "intern"; return BGPU_OK; }
   const uint32_t ng = g->n_groups;
@@ -787,6 +893,10 @@ int agg_update_impl(bgpu_agg* g, const bgpu_batch* batch, AggAsyncReq* req) {
   Bound b;
   BGPU_TRY(bind_batch(g, batch, &b));
   if (n_rows == 0) return BGPU_OK;
+  if (g->passthrough) {
+    if (passthrough_eligible(g, batch)) return passthrough_update(g, batch);
+    return ctx->fail(BGPU_EUNSUPPORTED, "a batch with nulls follows batches the Partial aggregate passed through");
+  }
   if (b.sh.any_validity && !g->seen_tracking) {
     // first batch with nulls in an aggregate input: groups created by earlier (null-free) batches have seen
     // every accumulator; groups new in this batch start at 0
@@ -806,7 +916,7 @@ int agg_update_impl(bgpu_agg* g, const bgpu_batch* batch, AggAsyncReq* req) {
   trace.mark(done ? "fused" : "fused (void)");
   if (!done) {
     g->async_ready = false;
-    BGPU_TRY(run_two_pass(g, &b, n_rows));
+    BGPU_TRY(run_two_pass(g, &b, n_rows, batch));
   }
   return BGPU_OK;
 }
@@ -826,6 +936,7 @@ int agg_async_result(bgpu_agg* g, AggAsyncReq* req, bool* replay) {
   BGPU_TRY(check_common_flags(g, c));
   if (h[0]) {
     g->n_groups = h[1];
+    g->any_committed = true;
     return BGPU_OK;
   }
   *replay = true;
@@ -871,6 +982,18 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) try {
   if (g->emitted) return ctx->fail(BGPU_EINVAL, "aggregate already emitted");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
   if (g->ingest_drain) BGPU_TRY(g->ingest_drain(g));  // end of input: everything pushed so far is aggregated first
+  if (g->passthrough) {  // the state rows are the chunks themselves
+    if (g->pass_chunks.size() == 1) {
+      *out_batch = g->pass_chunks[0].release();
+    } else {
+      std::vector<const bgpu_batch*> parts;
+      for (auto& c : g->pass_chunks) parts.push_back(c.get());
+      BGPU_TRY(bgpu_batch_concat(ctx, parts.data(), (int32_t)parts.size(), out_batch));
+    }
+    g->pass_chunks.clear();
+    g->emitted = true;
+    return BGPU_OK;
+  }
   const uint32_t n = g->n_groups, n1 = std::max<uint32_t>(n, 1);
   std::unique_ptr<bgpu_batch> out(new bgpu_batch(ctx));
   out->n_rows = n;

@@ -433,6 +433,18 @@ struct PlacedBuffer {
   uint64_t arena_off = 0, bytes = 0;
 };
 
+// offsets[0] >= 0, offsets non-decreasing, offsets[rows] <= bytes of the data buffer; *bad != 0 otherwise
+__global__ void __launch_bounds__(256) check_offsets_kernel(const int32_t* __restrict__ offs, int64_t rows, int64_t data_bytes,
+                                                            unsigned int* __restrict__ bad) {
+  bool wrong = false;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= rows; i += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t o = offs[i];
+    if (o < 0 || (int64_t)o > data_bytes) wrong = true;
+    if (i < rows && offs[i + 1] < o) wrong = true;
+  }
+  if (wrong) atomicOr(bad, 1u);
+}
+
 static int reader_next_impl(bgpu_ipc_reader* r, bgpu_batch** out) {
   if (!r || !out) return BGPU_EINVAL;
   *out = nullptr;
@@ -592,6 +604,33 @@ static int reader_next_impl(bgpu_ipc_reader* r, bgpu_batch** out) {
     if (!ok) {
       delete b;
       return ctx->fail(BGPU_EINVAL, "IPC reader: buffers of column " + proto[i].name + " are shorter than its length");
+    }
+  }
+  // The CONTENTS of utf8 / binary offset buffers come from another process: every kernel downstream indexes the data
+  // buffer with them, so they are checked here as arrow-rs's reader does (first offset >= 0, non-decreasing, last offset
+  // within the data buffer) before the batch is handed out.
+  {
+    DevAllocPtr d_bad;
+    for (const Column& c : b->cols) {
+      if ((c.kind != K_UTF8 && c.kind != K_BINARY) || rows == 0) continue;
+      if (!d_bad) {
+        int rc = dev_alloc(ctx, 4, &d_bad);
+        if (rc != BGPU_OK) { delete b; return rc; }
+        cudaMemsetAsync(d_bad->p, 0, 4, ctx->stream);
+      }
+      check_offsets_kernel<<<(int)std::min<int64_t>(ceil_div64(rows + 1, 256), (int64_t)ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+          c.offsets, rows, c.data_bytes, (unsigned int*)d_bad->p);
+      ctx->launches++;
+    }
+    if (d_bad) {
+      unsigned int bad = 0;
+      cudaError_t e = cudaMemcpyAsync(&bad, d_bad->p, 4, cudaMemcpyDeviceToHost, ctx->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+      if (e != cudaSuccess || bad) {
+        delete b;
+        if (e != cudaSuccess) return ctx->fail(BGPU_ECUDA, std::string("IPC reader: ") + cudaGetErrorString(e));
+        return ctx->fail(BGPU_EINVAL, "IPC reader: offsets of a utf8/binary column are negative, decreasing or beyond its data buffer");
+      }
     }
   }
   r->batches++;

@@ -2,8 +2,16 @@
 #include "jit.h"
 
 #include <dlfcn.h>
+#include <errno.h>
 #include <nvrtc.h>
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
+#include <atomic>
 #include <map>
 #include <mutex>
 
@@ -21,6 +29,7 @@ struct Api {
   nvrtcResult (*GetProgramLogSize)(nvrtcProgram, size_t*) = nullptr;
   nvrtcResult (*GetProgramLog)(nvrtcProgram, char*) = nullptr;
   nvrtcResult (*DestroyProgram)(nvrtcProgram*) = nullptr;
+  nvrtcResult (*Version)(int*, int*) = nullptr;
   // driver
   CUresult (*ModuleLoadData)(CUmodule*, const void*) = nullptr;
   CUresult (*ModuleGetFunction)(CUfunction*, CUmodule, const char*) = nullptr;
@@ -78,8 +87,74 @@ std::string cu_err(const Api& a, CUresult r) {
 
 std::mutex g_mu;
 std::map<std::pair<int, std::string>, JitModule*> g_cache;  // (device, source) -> module; never freed
+std::atomic<uint64_t> g_stats[4];  // NVRTC compiles, cubins loaded from the disk cache, in-memory module hits, cubins stored
+
+// ---- on-disk cache of compiled cubins -----------------------------------------------------------------------------------
+// NVRTC takes ~2 s per plan: an executor that sees a query once must not pay that in every process. Files live under
+// $BGPU_CACHE_DIR (default: $XDG_CACHE_HOME/bgpu, ~/.cache/bgpu, /tmp/bgpu-cache-<uid>; BGPU_CACHE_DIR=off disables),
+// named by a 128-bit hash of (format tag incl. arch and NVRTC version, source); the file repeats tag and source in full
+// and a load compares them byte for byte, so a hash collision or a stale file can only cost a recompile.
+uint64_t fnv1a(const std::string& s, uint64_t h) {
+  for (unsigned char c : s) { h ^= c; h *= 1099511628211ULL; }
+  return h;
+}
+std::string disk_cache_dir() {
+  const char* e = getenv("BGPU_CACHE_DIR");
+  if (e && (!strcmp(e, "off") || !*e)) return "";
+  std::string d;
+  if (e) d = e;
+  else if (const char* x = getenv("XDG_CACHE_HOME")) d = std::string(x) + "/bgpu";
+  else if (const char* h = getenv("HOME")) d = std::string(h) + "/.cache/bgpu";
+  else d = "/tmp/bgpu-cache-" + std::to_string((unsigned)getuid());
+  for (size_t i = 1; i <= d.size(); i++)  // mkdir -p
+    if (i == d.size() || d[i] == '/') {
+      const std::string part = d.substr(0, i);
+      if (mkdir(part.c_str(), 0700) != 0 && errno != EEXIST) return "";
+    }
+  return d;
+}
+std::string disk_cache_path(const std::string& tag, const std::string& source) {
+  static const std::string dir = disk_cache_dir();
+  if (dir.empty()) return "";
+  char name[64];
+  snprintf(name, sizeof name, "/%016llx%016llx.cubin", (unsigned long long)fnv1a(source, fnv1a(tag, 14695981039346656037ULL)),
+           (unsigned long long)fnv1a(source, fnv1a(tag, 0x9e3779b97f4a7c15ULL)));
+  return dir + name;
+}
+bool disk_cache_load(const std::string& path, const std::string& tag, const std::string& source, std::string* cubin) {
+  if (path.empty()) return false;
+  FILE* f = fopen(path.c_str(), "rb");
+  if (!f) return false;
+  bool ok = false;
+  uint64_t lens[3];
+  if (fread(lens, 8, 3, f) == 3 && lens[0] == tag.size() && lens[1] == source.size() && lens[2] > 0 && lens[2] < (1ULL << 30)) {
+    std::string t(lens[0], '\0'), s(lens[1], '\0');
+    cubin->assign(lens[2], '\0');
+    ok = fread(&t[0], 1, t.size(), f) == t.size() && fread(&s[0], 1, s.size(), f) == s.size() &&
+         fread(&(*cubin)[0], 1, cubin->size(), f) == cubin->size() && t == tag && s == source;
+  }
+  fclose(f);
+  return ok;
+}
+bool disk_cache_store(const std::string& path, const std::string& tag, const std::string& source, const std::string& cubin) {
+  if (path.empty()) return false;
+  const std::string tmp = path + ".tmp" + std::to_string((long)getpid()) + "_" + std::to_string((unsigned long)pthread_self());
+  FILE* f = fopen(tmp.c_str(), "wb");
+  if (!f) return false;
+  const uint64_t lens[3] = {tag.size(), source.size(), cubin.size()};
+  bool ok = fwrite(lens, 8, 3, f) == 3 && fwrite(tag.data(), 1, tag.size(), f) == tag.size() &&
+            fwrite(source.data(), 1, source.size(), f) == source.size() && fwrite(cubin.data(), 1, cubin.size(), f) == cubin.size();
+  ok = fclose(f) == 0 && ok;
+  if (ok) ok = rename(tmp.c_str(), path.c_str()) == 0;  // atomic: readers see the whole file or none
+  if (!ok) remove(tmp.c_str());
+  return ok;
+}
 
 }  // namespace
+
+void jit_stats(uint64_t* out4) {
+  for (int i = 0; i < 4; i++) out4[i] = g_stats[i].load();
+}
 
 // Host-side compile only (no driver needed): used by the CPU test-suite to check that every plan shape the tests
 // use generates source NVRTC accepts.
@@ -99,10 +174,19 @@ int jit_compile_cubin(bgpu_ctx* ctx, const std::string& source, std::string* cub
     *(void**)&rtc_only.GetProgramLogSize = sym("nvrtcGetProgramLogSize");
     *(void**)&rtc_only.GetProgramLog = sym("nvrtcGetProgramLog");
     *(void**)&rtc_only.DestroyProgram = sym("nvrtcDestroyProgram");
+    *(void**)&rtc_only.Version = sym("nvrtcVersion");
     rtc_only.ok = ok;
   });
   const Api& a = rtc_only;
   if (!a.ok) return ctx->fail(BGPU_ECUDA, "NVRTC unavailable: " + a.why);
+  int vmaj = 0, vmin = 0;
+  a.Version(&vmaj, &vmin);
+  const std::string tag = "bgpu-cubin-1 sm_100a nvrtc " + std::to_string(vmaj) + "." + std::to_string(vmin);
+  const std::string path = disk_cache_path(tag, source);
+  if (disk_cache_load(path, tag, source, cubin)) {
+    g_stats[1]++;
+    return BGPU_OK;
+  }
   nvrtcProgram prog;
   if (a.CreateProgram(&prog, source.c_str(), "bgpu_agg.cu", 0, nullptr, nullptr) != NVRTC_SUCCESS)
     return ctx->fail(BGPU_ECUDA, "nvrtcCreateProgram failed");
@@ -122,6 +206,8 @@ int jit_compile_cubin(bgpu_ctx* ctx, const std::string& source, std::string* cub
   cubin->assign(n, '\0');
   a.GetCUBIN(prog, &(*cubin)[0]);
   a.DestroyProgram(&prog);
+  g_stats[0]++;
+  if (disk_cache_store(path, tag, source, *cubin)) g_stats[3]++;
   return BGPU_OK;
 }
 
@@ -132,7 +218,7 @@ int jit_compile(bgpu_ctx* ctx, const char* prelude, const std::string& source, c
   std::lock_guard<std::mutex> lk(g_mu);
   auto key = std::make_pair(ctx->device, source);
   auto it = g_cache.find(key);
-  if (it != g_cache.end()) { *out = it->second; return BGPU_OK; }
+  if (it != g_cache.end()) { g_stats[2]++; *out = it->second; return BGPU_OK; }
   std::string cubin;
   BGPU_TRY(jit_compile_cubin(ctx, std::string(prelude) + source, &cubin));
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));

@@ -24,7 +24,9 @@ struct JitModule {
 // returned pointer stays valid for the life of the process.
 int jit_compile(bgpu_ctx* ctx, const char* prelude, const std::string& source, const std::vector<std::string>& names,
                 const JitModule** out);
-// NVRTC only (no driver, no device): source -> sm_100a cubin
+// {NVRTC compiles, cubins loaded from the on-disk cache, in-memory module hits, cubins stored on disk} of this process
+void jit_stats(uint64_t* out4);
+// NVRTC only (no driver, no device): source -> sm_100a cubin (through the on-disk cache, see jit.cu)
 int jit_compile_cubin(bgpu_ctx* ctx, const std::string& source, std::string* cubin);
 
 // cuLaunchKernel on ctx->stream with a single by-value argument struct.

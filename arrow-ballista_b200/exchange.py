@@ -53,6 +53,7 @@ class Exchange:
             dist.broadcast_object_list(ident, src=0)
         self._comm = C.c_void_p()
         ctx.check(lib().bgpu_nccl_comm_create(ctx._h, ident[0], self.rank, self.world, C.byref(self._comm)))
+        self.last_path, self.last_sent_bytes = "", None
 
     def all_to_all(self, partitioned, offsets, n_partitions):
         """partitioned / offsets: the result of BatchPartitioner.partition_device with the same n on every rank.
@@ -62,6 +63,31 @@ class Exchange:
         self.ctx.check(lib().bgpu_all_to_all(self.ctx._h, self._comm, self.rank, self.world, partitioned._h, offs,
                                              n_partitions, C.byref(out)))
         return DeviceBatch(self.ctx, out)
+
+    def small_exchange(self, batch, key_cols, n_partitions):
+        """bgpu_small_exchange: the exchange of a batch of a few rows as ONE ncclAllGather. COLLECTIVE. Returns the
+        received DeviceBatch, or None when some rank's batch does not fit the small path (every rank gets None together
+        and takes `partition_exchange` / `all_to_all`)."""
+        from ._lib import BGPU_EUNSUPPORTED
+
+        keys = (C.c_int32 * len(key_cols))(*key_cols)
+        out = C.c_void_p()
+        rc = lib().bgpu_small_exchange(self.ctx._h, self._comm, self.rank, self.world, batch._h, keys, len(keys),
+                                       n_partitions, C.byref(out))
+        if rc == BGPU_EUNSUPPORTED:
+            return None
+        self.ctx.check(rc)
+        self.last_path = "small_allgather"
+        return DeviceBatch(self.ctx, out)
+
+    def exchange_state(self, batch, key_cols, n_partitions, window_bytes=64 << 20):
+        """Hash repartition + exchange of an aggregate state, cheapest path first: one all-gather for a few rows, the fused
+        scatter into peer windows for null-free fixed-width states, hash partition + NCCL all-to-all otherwise. COLLECTIVE
+        (the ranks take the same path: each step's refusal is decided from data every rank has)."""
+        got = self.small_exchange(batch, key_cols, n_partitions)
+        if got is not None:
+            return got
+        return self.partition_exchange(batch, key_cols, n_partitions, window_bytes=window_bytes)
 
     def partition_exchange(self, batch, key_cols, n_partitions, window_bytes=64 << 20):
         """Fused hash repartition + exchange (bgpu_partition_exchange): == all_to_all(*partition_device(batch)), with the

@@ -227,9 +227,12 @@ class HotPath:
 
     def shuffle_and_final(self, state):
         bb = self.bb
-        part, offsets = self.partitioner.partition_device(state)
-        if self.world > 1:
-            part = self.comm.all_to_all(part, offsets, N_PARTITIONS)
+        keys = list(range(len(self.group_by)))
+        if self.world > 1:  # repartition + exchange: one all-gather for a state of a few rows, NVLink scatter / NCCL otherwise
+            part = self.comm.exchange_state(state, keys, N_PARTITIONS)
+            self.exchange_path = self.comm.last_path
+        else:
+            part, _ = self.partitioner.partition_device(state)
         # the partitions this rank owns hold disjoint keys: one merged FinalPartitioned table gives the union of the
         # per-partition results
         fin = self.final_op
@@ -499,6 +502,7 @@ def run_ours(args):
         "config": {"workload": "TPC-H Q1 Partial agg (fused filter+decimal exprs) + hash repartition n=16 + FinalPartitioned, "
                                f"lineitem {n} rows/GPU (SF100 = {SF100_ROWS})", "rows_per_gpu": n, "partitions": N_PARTITIONS,
                    "l2": "input (>= 46 GB at SF100) is larger than L2; no flush needed", "agg_path": hp.last_path,
+                   "exchange_path": getattr(hp, "exchange_path", "local"),
                    "result_rows": result_rows, "launches_per_step": launches_per_step,
                    "tail_ms": ms_per_step - kernel_ms},
         "verified": all(verified.values()), "verified_legs": verified,

@@ -213,6 +213,11 @@ const char* bgpu_agg_last_path(const bgpu_agg* agg);
  * the per-launch duration bench.py's roofline line is computed from */
 double bgpu_agg_hot_kernel_ms(const bgpu_agg* agg);
 void bgpu_agg_destroy(bgpu_agg* agg);
+/* Run-time compiled kernels are cached twice: per process (modules) and on disk (cubins, under $BGPU_CACHE_DIR, default
+ * ~/.cache/bgpu; "off" disables; keyed by source + sm_100a + NVRTC version, verified byte for byte on load), so that only
+ * the first process that ever sees a plan pays NVRTC's ~2 s. out4 = {NVRTC compiles, cubins loaded from disk, in-memory
+ * hits, cubins stored} of this process. */
+void bgpu_jit_stats(uint64_t* out4);
 /* Introspection, no device needed: generate the run-time specialised kernels of this plan (arguments as
  * bgpu_agg_create_expr) for a synthetic batch shape and compile them for sm_100a with NVRTC. flags bit 0: every column
  * carries validity; bit 1: dictionary keys need a remap; bit 2: per-accumulator seen masks are tracked.
@@ -231,6 +236,16 @@ int bgpu_agg_debug_compile(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema
  * every rank. out_received holds this rank's partitions from all ranks, grouped by (partition, source rank). */
 int bgpu_all_to_all(bgpu_ctx* ctx, void* nccl_comm, int32_t rank, int32_t world, const bgpu_batch* partitioned,
                     const uint64_t* offsets, uint32_t n_partitions, bgpu_batch** out_received);
+/* The exchange of a SMALL batch (an aggregate state of a few rows: TPC-H Q1 has four) as one fixed-size collective:
+ * every rank packs its batch into a 32 KB slot, ONE ncclAllGather hands every rank every slot, one kernel keeps the rows
+ * of the partitions this rank owns (create_hashes(keys) % n_partitions, owner = partition % world) - the rows
+ * bgpu_all_to_all(bgpu_hash_partition(batch)) delivers, ordered by (source rank, source row). Two kernels, one
+ * collective and one host round trip, whatever the number of ranks. COLLECTIVE: every rank calls it at the same point;
+ * when any rank's batch does not fit (more than 256 rows or 32 KB) EVERY rank gets BGPU_EUNSUPPORTED (the slots carry
+ * the flag) and takes bgpu_hash_partition + bgpu_all_to_all / bgpu_partition_exchange. Dictionary columns:
+ * BGPU_EUNSUPPORTED before any collective (schema-level, the same on every rank). world == 1 needs no communicator. */
+int bgpu_small_exchange(bgpu_ctx* ctx, void* nccl_comm, int32_t rank, int32_t world, const bgpu_batch* batch,
+                        const int32_t* key_cols, int32_t n_keys, uint32_t n_partitions, bgpu_batch** out_received);
 /* NCCL plumbing for harnesses that have no ncclComm_t of their own (libnccl.so.2 is dlopen'ed; the copy the process
  * already loaded is reused): rank 0 makes a 128-byte ncclUniqueId, the harness broadcasts it by its own means (the
  * Python mirror uses torch.distributed), every rank creates its communicator on the ctx's device. */

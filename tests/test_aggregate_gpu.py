@@ -208,3 +208,41 @@ def test_shared_rung_warp_private_copies(bb, ctx, oracle, domain, nulls, zipf):
     # (700 groups of this many accumulators no longer fit two CTAs per SM: the one-CTA shared rung takes them)
     assert gp.last_path == ("fused_shared2" if domain <= 128 else "fused_shared1"), gp.last_path
     run_both(bb, ctx, oracle, batches, ["id4"], aggs, n_partials=1)
+
+
+def test_partial_that_does_not_reduce_passes_rows_through(bb, ctx, oracle):
+    """A first batch of mostly distinct keys: the Partial aggregate emits its input rows as state rows (key, sum = the
+    argument, count = 1; what DataFusion later called skip_partial_aggregation) and the FinalPartitioned side does the
+    only aggregation. The final result equals the oracle's Partial -> Final, bit for bit; with BGPU_NO_PASSTHROUGH the
+    same input takes the two-pass path and gives the same result."""
+    import decimal
+    import os
+
+    rng = np.random.default_rng(31)
+    n = (1 << 20) + 77
+    b = pa.RecordBatch.from_arrays(
+        [pa.array(rng.integers(0, 3_000_000, n), type=pa.int64()),
+         pa.array([decimal.Decimal(int(x)).scaleb(-2) for x in rng.integers(100, 5000, n)], type=pa.decimal128(15, 2)),
+         pa.array(rng.integers(-10**6, 10**6, n), type=pa.int64()), pa.array(rng.random(n))],
+        names=["k", "d", "v", "f"])
+    aggs = [("sum", "d", "sd"), ("avg", "d", "ad"), ("sum", "v", "sv"), ("count", "v", "cv"), ("avg", "f", "af"), ("count", None, "n")]
+    gi, spec = [0], [(f, (None if c is None else b.schema.names.index(c)), nm) for f, c, nm in aggs]
+    op = oracle.GroupedAggregate("partial", gi, spec)
+    op.update(b)
+    of = oracle.GroupedAggregate("final", [0], spec, arg_types=[b.schema.field(c).type if c is not None else None for _, c, _ in spec])
+    of.update(op.emit())
+    want = of.emit()
+    for skip in (False, True):
+        if skip:
+            os.environ["BGPU_NO_PASSTHROUGH"] = "1"
+        try:
+            gp = bb.GpuAggregateExec(ctx, bb.AggregateMode.Partial, gi, spec, b.schema)
+            gp.update(bb.DeviceBatch.upload(ctx, b))
+            assert gp.last_path == ("global" if skip else "passthrough")
+            state = gp.emit()
+            assert (state.num_rows == n) == (not skip)
+            gf = bb.GpuAggregateExec(ctx, bb.AggregateMode.FinalPartitioned, gi, spec, b.schema)
+            gf.update(state)
+            assert_same_groups(gf.emit().download(), want, 1)
+        finally:
+            os.environ.pop("BGPU_NO_PASSTHROUGH", None)

@@ -55,6 +55,49 @@ def run_rank(bb, oracle, ctx, rank, world):
     ex.close()
 
 
+def make_small_input(rank, n):
+    """An aggregate-state-like batch of a few rows: utf8 + Int64 keys (nulls on some ranks only), Decimal128 / Int64 / Float64
+    payloads, a bool."""
+    import decimal
+
+    rng = np.random.default_rng(100 + rank)
+    flags = ["A", "N", "R", "", "OF"]
+    mask = rng.random(n) < 0.2 if rank % 2 else None
+    return pa.RecordBatch.from_arrays(
+        [pa.array([flags[i] for i in rng.integers(0, len(flags), n)], type=pa.string(), mask=mask),
+         pa.array(rng.integers(0, 9, n), type=pa.int64()),
+         pa.array([decimal.Decimal(int(x)).scaleb(-2) for x in rng.integers(-10**15, 10**15, n)], type=pa.decimal128(25, 2)),
+         pa.array(rng.integers(0, 10**9, n), type=pa.int64(), mask=rng.random(n) < 0.3),
+         pa.array(rng.random(n)), pa.array(rng.random(n) < 0.5)],
+        names=["rf", "k", "sum", "cnt", "f", "b"])
+
+
+def run_small_rank(bb, oracle, ctx, rank, world):
+    """bgpu_small_exchange == the rows all_to_all(hash_partition(batch)) delivers (as a multiset: the order is by source)."""
+    ex = bb.Exchange(ctx, rank, world)
+    for n_parts, rows in ((16, 5), (6, 200), (7, 0)):
+        inputs = [make_small_input(s, rows if s != 1 else max(0, rows - 3)) for s in range(world)]
+        got = ex.small_exchange(bb.DeviceBatch.upload(ctx, inputs[rank]), [0, 1], n_parts)
+        assert got is not None and ex.last_path == "small_allgather"
+        chunks = []
+        for s in range(world):
+            parts, _ = oracle.partition(inputs[s], [0, 1], n_parts)
+            chunks += [b for p, b in parts if p % world == rank]
+        want = pa.Table.from_batches(chunks, schema=inputs[0].schema) if chunks else inputs[0].schema.empty_table()
+        gt = pa.Table.from_batches([got.download()])
+        assert gt.num_rows == want.num_rows, (rank, n_parts, rows)
+        keys = [(nm, "ascending") for nm in ("k", "sum", "f")]
+        assert gt.sort_by(keys).equals(want.combine_chunks().sort_by(keys)), f"rank {rank}: small exchange differs ({n_parts}, {rows})"
+    # a batch beyond the small path on ONE rank: every rank is told to take the general path
+    big = make_small_input(rank, 300 if rank == world - 1 else 4)
+    assert ex.small_exchange(bb.DeviceBatch.upload(ctx, big), [0, 1], 16) is None
+    ex.close()
+
+
+def test_small_exchange_single_rank(bb, oracle, ctx):
+    run_small_rank(bb, oracle, ctx, 0, 1)
+
+
 def test_all_to_all_single_rank(bb, oracle, ctx):
     run_rank(bb, oracle, ctx, 0, 1)
 
@@ -75,6 +118,7 @@ def _worker(rank, world, port):
     try:
         ctx = bb.Context(rank)
         run_rank(bb, O, ctx, rank, world)
+        run_small_rank(bb, O, ctx, rank, world)
         ctx.close()
     finally:
         dist.destroy_process_group()

@@ -102,6 +102,29 @@ def test_stream_reader_rejects_a_corrupt_lz4_block(bb, ctx):
         assert not got.equals(batch)
 
 
+@pytest.mark.parametrize("damage", ["decreasing", "negative", "beyond_data"])
+def test_stream_reader_rejects_corrupt_utf8_offsets(bb, ctx, damage):
+    """A shuffle file from another executor whose utf8 offsets are not what Arrow promises (arrow-rs's reader validates
+    them): every kernel downstream would index the data buffer with them, so the reader refuses the batch."""
+    from ballista_b200 import ipc
+
+    strings = [f"s{i:05d}" for i in range(3000)]
+    batch = pa.RecordBatch.from_arrays([pa.array(np.arange(3000, dtype=np.int64)), pa.array(strings)], names=["a", "s"])
+    data = bytearray(_stream(batch.schema, [batch], None))
+    offs = np.arange(3001, dtype=np.int32) * 6  # every string is 6 bytes: find the offsets buffer in the body
+    at = bytes(data).find(offs.tobytes())
+    assert at > 0
+    word = {"decreasing": (at + 4 * 1500, 10), "negative": (at, -8), "beyond_data": (at + 4 * 3000, 6 * 3000 + 4096)}[damage]
+    data[word[0]: word[0] + 4] = np.int32(word[1]).tobytes()
+    r = ipc.StreamReader(ctx, bytes(data))
+    with pytest.raises(bb.BgpuError) as e:
+        r.maybe_next()
+    assert e.value.code == 1 and "offsets" in str(e.value)  # BGPU_EINVAL
+    # the undamaged stream still reads
+    ok = ipc.StreamReader(ctx, _stream(batch.schema, [batch], None)).maybe_next().download()
+    assert ok.equals(batch)
+
+
 @pytest.mark.parametrize("sizes", [[5], [3, 5], [8, 0, 9, 1], [1000, 1, 63, 64, 65], [40_000, 70_001, 13]])
 def test_concat_matches_arrow(bb, ctx, sizes):
     rng = np.random.default_rng(sum(sizes))
