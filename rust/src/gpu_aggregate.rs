@@ -67,6 +67,14 @@ pub fn lower(e: &Arc<dyn PhysicalExpr>, out: &mut Vec<BgpuExprNode>) -> Option<(
 }
 
 impl GpuAggregateExec {
+    #[allow(clippy::too_many_arguments)]
+    pub fn new(mode: AggregateMode, group_cols: Vec<usize>, aggr_expr: Vec<Arc<dyn AggregateExpr>>,
+               filter: Option<Arc<dyn PhysicalExpr>>, input: Arc<dyn ExecutionPlan>, input_schema: SchemaRef, schema: SchemaRef,
+               device: i32) -> Self {
+        GpuAggregateExec { mode, group_cols, aggr_expr, filter, input, input_schema, schema, device,
+                           metrics: ExecutionPlanMetricsSet::new() }
+    }
+
     /// bgpu_agg_create_expr for this plan on `ctx` (one aggregate per executed partition: a stream of the plan).
     fn create(&self, ctx: &Ctx) -> Result<Agg> {
         let schema = FFI_ArrowSchema::try_from(self.input_schema.as_ref())?;
