@@ -40,6 +40,9 @@ def parse_args():
     ap.add_argument("--cpu-rows", type=int, default=int(os.environ.get("BENCH_CPU_ROWS", 60_000_000)),
                     help="bounded sample for the CPU baseline")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-configs", action="store_true", help="skip BASELINE configs 2, 3 (N = 1) and 5 (N > 1)")
+    ap.add_argument("--cfg3-rows", type=int, default=int(os.environ.get("BENCH_CFG3_ROWS", 1_000_000_000)))
+    ap.add_argument("--cfg5-rows", type=int, default=int(os.environ.get("BENCH_CFG5_ROWS", 1_000_000_000)))
     ap.add_argument("--no-orderkey", action="store_true", help="skip the GROUP BY l_orderkey (exchange-bound) leg")
     ap.add_argument("--orderkey-rows", type=int, default=int(os.environ.get("BENCH_ORDERKEY_ROWS", SF100_ROWS)),
                     help="total rows of the GROUP BY l_orderkey leg (sharded over the ranks)")
@@ -493,7 +496,23 @@ def run_ours(args):
     upload_s = time.perf_counter() - t0
     pool.shutdown()
 
+    # ---- the other BASELINE configurations (bench_configs.py), once the lineitem shard is gone ---------------------------
     peak, peak_src = load_peaks()
+    other = {}
+    if not args.no_configs:
+        import bench_configs as BC
+
+        del batch, big, hbatches, exported, refs
+        cols.clear()
+        torch.cuda.empty_cache()
+        if world == 1:
+            other["cfg2"], verified["cfg2"] = BC.run_cfg2(bb, ctx, torch, dev, stream, peak)
+            torch.cuda.empty_cache()
+            other["cfg3"], verified["cfg3"] = BC.run_cfg3(bb, ctx, torch, dev, stream, peak, rows=args.cfg3_rows)
+        else:
+            other["cfg5"], verified["cfg5"] = BC.run_cfg5(bb, ctx, comm, torch, dist, dev, stream, rank, world, total=args.cfg5_rows)
+        torch.cuda.empty_cache()
+
     achieved = n * Q1_BYTES_PER_ROW / (kernel_ms * 1e-3) / 1e9
     line = {
         "metric": "input rows/s & HBM GB/s (% roofline), TPC-H Q1 agg+shuffle", "value": value, "unit": "rows/s",
@@ -506,7 +525,7 @@ def run_ours(args):
                    "result_rows": result_rows, "launches_per_step": launches_per_step,
                    "tail_ms": ms_per_step - kernel_ms},
         "verified": all(verified.values()), "verified_legs": verified,
-        "strong": strong, "orderkey": orderkey,
+        "strong": strong, "orderkey": orderkey, "configs": other,
         "clocks": clocks.summary(),
         "e2e": {"value": ne * world / e2e_s, "unit": "rows/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "rows_per_gpu": ne, "batch_rows": args.e2e_batch_rows, "feeder_threads": n_feed,
