@@ -59,7 +59,7 @@ def load_peaks():
 def load_traffic(rows):
     """dram__bytes_read + dram__bytes_write of one bgpu_fused launch from the committed ncu capture (profiles/), or None
     when this run's row count is not the one that was captured."""
-    p = os.path.join(ROOT, "profiles", "r1_fused_traffic.json")
+    p = os.path.join(ROOT, "profiles", "r2_fused_traffic.json")
     if not os.path.exists(p):
         return None
     t = json.load(open(p))

@@ -18,9 +18,17 @@ for k, ms in rows:
     tot[k] += ms
     cnt[k] += 1
 total = sum(tot.values())
-ours = sum(v for k, v in tot.items() if k.startswith("bgpu") or "bgpu::" in k)
+OURS = ("bgpu", "widen_kernel", "gather_kernel", "small_pack_kernel", "small_unpack_kernel", "check_offsets_kernel",
+        "partition_offsets_noalloc_kernel", "concat_kernel", "ipc_", "lz4_")
+
+
+def is_ours(k):
+    return any(t in k for t in OURS)
+
+
+ours = sum(v for k, v in tot.items() if is_ours(k))
 print(f"{len(rows)} launches, {total:.2f} ms in all kernels, {ours:.2f} ms in this library's kernels\n")
 print("| kernel | launches | total ms | share of all | share of ours |\n|---|---:|---:|---:|---:|")
 for k, v in sorted(tot.items(), key=lambda kv: -kv[1])[:28]:
-    mine = k.startswith("bgpu") or "bgpu::" in k
+    mine = is_ours(k)
     print(f"| `{k[:100]}` | {cnt[k]} | {v:.3f} | {100 * v / total:.1f}% | {f'{100 * v / ours:.1f}%' if mine and ours else ''} |")
