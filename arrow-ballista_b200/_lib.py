@@ -61,6 +61,7 @@ SIGNATURES = {
                                       C.POINTER(ArrowSchema)]),
     "bgpu_batch_export_device": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(ArrowArray), C.POINTER(ArrowSchema)]),
     "bgpu_batch_num_rows": (C.c_int64, [C.c_void_p]),
+    "bgpu_batch_memory_size": (C.c_int64, [C.c_void_p]),
     "bgpu_batch_num_columns": (C.c_int32, [C.c_void_p]),
     "bgpu_batch_destroy": (None, [C.c_void_p]),
     "bgpu_create_hashes": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_void_p]),

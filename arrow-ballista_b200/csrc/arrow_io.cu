@@ -171,6 +171,20 @@ extern "C" int bgpu_batch_wrap_device(bgpu_ctx* ctx, const struct ArrowArray* a,
 }
 extern "C" int64_t bgpu_batch_num_rows(const bgpu_batch* b) { return b ? b->n_rows : -1; }
 extern "C" int32_t bgpu_batch_num_columns(const bgpu_batch* b) { return b ? (int32_t)b->cols.size() : -1; }
+static int64_t column_memory_size(const Column& c, int64_t n) {
+  int64_t b = c.validity ? (n + 7) / 8 : 0;
+  if (c.kind == K_UTF8 || c.kind == K_BINARY) b += (n + 1) * 4 + (c.data_bytes > 0 ? c.data_bytes - c.data_first : 0);
+  else if (c.kind == K_BOOL) b += (n + 7) / 8;
+  else b += n * c.width;
+  if (c.kind == K_DICT32 && c.dict) b += column_memory_size(*c.dict, c.dict->length);
+  return b;
+}
+extern "C" int64_t bgpu_batch_memory_size(const bgpu_batch* b) {
+  if (!b) return -1;
+  int64_t total = 0;
+  for (const Column& c : b->cols) total += column_memory_size(c, b->n_rows);
+  return total;
+}
 extern "C" void bgpu_batch_destroy(bgpu_batch* b) {
   if (!b) return;
   if (b->ctx) cudaSetDevice(b->ctx->device);

@@ -152,7 +152,22 @@ extern "C" int bgpu_all_to_all(bgpu_ctx* ctx, void* comm, int32_t rank, int32_t 
     bgpu_exchange_plan(rows.data(), rank, world, P, recv_row.data(), nullptr);
   }
   const int64_t n_out = (int64_t)recv_row.back();
-  if (n_out > 0x7fffffffLL) return ctx->fail(BGPU_EUNSUPPORTED, "received batch too large");
+  // Limits are checked for EVERY rank from the gathered header, so that all ranks take the same branch: a rank that
+  // returned alone would leave its peers blocked in their receives.
+  for (int r = 0; r < world; r++) {
+    uint64_t rows_r = 0;
+    std::vector<uint64_t> bytes_r(var_cols.size(), 0);
+    for (uint32_t p = (uint32_t)r; p < P; p += (uint32_t)world)
+      for (int s = 0; s < world; s++) {
+        rows_r += row_off(s, p + 1) - row_off(s, p);
+        for (size_t v = 0; v < var_cols.size(); v++) bytes_r[v] += byte_off(s, v, p + 1) - byte_off(s, v, p);
+      }
+    if (rows_r > 0x7fffffffULL)
+      return ctx->fail(BGPU_EUNSUPPORTED, "received batch of rank " + std::to_string(r) + " too large");
+    for (uint64_t b : bytes_r)
+      if (b > 0x7fffffffULL)
+        return ctx->fail(BGPU_EUNSUPPORTED, "received utf8 column of rank " + std::to_string(r) + " exceeds 2 GiB (i32 offsets)");
+  }
   std::unique_ptr<bgpu_batch> ob(new bgpu_batch(ctx));
   ob->n_rows = n_out;
   struct Xfer { const char* src; char* dst; size_t elem; int var; };  // var >= 0: byte ranges of utf8 column var
@@ -160,6 +175,9 @@ extern "C" int bgpu_all_to_all(bgpu_ctx* ctx, void* comm, int32_t rank, int32_t 
   std::vector<DevAllocPtr> keep;
   struct Post { size_t col; DevAllocPtr vbytes, lens; };
   std::vector<Post> posts;
+  // Everything below that can fail on ONE rank (allocations, launches) runs inside `prepare`; its outcome is exchanged
+  // (one word per rank) before anybody posts a send or a receive, so that a failing rank takes its peers out with it.
+  auto prepare = [&]() -> int {
   for (size_t c = 0; c < n_cols; c++) {
     const Column& ic = in->cols[c];
     Column oc;
@@ -202,7 +220,6 @@ extern "C" int bgpu_all_to_all(bgpu_ctx* ctx, void* comm, int32_t rank, int32_t 
       uint64_t total_bytes = 0;
       for (uint32_t p : owned)
         for (int s = 0; s < world; s++) total_bytes += byte_off(s, v, p + 1) - byte_off(s, v, p);
-      if (total_bytes > 0x7fffffffULL) return ctx->fail(BGPU_EUNSUPPORTED, "received utf8 column exceeds 2 GiB (i32 offsets)");
       BGPU_TRY(dev_alloc(ctx, (size_t)total_bytes, &data));
       BGPU_TRY(dev_alloc(ctx, (size_t)(n_out + 1) * 4, &offs));
       xfers.push_back(Xfer{(const char*)lens_src->p, (char*)lens_dst->p, 4, -1});
@@ -215,7 +232,28 @@ extern "C" int bgpu_all_to_all(bgpu_ctx* ctx, void* comm, int32_t rank, int32_t 
     posts.push_back(post);
     ob->cols.push_back(std::move(oc));
   }
+  return BGPU_OK;
+  };
+  const int local_rc = prepare();
+  {
+    DevAllocPtr d_err;
+    uint32_t* pin = (uint32_t*)ctx->pinned + 128;  // [0] mine, [1 .. world] everybody's
+    pin[0] = (uint32_t)local_rc;
+    // d_all (the gathered header, already read) is reused as the device side of this one-word-per-rank collective
+    cudaError_t e = cudaMemcpyAsync(d_hdr->p, pin, 4, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return ctx->fail(BGPU_ECUDA, cudaGetErrorString(e));
+    BGPU_NCCL(ctx, nc.AllGather(d_hdr->p, d_all->p, 4, kNcclUint8, comm, st));
+    BGPU_CUDA(ctx, cudaMemcpyAsync(pin + 1, d_all->p, 4 * (size_t)world, cudaMemcpyDeviceToHost, st));
+    BGPU_CUDA(ctx, cudaStreamSynchronize(st));
+    if (local_rc != BGPU_OK) return local_rc;
+    for (int r = 0; r < world; r++)
+      if (pin[1 + r] != BGPU_OK)
+        return ctx->fail(BGPU_ENCCL, "exchange abandoned: rank " + std::to_string(r) + " failed to prepare its buffers (code " +
+                                         std::to_string(pin[1 + r]) + ")");
+  }
   // ---- 3. the exchange: one grouped send/recv per (buffer, peer, partition) --------------------------------------------
+  // (an error inside the group still closes it: an open group would poison every later NCCL call of this thread)
+  int nccl_rc = 0;
   BGPU_NCCL(ctx, nc.GroupStart());
   for (const Xfer& x : xfers) {
     // sends: my partition p goes to rank p % world
@@ -227,7 +265,7 @@ extern "C" int bgpu_all_to_all(bgpu_ctx* ctx, void* comm, int32_t rank, int32_t 
       } else {
         lo = row_off(rank, p) * x.elem; hi = row_off(rank, p + 1) * x.elem;
       }
-      if (hi > lo) BGPU_NCCL(ctx, nc.Send(x.src + lo, (size_t)(hi - lo), kNcclUint8, peer, comm, st));
+      if (hi > lo && !nccl_rc) nccl_rc = nc.Send(x.src + lo, (size_t)(hi - lo), kNcclUint8, peer, comm, st);
     }
     // receives, in the received batch's order (partition, source)
     uint64_t at = 0;
@@ -235,11 +273,15 @@ extern "C" int bgpu_all_to_all(bgpu_ctx* ctx, void* comm, int32_t rank, int32_t 
       for (int s = 0; s < world; s++) {
         const uint64_t n = x.var >= 0 ? byte_off(s, (size_t)x.var, p + 1) - byte_off(s, (size_t)x.var, p)
                                       : (row_off(s, p + 1) - row_off(s, p)) * x.elem;
-        if (n) BGPU_NCCL(ctx, nc.Recv(x.dst + at, (size_t)n, kNcclUint8, s, comm, st));
+        if (n && !nccl_rc) nccl_rc = nc.Recv(x.dst + at, (size_t)n, kNcclUint8, s, comm, st);
         at += n;
       }
   }
-  BGPU_NCCL(ctx, nc.GroupEnd());
+  {
+    const int end_rc = nc.GroupEnd();
+    if (nccl_rc) return ctx->fail(BGPU_ENCCL, std::string("ncclSend/ncclRecv: ") + nc.GetErrorString(nccl_rc));
+    if (end_rc) return ctx->fail(BGPU_ENCCL, std::string("ncclGroupEnd: ") + nc.GetErrorString(end_rc));
+  }
   // ---- 4. re-pack validity, rebuild utf8 offsets --------------------------------------------------------------------------
   for (const Post& post : posts) {
     Column& oc = ob->cols[post.col];

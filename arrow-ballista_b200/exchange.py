@@ -77,7 +77,7 @@ class Exchange:
         if rc == BGPU_EUNSUPPORTED:
             return None
         self.ctx.check(rc)
-        self.last_path = "small_allgather"
+        self.last_path, self.last_sent_bytes = "small_allgather", 0
         return DeviceBatch(self.ctx, out)
 
     def exchange_state(self, batch, key_cols, n_partitions, window_bytes=64 << 20):

@@ -166,7 +166,15 @@ class GpuQueryStageExec(QueryStageExecutor):
         partitions = self.partitions if self.partitions is not None else list(input_partitions or [])
         states = list(self._states(ctx, partitions))
         if not states:
-            return []
+            if self.shuffle_writer.shuffle_output_partitioning is not None:
+                return []  # hash arm: writers open lazily, no batch = no file (shuffle_writer.rs:351-362)
+            # un-partitioned output: the reference still writes an (empty) data.arrow and returns one zero-row entry
+            # (utils.rs:179-219): an aggregate that saw no input emits the zero-row batch that carries the schema
+            agg = self.aggregate.instantiate(ctx)
+            try:
+                states = [agg.emit()]
+            finally:
+                agg.close()
         self._schema = states[0].schema
         w = self.shuffle_writer
         mode = w.ipc

@@ -134,6 +134,11 @@ class DeviceBatch:
         return int(lib().bgpu_batch_num_rows(self._h))
 
     @property
+    def memory_size(self):
+        """Bytes of the batch's Arrow buffers in device memory (the reference's `get_array_memory_size` of a batch)."""
+        return int(lib().bgpu_batch_memory_size(self._h))
+
+    @property
     def num_columns(self):
         return int(lib().bgpu_batch_num_columns(self._h))
 

@@ -192,7 +192,14 @@ class GpuShuffleWriterExec:
             path = os.path.join(path, "data.arrow")
             w = None
             t0 = time.perf_counter()
+            # write_stream_to_disk (utils.rs:179-219): zero-row batches are skipped, and num_bytes is the sum of the
+            # batches' in-memory sizes (get_array_memory_size), not the file length (that is the hash arm's rule)
+            mem_bytes = 0
             for batch in self._stream():
+                if batch.num_rows == 0:
+                    if self._schema is None:
+                        self._schema = batch.schema
+                    continue
                 if isinstance(batch, DeviceBatch):
                     # a stage whose output is already on the device (a Final aggregate): framed by libbgpu like the hash
                     # arm's partitions, as one "partition" holding every row; dictionary columns go through the host writer
@@ -202,17 +209,19 @@ class GpuShuffleWriterExec:
                     else:
                         if w is None:
                             w = _IpcStreamFile(path, ipc.schema_message(schema, self.ctx))
-                        if batch.num_rows:
-                            enc = ipc.encode_partitions(self.ctx, batch, [0, batch.num_rows], self.compression)
-                            w.write_message(enc.message(0), batch.num_rows)
-                            enc.close()
+                        mem_bytes += batch.memory_size
+                        enc = ipc.encode_partitions(self.ctx, batch, [0, batch.num_rows], self.compression)
+                        w.write_message(enc.message(0), batch.num_rows)
+                        enc.close()
                         continue
                 if w is None:
                     w = _WriteTracker(path, batch.schema)
+                mem_bytes += batch.get_total_buffer_size()
                 w.write(batch)
             if w is None:
                 w = _WriteTracker(path, self._schema)
-            num_bytes = w.finish()
+            w.finish()
+            num_bytes = mem_bytes
             m.write_time += time.perf_counter() - t0
             m.input_rows += w.num_rows
             m.output_rows += w.num_rows

@@ -183,7 +183,9 @@ def run_cfg5(bb, ctx, comm, torch, dist, dev, stream, rank, world, total=1_000_0
                 best = t.tolist()
         # exact checks over all ranks: number of groups, and the first aggregate's counts / sums add up to the input's
         keycol = cols[gb[0]]
-        domain = int(keycol.max()) + 1
+        dmax = keycol.max().reshape(1).clone()
+        dist.all_reduce(dmax, op=dist.ReduceOp.MAX)  # the same tensor size on every rank
+        domain = int(dmax.item()) + 1
         present = torch.zeros(domain, dtype=torch.int64, device=dev)
         present[keycol] = 1
         dist.all_reduce(present, op=dist.ReduceOp.MAX)

@@ -67,6 +67,9 @@ int bgpu_batch_export_device(bgpu_ctx* ctx, const bgpu_batch* batch, struct Arro
                              struct ArrowSchema* out_schema);
 int64_t bgpu_batch_num_rows(const bgpu_batch* batch);
 int32_t bgpu_batch_num_columns(const bgpu_batch* batch);
+/* bytes of the batch's Arrow buffers (validity, offsets, values; utf8 data by its known bound): what write_stream_to_disk
+ * adds up as num_bytes (`batch.get_array_memory_size()`, /root/reference/ballista/core/src/utils.rs:203-207) */
+int64_t bgpu_batch_memory_size(const bgpu_batch* batch);
 void bgpu_batch_destroy(bgpu_batch* batch);
 
 /* ---- create_hashes ---------------------------------------------------------------------------------------
