@@ -95,6 +95,30 @@ extern "C" int bgpu_batch_concat(bgpu_ctx* ctx, const bgpu_batch* const* batches
   if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
   for (int32_t k = 0; k < n; k++)
     if (!batches[k]) return ctx->fail(BGPU_EINVAL, "null batch");
+  {  // dictionary columns: every input has its own dictionary, so the VALUES are concatenated and re-encoded (dictionary.cu)
+    bool any_dict = false;
+    for (int32_t k = 0; k < n; k++) any_dict |= batch_has_dictionary(batches[k]);
+    if (any_dict) {
+      std::vector<std::unique_ptr<bgpu_batch>> decoded((size_t)n);
+      std::vector<const bgpu_batch*> ptrs;
+      std::vector<size_t> dict_cols;
+      for (int32_t k = 0; k < n; k++) {
+        std::vector<size_t> dc;
+        if (batches[k]->cols.size() != batches[0]->cols.size()) return ctx->fail(BGPU_EINVAL, "concat: batches differ in column count");
+        BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+        BGPU_TRY(dict_decode_batch(ctx, batches[k], &decoded[(size_t)k], &dc));
+        if (k == 0) dict_cols = dc;
+        else if (dc != dict_cols) return ctx->fail(BGPU_EINVAL, "concat: batches differ in their dictionary columns");
+        ptrs.push_back(decoded[(size_t)k].get());
+      }
+      bgpu_batch* joined = nullptr;
+      BGPU_TRY(bgpu_batch_concat(ctx, ptrs.data(), n, &joined));
+      std::unique_ptr<bgpu_batch> res(joined);
+      for (size_t i : dict_cols) BGPU_TRY(dict_identity_encode(ctx, res.get(), i, batches[0]->cols[i], nullptr, 0));
+      *out = res.release();
+      return BGPU_OK;
+    }
+  }
   const std::vector<Column>& proto = batches[0]->cols;
   const size_t n_cols = proto.size();
   int64_t total_rows = 0;

@@ -110,6 +110,19 @@ extern "C" int bgpu_all_to_all(bgpu_ctx* ctx, void* comm, int32_t rank, int32_t 
   const Nccl& nc = nccl();
   if (!nc.ok) return ctx->fail(BGPU_ENCCL, "NCCL unavailable: " + nc.why);
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (bgpu::batch_has_dictionary(in)) {
+    // dictionary columns (schema-level: the same decision on every rank): the values travel, the received rows are
+    // re-encoded against a dictionary of their own (dictionary.cu)
+    std::unique_ptr<bgpu_batch> decoded;
+    std::vector<size_t> dict_cols;
+    BGPU_TRY(bgpu::dict_decode_batch(ctx, in, &decoded, &dict_cols));
+    bgpu_batch* got = nullptr;
+    BGPU_TRY(bgpu_all_to_all(ctx, comm, rank, world, decoded.get(), offsets, n_partitions, &got));
+    std::unique_ptr<bgpu_batch> res(got);
+    for (size_t i : dict_cols) BGPU_TRY(bgpu::dict_identity_encode(ctx, res.get(), i, in->cols[i], nullptr, 0));
+    *out = res.release();
+    return BGPU_OK;
+  }
   cudaStream_t st = ctx->stream;
   const size_t n_cols = in->cols.size();
   const uint32_t P = n_partitions, P1 = n_partitions + 1;

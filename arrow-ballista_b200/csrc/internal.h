@@ -121,6 +121,7 @@ struct Column {
   int64_t data_first = 0;      // utf8/binary: first byte behind `values` that is really allocated (uploads of sliced arrays
                                // keep their offsets and point `values` before the copied range)
   std::shared_ptr<Column> dict;  // K_DICT32: dictionary values column
+  int64_t dict_id = -1;          // K_DICT32 read from / written to an IPC stream: the dictionary's id in that stream
   std::vector<DevAllocPtr> owned;  // keeps buffers alive (shared with other batches when passed through)
 };
 
@@ -149,5 +150,13 @@ struct KCol {
   int32_t kind;
   int32_t width;
 };
+
+// dictionary.cu: dictionary columns on the move (decode to values, move, re-encode with identity indices)
+namespace bgpu {
+bool batch_has_dictionary(const bgpu_batch* b);
+int dict_decode_column(bgpu_ctx* ctx, const Column& c, int64_t n, Column* out);
+int dict_decode_batch(bgpu_ctx* ctx, const bgpu_batch* in, std::unique_ptr<bgpu_batch>* out, std::vector<size_t>* dict_cols);
+int dict_identity_encode(bgpu_ctx* ctx, bgpu_batch* b, size_t i, const Column& proto, const uint64_t* d_offsets, uint32_t n_parts);
+}  // namespace bgpu
 
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -120,7 +120,7 @@ class Fbb {
 
 // Arrow's Schema.fbs / Message.fbs, the part this path needs
 enum FbType : uint8_t { T_Int = 2, T_FloatingPoint = 3, T_Binary = 4, T_Utf8 = 5, T_Bool = 6, T_Decimal = 7, T_Date = 8, T_Time = 9, T_Timestamp = 10 };
-enum FbHeader : uint8_t { H_Schema = 1, H_RecordBatch = 3 };
+enum FbHeader : uint8_t { H_Schema = 1, H_DictionaryBatch = 2, H_RecordBatch = 3 };
 constexpr int16_t kMetadataV5 = 4;
 
 // the `type` union member of a Field from the Arrow C format string; false = not supported by this encoder
@@ -216,11 +216,28 @@ void wrap_message(const Fbb& b, std::vector<uint8_t>* out) {
 int schema_message(bgpu_ctx* ctx, const std::vector<Column>& cols, std::vector<uint8_t>* out) {
   Fbb b;
   std::vector<uint32_t> fields;
+  int64_t next_dict_id = 0;
   for (const Column& c : cols) {
-    if (c.kind == K_DICT32) return ctx->fail(BGPU_EUNSUPPORTED, "IPC encoder: dictionary column " + c.name);
+    // a dictionary-encoded field carries the type of its VALUES and a DictionaryEncoding{id, indexType Int32} (Schema.fbs);
+    // ids are the position among the dictionary fields, as bgpu_ipc_encode_partitions numbers its dictionary batches
+    const bool is_dict = c.kind == K_DICT32;
+    if (is_dict && (!c.dict || c.dict->kind == K_DICT32)) return ctx->fail(BGPU_EUNSUPPORTED, "IPC encoder: dictionary column " + c.name);
+    const std::string& fmt = is_dict ? c.dict->format : c.format;
     uint8_t tt = 0;
     uint32_t toff = 0;
-    if (!fb_type(b, c.format, &tt, &toff)) return ctx->fail(BGPU_EUNSUPPORTED, "IPC encoder: type '" + c.format + "' of column " + c.name);
+    if (!fb_type(b, fmt, &tt, &toff)) return ctx->fail(BGPU_EUNSUPPORTED, "IPC encoder: type '" + fmt + "' of column " + c.name);
+    uint32_t denc = 0;
+    if (is_dict) {
+      b.start_table(2);
+      b.add<int32_t>(0, 32);
+      b.add<uint8_t>(1, 1);
+      const uint32_t index_type = b.end_table();
+      b.start_table(4);
+      b.add<int64_t>(0, next_dict_id++);
+      b.add_ref(1, index_type);
+      b.add<uint8_t>(2, 0);
+      denc = b.end_table();
+    }
     const uint32_t children = b.offset_vector({});
     const uint32_t name = b.string(c.name);
     b.start_table(7);
@@ -228,6 +245,7 @@ int schema_message(bgpu_ctx* ctx, const std::vector<Column>& cols, std::vector<u
     b.add<uint8_t>(1, (c.flags & ARROW_FLAG_NULLABLE) ? 1 : 0);
     b.add<uint8_t>(2, tt);
     b.add_ref(3, toff);
+    if (denc) b.add_ref(4, denc);
     b.add_ref(5, children);
     fields.push_back(b.end_table());
   }
@@ -248,7 +266,7 @@ int schema_message(bgpu_ctx* ctx, const std::vector<Column>& cols, std::vector<u
 
 void record_batch_message(int64_t rows, const std::vector<std::pair<int64_t, int64_t>>& nodes,
                           const std::vector<std::pair<int64_t, int64_t>>& buffers, int64_t body_len, std::vector<uint8_t>* out,
-                          int compression = -1) {
+                          int compression = -1, int64_t dict_id = -1) {
   Fbb b;
   uint32_t comp = 0;
   if (compression >= 0) {  // BodyCompression{codec: LZ4_FRAME = 0 | ZSTD = 1, method: BUFFER = 0}
@@ -264,10 +282,19 @@ void record_batch_message(int64_t rows, const std::vector<std::pair<int64_t, int
   b.add_ref(1, nv);
   b.add_ref(2, bv);
   if (comp) b.add_ref(3, comp);
-  const uint32_t rb = b.end_table();
+  uint32_t rb = b.end_table();
+  uint8_t header = H_RecordBatch;
+  if (dict_id >= 0) {  // DictionaryBatch{id, data: RecordBatch, isDelta = false}: the batch's one column is the dictionary
+    b.start_table(3);
+    b.add<int64_t>(0, dict_id);
+    b.add_ref(1, rb);
+    b.add<uint8_t>(2, 0);
+    rb = b.end_table();
+    header = H_DictionaryBatch;
+  }
   b.start_table(5);
   b.add<int16_t>(0, kMetadataV5);
-  b.add<uint8_t>(1, H_RecordBatch);
+  b.add<uint8_t>(1, header);
   b.add_ref(2, rb);
   b.add<int64_t>(3, body_len);
   b.finish(b.end_table());
@@ -568,17 +595,12 @@ extern "C" int bgpu_ipc_record_batch_metadata(bgpu_ctx* ctx, int64_t rows, const
   return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }
 
-extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch, const uint64_t* offsets, uint32_t n,
-                                          int32_t compression, uint8_t** out_bytes, uint64_t* out_msg_off) try {
-  if (!ctx || !batch || !offsets || !out_bytes || !out_msg_off || n == 0) return BGPU_EINVAL;
-  if (compression < -1 || compression > 0) return ctx->fail(BGPU_EUNSUPPORTED, "compression must be -1 (none) or 0 (LZ4_FRAME)");
+// One encapsulated message per non-empty partition of a batch WITHOUT dictionary columns: RecordBatch messages, or
+// (dict_id >= 0, one column) DictionaryBatch messages whose body is that column.
+static int encode_impl(bgpu_ctx* ctx, const bgpu_batch* batch, const uint64_t* offsets, uint32_t n, int32_t compression,
+                       int64_t dict_id, uint8_t** out_bytes, uint64_t* out_msg_off) {
   *out_bytes = nullptr;
-  if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
-  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-  if (offsets[n] > (uint64_t)batch->n_rows) return ctx->fail(BGPU_EINVAL, "partition offsets beyond the batch");
   const size_t n_cols = batch->cols.size();
-  for (const Column& c : batch->cols)
-    if (c.kind == K_DICT32) return ctx->fail(BGPU_EUNSUPPORTED, "IPC encoder: dictionary column " + c.name);
 
   // 1. utf8 columns: the byte offsets at the partition boundaries (one small gather, one sync)
   std::vector<size_t> utf8_cols;
@@ -604,7 +626,7 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
   for (const Column& c : batch->cols) n_buffers += (c.kind == K_UTF8 || c.kind == K_BINARY) ? 3 : 2;
   std::vector<uint8_t> msg;
   record_batch_message(0, std::vector<std::pair<int64_t, int64_t>>(n_cols), std::vector<std::pair<int64_t, int64_t>>(n_buffers), 0, &msg,
-                       compression);
+                       compression, dict_id);
   const uint64_t meta_len = msg.size();
   struct Part { std::vector<std::pair<int64_t, int64_t>> buffers; std::vector<int> counter; uint64_t body_len = 0, body0 = 0; };
   std::vector<Part> parts(n);
@@ -786,7 +808,7 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
       std::vector<std::pair<int64_t, int64_t>> nodes;
       for (size_t i = 0; i < n_cols; i++)
         nodes.emplace_back((int64_t)rows, parts[p].counter[i] < 0 ? 0 : (int64_t)(rows - set_bits[(size_t)parts[p].counter[i]]));
-      record_batch_message((int64_t)rows, nodes, cbuffers[p], (int64_t)cbody_len[p], &msg, 0);
+      record_batch_message((int64_t)rows, nodes, cbuffers[p], (int64_t)cbody_len[p], &msg, 0, dict_id);
       if (msg.size() != meta_len) {
         pinned_pool().give(chost);
         return ctx->fail(BGPU_EINVAL, "internal: IPC metadata size is not constant");
@@ -816,7 +838,7 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
     std::vector<std::pair<int64_t, int64_t>> nodes;
     for (size_t i = 0; i < n_cols; i++)
       nodes.emplace_back((int64_t)rows, pt.counter[i] < 0 ? 0 : (int64_t)(rows - set_bits[(size_t)pt.counter[i]]));
-    record_batch_message((int64_t)rows, nodes, pt.buffers, (int64_t)pt.body_len, &msg);
+    record_batch_message((int64_t)rows, nodes, pt.buffers, (int64_t)pt.body_len, &msg, -1, dict_id);
     if (msg.size() != meta_len) {
       pinned_pool().give(host);
       return ctx->fail(BGPU_EINVAL, "internal: IPC metadata size is not constant");
@@ -824,6 +846,72 @@ extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch
     memcpy(host + out_msg_off[p], msg.data(), msg.size());
   }
   *out_bytes = host;
+  return BGPU_OK;
+}
+
+extern "C" int bgpu_ipc_encode_partitions(bgpu_ctx* ctx, const bgpu_batch* batch, const uint64_t* offsets, uint32_t n,
+                                          int32_t compression, uint8_t** out_bytes, uint64_t* out_msg_off) try {
+  if (!ctx || !batch || !offsets || !out_bytes || !out_msg_off || n == 0) return BGPU_EINVAL;
+  if (compression < -1 || compression > 0) return ctx->fail(BGPU_EUNSUPPORTED, "compression must be -1 (none) or 0 (LZ4_FRAME)");
+  *out_bytes = nullptr;
+  if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
+  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (offsets[n] > (uint64_t)batch->n_rows) return ctx->fail(BGPU_EINVAL, "partition offsets beyond the batch");
+  if (!batch_has_dictionary(batch)) return encode_impl(ctx, batch, offsets, n, compression, -1, out_bytes, out_msg_off);
+  // Dictionary columns. A partition's message becomes [DictionaryBatch per dictionary column][RecordBatch]: the
+  // partition's VALUES are its dictionary (one entry per row), its indices count 0 .. rows-1 - the stream the reference's
+  // reader expects (/root/reference/ballista/core/src/async_reader/mod.rs:168-258: a dictionary batch replaces the
+  // dictionary of its id for the record batches that follow).
+  std::unique_ptr<bgpu_batch> main;
+  std::vector<size_t> dict_cols;
+  BGPU_TRY(dict_decode_batch(ctx, batch, &main, &dict_cols));
+  struct Piece { uint8_t* bytes = nullptr; std::vector<uint64_t> off; };
+  std::vector<Piece> pieces(dict_cols.size() + 1);
+  auto cleanup = [&]() { for (Piece& pc : pieces) if (pc.bytes) pinned_pool().give(pc.bytes); };
+  DevAllocPtr d_offs;
+  BGPU_TRY(dev_alloc(ctx, (size_t)(n + 1) * 8, &d_offs));
+  BGPU_CUDA(ctx, cudaMemcpyAsync(d_offs->p, offsets, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+  int rc = BGPU_OK;
+  for (size_t k = 0; k < dict_cols.size() && rc == BGPU_OK; k++) {
+    bgpu_batch one(ctx);  // the decoded values of dictionary column k, as a one-column batch
+    one.n_rows = main->n_rows;
+    one.cols.push_back(main->cols[dict_cols[k]]);
+    pieces[k].off.assign(n + 1, 0);
+    rc = encode_impl(ctx, &one, offsets, n, compression, (int64_t)k, &pieces[k].bytes, pieces[k].off.data());
+  }
+  if (rc == BGPU_OK) {
+    for (size_t i : dict_cols) {
+      rc = dict_identity_encode(ctx, main.get(), i, batch->cols[i], (const uint64_t*)d_offs->p, n);
+      if (rc != BGPU_OK) break;
+      Column& c = main->cols[i];  // encoded as its Int32 indices
+      c.kind = K_FIXED; c.format = "i"; c.dict = nullptr;
+    }
+  }
+  if (rc == BGPU_OK) {
+    pieces.back().off.assign(n + 1, 0);
+    rc = encode_impl(ctx, main.get(), offsets, n, compression, -1, &pieces.back().bytes, pieces.back().off.data());
+  }
+  if (rc != BGPU_OK) { cleanup(); return rc; }
+  uint64_t total = 0;
+  for (uint32_t p = 0; p < n; p++) {
+    out_msg_off[p] = total;
+    for (const Piece& pc : pieces) total += pc.off[p + 1] - pc.off[p];
+  }
+  out_msg_off[n] = total;
+  if (total) {
+    uint8_t* host = nullptr;
+    const cudaError_t e = pinned_pool().take(total, &host);
+    if (e != cudaSuccess) { cleanup(); return ctx->fail(BGPU_ECUDA, std::string("IPC encode: ") + cudaGetErrorString(e)); }
+    uint64_t at = 0;
+    for (uint32_t p = 0; p < n; p++)
+      for (const Piece& pc : pieces) {
+        const uint64_t len = pc.off[p + 1] - pc.off[p];
+        if (len) memcpy(host + at, pc.bytes + pc.off[p], len);
+        at += len;
+      }
+    *out_bytes = host;
+  }
+  cleanup();
   return BGPU_OK;
 } catch (const std::exception& e) {
   return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI

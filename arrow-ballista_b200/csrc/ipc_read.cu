@@ -20,6 +20,8 @@
 #include <string>
 #include <vector>
 
+#include <map>
+
 #include "internal.h"
 
 void export_batch_schema(const bgpu_batch* b, struct ArrowSchema* out);  // arrow_io.cu
@@ -120,6 +122,7 @@ bool valid_utf8(const std::string& s) {
   return true;
 }
 
+int field_type_to_column(bgpu_ctx* ctx, Table f, Column* c);
 int field_to_column(bgpu_ctx* ctx, Table f, Column* c) {
   c->name = f.str(0);
   if (!valid_utf8(c->name)) {
@@ -127,7 +130,30 @@ int field_to_column(bgpu_ctx* ctx, Table f, Column* c) {
     return ctx->fail(BGPU_EINVAL, "IPC reader: field name is not UTF-8");
   }
   c->flags = f.scalar<uint8_t>(1, 0) ? ARROW_FLAG_NULLABLE : 0;
-  if (f.field(4)) return ctx->fail(BGPU_EUNSUPPORTED, "IPC reader: dictionary-encoded column " + c->name);
+  if (f.field(4)) {
+    // DictionaryEncoding{id, indexType (absent = Int32), isOrdered}: the field's type is the type of the VALUES
+    const Table enc = f.table(4);
+    const Table it = enc.table(1);
+    if (it && (it.scalar<int32_t>(0, 0) != 32 || it.scalar<uint8_t>(1, 0) == 0))
+      return ctx->fail(BGPU_EUNSUPPORTED, "IPC reader: dictionary indices of column " + c->name + " are not Int32");
+    const int64_t id = enc.scalar<int64_t>(0, 0);
+      auto values = std::make_shared<Column>();
+    BGPU_TRY(field_type_to_column(ctx, f, values.get()));
+    values->name = "";
+    values->flags = ARROW_FLAG_NULLABLE;
+    if (values->kind == K_BOOL) return ctx->fail(BGPU_EUNSUPPORTED, "IPC reader: dictionary of Boolean values (column " + c->name + ")");
+    c->format = "i";
+    c->kind = K_DICT32;
+    c->width = 4;
+    c->dict = values;
+    c->dict_id = id;
+    return BGPU_OK;
+  }
+  return field_type_to_column(ctx, f, c);
+}
+
+// the `type` union of a Field -> format / kind / width
+int field_type_to_column(bgpu_ctx* ctx, Table f, Column* c) {
   const uint8_t tt = f.scalar<uint8_t>(2, 0);
   const Table t = f.table(3);
   auto fixed = [&](const std::string& fmt, int w) {
@@ -357,6 +383,7 @@ struct bgpu_ipc_reader {
   bool finished = false;
   bgpu_batch* schema = nullptr;  // zero-row batch carrying the column descriptors
   uint64_t batches = 0, rows = 0;
+  std::map<int64_t, std::shared_ptr<Column>> dicts;  // the current dictionary of every id (a later batch of an id replaces it)
 };
 
 // Reads the framing of the next message. *meta = flatbuffer bytes, *meta_len = 0 at end of stream.
@@ -445,12 +472,28 @@ __global__ void __launch_bounds__(256) check_offsets_kernel(const int32_t* __res
   if (wrong) atomicOr(bad, 1u);
 }
 
+static int decode_record_batch(bgpu_ipc_reader* r, Fb& fb, const Table rb, const uint8_t* body, uint64_t body_len,
+                               const std::vector<Column>& proto, bgpu_batch** out);
+
+// every valid dictionary index lies in [0, dictionary length); *bad != 0 otherwise
+__global__ void __launch_bounds__(256) check_indices_kernel(const int32_t* __restrict__ idx, const uint8_t* __restrict__ valid,
+                                                            int64_t rows, int64_t dict_len, unsigned int* __restrict__ bad) {
+  bool wrong = false;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < rows; i += (int64_t)gridDim.x * blockDim.x) {
+    if (valid && !((valid[i >> 3] >> (i & 7)) & 1)) continue;
+    const int32_t k = idx[i];
+    if (k < 0 || (int64_t)k >= dict_len) wrong = true;
+  }
+  if (wrong) atomicOr(bad, 1u);
+}
+
 static int reader_next_impl(bgpu_ipc_reader* r, bgpu_batch** out) {
   if (!r || !out) return BGPU_EINVAL;
   *out = nullptr;
   bgpu_ctx* ctx = r->ctx;
-  if (r->finished) return BGPU_OK;
   if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
+  for (;;) {
+  if (r->finished) return BGPU_OK;
   const uint8_t* meta = nullptr;
   uint32_t meta_len = 0;
   BGPU_TRY(next_message(r, &meta, &meta_len));
@@ -466,14 +509,77 @@ static int reader_next_impl(bgpu_ipc_reader* r, bgpu_batch** out) {
   const uint8_t* body = r->bytes + r->pos;
   r->pos += body_len;
   if (header == H_Schema) return ctx->fail(BGPU_EINVAL, "IPC reader: Not expecting a schema when messages are read");
-  if (header == H_DictionaryBatch) return ctx->fail(BGPU_EUNSUPPORTED, "IPC reader: dictionary batch");
   if (header == H_NONE) {
     r->finished = true;
     return BGPU_OK;
   }
+  if (header == H_DictionaryBatch) {
+    // DictionaryBatch{id, data: RecordBatch of ONE column (the values), isDelta}: becomes the dictionary of every
+    // record batch that follows, until a batch of the same id replaces it (async_reader/mod.rs:168-258)
+    const Table db = msg.table(2);
+    const int64_t id = db.scalar<int64_t>(0, 0);
+    if (db.scalar<uint8_t>(2, 0)) return ctx->fail(BGPU_EUNSUPPORTED, "IPC reader: delta dictionary batch");
+    const Column* field = nullptr;
+    for (const Column& c : r->schema->cols)
+      if (c.kind == K_DICT32 && c.dict_id == id) field = &c;
+    if (!fb.ok || !field) return ctx->fail(BGPU_EINVAL, "IPC reader: dictionary batch for an id the schema does not have");
+    std::vector<Column> one{*field->dict};
+    bgpu_batch* values = nullptr;
+    BGPU_TRY(decode_record_batch(r, fb, db.table(1), body, body_len, one, &values));
+    auto col = std::make_shared<Column>(values->cols[0]);
+    col->length = values->n_rows;
+    delete values;
+    r->dicts[id] = col;
+    continue;
+  }
   if (header != H_RecordBatch) return ctx->fail(BGPU_EINVAL, "IPC reader: unexpected message header type " + std::to_string((int)header));
+  bgpu_batch* b = nullptr;
+  BGPU_TRY(decode_record_batch(r, fb, msg.table(2), body, body_len, r->schema->cols, &b));
+  for (Column& c : b->cols) {
+    if (c.kind != K_DICT32) continue;
+    auto it = r->dicts.find(c.dict_id);
+    if (it == r->dicts.end()) {
+      delete b;
+      return ctx->fail(BGPU_EINVAL, "IPC reader: record batch before the dictionary of column " + c.name);
+    }
+    c.dict = it->second;
+  }
+  {  // indices come from another process: checked before any kernel looks a value up with them
+    DevAllocPtr d_bad;
+    for (const Column& c : b->cols) {
+      if (c.kind != K_DICT32 || b->n_rows == 0) continue;
+      if (!d_bad) {
+        const int rc = dev_alloc(ctx, 4, &d_bad);
+        if (rc != BGPU_OK) { delete b; return rc; }
+        cudaMemsetAsync(d_bad->p, 0, 4, ctx->stream);
+      }
+      check_indices_kernel<<<(int)std::min<int64_t>(ceil_div64(b->n_rows, 256), (int64_t)ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+          (const int32_t*)c.values, c.validity, b->n_rows, c.dict->length, (unsigned int*)d_bad->p);
+      ctx->launches++;
+    }
+    if (d_bad) {
+      unsigned int bad = 0;
+      cudaError_t e = cudaMemcpyAsync(&bad, d_bad->p, 4, cudaMemcpyDeviceToHost, ctx->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+      if (e != cudaSuccess || bad) {
+        delete b;
+        if (e != cudaSuccess) return ctx->fail(BGPU_ECUDA, std::string("IPC reader: ") + cudaGetErrorString(e));
+        return ctx->fail(BGPU_EINVAL, "IPC reader: dictionary index beyond its dictionary");
+      }
+    }
+  }
+  r->batches++;
+  r->rows += (uint64_t)b->n_rows;
+  *out = b;
+  return BGPU_OK;
+  }
+}
 
-  const Table rb = msg.table(2);
+// One RecordBatch table + its body -> a device batch with the columns of `proto` (the stream's fields, or the one value
+// column of a dictionary batch). Dictionary-encoded fields are read as their Int32 indices.
+static int decode_record_batch(bgpu_ipc_reader* r, Fb& fb, const Table rb, const uint8_t* body, uint64_t body_len,
+                               const std::vector<Column>& proto, bgpu_batch** out) {
+  bgpu_ctx* ctx = r->ctx;
   const int64_t rows = rb.scalar<int64_t>(0, 0);
   uint32_t n_nodes = 0, n_buffers = 0;
   const size_t nodes = rb.vec(1, &n_nodes), buffers = rb.vec(2, &n_buffers);
@@ -481,7 +587,6 @@ static int reader_next_impl(bgpu_ipc_reader* r, bgpu_batch** out) {
   const bool compressed = (bool)comp;
   if (compressed && (comp.scalar<int8_t>(0, 0) != 0 || comp.scalar<int8_t>(1, 0) != 0))
     return ctx->fail(BGPU_EUNSUPPORTED, "IPC reader: only LZ4_FRAME buffer compression is supported");
-  const std::vector<Column>& proto = r->schema->cols;
   size_t want_buffers = 0;
   for (const Column& c : proto) want_buffers += (c.kind == K_UTF8 || c.kind == K_BINARY) ? 3 : 2;
   if (!fb.ok || rows < 0 || n_nodes != proto.size() || n_buffers != want_buffers)
@@ -633,8 +738,6 @@ static int reader_next_impl(bgpu_ipc_reader* r, bgpu_batch** out) {
       }
     }
   }
-  r->batches++;
-  r->rows += (uint64_t)rows;
   *out = b;
   return BGPU_OK;
 }

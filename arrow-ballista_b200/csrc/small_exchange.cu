@@ -279,8 +279,18 @@ extern "C" int bgpu_small_exchange(bgpu_ctx* ctx, void* comm, int32_t rank, int3
   const size_t n_cols = in->cols.size();
   if (n_cols > (size_t)kSmallCols || world > kSmallWorld || n_keys < 1 || n_keys > kMaxKeys)
     return ctx->fail(BGPU_EUNSUPPORTED, "bgpu_small_exchange: schema or world beyond the small path");
-  for (const Column& c : in->cols)
-    if (c.kind == K_DICT32) return ctx->fail(BGPU_EUNSUPPORTED, "bgpu_small_exchange: dictionary column " + c.name);
+  if (batch_has_dictionary(in)) {  // schema-level, the same on every rank: values travel, re-encoded on arrival (dictionary.cu)
+    BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    std::unique_ptr<bgpu_batch> decoded;
+    std::vector<size_t> dict_cols;
+    BGPU_TRY(dict_decode_batch(ctx, in, &decoded, &dict_cols));
+    bgpu_batch* got = nullptr;
+    BGPU_TRY(bgpu_small_exchange(ctx, comm, rank, world, decoded.get(), key_cols, n_keys, n_partitions, &got));
+    std::unique_ptr<bgpu_batch> res(got);
+    for (size_t i : dict_cols) BGPU_TRY(dict_identity_encode(ctx, res.get(), i, in->cols[i], nullptr, 0));
+    *out = res.release();
+    return BGPU_OK;
+  }
   for (int32_t k = 0; k < n_keys; k++)
     if (key_cols[k] < 0 || key_cols[k] >= (int32_t)n_cols) return ctx->fail(BGPU_EINVAL, "key column index out of range");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));

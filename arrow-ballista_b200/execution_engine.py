@@ -181,7 +181,7 @@ class GpuQueryStageExec(QueryStageExecutor):
         if mode is None:
             import pyarrow as pa
 
-            mode = "host" if any(pa.types.is_dictionary(f.type) for f in self._schema) else "device"
+            mode = "device"
         if mode == "host":
             states = [s.download() if isinstance(s, DeviceBatch) else s for s in states]
         self.shuffle_writer = _recreate(w, w.job_id, w.stage_id, w.work_dir, plan=states, ctx=ctx, input_schema=self._schema)

@@ -112,7 +112,7 @@ class GpuShuffleWriterExec:
 
     def __init__(self, job_id, stage_id, partitions, plan, work_dir, shuffle_output_partitioning, ctx=None,
                  input_schema=None, input_partitioning=None, ipc=None, compression="lz4"):
-        self.ipc = ipc  # "device", "host" or None = device unless the schema has a dictionary column
+        self.ipc = ipc  # "device" (None = device) or "host" (pyarrow's writer: tests compare the two)
         self.compression = compression  # device framing: "lz4" (LZ4_FRAME, as the reference writes) or None
         self.job_id, self.stage_id, self.partitions = str(job_id), int(stage_id), list(partitions)
         self.plan, self.work_dir = plan, str(work_dir)
@@ -202,9 +202,9 @@ class GpuShuffleWriterExec:
                     continue
                 if isinstance(batch, DeviceBatch):
                     # a stage whose output is already on the device (a Final aggregate): framed by libbgpu like the hash
-                    # arm's partitions, as one "partition" holding every row; dictionary columns go through the host writer
+                    # arm's partitions, as one "partition" holding every row
                     schema = self._schema if self._schema is not None else batch.schema
-                    if self.ipc == "host" or any(pa.types.is_dictionary(f.type) for f in schema):
+                    if self.ipc == "host":
                         batch = batch.download()
                     else:
                         if w is None:
@@ -236,7 +236,7 @@ class GpuShuffleWriterExec:
         mode = self.ipc
         if mode is None:
             sch = self._schema
-            mode = "host" if sch is not None and any(pa.types.is_dictionary(f.type) for f in sch) else "device"
+            mode = "device"  # dictionary columns included: DictionaryBatch messages are framed on the device too
         if mode == "device":
             return self._write_device_ipc(base, shuffle_id, partitioner, n)
 

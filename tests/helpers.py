@@ -273,3 +273,19 @@ def alltypes_plain():
          pa.array(c["bigint_col"], type=pa.int64()), pa.array(c["double_col"], type=pa.float64()), pa.array(c["string_col"])],
         names=["g", "id", "bool_col", "bigint_col", "double_col", "string_col"])
     return batch, d["reference_asserts"]
+
+
+def decode_dictionaries(t):
+    """A Table / RecordBatch with every dictionary column cast to its value type (logical comparison: two encodings of the
+    same rows differ in dictionaries and indices)."""
+    import pyarrow as pa
+
+    tbl = pa.Table.from_batches([t]) if isinstance(t, pa.RecordBatch) else t
+    cols, fields = [], []
+    for f, c in zip(tbl.schema, tbl.columns):
+        if pa.types.is_dictionary(f.type):
+            c = c.cast(f.type.value_type)
+            f = pa.field(f.name, f.type.value_type, f.nullable)
+        cols.append(c)
+        fields.append(f)
+    return pa.Table.from_arrays(cols, schema=pa.schema(fields))

@@ -25,11 +25,17 @@ def test_schema_message_round_trips_every_supported_type(bb):
     assert pa.ipc.open_stream(io.BytesIO(ipc.schema_message(pa.schema([])) + ipc.EOS)).schema.equals(pa.schema([]))
 
 
-def test_dictionary_schema_is_unsupported(bb):
+def test_dictionary_fields_carry_their_encoding(bb):
+    """Dictionary<Int32, Utf8 | Binary | Int64> fields: value type + DictionaryEncoding{id = position among the dictionary
+    fields, Int32 indices}; Arrow's reader accepts the message and reports the same schema. Other index types are refused."""
     from ballista_b200 import ipc
 
+    schema = pa.schema([("a", pa.int64()), ("id1", pa.dictionary(pa.int32(), pa.string())), ("x", pa.float64()),
+                        pa.field("id3", pa.dictionary(pa.int32(), pa.binary()), False), ("n", pa.dictionary(pa.int32(), pa.int64()))])
+    msg = ipc.schema_message(schema)
+    assert pa.ipc.open_stream(io.BytesIO(msg + ipc.EOS)).schema.equals(schema)
     with pytest.raises(bb.BgpuError):
-        ipc.schema_message(pa.schema([("d", pa.dictionary(pa.int32(), pa.string()))]))
+        ipc.schema_message(pa.schema([("d", pa.dictionary(pa.int8(), pa.string()))]))
 
 
 def test_record_batch_metadata_frames_a_hand_laid_body(bb):

@@ -62,7 +62,7 @@ def test_reference_shuffle_writer_tests(bb, ctx, oracle, tmp_path, copies, total
     assert m.input_rows == total and m.output_rows == total
 
 
-@pytest.mark.parametrize("with_dict", [False, True])  # no dictionary column: device IPC framing; with one: host framing
+@pytest.mark.parametrize("with_dict", [False, True])  # with a dictionary column: DictionaryBatch messages framed on the device
 def test_written_partitions_match_oracle(bb, ctx, oracle, tmp_path, with_dict):
     from ballista_b200.shuffle_writer import GpuShuffleWriterExec
     from helpers import random_batch
@@ -83,6 +83,10 @@ def test_written_partitions_match_oracle(bb, ctx, oracle, tmp_path, with_dict):
         exp = pa.Table.from_batches(want[l.output_partition])
         assert l.num_batches == len(want[l.output_partition]) and l.num_rows == exp.num_rows
         assert l.partitions == [0, 1]
+        if with_dict:  # the file's dictionaries are per partition: compare the rows, and that the schema kept its type
+            from helpers import decode_dictionaries
+            assert got.schema.equals(exp.schema)
+            got, exp = decode_dictionaries(got), decode_dictionaries(exp)
         assert got.equals(exp), f"partition {l.output_partition} differs from the oracle"
 
 
