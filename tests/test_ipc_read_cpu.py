@@ -53,8 +53,11 @@ def test_reader_rejects_malformed_streams(bb):
     first = 8 + int.from_bytes(data[4:8], "little")
     with pytest.raises(bb.BgpuError, match="Unable to read IPC message as schema"):
         ipc.StreamReader(host, data[first:])  # starts with a RecordBatch message
+    # Dictionary<Int32, T> fields are read (round 2); other index types are not
+    dsch = pa.schema([("d", pa.dictionary(pa.int32(), pa.string())), ("n", pa.dictionary(pa.int32(), pa.int64()))])
+    assert ipc.StreamReader(host, _stream(dsch)).schema.equals(dsch)
     with pytest.raises(bb.BgpuError) as e:
-        ipc.StreamReader(host, _stream(pa.schema([("d", pa.dictionary(pa.int32(), pa.string()))])))
+        ipc.StreamReader(host, _stream(pa.schema([("d", pa.dictionary(pa.int16(), pa.string()))])))
     assert "dictionary" in str(e.value)
     with pytest.raises(bb.BgpuError):
         ipc.StreamReader(host, _stream(pa.schema([("l", pa.list_(pa.int64()))])))
