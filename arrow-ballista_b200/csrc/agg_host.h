@@ -9,7 +9,7 @@
 
 #include "agg_plan.h"
 
-namespace bgpu { struct JitModule; }
+namespace bgpu { struct JitModule; struct Interner; }
 
 struct PhysAcc {
   int32_t op = 0;
@@ -36,6 +36,11 @@ struct bgpu_agg {
   std::vector<int32_t> group_cols;  // indices into `fields`
   std::vector<int32_t> key_off, key_width;  // packed-key layout per group column
   int32_t key_words = 1;
+  // interned layout (agg_key_layout): group columns that enter the packed key as 4-byte ids of an Interner
+  bool interned_mode = false;
+  bool key_too_long = false;  // the last pass met a string key beyond its inline field (check_common_flags)
+  std::vector<uint8_t> key_interned;
+  std::vector<std::shared_ptr<bgpu::Interner>> interners;
   std::vector<bgpu::HValue> values;  // distinct aggregate arguments; a value that extends another follows it
   std::vector<bool> value_from_prev;
   std::vector<bgpu::HFilterTerm> filter;
@@ -58,6 +63,7 @@ struct bgpu_agg {
     std::vector<std::string> values;
     std::string value_format = "u";
     ColKind value_kind = K_UTF8;
+    std::shared_ptr<bgpu::Interner> interner;  // exact path: the canonical dictionary, built on the device (interner.cu)
     std::shared_ptr<Column> canon_dev;  // fast path: the first dictionary seen IS the canonical one (device resident)
     std::shared_ptr<Column> last;  // last batch dictionary seen (kept alive so its identity cannot be recycled)
     DevAllocPtr last_remap;        // nullptr = identity
@@ -135,6 +141,7 @@ int agg_generate_source(const bgpu_agg* g, const JitShape& sh, std::string* out)
 const char* agg_jit_prelude();
 
 int agg_launch_grid(bgpu_ctx* ctx, int64_t n, int per_block);
+int agg_key_layout(bgpu_agg* g, bool interned);
 // One update whose outcome is read later (streamed input): the fused launch is followed by a device-side conditional
 // commit, the status words arrive in pinned memory once `done` has completed.
 struct AggAsyncReq {

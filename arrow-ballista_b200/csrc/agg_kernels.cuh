@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(kAggThreads)
     commit_cond_kernel(const __grid_constant__ AccPlan plan, const uint64_t* __restrict__ scratch, uint32_t n_ctas,
                        uint32_t g_cap, const uint32_t* __restrict__ counters, uint32_t* __restrict__ status) {
   const uint32_t n_groups = counters[0];
-  const bool ok = counters[1] == 0 && counters[4] == 0 && n_groups <= g_cap;
+  const bool ok = counters[1] == 0 && counters[2] == 0 && counters[3] == 0 && counters[4] == 0 && n_groups <= g_cap;
   if (blockIdx.x == 0 && threadIdx.x < 8)
     status[threadIdx.x] = threadIdx.x == 0 ? (ok ? 1u : 0u) : threadIdx.x == 1 ? n_groups : counters[threadIdx.x - 1];
   if (ok) commit_body(plan, scratch, n_ctas, g_cap, n_groups);

@@ -20,6 +20,59 @@ int agg_launch_grid(bgpu_ctx* ctx, int64_t n, int per_block) {
 static std::string decimal_format(int p, int s) { return "d:" + std::to_string(p) + "," + std::to_string(s); }
 static bool is_unsigned(int vk) { return vk == V_U8 || vk == V_U16 || vk == V_U32 || vk == V_U64; }
 
+// The packed key of a group table slot: <= 16 bytes, fields in group-column order, never straddling the 8-byte boundary.
+//   inline layout   fixed-width columns by value, utf8 / binary columns as [length byte][bytes] sharing what is left
+//                   (strings beyond that budget raise a flag at run time);
+//   interned layout utf8 / binary columns - and, while the key is still too wide, the widest fixed-width columns - are
+//                   replaced by 4-byte ids from an Interner (interner.cu): keys of any width (GroupValuesRows has no limit).
+// Returns BGPU_EUNSUPPORTED (without touching ctx->err) when the layout does not fit.
+int agg_key_layout(bgpu_agg* g, bool interned) {
+  const size_t n_group = g->group_cols.size();
+  std::vector<uint8_t> by_id(n_group, 0);
+  int fixed_bytes = 0, n_var = 0;
+  for (size_t i = 0; i < n_group; i++) {
+    const Column& f = g->fields[(size_t)g->group_cols[i]];
+    const bool var = f.kind == K_UTF8 || f.kind == K_BINARY;
+    if (var && interned) { by_id[i] = 1; fixed_bytes += 4; }
+    else if (var) n_var++;
+    else fixed_bytes += f.kind == K_BOOL ? 1 : f.width;
+  }
+  if (interned) {
+    while (fixed_bytes > 16) {  // widest fixed-width column not interned yet
+      int best = -1;
+      for (size_t i = 0; i < n_group; i++) {
+        const Column& f = g->fields[(size_t)g->group_cols[i]];
+        if (by_id[i] || f.kind != K_FIXED || f.width <= 4) continue;
+        if (best < 0 || f.width > g->fields[(size_t)g->group_cols[(size_t)best]].width) best = (int)i;
+      }
+      if (best < 0) return BGPU_EUNSUPPORTED;
+      fixed_bytes -= g->fields[(size_t)g->group_cols[(size_t)best]].width - 4;
+      by_id[(size_t)best] = 1;
+    }
+  }
+  const int var_budget = n_var ? (16 - fixed_bytes) / n_var : 0;  // bytes per inline utf8 key incl. its length byte
+  if (fixed_bytes > 16 || (n_var && var_budget < 2)) return BGPU_EUNSUPPORTED;
+  std::vector<int32_t> key_off, key_width;
+  int off = 0;
+  for (size_t i = 0; i < n_group; i++) {
+    const Column& f = g->fields[(size_t)g->group_cols[i]];
+    const bool var = (f.kind == K_UTF8 || f.kind == K_BINARY) && !by_id[i];
+    const int w = by_id[i] ? 4 : var ? var_budget : (f.kind == K_BOOL ? 1 : f.width);
+    if (!var && w <= 8 && off < 8 && off + w > 8) off = 8;  // do not straddle
+    if (off + w > 16) return BGPU_EUNSUPPORTED;
+    key_off.push_back(off);
+    key_width.push_back(var ? w - 1 : w);
+    off += w;
+  }
+  g->key_off = key_off;
+  g->key_width = key_width;
+  g->key_words = off > 8 ? 2 : 1;
+  g->key_interned = by_id;
+  g->interned_mode = interned;
+  g->interners.assign(n_group, nullptr);
+  return BGPU_OK;
+}
+
 static int agg_create_impl(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema* input_schema,
                            const int32_t* group_cols, int32_t n_group, const int32_t* agg_fns,
                            const bgpu_expr_node* nodes, const int32_t* agg_expr_offsets, const char* const* agg_names,
@@ -63,31 +116,14 @@ static int agg_create_impl(bgpu_ctx* ctx, int32_t mode, const struct ArrowSchema
     }
   }
   BGPU_TRY(compile_filter(ctx, g->fields, filter, n_filter, &g->filter));
-  // packed key layout: fields in order, never straddling the 8-byte boundary; utf8 shares what is left
-  int fixed_bytes = 0, n_var = 0;
   for (int32_t i = 0; i < n_group; i++) {
     const int32_t c = group_cols[i];
     if (c < 0 || c >= (int32_t)g->fields.size()) return ctx->fail(BGPU_EINVAL, "group column out of range");
-    const Column& f = g->fields[(size_t)c];
     g->group_cols.push_back(c);
-    if (f.kind == K_UTF8 || f.kind == K_BINARY) n_var++;
-    else fixed_bytes += f.kind == K_BOOL ? 1 : f.width;
   }
-  int off = 0;
-  const int var_budget = n_var ? (16 - fixed_bytes) / n_var : 0;  // bytes per utf8 key incl. its length byte
-  if (fixed_bytes > 16 || (n_var && var_budget < 2))
-    return ctx->fail(BGPU_EUNSUPPORTED, "group key wider than 16 packed bytes");
-  for (int32_t i = 0; i < n_group; i++) {
-    const Column& f = g->fields[(size_t)g->group_cols[(size_t)i]];
-    const bool var = f.kind == K_UTF8 || f.kind == K_BINARY;
-    const int w = var ? var_budget : (f.kind == K_BOOL ? 1 : f.width);
-    if (!var && w <= 8 && off < 8 && off + w > 8) off = 8;  // do not straddle
-    if (off + w > 16) return ctx->fail(BGPU_EUNSUPPORTED, "group key wider than 16 packed bytes");
-    g->key_off.push_back(off);
-    g->key_width.push_back(var ? w - 1 : w);
-    off += w;
-  }
-  g->key_words = off > 8 ? 2 : 1;
+  // packed key layout: inline when it fits 16 bytes, otherwise with the wide columns interned (agg_key_layout)
+  if (agg_key_layout(g.get(), false) != BGPU_OK && agg_key_layout(g.get(), true) != BGPU_OK)
+    return ctx->fail(BGPU_EUNSUPPORTED, "group key wider than 16 packed bytes even with every wide column interned (more than 4 such columns)");
   g->dicts.resize((size_t)n_group);
 
   // distinct values and accumulators (deduplicated: the reference computes sum(x) and avg(x)'s sum separately; the
@@ -345,6 +381,7 @@ extern "C" int bgpu_agg_reset(bgpu_agg* g) try {
   g->n_groups = 0;
   g->passthrough = false;
   g->any_committed = false;
+  for (auto& in : g->interners) in = nullptr;  // a new stream interns afresh
   g->pass_chunks.clear();
   g->emitted = false;
   g->hot_kernel_ms = 0.0;

@@ -25,6 +25,7 @@
 
 #include "agg_host.h"
 #include "agg_kernels.cuh"
+#include "interner.h"
 #include "jit.h"
 
 using namespace bgpu;
@@ -138,55 +139,13 @@ static int own_dictionary(bgpu_agg* g, const Column& d, std::shared_ptr<Column>*
   return BGPU_OK;
 }
 
-// Fold dictionary `d` into the host-side canonical index of group column state `ds`; map[j] = canonical id of value j
-// (-1 for a null value).
-static int index_dictionary(bgpu_agg* g, bgpu_agg::DictState& ds, const Column& d, std::vector<int32_t>* map, bool* identity) {
-  bgpu_ctx* ctx = g->ctx;
-  const int64_t n = d.length;
-  std::vector<int32_t> offs((size_t)n + 1, 0);
-  std::vector<uint8_t> valid;
-  std::vector<char> bytes;
-  if (n) {
-    BGPU_CUDA(ctx, cudaMemcpyAsync(offs.data(), d.offsets, (size_t)(n + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    if (d.validity) {
-      valid.resize((size_t)((n + 7) / 8));
-      BGPU_CUDA(ctx, cudaMemcpyAsync(valid.data(), d.validity, valid.size(), cudaMemcpyDeviceToHost, ctx->stream));
-    }
-    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    bytes.resize((size_t)(offs[(size_t)n] - offs[0]));
-    if (!bytes.empty()) {
-      BGPU_CUDA(ctx, cudaMemcpyAsync(bytes.data(), (const char*)d.values + offs[0], bytes.size(), cudaMemcpyDeviceToHost, ctx->stream));
-      BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    }
-  }
-  map->assign((size_t)n, -1);
-  *identity = true;
-  for (int64_t j = 0; j < n; j++) {
-    int32_t id = -1;
-    if (valid.empty() || ((valid[(size_t)(j >> 3)] >> (j & 7)) & 1)) {
-      std::string v(bytes.data() + (offs[(size_t)j] - offs[0]), (size_t)(offs[(size_t)j + 1] - offs[(size_t)j]));
-      auto it = ds.index.find(v);
-      if (it == ds.index.end()) {
-        id = (int32_t)ds.values.size();
-        ds.index.emplace(v, id);
-        ds.values.push_back(std::move(v));
-      } else {
-        id = it->second;
-      }
-    }
-    (*map)[(size_t)j] = id;
-    *identity &= id == (int32_t)j;
-  }
-  return BGPU_OK;
-}
-
 // Map the batch's dictionary onto the aggregate's canonical dictionary of group column i (group keys are compared by
 // VALUE, as the reference does). *remap = device array or nullptr for the identity.
 //   fast path: the first dictionary an aggregate sees, when its values are pairwise distinct and non-null, IS the
 //              canonical dictionary (identity map, nothing leaves the device) — the common case of one dictionary
 //              shared by every batch of a scan (db-benchmark id3 has 1e5..1e7 values);
-//   exact path: a different dictionary arrives (or duplicates / nulls): dictionaries are folded into a host-side
-//              index by value (they are small next to the batches that reference them).
+//   exact path: a different dictionary arrives (or duplicates / nulls): every dictionary is folded, on the device, into an
+//              Interner keyed by value (round 1 did this on the host through a std::unordered_map).
 static int canonicalize_dictionary(bgpu_agg* g, int32_t i, const Column& c, const int32_t** remap) {
   bgpu_ctx* ctx = g->ctx;
   bgpu_agg::DictState& ds = g->dicts[(size_t)i];
@@ -200,7 +159,7 @@ static int canonicalize_dictionary(bgpu_agg* g, int32_t i, const Column& c, cons
     return ctx->fail(BGPU_EUNSUPPORTED, "group column " + c.name + ": only Dictionary<Int32, Utf8|Binary> keys are supported");
   ds.value_format = d.format;
   ds.value_kind = d.kind;
-  if (!ds.canon_dev && ds.values.empty()) {
+  if (!ds.canon_dev && !ds.interner) {
     bool unique = false;
     BGPU_TRY(dict_values_unique(g, c.dict, &unique));
     if (unique) {
@@ -211,24 +170,23 @@ static int canonicalize_dictionary(bgpu_agg* g, int32_t i, const Column& c, cons
       return BGPU_OK;
     }
   }
-  std::vector<int32_t> map;
-  bool identity = true;
-  if (ds.canon_dev) {  // leave the fast path: the device-resident canonical dictionary becomes ids 0..n-1 of the index
-    std::shared_ptr<Column> first = ds.canon_dev;
-    ds.canon_dev = nullptr;
-    BGPU_TRY(index_dictionary(g, ds, *first, &map, &identity));
-    if (!identity) return ctx->fail(BGPU_EINVAL, "internal: canonical dictionary is not duplicate free");
+  // exact path, on the device: every dictionary is folded into the column's Interner (interner.cu); remap[j] = the
+  // canonical id of value j (-1 for a null value). A canonical dictionary from the fast path seeds it with ids = indices.
+  if (!ds.interner) {
+    BGPU_TRY(interner_create(ctx, &ds.interner));
+    if (ds.canon_dev) {
+      std::shared_ptr<Column> first = ds.canon_dev;
+      ds.canon_dev = nullptr;
+      DevAllocPtr seed_ids;
+      BGPU_TRY(dev_alloc(ctx, (size_t)std::max<int64_t>(first->length, 1) * 4, &seed_ids));
+      BGPU_TRY(interner_intern(ds.interner.get(), *first, first->length, (int32_t*)seed_ids->p, true));
+    }
   }
-  BGPU_TRY(index_dictionary(g, ds, d, &map, &identity));
+  const int64_t n = d.length;
+  BGPU_TRY(dev_alloc(ctx, (size_t)std::max<int64_t>(n, 1) * 4, &ds.last_remap));
+  BGPU_TRY(interner_intern(ds.interner.get(), d, n, (int32_t*)ds.last_remap->p, false));
   ds.last = c.dict;
-  ds.last_remap = nullptr;
-  if (!identity) {
-    const int64_t n = d.length;
-    BGPU_TRY(dev_alloc(ctx, (size_t)n * 4, &ds.last_remap));
-    BGPU_CUDA(ctx, cudaMemcpyAsync(ds.last_remap->p, map.data(), (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
-    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // `map` dies here
-    *remap = (const int32_t*)ds.last_remap->p;
-  }
+  *remap = (const int32_t*)ds.last_remap->p;
   return BGPU_OK;
 }
 
@@ -238,6 +196,14 @@ static int upload_canonical_dictionary(bgpu_agg* g, size_t i, std::shared_ptr<Co
   const bgpu_agg::DictState& ds = g->dicts[i];
   if (ds.canon_dev) {  // fast path: the (only) dictionary seen is the canonical one and already lives on the device
     *out = ds.canon_dev;
+    return BGPU_OK;
+  }
+  if (ds.interner) {  // every value folded in, in id order
+    Column proto;
+    proto.format = ds.value_format; proto.kind = ds.value_kind; proto.flags = ARROW_FLAG_NULLABLE;
+    auto d = std::make_shared<Column>();
+    BGPU_TRY(interner_export(ds.interner.get(), proto, d.get()));
+    *out = d;
     return BGPU_OK;
   }
   auto d = std::make_shared<Column>();
@@ -269,6 +235,7 @@ struct Bound {
   JitArgs args{};
   AccPlan ap{};
   const JitModule* mod = nullptr;
+  std::vector<DevAllocPtr> ids;  // interned group columns: the batch's ids (freed on the stream once the kernels have run)
 };
 enum JitKernel : int { JK_FUSED = 0, JK_INTERN = 0, JK_ACC_SHARED = 1, JK_ACC_GLOBAL = 2, JK_SKETCH = 3 };  // index into the module of its kind
 
@@ -281,6 +248,7 @@ static int bind_value_atom(bgpu_ctx* ctx, const bgpu_batch* batch, const HAtom& 
   const int32_t s = jit_slot(&b->sh, h.col);
   if (s < 0) return ctx->fail(BGPU_EUNSUPPORTED, "aggregate reads more than 24 distinct columns");
   JitSlot& sl = b->sh.slots[(size_t)s];
+  if (sl.key_use && sl.kind != c.kind) return ctx->fail(BGPU_EUNSUPPORTED, "a wide (interned) group column that is also an aggregate argument");
   sl.kind = c.kind; sl.width = c.width; sl.vk = h.vk; sl.value_use = true;
   sl.nullable = c.validity != nullptr;
   b->args.col[s] = c.values;
@@ -298,6 +266,26 @@ static int bind_batch(bgpu_agg* g, const bgpu_batch* batch, Bound* b) {
     const Column& c = batch->cols[(size_t)bc];
     const Column& f = g->fields[(size_t)g->group_cols[(size_t)i]];
     if (!same_shape(c, f)) return ctx->fail(BGPU_EINVAL, "group column " + f.name + " does not match input_schema");
+    if (g->key_interned[(size_t)i]) {
+      // a wide group column: its values become dense ids (interner.cu) and enter the packed key like dictionary
+      // indices: 4 bytes, -1 = null
+      if (!g->interners[(size_t)i]) BGPU_TRY(interner_create(ctx, &g->interners[(size_t)i]));
+      DevAllocPtr ids;
+      BGPU_TRY(dev_alloc(ctx, (size_t)std::max<int64_t>(batch->n_rows, 1) * 4, &ids));
+      BGPU_TRY(interner_intern(g->interners[(size_t)i].get(), c, batch->n_rows, (int32_t*)ids->p, false));
+      b->ids.push_back(ids);
+      // the ids are a column of their own (slot keyed beyond any batch column): the same batch column may also be an
+      // aggregate argument or a filter operand, read by value through its own slot
+      const int32_t s = jit_slot(&b->sh, 100000 + i);
+      if (s < 0) return ctx->fail(BGPU_EUNSUPPORTED, "aggregate reads more than 24 distinct columns");
+      JitSlot& sl = b->sh.slots[(size_t)s];
+      sl.kind = K_DICT32; sl.width = 4; sl.key_use = true; sl.nullable = false; sl.remap = false;
+      b->args.col[s] = ids->p;
+      b->args.valid[s] = nullptr;
+      b->args.aux[s] = nullptr;
+      b->sh.key_slot.push_back(s);
+      continue;
+    }
     const int32_t* remap = nullptr;
     if (c.kind == K_DICT32) BGPU_TRY(canonicalize_dictionary(g, i, c, &remap));
     const int32_t s = jit_slot(&b->sh, bc);
@@ -320,6 +308,7 @@ static int bind_batch(bgpu_agg* g, const bgpu_batch* batch, Bound* b) {
     const int32_t s = jit_slot(&b->sh, h.col);
     if (s < 0) return ctx->fail(BGPU_EUNSUPPORTED, "aggregate reads more than 24 distinct columns");
     JitSlot& sl = b->sh.slots[(size_t)s];
+    if (sl.key_use && sl.kind != c.kind) return ctx->fail(BGPU_EUNSUPPORTED, "a wide (interned) group column that is also a filter column");
     sl.kind = c.kind; sl.width = c.width; sl.vk = h.vk; sl.filter_use = true;
     sl.nullable = c.validity != nullptr;
     b->args.col[s] = c.values;
@@ -404,6 +393,8 @@ static int specialise(bgpu_agg* g, Bound* b, int kernels, int T, int R, int min_
   key.reserve(g->plan_key.size() + 256);
   key.append((const char*)&g->ctx->device, sizeof(int));
   key += g->plan_key;
+  key.push_back(g->interned_mode ? 'I' : 'i');  // the key layout the source is generated for
+  key.append((const char*)g->key_interned.data(), g->key_interned.size());
   shape_key(b->sh, &key);
   {
     std::lock_guard<std::mutex> lk(mu);
@@ -469,6 +460,7 @@ static int write_counters(bgpu_agg* g, const uint32_t* h) {
 // counters layout: [0] n_groups, [1] table overflow, [2] string key too long, [3] arithmetic overflow, [4] fused abort
 static int check_common_flags(bgpu_agg* g, const uint32_t* h) {
   bgpu_ctx* ctx = g->ctx;
+  if (h[2]) g->key_too_long = true;
   if (h[2]) return ctx->fail(BGPU_EUNSUPPORTED, "string group key longer than the packed-key budget (" +
                                                     std::to_string(16 / std::max<size_t>(1, g->group_cols.size()) - 1) + " bytes)");
   if (h[3]) return ctx->fail(BGPU_EOVERFLOW, "Arithmetic overflow in an aggregate argument (Decimal128)");
@@ -885,7 +877,26 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows, const bgpu_batch*
   return BGPU_OK;
 }
 
+static int agg_update_body(bgpu_agg* g, const bgpu_batch* batch, AggAsyncReq* req);
+
 int agg_update_impl(bgpu_agg* g, const bgpu_batch* batch, AggAsyncReq* req) {
+  g->key_too_long = false;
+  const int rc = agg_update_body(g, batch, req);
+  if (rc == BGPU_OK || !g->key_too_long) return rc;
+  // A string key did not fit its inline field. Nothing of this stream has been aggregated yet: switch the key layout to
+  // interned ids (keys of any width) and run the batch again. Later in a stream the error stands.
+  g->key_too_long = false;
+  if (g->any_committed || g->interned_mode || !g->pass_chunks.empty() || agg_key_layout(g, true) != BGPU_OK) return rc;
+  const uint32_t zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  BGPU_TRY(write_counters(g, zero));
+  g->n_groups = 0;
+  g->fused_rung = 0;
+  g->async_ready = false;
+  BGPU_TRY(agg_resize(g, g->max_groups, 0));  // the slot size follows the key width
+  return agg_update_body(g, batch, req);
+}
+
+static int agg_update_body(bgpu_agg* g, const bgpu_batch* batch, AggAsyncReq* req) {
   bgpu_ctx* ctx = g->ctx;
   if (req) req->launched = false;
   const int64_t n_rows = batch->n_rows;
@@ -932,8 +943,8 @@ int agg_async_result(bgpu_agg* g, AggAsyncReq* req, bool* replay) {
   if (cudaEventElapsedTime(&ms, req->k0, req->k1) == cudaSuccess) g->hot_kernel_ms += ms;
   req->launched = false;
   // h = {committed, n_groups, counters[1..6]}: counters[2] string key too long, counters[3] arithmetic overflow
-  const uint32_t c[8] = {h[1], h[2], h[3], h[4], h[5], h[6], h[7], 0};
-  BGPU_TRY(check_common_flags(g, c));
+  // a launch that did not commit (capacity, table growth, a key too long for the inline layout, an arithmetic overflow)
+  // is run again synchronously: that path grows / switches / reports
   if (h[0]) {
     g->n_groups = h[1];
     g->any_committed = true;
@@ -1037,7 +1048,15 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) try {
     c.owned.push_back(valid);
     c.validity = (uint8_t*)valid->p;
     kc.valid = (uint32_t*)valid->p;
-    if (f.kind == K_UTF8 || f.kind == K_BINARY) {
+    if (g->key_interned[i]) {
+      // the packed key holds the value's id: emitted as Int32, looked up in the interner after the kernel
+      DevAllocPtr ids;
+      BGPU_TRY(dev_alloc(ctx, (size_t)n1 * 4, &ids));
+      kc.kind = K_FIXED; kc.width = 4;
+      kc.values = ids->p;
+      c.values = ids->p;
+      c.owned.push_back(ids);
+    } else if (f.kind == K_UTF8 || f.kind == K_BINARY) {
       DevAllocPtr offs, data;
       const size_t cap = (size_t)n1 * (size_t)std::max(1, g->key_width[i]) + 16;  // the packed key bounds every string
       BGPU_TRY(dev_alloc(ctx, (size_t)(n + 1) * 4, &offs));
@@ -1130,6 +1149,18 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) try {
       ctx->launches += 2;
       BGPU_CUDA(ctx, cudaGetLastError());
     }
+  }
+  for (size_t i = 0; i < g->group_cols.size(); i++) {  // interned key columns: ids -> values
+    if (!g->key_interned[i]) continue;
+    const Column& f = g->fields[(size_t)g->group_cols[i]];
+    Column proto;
+    proto.name = f.name; proto.format = f.format; proto.flags = f.flags; proto.kind = f.kind; proto.width = f.width;
+    Column looked_up;
+    if (!g->interners[i]) BGPU_TRY(interner_create(ctx, &g->interners[i]));  // a stream without rows
+    const Column& idc = out->cols[i];
+    BGPU_TRY(interner_take(g->interners[i].get(), (const int32_t*)idc.values, (const uint32_t*)idc.validity, n, proto, &looked_up));
+    looked_up.owned.insert(looked_up.owned.end(), idc.owned.begin(), idc.owned.end());
+    out->cols[i] = std::move(looked_up);
   }
   trace.mark("emit kernels");
   uint32_t h[8];

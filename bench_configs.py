@@ -143,13 +143,34 @@ def run_cfg5(bb, ctx, comm, torch, dist, dev, stream, rank, world, total=1_000_0
         u = torch.rand(n, device=dev, generator=g, dtype=torch.float64)
         return torch.exp(u * math.log(domain + 1.0)).floor_().clamp_(1, domain).to(torch.int64)
     id4, id6 = zipf(k), zipf(max(1, total // k))
+    # id1 / id3 are Dictionary<Int32, Utf8> ("id%03d" over k values, "id%010d" over total / k values), as
+    # groupby-datafusion.py:56 reads them; the dictionaries are built on the device
+    keep = []
+
+    def dict_col(card, digits):
+        i = torch.arange(1, card + 1, device=dev, dtype=torch.int64)
+        data = torch.empty((card, 2 + digits), dtype=torch.uint8, device=dev)
+        data[:, 0], data[:, 1] = ord("i"), ord("d")
+        for p in range(digits):
+            data[:, 2 + p] = ((i // (10 ** (digits - 1 - p))) % 10 + 48).to(torch.uint8)
+        offs = (torch.arange(card + 1, device=dev, dtype=torch.int64) * (2 + digits)).to(torch.int32)
+        idx = (zipf(card) - 1).to(torch.int32)
+        keep.extend([data, offs, idx])
+        return idx, dict(values=idx.data_ptr(), dictionary=dict(values=data.data_ptr(), offsets=offs.data_ptr(), length=card))
+    id1, id1_col = dict_col(k, 3)
+    id3, id3_col = dict_col(max(1, total // k), 10)
     v1 = torch.randint(1, 6, (n,), device=dev, generator=g)
     v2 = torch.randint(1, 16, (n,), device=dev, generator=g)
     v3 = torch.round(torch.rand(n, device=dev, generator=g, dtype=torch.float64) * 1e8) / 1e6
-    schema = pa.schema([("id4", pa.int64()), ("id6", pa.int64()), ("v1", pa.int64()), ("v2", pa.int64()), ("v3", pa.float64())])
-    cols = (id4, id6, v1, v2, v3)
-    batch = bb.DeviceBatch.wrap_device(ctx, schema, [dict(values=t.data_ptr()) for t in cols], n, keepalive=cols)
-    queries = [("q4", "avg(v1..v3) by id4 (k=1e2)", [0], [("avg", 2, "v1"), ("avg", 3, "v2"), ("avg", 4, "v3")]),
+    dtype = pa.dictionary(pa.int32(), pa.string())
+    schema = pa.schema([("id4", pa.int64()), ("id6", pa.int64()), ("v1", pa.int64()), ("v2", pa.int64()), ("v3", pa.float64()),
+                        ("id1", dtype), ("id3", dtype)])
+    cols = (id4, id6, v1, v2, v3, id1, id3)
+    batch = bb.DeviceBatch.wrap_device(ctx, schema, [dict(values=t.data_ptr()) for t in cols[:5]] + [id1_col, id3_col], n,
+                                       keepalive=(cols, keep))
+    queries = [("q1", "sum(v1) by id1 (Dictionary key, k=1e2)", [5], [("sum", 2, "v1")]),
+               ("q3", "sum(v1), avg(v3) by id3 (Dictionary key, k=1e7)", [6], [("sum", 2, "v1"), ("avg", 4, "v3")]),
+               ("q4", "avg(v1..v3) by id4 (k=1e2)", [0], [("avg", 2, "v1"), ("avg", 3, "v2"), ("avg", 4, "v3")]),
                ("q5", "sum(v1..v3) by id6 (k=1e7)", [1], [("sum", 2, "v1"), ("sum", 3, "v2"), ("sum", 4, "v3")])]
     out, ok = {}, True
     for name, text, gb, aggs in queries:
@@ -182,7 +203,7 @@ def run_cfg5(bb, ctx, comm, torch, dist, dev, stream, rank, world, total=1_000_0
             if i >= 2 and (best is None or t[3].item() < best[3]):
                 best = t.tolist()
         # exact checks over all ranks: number of groups, and the first aggregate's counts / sums add up to the input's
-        keycol = cols[gb[0]]
+        keycol = cols[gb[0]].to(torch.int64)
         dmax = keycol.max().reshape(1).clone()
         dist.all_reduce(dmax, op=dist.ReduceOp.MAX)  # the same tensor size on every rank
         domain = int(dmax.item()) + 1

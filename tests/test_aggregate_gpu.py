@@ -117,12 +117,42 @@ def test_int64_sum_wraps(bb, ctx, oracle):
     assert sorted(out.column(1).to_pylist()) == [-(2**62), -5]
 
 
-def test_long_string_key_is_an_error(bb, ctx):
-    b = pa.RecordBatch.from_arrays([pa.array(["short", "this string is far too long to pack"]), pa.array([1, 2])],
+def test_long_string_key_switches_to_interned_keys(bb, ctx, oracle):
+    """A string key beyond its inline field in the FIRST batch of a stream: the key layout switches to interned ids
+    (GroupValuesRows has no width limit) and the batch runs again; the result is the oracle's."""
+    b = pa.RecordBatch.from_arrays([pa.array(["short", "this string is far too long to pack", "short", None, "",
+                                              "this string is far too long to pack"]), pa.array([1, 2, 3, 4, 5, 6])],
                                    names=["k", "v"])
-    agg = bb.GpuAggregateExec(ctx, bb.AggregateMode.Partial, [0], [("sum", 1, "s")], b.schema)
-    with pytest.raises(bb.BgpuError):
-        agg.update(b)
+    out = run_both(bb, ctx, oracle, [b, b.slice(1, 3)], ["k"], [("sum", "v", "s"), ("count", None, "n")], 1)
+    assert out.num_rows == 4
+
+
+def test_long_string_key_after_committed_batches_is_an_error(bb, ctx):
+    """Later in a stream the table is keyed inline already: the error stands (and names the budget)."""
+    short = pa.RecordBatch.from_arrays([pa.array(["a", "bc"]), pa.array([1, 2])], names=["k", "v"])
+    long = pa.RecordBatch.from_arrays([pa.array(["this string is far too long to pack"]), pa.array([3])], names=["k", "v"])
+    agg = bb.GpuAggregateExec(ctx, bb.AggregateMode.Partial, [0], [("sum", 1, "s")], short.schema)
+    agg.update(short)
+    with pytest.raises(bb.BgpuError, match="packed-key budget"):
+        agg.update(long)
+
+
+@pytest.mark.parametrize("groups", [["s"], ["s", "flag", "k64"], ["k64", "dec"], ["k64", "small", "date", "s"], ["dec", "s", "b"]])
+def test_group_keys_wider_than_16_bytes(bb, ctx, oracle, groups):
+    """Keys that do not fit the 16-byte packed key - strings up to 51 bytes, Int64 + Decimal128, four columns - go through
+    the interner: bit-exact against the oracle through Partial (two partitions, several batches each) and Final."""
+    rng = np.random.default_rng(41)
+    whole = random_batch(rng, 60_000, with_dict=False)
+    batches = [whole.slice(i, 8192) for i in range(0, whole.num_rows, 8192)]
+    run_both(bb, ctx, oracle, batches, groups, Q1_AGGS, n_partials=2)
+
+
+def test_wide_keys_many_distinct_values_grow_the_interner(bb, ctx, oracle):
+    rng = np.random.default_rng(43)
+    n = 300_000
+    keys = [f"customer#{int(i):09d}-{'x' * int(i % 7)}" for i in rng.integers(0, 200_000, n)]
+    b = pa.RecordBatch.from_arrays([pa.array(keys), pa.array(rng.integers(-5, 5, n), type=pa.int64())], names=["k", "v"])
+    run_both(bb, ctx, oracle, [b.slice(0, 100_000), b.slice(100_000)], ["k"], [("sum", "v", "s"), ("count", None, "n")], 2)
 
 
 def test_empty_input(bb, ctx):
