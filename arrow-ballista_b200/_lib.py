@@ -118,6 +118,8 @@ SIGNATURES = {
     "bgpu_ipc_reader_next": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "bgpu_ipc_reader_close": (None, [C.c_void_p]),
     "bgpu_debug_lz4_frame_decode_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]),
+    "bgpu_batch_sort": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_uint8), C.POINTER(C.c_uint8), C.c_int32,
+                                  C.POINTER(C.c_void_p)]),
     "bgpu_batch_concat": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int32, C.POINTER(C.c_void_p)]),
 }
 

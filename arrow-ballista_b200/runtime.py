@@ -192,6 +192,17 @@ class DeviceBatch:
         ctx.check(lib().bgpu_batch_concat(ctx._h, hs, len(batches), C.byref(out)))
         return cls(ctx, out)
 
+    def sort(self, sort_cols, descending=None, nulls_first=None):
+        """A stable sort of the rows by the columns `sort_cols` (bgpu_batch_sort); `descending` / `nulls_first`: one flag
+        per key (DataFusion's SortOptions; default ascending, nulls last)."""
+        k = len(sort_cols)
+        cols = (C.c_int32 * k)(*sort_cols)
+        desc = (C.c_uint8 * k)(*[1 if x else 0 for x in (descending or [False] * k)])
+        nf = (C.c_uint8 * k)(*[1 if x else 0 for x in (nulls_first or [False] * k)])
+        out = C.c_void_p()
+        self.ctx.check(lib().bgpu_batch_sort(self.ctx._h, self._h, cols, desc, nf, k, C.byref(out)))
+        return DeviceBatch(self.ctx, out)
+
     def close(self):
         if getattr(self, "_h", None):
             lib().bgpu_batch_destroy(self._h)

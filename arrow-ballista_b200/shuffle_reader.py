@@ -183,20 +183,22 @@ class CoalesceTasksExec:
     """`input` is the child: a plan node with `execute(p)` (kept as `.input`, what `children()` returns), or just that
     function (returns an iterable of batches); `partitions` the task group's input partitions."""
 
-    def __init__(self, input, partitions, schema=None):
+    def __init__(self, input, partitions, schema=None, order_by=None, ctx=None):
+        """order_by: [(column index, descending, nulls_first)] when the child is ordered (coalesce_tasks.rs:148-173)."""
         self.input = input if callable(getattr(input, "execute", None)) else None
         self.execute_partition = input.execute if self.input is not None else input
         self.partitions, self._schema = list(partitions), schema
+        self.order_by, self.ctx = (list(order_by) if order_by else None), ctx
 
     def children(self):
         return [self.input] if self.input is not None else []
 
     def with_new_children(self, children):
         # coalesce_tasks.rs:118-128: same partitions, new input
-        return CoalesceTasksExec(children[0], self.partitions, self._schema)
+        return CoalesceTasksExec(children[0], self.partitions, self._schema, self.order_by, self.ctx)
 
     def output_ordering(self):
-        return None  # the unordered fan-in; streaming_merge over ordered children is not built
+        return self.order_by  # coalesce_tasks.rs:109-111: the child's ordering survives the ordered fan-in
 
     def schema(self):
         return self._schema
@@ -208,6 +210,21 @@ class CoalesceTasksExec:
     def execute(self, _partition=0):
         if len(self.partitions) == 1:
             yield from self.execute_partition(self.partitions[0])
+            return
+        if self.order_by:
+            # the ordered fan-in: the reference merges the partitions' sorted streams (streaming_merge, ties to the lower
+            # stream index); here: the batches concatenated in stream order, then one STABLE sort on the device
+            batches = []
+            for p in self.partitions:
+                for b in self.execute_partition(p):
+                    if not isinstance(b, DeviceBatch):
+                        b = DeviceBatch.upload(self.ctx, b)
+                    batches.append(b)
+            if not batches:
+                return
+            ctx = self.ctx or batches[0].ctx
+            whole = batches[0] if len(batches) == 1 else DeviceBatch.concat(ctx, batches)
+            yield whole.sort([c for c, _, _ in self.order_by], [d for _, d, _ in self.order_by], [n for _, _, n in self.order_by])
             return
         live = [iter(self.execute_partition(p)) for p in self.partitions]
         while live:

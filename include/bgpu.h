@@ -340,6 +340,16 @@ int bgpu_debug_lz4_frame_decode_host(bgpu_ctx* ctx, const uint8_t* frame, uint64
  * has nulls). Dictionary columns: BGPU_EUNSUPPORTED. */
 int bgpu_batch_concat(bgpu_ctx* ctx, const bgpu_batch* const* batches, int32_t n, bgpu_batch** out);
 
+/* ---- stable sort of a device batch: the ordered fan-in of CoalesceTasksExec --------------------------
+ * When the child of a task group is ordered, the reference merges its partitions' sorted streams with `streaming_merge`
+ * (/root/reference/ballista/core/src/execution_plans/coalesce_tasks.rs:148-173; ties go to the lower stream index). On
+ * the device: bgpu_batch_concat of the partitions' batches in stream order, then this STABLE sort by the sort expressions -
+ * for sorted inputs the same rows in the same order. sort_cols index the batch's columns (fixed-width incl. Decimal128 and
+ * floats in IEEE total order, Boolean, Utf8 / Binary up to 4096 bytes); descending[k] / nulls_first[k] are the
+ * SortOptions of key k (NULL pointers = ascending, nulls last). Dictionary-encoded KEY columns: BGPU_EUNSUPPORTED. */
+int bgpu_batch_sort(bgpu_ctx* ctx, const bgpu_batch* batch, const int32_t* sort_cols, const uint8_t* descending,
+                    const uint8_t* nulls_first, int32_t n_keys, bgpu_batch** out);
+
 #ifdef __cplusplus
 }
 #endif
