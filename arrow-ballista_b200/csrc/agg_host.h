@@ -64,6 +64,7 @@ struct bgpu_agg {
     std::string value_format = "u";
     ColKind value_kind = K_UTF8;
     std::shared_ptr<bgpu::Interner> interner;  // exact path: the canonical dictionary, built on the device (interner.cu)
+    std::shared_ptr<bgpu::Interner> spare;     // the last stream's interner, emptied by bgpu_agg_reset (capacity kept)
     std::shared_ptr<Column> canon_dev;  // fast path: the first dictionary seen IS the canonical one (device resident)
     std::shared_ptr<Column> last;  // last batch dictionary seen (kept alive so its identity cannot be recycled)
     DevAllocPtr last_remap;        // nullptr = identity

@@ -9,6 +9,7 @@
 #include <algorithm>
 
 #include "agg_host.h"
+#include "interner.h"
 #include "jit.h"
 
 using namespace bgpu;
@@ -381,11 +382,17 @@ extern "C" int bgpu_agg_reset(bgpu_agg* g) try {
   g->n_groups = 0;
   g->passthrough = false;
   g->any_committed = false;
-  for (auto& in : g->interners) in = nullptr;  // a new stream interns afresh
+  for (auto& in : g->interners)  // a new stream interns afresh, in the room the last one grew
+    if (in) BGPU_TRY(bgpu::interner_clear(in.get()));
   g->pass_chunks.clear();
   g->emitted = false;
   g->hot_kernel_ms = 0.0;
-  for (auto& d : g->dicts) d = bgpu_agg::DictState();
+  for (auto& d : g->dicts) {
+    std::shared_ptr<bgpu::Interner> spare = d.interner ? d.interner : d.spare;
+    if (spare) BGPU_TRY(bgpu::interner_clear(spare.get()));
+    d = bgpu_agg::DictState();
+    d.spare = spare;
+  }
   return BGPU_OK;
 } catch (const std::exception& e) {
   return bgpu::abi_guard(g ? g->ctx : nullptr, e);  // nothing is thrown across the C ABI

@@ -173,7 +173,8 @@ static int canonicalize_dictionary(bgpu_agg* g, int32_t i, const Column& c, cons
   // exact path, on the device: every dictionary is folded into the column's Interner (interner.cu); remap[j] = the
   // canonical id of value j (-1 for a null value). A canonical dictionary from the fast path seeds it with ids = indices.
   if (!ds.interner) {
-    BGPU_TRY(interner_create(ctx, &ds.interner));
+    if (ds.spare) std::swap(ds.interner, ds.spare);  // emptied by bgpu_agg_reset, capacity kept
+    else BGPU_TRY(interner_create(ctx, &ds.interner));
     if (ds.canon_dev) {
       std::shared_ptr<Column> first = ds.canon_dev;
       ds.canon_dev = nullptr;

@@ -15,6 +15,7 @@ namespace bgpu {
 namespace {
 constexpr int kThreads = 256;
 constexpr uint32_t kDead = 0xffffffffu;
+constexpr uint32_t kMaxProbes = 512;   // at load <= 1/2 a probe sequence this long does not happen; it means "full"
 struct Slot { unsigned long long tag; uint32_t idp1; uint32_t pad; };   // tag 0 = empty; idp1 0 = being published
 struct Span { unsigned long long off; uint32_t len; uint32_t pad; };
 struct Counters { uint32_t n_ids; uint32_t flags; unsigned long long data_bytes; };  // flags: 1 ids/table full, 2 arena full
@@ -52,16 +53,21 @@ __global__ void __launch_bounds__(kThreads) intern_kernel(const __grid_constant_
     const unsigned long long tag = h | 1ULL;
     uint32_t i = (uint32_t)(h >> 17) & a.mask;
     int32_t result = -2;
-    for (uint32_t probes = 0; probes <= a.mask; probes++, i = (i + 1) & a.mask) {
+    // once the table or the arena is known to be full the launch is void (the host grows and runs the batch again): later rows do not
+    // probe at all, and no row walks more than kMaxProbes slots of a nearly full table
+    if (*(volatile uint32_t*)&a.cnt->flags) { a.out_ids[r] = -2; continue; }
+    const uint32_t max_probes = a.mask < kMaxProbes ? a.mask : kMaxProbes;
+    for (uint32_t probes = 0; probes <= max_probes; probes++, i = (i + 1) & a.mask) {
       Slot* s = a.slots + i;
       unsigned long long t = *(volatile unsigned long long*)&s->tag;
       if (t == 0) {
         t = atomicCAS(&s->tag, 0ULL, tag);
-        if (t == 0) {  // this thread owns the slot: allocate an id and arena bytes, copy, publish
-          const uint32_t id = a.seed ? (uint32_t)r : atomicAdd(&a.cnt->n_ids, 1u);
-          if (id >= a.cap_ids) { atomicOr(&a.cnt->flags, 1u); *(volatile uint32_t*)&s->idp1 = kDead; break; }
+        if (t == 0) {  // this thread owns the slot: arena bytes first, then an id (so that every id handed out below the
+                       // capacity has its span), copy, publish
           const unsigned long long off = atomicAdd(&a.cnt->data_bytes, (unsigned long long)len);
           if (off + len > a.cap_data) { atomicOr(&a.cnt->flags, 2u); *(volatile uint32_t*)&s->idp1 = kDead; break; }
+          const uint32_t id = a.seed ? (uint32_t)r : atomicAdd(&a.cnt->n_ids, 1u);
+          if (id >= a.cap_ids) { atomicOr(&a.cnt->flags, 1u); *(volatile uint32_t*)&s->idp1 = kDead; break; }
           for (uint32_t k = 0; k < len; k++) a.arena[off + k] = p[k];
           a.spans[id] = Span{off, len, 0};
           __threadfence();
@@ -160,31 +166,42 @@ int interner_create(bgpu_ctx* ctx, std::shared_ptr<Interner>* out) {
 
 uint32_t interner_size(const Interner* in) { return in->n_ids; }
 
-static int grow(Interner* in, bool table, uint64_t want_ids, uint64_t want_data) {
+// Forget every value, keep the capacity (a new stream through the same operator usually needs the same room again).
+int interner_clear(Interner* in) {
   bgpu_ctx* ctx = in->ctx;
-  if (table) {
-    uint32_t cap = in->cap_slots;
-    while ((uint64_t)cap / 2 < want_ids) {
-      if (cap >= (1u << 30)) return ctx->fail(BGPU_EUNSUPPORTED, "interner: more than 2^29 distinct values");
-      cap <<= 1;
-    }
-    DevAllocPtr slots, spans;
-    BGPU_TRY(dev_alloc(ctx, (size_t)cap * sizeof(Slot), &slots));
-    BGPU_TRY(dev_alloc(ctx, (size_t)(cap / 2) * sizeof(Span), &spans));
-    BGPU_CUDA(ctx, cudaMemsetAsync(slots->p, 0, (size_t)cap * sizeof(Slot), ctx->stream));
-    BGPU_CUDA(ctx, cudaMemcpyAsync(spans->p, in->spans->p, (size_t)in->cap_ids * sizeof(Span), cudaMemcpyDeviceToDevice, ctx->stream));
-    rehash_kernel<<<grid_for(ctx, in->cap_slots), kThreads, 0, ctx->stream>>>((const Slot*)in->slots->p, in->cap_slots, (Slot*)slots->p, cap - 1);
-    ctx->launches++;
-    BGPU_CUDA(ctx, cudaGetLastError());
-    in->slots = slots; in->spans = spans; in->cap_slots = cap; in->cap_ids = cap / 2;
+  BGPU_CUDA(ctx, cudaMemsetAsync(in->slots->p, 0, (size_t)in->cap_slots * sizeof(Slot), ctx->stream));
+  BGPU_CUDA(ctx, cudaMemsetAsync(in->cnt->p, 0, sizeof(Counters), ctx->stream));
+  in->n_ids = 0;
+  return BGPU_OK;
+}
+
+// Make room: a table for `want_ids` ids (never smaller than now) and an arena of `want_data` bytes. The table is ALWAYS
+// rebuilt: slots whose owner ran out of room (kDead) must not survive into the next attempt.
+static int grow(Interner* in, uint64_t want_ids, uint64_t want_data) {
+  bgpu_ctx* ctx = in->ctx;
+  uint32_t cap = in->cap_slots;
+  while ((uint64_t)cap / 2 < want_ids) {
+    if (cap >= (1u << 30)) return ctx->fail(BGPU_EUNSUPPORTED, "interner: more than 2^29 distinct values");
+    cap <<= 1;
   }
+  DevAllocPtr slots, spans = in->spans;
+  BGPU_TRY(dev_alloc(ctx, (size_t)cap * sizeof(Slot), &slots));
+  BGPU_CUDA(ctx, cudaMemsetAsync(slots->p, 0, (size_t)cap * sizeof(Slot), ctx->stream));
+  if (cap != in->cap_slots) {
+    BGPU_TRY(dev_alloc(ctx, (size_t)(cap / 2) * sizeof(Span), &spans));
+    BGPU_CUDA(ctx, cudaMemcpyAsync(spans->p, in->spans->p, (size_t)in->cap_ids * sizeof(Span), cudaMemcpyDeviceToDevice, ctx->stream));
+  }
+  rehash_kernel<<<grid_for(ctx, in->cap_slots), kThreads, 0, ctx->stream>>>((const Slot*)in->slots->p, in->cap_slots, (Slot*)slots->p, cap - 1);
+  ctx->launches++;
+  BGPU_CUDA(ctx, cudaGetLastError());
+  in->slots = slots; in->spans = spans; in->cap_slots = cap; in->cap_ids = cap / 2;
   if (want_data > in->cap_data) {
-    uint64_t cap = in->cap_data;
-    while (cap < want_data) cap <<= 1;
+    uint64_t dcap = in->cap_data;
+    while (dcap < want_data) dcap <<= 1;
     DevAllocPtr arena;
-    BGPU_TRY(dev_alloc(ctx, cap, &arena));
+    BGPU_TRY(dev_alloc(ctx, dcap, &arena));
     BGPU_CUDA(ctx, cudaMemcpyAsync(arena->p, in->arena->p, in->cap_data, cudaMemcpyDeviceToDevice, ctx->stream));
-    in->arena = arena; in->cap_data = cap;
+    in->arena = arena; in->cap_data = dcap;
   }
   return BGPU_OK;
 }
@@ -198,7 +215,8 @@ int interner_intern(Interner* in, const Column& col, int64_t n, int32_t* d_ids, 
   if (!var && col.kind != K_FIXED) return ctx->fail(BGPU_EUNSUPPORTED, "interner: column kind");
   if (seed) {
     if (in->n_ids) return ctx->fail(BGPU_EINVAL, "internal: seeding a non-empty interner");
-    BGPU_TRY(grow(in, (uint64_t)n > in->cap_ids, (uint64_t)n, 0));
+    const uint64_t bytes = var ? (col.data_bytes > 0 ? (uint64_t)col.data_bytes : 0) : (uint64_t)n * (uint64_t)col.width;
+    if ((uint64_t)n > in->cap_ids || bytes > in->cap_data) BGPU_TRY(grow(in, (uint64_t)n, bytes));
   }
   Counters* pin = (Counters*)((uint8_t*)ctx->pinned + 1024);
   for (int attempt = 0; attempt < 40; attempt++) {
@@ -229,13 +247,17 @@ int interner_intern(Interner* in, const Column& col, int64_t n, int32_t* d_ids, 
     // found again; ids handed out beyond the capacity were never published)
     Counters reset = c;
     reset.flags = 0;
-    reset.n_ids = std::min(c.n_ids, in->cap_ids);
+    reset.n_ids = seed ? 0u : std::min(c.n_ids, in->cap_ids);
+    reset.data_bytes = std::min<unsigned long long>(c.data_bytes, in->cap_data);
     *pin = reset;
     BGPU_CUDA(ctx, cudaMemcpyAsync(in->cnt->p, pin, sizeof(Counters), cudaMemcpyHostToDevice, ctx->stream));
     BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    const uint64_t want_ids = (c.flags & 1) ? std::max<uint64_t>((uint64_t)in->cap_ids * 4, (uint64_t)reset.n_ids + 1) : 0;
+    uint64_t want_ids = in->cap_ids;
+    if (c.flags & 1)  // x4, or an eighth of the batch if that is more; never more than the batch can add
+      want_ids = std::min<uint64_t>(std::max<uint64_t>((uint64_t)in->cap_ids * 4, (uint64_t)reset.n_ids + (uint64_t)n / 8),
+                                    (uint64_t)reset.n_ids + (uint64_t)n + 1024);
     const uint64_t want_data = (c.flags & 2) ? std::max<uint64_t>(in->cap_data * 4, c.data_bytes + (1u << 20)) : 0;
-    BGPU_TRY(grow(in, (c.flags & 1) != 0, std::min<uint64_t>(want_ids, (uint64_t)reset.n_ids + (uint64_t)n + 1024), want_data));
+    BGPU_TRY(grow(in, want_ids, want_data));
   }
   return ctx->fail(BGPU_EUNSUPPORTED, "interner: could not make room for the batch's values");
 }

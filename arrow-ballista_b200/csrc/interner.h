@@ -8,6 +8,8 @@ namespace bgpu {
 struct Interner;
 int interner_create(bgpu_ctx* ctx, std::shared_ptr<Interner>* out);
 uint32_t interner_size(const Interner* in);
+// forget every value, keep the capacity
+int interner_clear(Interner* in);
 // d_ids[r] = id of value r of `col` (utf8 / binary / fixed-width read as bytes), -1 for null rows. Synchronises the stream.
 // seed: the interner is empty and the values are known to be pairwise distinct: value r gets id r.
 int interner_intern(Interner* in, const Column& col, int64_t n, int32_t* d_ids, bool seed);

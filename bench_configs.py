@@ -174,9 +174,6 @@ def run_cfg5(bb, ctx, comm, torch, dist, dev, stream, rank, world, total=1_000_0
                ("q5", "sum(v1..v3) by id6 (k=1e7)", [1], [("sum", 2, "v1"), ("sum", 3, "v2"), ("sum", 4, "v3")])]
     out, ok = {}, True
     for name, text, gb, aggs in queries:
-        if rank == 0:
-            import sys
-            print(f"[cfg5] {name}: {text}", file=sys.stderr, flush=True)
         pop = bb.GpuAggregateExec(ctx, bb.AggregateMode.Partial, gb, aggs, schema)
         fop = bb.GpuAggregateExec(ctx, bb.AggregateMode.FinalPartitioned, gb, aggs, schema)
         best, res, sent, xpath = None, None, 0, ""

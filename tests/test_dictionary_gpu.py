@@ -148,3 +148,34 @@ def ipc_batches(bb, ctx, path):
     with open(path, "rb") as f:
         data = f.read()
     return list(ipc.StreamReader(ctx, data))
+
+
+@pytest.mark.parametrize("distinct", [3_000, 180_000])
+def test_many_dictionaries_with_many_values_fold_into_one(bb, ctx, oracle, distinct):
+    """Every batch brings its OWN dictionary (duplicates inside, values shared between batches - the shape of states that
+    arrive from several ranks): the canonical dictionary the aggregate emits holds every value once, whatever growth of
+    the value table and its byte arena (1 MiB at first) the batches forced; groups and sums are the oracle's."""
+    rng = np.random.default_rng(distinct)
+    batches = []
+    for j in range(3):
+        n = 120_000
+        ids = rng.integers(0, distinct, n)
+        dict_vals = pa.array([f"id{int(i):010d}" for i in ids], type=pa.string())   # an identity dictionary with duplicates
+        key = pa.DictionaryArray.from_arrays(pa.array(np.arange(n, dtype=np.int32)), dict_vals)
+        batches.append(pa.RecordBatch.from_arrays([key, pa.array(rng.integers(-9, 9, n), type=pa.int64())], names=["id3", "v"]))
+    spec = [("sum", 1, "s"), ("count", None, "n")]
+    want = oracle.GroupedAggregate("partial", [0], spec)
+    agg = bb.GpuAggregateExec(ctx, bb.AggregateMode.Partial, [0], spec, batches[0].schema)
+    for round_ in range(2):      # a second stream through the same operator (reset) starts from an empty dictionary again
+        for b in batches:
+            agg.update(b)
+            if round_ == 0:
+                want.update(b)
+        got = agg.emit().download()
+        if round_ == 0:
+            expect = want.emit()
+        from test_aggregate_gpu import assert_same_groups
+        assert_same_groups(got, expect, 1)
+        d = got.column(0).dictionary
+        assert len(d) == len(set(d.to_pylist())) == got.num_rows   # every value once, none invented
+        agg.reset()
