@@ -61,6 +61,9 @@ extern "C" {
     pub fn bgpu_ipc_reader_next(r: *mut BgpuIpcReader, out: *mut *mut BgpuBatch) -> i32;
     pub fn bgpu_ipc_reader_close(r: *mut BgpuIpcReader);
     pub fn bgpu_batch_concat(ctx: *mut BgpuCtx, batches: *const *const BgpuBatch, n: i32, out: *mut *mut BgpuBatch) -> i32;
+    // ordered CoalesceTasksExec: concat in stream order + stable sort == streaming_merge of sorted children
+    pub fn bgpu_batch_sort(ctx: *mut BgpuCtx, batch: *const BgpuBatch, sort_cols: *const i32, descending: *const u8,
+                           nulls_first: *const u8, n_keys: i32, out: *mut *mut BgpuBatch) -> i32;
     // intra-node exchange (replaces files + Flight do_get + reader fan-in)
     pub fn bgpu_small_exchange(ctx: *mut BgpuCtx, comm: *mut c_void, rank: i32, world: i32, batch: *const BgpuBatch,
                                key_cols: *const i32, n_keys: i32, n_partitions: u32, out: *mut *mut BgpuBatch) -> i32;
