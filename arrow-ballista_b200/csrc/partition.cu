@@ -5,13 +5,14 @@
 //   hash = create_hashes(keys, seeds 0,0,0,0); partition = hash % n; per partition, rows in input order.
 //
 // Layout: the batch is cut into G contiguous row chunks, one per persistent CTA (G = resident CTAs).
-//   pass 1 (count):   each CTA histograms its chunk's partition ids in shared memory -> hist[p][chunk]
+//   pass 1 (count):   each CTA hashes its chunk's keys, keeps the partition ids (2 B/row) and histograms them in shared
+//                     memory -> hist[p][chunk]
 //   scan:             exclusive scan of hist in (partition, chunk) order -> base[p][chunk], offsets[p]
-//   pass 2 (scatter): each CTA walks its chunk in tiles of kTile rows; a tile is ranked stably by partition
-//                     with warp match + per-warp counters, every column is staged through shared memory in
-//                     partition order and written out in runs (coalesced), validity bits with atomicOr.
-// HBM traffic per row: key columns twice (pass 1 + pass 2, which scatters them anyway), other columns once,
-// every output byte once: 88 B/row for the Int64-key + 4x8 B payload microbench vs 80 B/row algorithmic.
+//   pass 2 (scatter): each CTA walks its chunk in tiles; a tile is ranked stably by partition (pass 1's ids, warp match +
+//                     per-warp counters), every column is staged through shared memory in partition order and written
+//                     out in runs (coalesced), validity bits with atomicOr.
+// HBM traffic per row: key columns once for the hash, 2 + 2 B for the partition id, every column once in and once out:
+// 92 B/row for the Int64-key + 4x8 B payload microbench vs 80 B/row algorithmic.
 #include <cub/device/device_scan.cuh>
 
 #include "hash.cuh"
@@ -23,7 +24,6 @@ namespace bgpu {
 #define BGPU_PART_THREADS 256
 #endif
 constexpr int kThreads = BGPU_PART_THREADS;
-constexpr int kWarps = kThreads / 32;
 constexpr uint32_t kMaxPartitions = 2048;
 
 // ---- K1: create_hashes -----------------------------------------------------------------------------------
@@ -34,11 +34,28 @@ __global__ void __launch_bounds__(kThreads) hash_kernel(const __grid_constant__ 
 }
 
 // ---- K2: partition ids + per-chunk histogram ----------------------------------------------------------------
+constexpr uint32_t kNoPartition = 0xffffffffu;
+// The lanes of the warp whose id equals this lane's (ids < 2^bits; lanes with valid = false match nobody). MATCH.ANY takes
+// time in proportion to the number of DISTINCT values among the lanes; one ballot per id bit costs the same whatever the
+// ids are.
+__device__ __forceinline__ uint32_t match_bits(uint32_t id, bool valid, int bits) {
+  if (bits <= 4) {  // at most 16 distinct ids: the hardware match wins (n = 8: 1.84 ms against 2.04 ms per 1e8 rows)
+    const uint32_t peers = __match_any_sync(0xffffffffu, valid ? id : kNoPartition);
+    return valid ? peers : 0u;
+  }
+  uint32_t peers = __ballot_sync(0xffffffffu, valid);
+  for (int b = 0; b < bits; b++) {
+    const bool one = (id >> b) & 1u;
+    const uint32_t m = __ballot_sync(0xffffffffu, one);
+    peers &= one ? m : ~m;
+  }
+  return valid ? peers : 0u;
+}
 constexpr int kCountThreads = 1024;  // the chunk layout is the scatter's; the histogram pass just wants residency
 __global__ void __launch_bounds__(kCountThreads)
     count_kernel(const __grid_constant__ KeySet ks, const __grid_constant__ Modulo mod, int64_t n_rows,
                  int64_t chunk_rows, uint32_t* __restrict__ hist /* [n][gridDim.x] */,
-                 uint64_t* __restrict__ out_hashes) {
+                 uint64_t* __restrict__ out_hashes, uint16_t* __restrict__ out_pids /* n <= 2048: the scatter's input */) {
   extern __shared__ uint32_t s_hist[];
   const uint32_t n = mod.n;
   for (uint32_t p = threadIdx.x; p < n; p += kCountThreads) s_hist[p] = 0;
@@ -58,14 +75,18 @@ __global__ void __launch_bounds__(kCountThreads)
       for (int u = 0; u < U; u++) {
         const uint64_t h = hash_u64(k[u]);
         if (out_hashes) out_hashes[r + (int64_t)u * kCountThreads] = h;
-        atomicAdd(&s_hist[partition_of(h, mod)], 1u);
+        const uint32_t p = partition_of(h, mod);
+        out_pids[r + (int64_t)u * kCountThreads] = (uint16_t)p;
+        atomicAdd(&s_hist[p], 1u);  // (electing one lane per distinct id with a warp match was measured slower: 0.30 vs 0.20 ms)
       }
     }
   }
   for (; r < end; r += kCountThreads) {
     const uint64_t h = row_hash(ks, r);
     if (out_hashes) out_hashes[r] = h;
-    atomicAdd(&s_hist[partition_of(h, mod)], 1u);
+    const uint32_t p = partition_of(h, mod);
+    out_pids[r] = (uint16_t)p;
+    atomicAdd(&s_hist[p], 1u);
   }
   __syncthreads();
   for (uint32_t p = threadIdx.x; p < n; p += kCountThreads) hist[(size_t)p * gridDim.x + blockIdx.x] = s_hist[p];
@@ -116,11 +137,15 @@ __global__ void __launch_bounds__(1024) scan_kernel(const uint32_t* __restrict__
 }
 
 // ---- K3: stable scatter ---------------------------------------------------------------------------------------
-// Per tile of THREADS x ITEMS rows: rank every row stably by partition, then move the columns through shared memory
-// in partition order and write them out in runs. Fixed-width columns of 4, 8 and 16 bytes are staged ALL AT ONCE with
-// cp.async (LDGSTS: global -> shared at the row's sorted position, no registers held), so a tile exposes one DRAM
-// latency for all of them instead of one per column; the remaining kinds (1/2-byte values, utf8 (length, start)
-// pairs) go one at a time through a small side buffer while the async copies are in flight, bitmaps with atomics.
+// ONE kernel for the local repartition (bgpu_hash_partition) and for the fused repartition + exchange over peer memory
+// (bgpu_partition_exchange, PEER = true: the destination of a run is the owner rank's window). Per tile of
+// THREADS x ITEMS rows: the partition ids pass 1 left behind (2 B/row; no key is read or hashed again) are ranked stably
+// with warp match + per-warp 16-bit counters; fixed-width columns of 4, 8 and 16 bytes are staged ALL AT ONCE with cp.async
+// (LDGSTS: global -> shared at the row's sorted position, no registers held), so a tile exposes one DRAM latency for all
+// of them; then every column is written out in partition runs, the destination row of a sorted position computed once.
+// The remaining kinds (SIDE = true: 1/2-byte values, utf8 (length, start) pairs, bitmaps with atomics) go one at a time
+// through a small side buffer while the async copies are in flight. The lean instantiation (no SIDE work) fits 64
+// registers: four 256-thread CTAs per SM, so one CTA's loads overlap another's ranking and stores.
 constexpr int kMaxCols = 32;
 struct ScatterCol {
   const void* in;           // fixed values / dict keys / bool bits
@@ -138,14 +163,12 @@ struct AsyncCol { const void* in; void* out; int32_t width; int32_t stage_off; }
 struct ScatterArgs {
   ScatterCol cols[kMaxCols];
   AsyncCol async_cols[kMaxCols];  // the cp.async-staged columns, widest first
-  int8_t side_cols[kMaxCols];     // the columns step 4 has work for (bitmaps, utf8, side-buffer values)
+  int8_t side_cols[kMaxCols];     // the columns with side work (bitmaps, utf8, side-buffer values)
   int32_t n_cols, n_async, n_side;
   int32_t async_width;  // sum of the widths of the async-staged columns
   int32_t side_width;   // bytes per element of the side buffer (0 = none needed)
 };
-
-// peers of this lane's partition id within the warp
-__device__ __forceinline__ uint32_t match_peers(uint32_t pid) { return __match_any_sync(0xffffffffu, pid); }
+constexpr uint32_t kNoPid = 0xffffffffu;
 
 template <int BYTES>
 __device__ __forceinline__ void cp_async(uint32_t smem_dst, const void* gsrc) {
@@ -155,12 +178,12 @@ __device__ __forceinline__ void cp_async(uint32_t smem_dst, const void* gsrc) {
 }
 
 // rows w*32*ITEMS + it*32 + lane of the tile: `in` points at the column's element of this thread's first row
-template <int THREADS, int ITEMS, typename T>
-__device__ __forceinline__ void stage_async(const T* __restrict__ in, uint32_t stage /* shared address */, int valid_items,
+template <int ITEMS, typename T>
+__device__ __forceinline__ void stage_async(const T* __restrict__ in, uint32_t stage /* shared address */, const uint32_t (&pid)[ITEMS],
                                             const uint32_t (&pos)[ITEMS]) {
 #pragma unroll
   for (int it = 0; it < ITEMS; it++)
-    if (it < valid_items) cp_async<sizeof(T)>(stage + pos[it] * (uint32_t)sizeof(T), in + it * 32);
+    if (pid[it] != kNoPid) cp_async<sizeof(T)>(stage + pos[it] * (uint32_t)sizeof(T), in + it * 32);
 }
 
 // write one staged column out: sorted position j = threadIdx.x + k * THREADS goes to output row d[k] (-1 = none)
@@ -169,6 +192,13 @@ __device__ __forceinline__ void write_runs(T* __restrict__ out, const T* stage, 
 #pragma unroll
   for (int k = 0; k < ITEMS; k++)
     if (d[k] >= 0) out[d[k]] = stage[threadIdx.x + k * THREADS];
+}
+// the same into the owner ranks' windows: outs[own[k]] is the column's region in the window of the run's owner
+template <int THREADS, int ITEMS, typename T>
+__device__ __forceinline__ void write_runs_peer(void* const* outs, const T* stage, const int64_t (&d)[ITEMS], const int (&own)[ITEMS]) {
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++)
+    if (d[k] >= 0) ((T*)outs[own[k]])[d[k]] = stage[threadIdx.x + k * THREADS];
 }
 // the same with the output row recomputed per element (side-buffer columns: keeps registers for the loads)
 template <int THREADS, int ITEMS, typename T>
@@ -224,36 +254,47 @@ __device__ __forceinline__ void scatter_bits(const uint8_t* __restrict__ in, uin
   }
 }
 
-// shared memory of one scatter CTA (tile = THREADS * items rows)
-static size_t scatter_smem_bytes(uint32_t n, int threads, int items, int async_width, int side_width) {
+// shared memory of one scatter CTA (tile = threads * items rows); peer_ptrs = n_async * world for the fused exchange
+static size_t scatter_smem_bytes(uint32_t n, int threads, int items, int async_width, int side_width, int peer_ptrs = 0) {
   const size_t tile = (size_t)threads * items;
+  const size_t ns = ((size_t)n + 1) & ~(size_t)1;
   size_t b = tile * (size_t)(async_width + side_width);
   b = (b + 15) & ~(size_t)15;
-  b += (size_t)n * 8 * 2 + (size_t)(threads / 32) * n * 4 + (size_t)n * 4 * 2 + tile * 2;
+  b += (size_t)n * 8 * 2 + (size_t)n * 4 + (size_t)(threads / 32) * ns * 2 + tile * 2;
+  b = (b + 7) & ~(size_t)7;
+  b += (size_t)peer_ptrs * 8 + (peer_ptrs ? (size_t)n : 0);
   return b + 16;
 }
 
-template <int THREADS, int ITEMS>
-__global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2)
-    scatter_kernel(const __grid_constant__ KeySet ks, const __grid_constant__ Modulo mod,
-                   const __grid_constant__ ScatterArgs args, int64_t n_rows, int64_t chunk_rows,
-                   const uint64_t* __restrict__ base /* [n][gridDim.x] */) {
+template <int THREADS, bool SIDE> struct ScatterCtas {  // resident CTAs per SM the register budget is set for
+  static constexpr int value = THREADS >= 1024 ? 1 : (THREADS >= 512 ? (SIDE ? 1 : 2) : (SIDE ? 2 : 4));
+};
+
+template <int THREADS, int ITEMS, bool SIDE, bool PEER>
+__global__ void __launch_bounds__(THREADS, ScatterCtas<THREADS, SIDE>::value)
+    scatter_kernel(const __grid_constant__ ScatterArgs args, const uint16_t* __restrict__ pids /* pass 1's partition ids */,
+                   uint32_t n, int64_t n_rows, int64_t chunk_rows, const uint64_t* __restrict__ base /* [n][gridDim.x] */,
+                   void* const* __restrict__ peer_out /* PEER: [n_async][world] column regions in the owners' windows */, int world) {
   constexpr int kTile = THREADS * ITEMS;
+  constexpr int W = THREADS / 32;
   extern __shared__ __align__(16) unsigned char smem[];
-  const uint32_t n = mod.n;
   // shared layout: async stage areas (column c at stage_off * kTile, 16 B aligned) | side buffer | gdelta i64[n] |
-  //                chunk_base u64[n] | warp_cnt u32[(THREADS / 32)*n] | tile_off u32[n] | tile_cnt u32[n] | pid_sorted u16[kTile]
+  //   chunk_base u64[n] | tile_off u32[n] | warp_cnt u16[W][ns] | pid_sorted u16[kTile] | PEER: out ptrs [n_async][world], owner u8[n]
+  const uint32_t ns = (n + 1) & ~1u;
   unsigned char* sp = smem;
   unsigned char* stage = sp;              sp += (size_t)kTile * args.async_width;
-  void* side = sp;                        sp += (size_t)kTile * args.side_width;
+  void* side = sp;                        if (SIDE) sp += (size_t)kTile * args.side_width;
   sp = (unsigned char*)(((uintptr_t)sp + 15) & ~(uintptr_t)15);
   int64_t* gdelta = (int64_t*)sp;         sp += (size_t)n * 8;
   uint64_t* chunk_base = (uint64_t*)sp;   sp += (size_t)n * 8;
-  uint32_t* warp_cnt = (uint32_t*)sp;     sp += (size_t)(THREADS / 32) * n * 4;
   uint32_t* tile_off = (uint32_t*)sp;     sp += (size_t)n * 4;
-  uint32_t* tile_cnt = (uint32_t*)sp;     sp += (size_t)n * 4;
-  uint16_t* pid_sorted = (uint16_t*)sp;
-  __shared__ uint32_t s_scan[(THREADS / 32)];
+  uint16_t* warp_cnt = (uint16_t*)sp;     sp += (size_t)W * ns * 2;
+  uint16_t* pid_sorted = (uint16_t*)sp;   sp += (size_t)kTile * 2;
+  sp = (unsigned char*)(((uintptr_t)sp + 7) & ~(uintptr_t)7);
+  void** s_out = (void**)sp;              if (PEER) sp += (size_t)args.n_async * world * 8;
+  uint8_t* s_owner = (uint8_t*)sp;
+  __shared__ uint32_t s_scan[W];
+  (void)side; (void)s_out; (void)s_owner;
 
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1;
@@ -261,42 +302,40 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2)
   int64_t end = begin + chunk_rows;
   if (end > n_rows) end = n_rows;
   for (uint32_t p = threadIdx.x; p < n; p += THREADS) chunk_base[p] = base[(size_t)p * gridDim.x + blockIdx.x];
+  for (uint32_t i = threadIdx.x; i < W * ns / 2; i += THREADS) ((uint32_t*)warp_cnt)[i] = 0;
+  if (PEER) {
+    for (int i = threadIdx.x; i < args.n_async * world; i += THREADS) s_out[i] = peer_out[i];
+    for (uint32_t p = threadIdx.x; p < n; p += THREADS) s_owner[p] = (uint8_t)(p % (uint32_t)world);
+  }
+  uint16_t* wc = warp_cnt + (size_t)w * ns;  // this warp's counters
+  const int id_bits = 32 - __clz(n > 1 ? n - 1 : 1);
 
-  // single 8-byte key column (ks.fast64): the next tile's keys are loaded into registers while this tile is moved,
-  // so the ranking never waits on DRAM
-  uint64_t next_key[ITEMS];
-  auto prefetch_keys = [&](int64_t tb) {
-    if (!ks.fast64) return;
-    const uint64_t* keys = (const uint64_t*)ks.cols[0].values;
+  // the next tile's partition ids are loaded while this tile is moved: the ranking never waits on DRAM
+  uint32_t next_pid[ITEMS];
+  auto prefetch_pids = [&](int64_t tb) {
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
       const int64_t r = tb + w * (32 * ITEMS) + it * 32 + lane;
-      next_key[it] = r < end ? __ldg(keys + r) : 0;
+      next_pid[it] = r < end ? (uint32_t)__ldg(pids + r) : kNoPid;
     }
   };
-  prefetch_keys(begin);
+  prefetch_pids(begin);
+  __syncthreads();
 
   for (int64_t tile_base = begin; tile_base < end; tile_base += kTile) {
     const int tile_n = (int)((end - tile_base) < kTile ? (end - tile_base) : kTile);
-    for (uint32_t i = threadIdx.x; i < (THREADS / 32) * n; i += THREADS) warp_cnt[i] = 0;
-    __syncthreads();
-    // 1. partition id and stable rank within this warp's segment
+    // 1. stable rank within this warp's segment
     uint32_t pid[ITEMS], pos[ITEMS];
-    uint32_t* wc = warp_cnt + (size_t)w * n;
+#pragma unroll
+    for (int it = 0; it < ITEMS; it++) pid[it] = next_pid[it];
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
-      const int local = w * (32 * ITEMS) + it * 32 + lane;
-      const bool valid = local < tile_n;
-      pid[it] = valid ? partition_of(ks.fast64 ? hash_u64(next_key[it]) : row_hash(ks, tile_base + local), mod) : 0xffffffffu;
-    }
-#pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-      const uint32_t peers = match_peers(pid[it]);
+      const uint32_t peers = match_bits(pid[it], pid[it] != kNoPid, id_bits);
       const int leader = __ffs(peers) - 1;
       uint32_t old = 0;
-      if (lane == leader && pid[it] != 0xffffffffu) {
+      if (lane == leader) {  // (lanes without a row have no peers: leader = -1)
         old = wc[pid[it]];
-        wc[pid[it]] = old + __popc(peers);
+        wc[pid[it]] = (uint16_t)(old + __popc(peers));
       }
       old = __shfl_sync(0xffffffffu, old, leader);
       pos[it] = old + __popc(peers & lt_mask);
@@ -307,20 +346,20 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2)
     for (uint32_t p = threadIdx.x; p < n; p += THREADS) {
       uint32_t run = 0;
 #pragma unroll
-      for (int ww = 0; ww < (THREADS / 32); ww++) {
-        const uint32_t c = warp_cnt[(size_t)ww * n + p];
-        warp_cnt[(size_t)ww * n + p] = run;
+      for (int ww = 0; ww < W; ww++) {
+        const uint32_t c = warp_cnt[(size_t)ww * ns + p];
+        warp_cnt[(size_t)ww * ns + p] = (uint16_t)run;
         run += c;
       }
-      tile_cnt[p] = run;
+      tile_off[p] = run;  // the count; the scan below turns it into the offset
     }
     __syncthreads();
-    {  // block exclusive scan of tile_cnt[0..n) into tile_off; each thread owns a contiguous slice
+    {  // block exclusive scan of the counts in tile_off[0..n), in place; each thread owns a contiguous slice
       const uint32_t per = (n + THREADS - 1) / THREADS;
       const uint32_t p0 = threadIdx.x * per;
       uint32_t sum = 0;
       for (uint32_t k = 0; k < per; k++)
-        if (p0 + k < n) sum += tile_cnt[p0 + k];
+        if (p0 + k < n) sum += tile_off[p0 + k];
       uint32_t x = sum;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
@@ -335,98 +374,115 @@ __global__ void __launch_bounds__(THREADS, THREADS >= 1024 ? 1 : 2)
       for (uint32_t k = 0; k < per; k++)
         if (p0 + k < n) {
           const uint32_t p = p0 + k;
+          const uint32_t cnt = tile_off[p];
           tile_off[p] = run;
-          gdelta[p] = (int64_t)chunk_base[p] - (int64_t)run;
-          chunk_base[p] += tile_cnt[p];
-          run += tile_cnt[p];
+          gdelta[p] = (int64_t)chunk_base[p] - (int64_t)run;  // sorted position -> output row (PEER: row in the owner's window)
+          chunk_base[p] += cnt;
+          run += cnt;
         }
     }
     __syncthreads();
     // 3. position of every row in the partition-ordered tile; all async columns go in flight
 #pragma unroll
     for (int it = 0; it < ITEMS; it++) {
-      if (pid[it] != 0xffffffffu) {
+      if (pid[it] != kNoPid) {
         pos[it] += tile_off[pid[it]] + wc[pid[it]];
         pid_sorted[pos[it]] = (uint16_t)pid[it];
       }
     }
     {
-      const int first = w * (32 * ITEMS) + lane;  // this thread's rows: first + it * 32
-      const int valid_items = first < tile_n ? (tile_n - first + 31) / 32 : 0;
-      const int64_t r0 = tile_base + first;
+      const int64_t r0 = tile_base + w * (32 * ITEMS) + lane;  // this thread's rows: r0 + it * 32
       const uint32_t stage_s = (uint32_t)__cvta_generic_to_shared(stage);
       for (int c = 0; c < args.n_async; c++) {
         const AsyncCol& ac = args.async_cols[c];
         const uint32_t st = stage_s + (uint32_t)ac.stage_off * kTile;
-        if (ac.width == 8) stage_async<THREADS, ITEMS, uint64_t>((const uint64_t*)ac.in + r0, st, valid_items, pos);
-        else if (ac.width == 16) stage_async<THREADS, ITEMS, uint4>((const uint4*)ac.in + r0, st, valid_items, pos);
-        else stage_async<THREADS, ITEMS, uint32_t>((const uint32_t*)ac.in + r0, st, valid_items, pos);
+        if (ac.width == 8) stage_async<ITEMS, uint64_t>((const uint64_t*)ac.in + r0, st, pid, pos);
+        else if (ac.width == 16) stage_async<ITEMS, uint4>((const uint4*)ac.in + r0, st, pid, pos);
+        else stage_async<ITEMS, uint32_t>((const uint32_t*)ac.in + r0, st, pid, pos);
       }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
-    prefetch_keys(tile_base + kTile);
-    __syncthreads();
+    prefetch_pids(tile_base + kTile);
+    __syncwarp();  // this warp's counters were read above: clear them for the next tile (no other warp touches them before
+    for (uint32_t i = lane; i < ns / 2; i += 32) ((uint32_t*)wc)[i] = 0;  // the next tile's barrier)
     // 4. bitmaps and side-buffer columns while the async copies land
-    for (int sc = 0; sc < args.n_side; sc++) {
-      const ScatterCol& col = args.cols[args.side_cols[sc]];
-      if (col.in_valid) scatter_bits<THREADS, ITEMS>(col.in_valid, col.out_valid, gdelta, pid_sorted, tile_base, tile_n, pos);
-      if (col.kind == K_BOOL) {
-        scatter_bits<THREADS, ITEMS>((const uint8_t*)col.in, (uint32_t*)col.out, gdelta, pid_sorted, tile_base, tile_n, pos);
-      } else if (col.kind == K_UTF8 || col.kind == K_BINARY) {
-        const int32_t* offs = col.in_offsets;
-        scatter_side<THREADS, ITEMS, int32_t>([=](int64_t r) { return offs[r + 1] - offs[r]; }, col.out_len, (int32_t*)side,
-                                     tile_base, tile_n, pos, pid_sorted, gdelta);
-        scatter_side<THREADS, ITEMS, int32_t>([=](int64_t r) { return offs[r]; }, col.out_src, (int32_t*)side, tile_base, tile_n,
-                                     pos, pid_sorted, gdelta);
-      } else if (col.stage_off < 0) {
-        switch (col.width) {
-          case 16: {
-            const uint4* in = (const uint4*)col.in;
-            scatter_side<THREADS, ITEMS, uint4>([=](int64_t r) { return in[r]; }, (uint4*)col.out, (uint4*)side, tile_base,
-                                       tile_n, pos, pid_sorted, gdelta);
-          } break;
-          case 8: {
-            const uint64_t* in = (const uint64_t*)col.in;
-            scatter_side<THREADS, ITEMS, uint64_t>([=](int64_t r) { return in[r]; }, (uint64_t*)col.out, (uint64_t*)side,
-                                          tile_base, tile_n, pos, pid_sorted, gdelta);
-          } break;
-          case 4: {
-            const uint32_t* in = (const uint32_t*)col.in;
-            scatter_side<THREADS, ITEMS, uint32_t>([=](int64_t r) { return in[r]; }, (uint32_t*)col.out, (uint32_t*)side,
-                                          tile_base, tile_n, pos, pid_sorted, gdelta);
-          } break;
-          case 2: {
-            const uint16_t* in = (const uint16_t*)col.in;
-            scatter_side<THREADS, ITEMS, uint16_t>([=](int64_t r) { return in[r]; }, (uint16_t*)col.out, (uint16_t*)side,
-                                          tile_base, tile_n, pos, pid_sorted, gdelta);
-          } break;
-          default: {
-            const uint8_t* in = (const uint8_t*)col.in;
-            scatter_side<THREADS, ITEMS, uint8_t>([=](int64_t r) { return in[r]; }, (uint8_t*)col.out, (uint8_t*)side, tile_base,
+    if (SIDE) {
+      __syncthreads();
+      for (int sc = 0; sc < args.n_side; sc++) {
+        const ScatterCol& col = args.cols[args.side_cols[sc]];
+        if (col.in_valid) scatter_bits<THREADS, ITEMS>(col.in_valid, col.out_valid, gdelta, pid_sorted, tile_base, tile_n, pos);
+        if (col.kind == K_BOOL) {
+          scatter_bits<THREADS, ITEMS>((const uint8_t*)col.in, (uint32_t*)col.out, gdelta, pid_sorted, tile_base, tile_n, pos);
+        } else if (col.kind == K_UTF8 || col.kind == K_BINARY) {
+          const int32_t* offs = col.in_offsets;
+          scatter_side<THREADS, ITEMS, int32_t>([=](int64_t r) { return offs[r + 1] - offs[r]; }, col.out_len, (int32_t*)side,
+                                       tile_base, tile_n, pos, pid_sorted, gdelta);
+          scatter_side<THREADS, ITEMS, int32_t>([=](int64_t r) { return offs[r]; }, col.out_src, (int32_t*)side, tile_base, tile_n,
+                                       pos, pid_sorted, gdelta);
+        } else if (col.stage_off < 0) {
+          switch (col.width) {
+            case 16: {
+              const uint4* in = (const uint4*)col.in;
+              scatter_side<THREADS, ITEMS, uint4>([=](int64_t r) { return in[r]; }, (uint4*)col.out, (uint4*)side, tile_base,
                                          tile_n, pos, pid_sorted, gdelta);
-          } break;
+            } break;
+            case 8: {
+              const uint64_t* in = (const uint64_t*)col.in;
+              scatter_side<THREADS, ITEMS, uint64_t>([=](int64_t r) { return in[r]; }, (uint64_t*)col.out, (uint64_t*)side,
+                                            tile_base, tile_n, pos, pid_sorted, gdelta);
+            } break;
+            case 4: {
+              const uint32_t* in = (const uint32_t*)col.in;
+              scatter_side<THREADS, ITEMS, uint32_t>([=](int64_t r) { return in[r]; }, (uint32_t*)col.out, (uint32_t*)side,
+                                            tile_base, tile_n, pos, pid_sorted, gdelta);
+            } break;
+            case 2: {
+              const uint16_t* in = (const uint16_t*)col.in;
+              scatter_side<THREADS, ITEMS, uint16_t>([=](int64_t r) { return in[r]; }, (uint16_t*)col.out, (uint16_t*)side,
+                                            tile_base, tile_n, pos, pid_sorted, gdelta);
+            } break;
+            default: {
+              const uint8_t* in = (const uint8_t*)col.in;
+              scatter_side<THREADS, ITEMS, uint8_t>([=](int64_t r) { return in[r]; }, (uint8_t*)col.out, (uint8_t*)side, tile_base,
+                                           tile_n, pos, pid_sorted, gdelta);
+            } break;
+          }
         }
       }
     }
-    // 5. the async-staged columns
+    // 5. the async-staged columns: sorted position j = threadIdx.x + k * THREADS -> output row d[k], once for all columns
     asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
-    {  // sorted position j = threadIdx.x + k * THREADS -> output row d[k], once for all columns
+    {
       int64_t d[ITEMS];
+      int own[ITEMS];
 #pragma unroll
       for (int k = 0; k < ITEMS; k++) {
         const int j = threadIdx.x + k * THREADS;
-        d[k] = j < tile_n ? (int64_t)j + gdelta[pid_sorted[j]] : -1;
+        d[k] = -1;
+        if (PEER) own[k] = 0;
+        if (j < tile_n) {
+          const uint32_t p = pid_sorted[j];
+          d[k] = (int64_t)j + gdelta[p];
+          if (PEER) own[k] = s_owner[p];
+        }
       }
       for (int c = 0; c < args.n_async; c++) {
         const AsyncCol& ac = args.async_cols[c];
         const unsigned char* st = stage + (size_t)ac.stage_off * kTile;
-        if (ac.width == 8) write_runs<THREADS, ITEMS, uint64_t>((uint64_t*)ac.out, (const uint64_t*)st, d);
-        else if (ac.width == 16) write_runs<THREADS, ITEMS, uint4>((uint4*)ac.out, (const uint4*)st, d);
-        else write_runs<THREADS, ITEMS, uint32_t>((uint32_t*)ac.out, (const uint32_t*)st, d);
+        if (PEER) {  // a run of one partition is contiguous in the owner's window: a warp's stores fill whole NVLink packets
+          void* const* outs = s_out + c * world;
+          if (ac.width == 8) write_runs_peer<THREADS, ITEMS, uint64_t>(outs, (const uint64_t*)st, d, own);
+          else if (ac.width == 16) write_runs_peer<THREADS, ITEMS, uint4>(outs, (const uint4*)st, d, own);
+          else write_runs_peer<THREADS, ITEMS, uint32_t>(outs, (const uint32_t*)st, d, own);
+        } else {
+          if (ac.width == 8) write_runs<THREADS, ITEMS, uint64_t>((uint64_t*)ac.out, (const uint64_t*)st, d);
+          else if (ac.width == 16) write_runs<THREADS, ITEMS, uint4>((uint4*)ac.out, (const uint4*)st, d);
+          else write_runs<THREADS, ITEMS, uint32_t>((uint32_t*)ac.out, (const uint32_t*)st, d);
+        }
       }
     }
-    // (the next tile's first __syncthreads orders these reads before its cp.async writes)
+    // (the next tile's barriers order these reads before its writes of gdelta / pid_sorted / the stage areas)
   }
 }
 
@@ -508,28 +564,54 @@ extern "C" int bgpu_create_hashes(bgpu_ctx* ctx, const bgpu_batch* batch, const 
 
 // scatter geometries (threads per CTA, rows per thread): tile = threads x items rows
 struct ScatterGeom { int threads, items; };
-constexpr ScatterGeom kGeomSmall{256, 4};    // 1024-row tiles, two CTAs per SM: few partitions (runs stay long)
-constexpr ScatterGeom kGeomMedium{256, 8};   // 2048-row tiles
-constexpr ScatterGeom kGeomLarge{1024, 4};   // 4096-row tiles, one CTA per SM: many partitions
+constexpr ScatterGeom kGeomNarrow{256, 2};   //  512-row tiles: rows too wide for two 1024-row CTAs per SM
+constexpr ScatterGeom kGeomSmall{256, 4};    // 1024-row tiles, up to four CTAs per SM: few partitions (runs stay long)
+constexpr ScatterGeom kGeomMedium{512, 4};   // 2048-row tiles, two CTAs per SM: many partitions
+constexpr ScatterGeom kGeomLarge{1024, 4};   // 4096-row tiles, one CTA per SM
+constexpr size_t kTwoCtasBudget = 112 * 1024;  // dynamic shared memory that still lets two CTAs share an SM
 
-template <int THREADS, int ITEMS>
-static int scatter_run(bgpu_ctx* ctx, bool launch, int64_t g, size_t smem, const KeySet& ks, const Modulo& mod,
-                       const ScatterArgs& args, int64_t n_rows, int64_t chunk_rows, const uint64_t* base, int* occ) {
-  BGPU_CUDA(ctx, raise_max_dynamic_smem((const void*)scatter_kernel<THREADS, ITEMS>, ctx->device, smem));
+struct ScatterLaunch {
+  const ScatterArgs* args;
+  const uint16_t* pids;
+  uint32_t n;
+  int64_t n_rows, chunk_rows;
+  const uint64_t* base;
+  void* const* peer_out;  // fused exchange only
+  int world;
+};
+template <int THREADS, int ITEMS, bool SIDE, bool PEER>
+static int scatter_run(bgpu_ctx* ctx, bool launch, int64_t g, size_t smem, const ScatterLaunch& l, int* occ) {
+  BGPU_CUDA(ctx, raise_max_dynamic_smem((const void*)scatter_kernel<THREADS, ITEMS, SIDE, PEER>, ctx->device, smem));
   if (!launch) {
-    BGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, scatter_kernel<THREADS, ITEMS>, THREADS, smem));
+    BGPU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, scatter_kernel<THREADS, ITEMS, SIDE, PEER>, THREADS, smem));
     return BGPU_OK;
   }
-  scatter_kernel<THREADS, ITEMS><<<(int)g, THREADS, smem, ctx->stream>>>(ks, mod, args, n_rows, chunk_rows, base);
+  scatter_kernel<THREADS, ITEMS, SIDE, PEER><<<(int)g, THREADS, smem, ctx->stream>>>(*l.args, l.pids, l.n, l.n_rows, l.chunk_rows, l.base,
+                                                                                   l.peer_out, l.world);
   return BGPU_OK;
 }
-static int scatter_dispatch(bgpu_ctx* ctx, ScatterGeom geom, bool launch, int64_t g, size_t smem, const KeySet& ks,
-                            const Modulo& mod, const ScatterArgs& args, int64_t n_rows, int64_t chunk_rows,
-                            const uint64_t* base, int* occ) {
-  if (geom.threads == 256 && geom.items == 4) return scatter_run<256, 4>(ctx, launch, g, smem, ks, mod, args, n_rows, chunk_rows, base, occ);
-  if (geom.threads == 256 && geom.items == 8) return scatter_run<256, 8>(ctx, launch, g, smem, ks, mod, args, n_rows, chunk_rows, base, occ);
-  if (geom.threads == 1024 && geom.items == 4) return scatter_run<1024, 4>(ctx, launch, g, smem, ks, mod, args, n_rows, chunk_rows, base, occ);
+// launch = false: *occ = resident CTAs per SM of the instantiation (the grid and the chunks follow from it)
+static int scatter_dispatch(bgpu_ctx* ctx, ScatterGeom geom, bool side, bool peer, bool launch, int64_t g, size_t smem,
+                            const ScatterLaunch& l, int* occ) {
+#define BGPU_SCATTER_CASE(T, I)                                                                      \
+  if (geom.threads == T && geom.items == I) {                                                        \
+    if (peer) return scatter_run<T, I, false, true>(ctx, launch, g, smem, l, occ);                   \
+    if (side) return scatter_run<T, I, true, false>(ctx, launch, g, smem, l, occ);                   \
+    return scatter_run<T, I, false, false>(ctx, launch, g, smem, l, occ);                            \
+  }
+  BGPU_SCATTER_CASE(256, 2)
+  BGPU_SCATTER_CASE(256, 4)
+  BGPU_SCATTER_CASE(512, 4)
+  BGPU_SCATTER_CASE(1024, 4)
+#undef BGPU_SCATTER_CASE
   return ctx->fail(BGPU_EINVAL, "internal: unknown scatter geometry");
+}
+static bool parse_geometry(const char* e, ScatterGeom* geom) {
+  int t = 0, it = 0;
+  if (!e || sscanf(e, "%d,%d", &t, &it) != 2) return false;
+  if (!((t == 256 && (it == 2 || it == 4)) || (t == 512 && it == 4) || (t == 1024 && it == 4))) return false;
+  *geom = ScatterGeom{t, it};
+  return true;
 }
 
 extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const int32_t* key_cols, int32_t n_keys,
@@ -609,26 +691,33 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
     else side_width = std::max(side_width, (int)c.width);
   }
   std::stable_sort(async_cols.begin(), async_cols.end(), [&](size_t a, size_t b) { return in->cols[a].width > in->cols[b].width; });
-  // Geometry: long output runs need tile rows >> n_partitions; overlap of one CTA's loads with another's stores needs
-  // two CTAs per SM. Measured (config 3, 2e8 rows): n = 8 / 64: 256x4 4.1 / 5.1 ms, 256x8 5.4 / 6.3 ms; n = 512 wants the
-  // 4096-row tile. A schema too wide for the chosen tile demotes columns to the side buffer, widest first.
-  ScatterGeom geom = n <= 128 ? kGeomSmall : kGeomLarge;
-  if (const char* e = getenv("BGPU_PART_GEOMETRY")) {  // tuning knob: "threads,items"
-    int t = 0, it = 0;
-    if (sscanf(e, "%d,%d", &t, &it) == 2 && ((t == 256 && (it == 4 || it == 8)) || (t == 1024 && it == 4))) geom = ScatterGeom{t, it};
-  }
-  for (;;) {
+  // Geometry: what decides the speed is the length of a run (tile rows / n): below ~32 rows (256 B of an 8-byte column) the
+  // head and tail sectors of every run are partial writes and the time climbs steeply (1e8 rows, ms: 128-row runs 1.85,
+  // 64: 1.96, 32: 2.2, 16: 2.8, 8: 4.5, 4: 7.4); small tiles in turn keep four CTAs per SM busy. n <= 16: 1024-row tiles,
+  // n <= 64: 2048-row tiles x two CTAs, more: 4096-row tiles; rows too wide for that take the next smaller tile, and a
+  // schema too wide even for 512-row tiles demotes columns to the side buffer, widest first.
+  auto need_for = [&](ScatterGeom gm) {
     int aw = 0;
     for (size_t i : async_cols) aw += in->cols[i].width;
-    const size_t need = scatter_smem_bytes(n, geom.threads, geom.items, aw, side_width);
-    const size_t budget = geom.threads >= 1024 ? ctx->smem_optin : (ctx->smem_optin + 1024) / 2 - 1024 - 512;
+    return scatter_smem_bytes(n, gm.threads, gm.items, aw, side_width);
+  };
+  ScatterGeom geom = kGeomSmall;
+  bool forced = parse_geometry(getenv("BGPU_PART_GEOMETRY"), &geom);  // tuning knob: "threads,items"
+  for (;;) {
+    if (!forced) {
+      geom = kGeomNarrow;
+      if (need_for(kGeomSmall) <= kTwoCtasBudget) geom = kGeomSmall;
+      if (n > 16 && need_for(kGeomMedium) <= kTwoCtasBudget) geom = kGeomMedium;
+      if (n > 64 && need_for(kGeomLarge) <= ctx->smem_optin) geom = kGeomLarge;
+    }
+    const size_t need = need_for(geom);
+    const size_t budget = geom.threads >= 1024 ? ctx->smem_optin : std::min<size_t>(kTwoCtasBudget, ctx->smem_optin);
     if (need <= budget) break;
     if (async_cols.empty()) {
-      if (geom.threads == 256 && geom.items == 4) {
-        if (need <= ctx->smem_optin) break;
-        return ctx->fail(BGPU_EUNSUPPORTED, "n_partitions too large for shared memory");
-      }
-      geom = kGeomSmall;  // the per-partition arrays alone overflow the larger tile
+      if (need <= ctx->smem_optin) break;
+      if (geom.threads == 256 && geom.items == 2) return ctx->fail(BGPU_EUNSUPPORTED, "n_partitions too large for shared memory");
+      geom = kGeomNarrow;  // the per-partition arrays alone overflow the larger tile
+      forced = true;
       continue;
     }
     side_width = std::max(side_width, (int)in->cols[async_cols.front()].width);  // demote the widest async column
@@ -666,9 +755,11 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
 
   // grid: one persistent CTA per resident slot, contiguous chunks of whole tiles
   const size_t smem = scatter_smem_bytes(n, geom.threads, geom.items, args.async_width, args.side_width);
+  const bool side = args.n_side > 0;
   const int64_t kTile = (int64_t)geom.threads * geom.items;
+  ScatterLaunch l{&args, nullptr, n, n_rows, 0, nullptr, nullptr, 1};
   int occ = 1;
-  BGPU_TRY(scatter_dispatch(ctx, geom, false, 0, smem, ks, mod, args, n_rows, 0, nullptr, &occ));
+  BGPU_TRY(scatter_dispatch(ctx, geom, side, false, false, 0, smem, l, &occ));
   if (occ < 1) occ = 1;
   int64_t g = (int64_t)ctx->sm_count * occ;
   const int64_t tiles = ceil_div64(n_rows, kTile);
@@ -676,16 +767,18 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
   const int64_t chunk_rows = ceil_div64(tiles, g) * kTile;
   g = ceil_div64(n_rows, chunk_rows);
 
-  DevAllocPtr hist, base, offs;
+  DevAllocPtr hist, base, offs, pids;
   BGPU_TRY(dev_alloc(ctx, (size_t)n * g * 4, &hist));
   BGPU_TRY(dev_alloc(ctx, (size_t)n * g * 8, &base));
   BGPU_TRY(dev_alloc(ctx, (size_t)(n + 1) * 8, &offs));
+  BGPU_TRY(dev_alloc(ctx, (size_t)n_rows * 2, &pids));
 
   count_kernel<<<(int)g, kCountThreads, n * 4, ctx->stream>>>(ks, mod, n_rows, chunk_rows, (uint32_t*)hist->p,
-                                                        out_hashes_device);
+                                                        out_hashes_device, (uint16_t*)pids->p);
   scan_kernel<<<1, 1024, 0, ctx->stream>>>((const uint32_t*)hist->p, (uint64_t*)base->p, (uint64_t*)offs->p, n,
                                            (uint32_t)g, n_rows);
-  BGPU_TRY(scatter_dispatch(ctx, geom, true, g, smem, ks, mod, args, n_rows, chunk_rows, (const uint64_t*)base->p, nullptr));
+  l.pids = (const uint16_t*)pids->p; l.chunk_rows = chunk_rows; l.base = (const uint64_t*)base->p;
+  BGPU_TRY(scatter_dispatch(ctx, geom, side, false, true, g, smem, l, nullptr));
   ctx->launches += 3;
   BGPU_CUDA(ctx, cudaGetLastError());
 

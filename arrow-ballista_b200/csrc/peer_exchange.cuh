@@ -17,7 +17,7 @@
 //      computes every receive layout (bgpu_exchange_plan) and the same decisions (fallback, window growth)
 //      [this collective also orders the peers' stores after the owner's copy-out of the previous exchange]
 //   3. base[p][chunk] += (first row of (p, this rank) in the owner's window) - offsets[p]
-//   4. scatter_peer_kernel: out pointer of a run = window of owner(p) + column region + row * width
+//   4. scatter_kernel<.., PEER = true> (partition.cu): out pointer of a run = window of owner(p) + column region + row * width
 //   5. ncclAllGather of one word: all ranks' stores have landed
 //   6. copy the window's column regions out into the result batch (local HBM copy; the window is reused)
 #include "nccl_dl.h"
@@ -25,174 +25,6 @@
 namespace bgpu {
 
 constexpr int kMaxPeers = 16;
-
-template <int THREADS, int ITEMS>
-__global__ void __launch_bounds__(THREADS, 2)
-    scatter_peer_kernel(const __grid_constant__ KeySet ks, const __grid_constant__ Modulo mod,
-                        const __grid_constant__ ScatterArgs args, int64_t n_rows, int64_t chunk_rows,
-                        const uint64_t* __restrict__ base /* [n][gridDim.x], window rows */,
-                        void* const* __restrict__ peer_out /* [n_async][world] column regions in the owners' windows */, int world) {
-  constexpr int kTile = THREADS * ITEMS;
-  extern __shared__ __align__(16) unsigned char smem[];
-  const uint32_t n = mod.n;
-  unsigned char* sp = smem;
-  unsigned char* stage = sp;              sp += (size_t)kTile * args.async_width;
-  sp = (unsigned char*)(((uintptr_t)sp + 15) & ~(uintptr_t)15);
-  int64_t* gdelta = (int64_t*)sp;         sp += (size_t)n * 8;
-  uint64_t* chunk_base = (uint64_t*)sp;   sp += (size_t)n * 8;
-  uint32_t* warp_cnt = (uint32_t*)sp;     sp += (size_t)(THREADS / 32) * n * 4;
-  uint32_t* tile_off = (uint32_t*)sp;     sp += (size_t)n * 4;
-  uint32_t* tile_cnt = (uint32_t*)sp;     sp += (size_t)n * 4;
-  uint16_t* pid_sorted = (uint16_t*)sp;   sp += (size_t)kTile * 2;
-  sp = (unsigned char*)(((uintptr_t)sp + 7) & ~(uintptr_t)7);
-  void** s_out = (void**)sp;              // [n_async][world]
-  __shared__ uint32_t s_scan[(THREADS / 32)];
-
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t lt_mask = (1u << lane) - 1;
-  const int64_t begin = (int64_t)blockIdx.x * chunk_rows;
-  int64_t end = begin + chunk_rows;
-  if (end > n_rows) end = n_rows;
-  for (uint32_t p = threadIdx.x; p < n; p += THREADS) chunk_base[p] = base[(size_t)p * gridDim.x + blockIdx.x];
-  for (int i = threadIdx.x; i < args.n_async * world; i += THREADS) s_out[i] = peer_out[i];
-
-  uint64_t next_key[ITEMS];
-  auto prefetch_keys = [&](int64_t tb) {
-    if (!ks.fast64) return;
-    const uint64_t* keys = (const uint64_t*)ks.cols[0].values;
-#pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-      const int64_t r = tb + w * (32 * ITEMS) + it * 32 + lane;
-      next_key[it] = r < end ? __ldg(keys + r) : 0;
-    }
-  };
-  prefetch_keys(begin);
-
-  for (int64_t tile_base = begin; tile_base < end; tile_base += kTile) {
-    const int tile_n = (int)((end - tile_base) < kTile ? (end - tile_base) : kTile);
-    for (uint32_t i = threadIdx.x; i < (THREADS / 32) * n; i += THREADS) warp_cnt[i] = 0;
-    __syncthreads();
-    // 1. partition id and stable rank within this warp's segment (as scatter_kernel)
-    uint32_t pid[ITEMS], pos[ITEMS];
-    uint32_t* wc = warp_cnt + (size_t)w * n;
-#pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-      const int local = w * (32 * ITEMS) + it * 32 + lane;
-      const bool valid = local < tile_n;
-      pid[it] = valid ? partition_of(ks.fast64 ? hash_u64(next_key[it]) : row_hash(ks, tile_base + local), mod) : 0xffffffffu;
-    }
-#pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-      const uint32_t peers = match_peers(pid[it]);
-      const int leader = __ffs(peers) - 1;
-      uint32_t old = 0;
-      if (lane == leader && pid[it] != 0xffffffffu) {
-        old = wc[pid[it]];
-        wc[pid[it]] = old + __popc(peers);
-      }
-      old = __shfl_sync(0xffffffffu, old, leader);
-      pos[it] = old + __popc(peers & lt_mask);
-      __syncwarp();
-    }
-    __syncthreads();
-    // 2. per partition: exclusive scan over warps, tile totals, exclusive scan over partitions
-    for (uint32_t p = threadIdx.x; p < n; p += THREADS) {
-      uint32_t run = 0;
-#pragma unroll
-      for (int ww = 0; ww < (THREADS / 32); ww++) {
-        const uint32_t c = warp_cnt[(size_t)ww * n + p];
-        warp_cnt[(size_t)ww * n + p] = run;
-        run += c;
-      }
-      tile_cnt[p] = run;
-    }
-    __syncthreads();
-    {
-      const uint32_t per = (n + THREADS - 1) / THREADS;
-      const uint32_t p0 = threadIdx.x * per;
-      uint32_t sum = 0;
-      for (uint32_t k = 0; k < per; k++)
-        if (p0 + k < n) sum += tile_cnt[p0 + k];
-      uint32_t x = sum;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
-        if (lane >= d) x += y;
-      }
-      if (lane == 31) s_scan[w] = x;
-      __syncthreads();
-      uint32_t wpre = 0;
-      for (int ww = 0; ww < w; ww++) wpre += s_scan[ww];
-      uint32_t run = wpre + x - sum;
-      for (uint32_t k = 0; k < per; k++)
-        if (p0 + k < n) {
-          const uint32_t p = p0 + k;
-          tile_off[p] = run;
-          gdelta[p] = (int64_t)chunk_base[p] - (int64_t)run;  // sorted position -> row in the owner's window
-          chunk_base[p] += tile_cnt[p];
-          run += tile_cnt[p];
-        }
-    }
-    __syncthreads();
-    // 3. position of every row in the partition-ordered tile; all columns go in flight
-#pragma unroll
-    for (int it = 0; it < ITEMS; it++) {
-      if (pid[it] != 0xffffffffu) {
-        pos[it] += tile_off[pid[it]] + wc[pid[it]];
-        pid_sorted[pos[it]] = (uint16_t)pid[it];
-      }
-    }
-    {
-      const int first = w * (32 * ITEMS) + lane;
-      const int valid_items = first < tile_n ? (tile_n - first + 31) / 32 : 0;
-      const int64_t r0 = tile_base + first;
-      const uint32_t stage_s = (uint32_t)__cvta_generic_to_shared(stage);
-      for (int c = 0; c < args.n_async; c++) {
-        const AsyncCol& ac = args.async_cols[c];
-        const uint32_t st = stage_s + (uint32_t)ac.stage_off * kTile;
-        if (ac.width == 8) stage_async<THREADS, ITEMS, uint64_t>((const uint64_t*)ac.in + r0, st, valid_items, pos);
-        else if (ac.width == 16) stage_async<THREADS, ITEMS, uint4>((const uint4*)ac.in + r0, st, valid_items, pos);
-        else stage_async<THREADS, ITEMS, uint32_t>((const uint32_t*)ac.in + r0, st, valid_items, pos);
-      }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    prefetch_keys(tile_base + kTile);
-    asm volatile("cp.async.wait_all;" ::: "memory");
-    __syncthreads();
-    // 4. runs go out: sorted position j -> (owner rank, row in its window), once for all columns; a run of one
-    //    partition is contiguous in the owner's window, so the stores of a warp coalesce into full NVLink packets
-    {
-      int64_t d[ITEMS];
-      int own[ITEMS];
-#pragma unroll
-      for (int k = 0; k < ITEMS; k++) {
-        const int j = threadIdx.x + k * THREADS;
-        if (j < tile_n) {
-          const uint32_t p = pid_sorted[j];
-          d[k] = (int64_t)j + gdelta[p];
-          own[k] = (int)(p % (uint32_t)world);
-        } else {
-          d[k] = -1;
-          own[k] = 0;
-        }
-      }
-      for (int c = 0; c < args.n_async; c++) {
-        const AsyncCol& ac = args.async_cols[c];
-        const unsigned char* st = stage + (size_t)ac.stage_off * kTile;
-        void* const* outs = s_out + c * world;
-#pragma unroll
-        for (int k = 0; k < ITEMS; k++) {
-          if (d[k] < 0) continue;
-          const int j = threadIdx.x + k * THREADS;
-          if (ac.width == 8) ((uint64_t*)outs[own[k]])[d[k]] = ((const uint64_t*)st)[j];
-          else if (ac.width == 16) ((uint4*)outs[own[k]])[d[k]] = ((const uint4*)st)[j];
-          else ((uint32_t*)outs[own[k]])[d[k]] = ((const uint32_t*)st)[j];
-        }
-      }
-    }
-    // (the next tile's first __syncthreads orders these reads before its cp.async writes)
-  }
-}
 
 // base[p][chunk] += delta[p] (rows of partition p start at a different place in the owner's window)
 __global__ void add_delta_kernel(uint64_t* __restrict__ base, const int64_t* __restrict__ delta, uint32_t n, uint32_t g) {
@@ -332,8 +164,6 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
   x->exchanges++;
 
   // can this rank's batch take the fused path? (every rank must agree: the flag travels with the counts)
-  const ScatterGeom geom = kGeomSmall;
-  const int64_t kTile = (int64_t)geom.threads * geom.items;
   uint64_t can_fuse = n_cols > 0 && n_cols <= (size_t)kMaxCols && n <= 128;
   int row_bytes = 0;
   for (const Column& c : in->cols) {
@@ -342,27 +172,36 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
       can_fuse = 0;
     row_bytes += c.width;
   }
-  const size_t smem = scatter_smem_bytes(n, geom.threads, geom.items, row_bytes, 0) + (size_t)kMaxCols * kMaxPeers * 8 + 16;
-  if (smem > (ctx->smem_optin + 1024) / 2 - 1024 - 512) can_fuse = 0;
+  const int peer_ptrs = (int)n_cols * world;
+  ScatterGeom geom = scatter_smem_bytes(n, kGeomSmall.threads, kGeomSmall.items, row_bytes, 0, peer_ptrs) <= kTwoCtasBudget ? kGeomSmall : kGeomNarrow;
+  const int64_t kTile = (int64_t)geom.threads * geom.items;
+  const size_t smem = scatter_smem_bytes(n, geom.threads, geom.items, row_bytes, 0, peer_ptrs);
+  if (smem > kTwoCtasBudget) can_fuse = 0;
+  ScatterArgs args{};
+  ScatterLaunch l{&args, nullptr, n, n_rows, 0, nullptr, nullptr, world};
+  int occ = 2;
+  if (can_fuse) BGPU_TRY(scatter_dispatch(ctx, geom, false, true, false, 0, smem, l, &occ));
+  if (occ < 1) occ = 1;
 
   // 1. local histogram + scan (grid fixed here: the scatter uses the same chunks)
   KeySet ks{};
   std::vector<DevAllocPtr> temps;
   BGPU_TRY(make_keyset(ctx, in, key_cols, n_keys, &ks, &temps));
   const Modulo mod = make_modulo(n);
-  int64_t g = (int64_t)ctx->sm_count * 2;
+  int64_t g = (int64_t)ctx->sm_count * occ;
   const int64_t tiles = std::max<int64_t>(1, ceil_div64(n_rows, kTile));
   if (g > tiles) g = tiles;
   const int64_t chunk_rows = ceil_div64(tiles, g) * kTile;
   g = std::max<int64_t>(1, ceil_div64(n_rows, chunk_rows));
-  DevAllocPtr hist, base, hdr, all_hdr;
+  DevAllocPtr hist, base, hdr, all_hdr, pids;
+  BGPU_TRY(dev_alloc(ctx, (size_t)std::max<int64_t>(n_rows, 1) * 2, &pids));
   BGPU_TRY(dev_alloc(ctx, (size_t)n * g * 4, &hist));
   BGPU_TRY(dev_alloc(ctx, (size_t)n * g * 8, &base));
   const size_t hdr_words = (size_t)n + 2;  // offsets[n + 1], can_fuse
   BGPU_TRY(dev_alloc(ctx, hdr_words * 8, &hdr));
   BGPU_TRY(dev_alloc(ctx, hdr_words * 8 * (size_t)world, &all_hdr));
   if (n_rows > 0) {
-    count_kernel<<<(int)g, kCountThreads, n * 4, ctx->stream>>>(ks, mod, n_rows, chunk_rows, (uint32_t*)hist->p, nullptr);
+    count_kernel<<<(int)g, kCountThreads, n * 4, ctx->stream>>>(ks, mod, n_rows, chunk_rows, (uint32_t*)hist->p, nullptr, (uint16_t*)pids->p);
     scan_kernel<<<1, 1024, 0, ctx->stream>>>((const uint32_t*)hist->p, (uint64_t*)base->p, (uint64_t*)hdr->p, n, (uint32_t)g, n_rows);
     ctx->launches += 2;
     BGPU_CUDA(ctx, cudaGetLastError());
@@ -412,7 +251,6 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
     delta[p] = (int64_t)recv[(size_t)d][(size_t)k * world + me] - (int64_t)offs[(size_t)me * (n + 1) + p];
     if (d != me) sent_rows += offs[(size_t)me * (n + 1) + p + 1] - offs[(size_t)me * (n + 1) + p];
   }
-  ScatterArgs args{};
   args.n_cols = (int32_t)n_cols;
   std::vector<size_t> order(n_cols);
   for (size_t i = 0; i < n_cols; i++) order[i] = i;
@@ -446,10 +284,10 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
     BGPU_CUDA(ctx, cudaMemcpyAsync(d_delta->p, delta.data(), (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
     BGPU_CUDA(ctx, cudaMemcpyAsync(d_ptrs->p, ptrs.data(), ptrs.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
     add_delta_kernel<<<(unsigned)((n * g + 255) / 256), 256, 0, ctx->stream>>>((uint64_t*)base->p, (const int64_t*)d_delta->p, n, (uint32_t)g);
-    BGPU_CUDA(ctx, raise_max_dynamic_smem((const void*)scatter_peer_kernel<256, 4>, ctx->device, smem));
     // 4. the fused scatter: runs go straight into the owners' windows
-    scatter_peer_kernel<256, 4><<<(int)g, 256, smem, ctx->stream>>>(ks, mod, args, n_rows, chunk_rows, (const uint64_t*)base->p,
-                                                                   (void* const*)d_ptrs->p, world);
+    l.pids = (const uint16_t*)pids->p; l.chunk_rows = chunk_rows; l.base = (const uint64_t*)base->p;
+    l.peer_out = (void* const*)d_ptrs->p;
+    BGPU_TRY(scatter_dispatch(ctx, geom, false, true, true, g, smem, l, nullptr));
     ctx->launches += 2;
     BGPU_CUDA(ctx, cudaGetLastError());
     BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // delta / ptrs are host temporaries of this call
