@@ -449,6 +449,7 @@ int agg_generate_source(const bgpu_agg* g, const JitShape& sh, std::string* out)
     o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_acc_shared(const __grid_constant__ JitArgs a) { accumulate_body<Plan, 1>(a); }");
     o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T, Plan::MIN_CTAS) bgpu_acc_global(const __grid_constant__ JitArgs a) { accumulate_body<Plan, 2>(a); }");
     o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_sketch(const __grid_constant__ JitArgs a) { sketch_body<Plan>(a); }");
+    o.line("extern \"C\" __global__ void __launch_bounds__(Plan::T) bgpu_bucket(const __grid_constant__ JitArgs a) { bucket_body<Plan>(a); }");
   }
   *out = std::move(o.s);
   return BGPU_OK;

@@ -85,6 +85,7 @@ struct bgpu_agg {
   // pass would barely reduce (most rows are their own group), input rows are emitted as state rows - key, sum = the
   // argument, count = 1 - and the FinalPartitioned side does the only aggregation, after the exchange. What DataFusion
   // later added as skip_partial_aggregation; results are identical (a Partial aggregate never promised full reduction).
+  uint64_t radix_batches = 0;  // batches whose rows were moved into table-bucket order first (radix pre-pass)
   bool passthrough = false;
   bool any_committed = false;  // some batch of this stream has been aggregated into the table
   std::vector<std::unique_ptr<bgpu_batch>> pass_chunks;

@@ -61,6 +61,10 @@ struct JitArgs {
   uint32_t cache_slots;              // fused: key cache slots (power of two)
   uint32_t n_groups;                 // accumulate: groups so far
   uint32_t replicas;                 // accumulate TIER 1: shared-memory copies per CTA
+  uint16_t* bucket_ids;              // radix pre-pass: table bucket per row
+  uint32_t* bucket_hist;             // radix pre-pass: hist[bucket][chunk]
+  uint32_t bucket_shift;             // bucket = (table slot index) >> bucket_shift
+  uint32_t bucket_chunk;             // rows per CTA chunk (the scatter's chunk layout)
 };
 
 __device__ __forceinline__ bool bit_set(const uint8_t* bits, int64_t i) { return (bits[i >> 3] >> (i & 7)) & 1; }
@@ -902,6 +906,55 @@ __device__ __forceinline__ void sketch_body(const JitArgs& a) {
     for (int u = 0; u < R; u++)
       if (bit[u] & ~cur[u]) atomicOr(&a.gids[word[u]], bit[u]);
   }
+}
+
+// two-pass path, radix pre-pass (tables far beyond the L2): the bucket of a row is the top bits of its first slot index, so
+// that rows of one bucket touch one contiguous slice of the table; the host scatters the rows into bucket order
+// (partition.cu's scan + scatter: the chunk layout and hist[bucket][chunk] are its) before pass 1 and 2 run over them.
+// Rows the filter drops go to bucket 0 (they are dropped again later).
+template <class Plan>
+__device__ __forceinline__ void bucket_body(const JitArgs& a) {
+  constexpr int T = Plan::T, R = Plan::R;
+  extern __shared__ __align__(16) uint64_t smem[];
+  uint32_t* s_hist = (uint32_t*)smem;
+  const uint32_t nb = a.n_groups;
+  for (uint32_t i = threadIdx.x; i < nb; i += T) s_hist[i] = 0;
+  __syncthreads();
+  // a.replicas CTAs share one chunk of the scatter's layout (its grid alone would leave the SMs nearly empty here)
+  const int64_t tile = (int64_t)T * R, last = a.n_rows - 1;
+  const uint32_t chunk = blockIdx.x / a.replicas, sub = blockIdx.x % a.replicas, n_chunks = gridDim.x / a.replicas;
+  const int64_t sub_rows = (((int64_t)a.bucket_chunk + a.replicas - 1) / a.replicas + tile - 1) / tile * tile;
+  int64_t chunk_end = ((int64_t)chunk + 1) * (int64_t)a.bucket_chunk;
+  if (chunk_end > a.n_rows) chunk_end = a.n_rows;
+  const int64_t begin = (int64_t)chunk * (int64_t)a.bucket_chunk + (int64_t)sub * sub_rows;
+  int64_t end = begin + sub_rows;
+  if (end > chunk_end) end = chunk_end;
+  for (int64_t base = begin; base < end; base += tile) {
+    typename Plan::Raw x[R];
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      Plan::template load0<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
+      Plan::template load1<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      Plan::template load2<NEED_FILTER | NEED_KEY>(a, r < last ? r : last, x[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t r = base + u * T + threadIdx.x;
+      if (r >= end) continue;
+      uint32_t p = 0;
+      if (Plan::filter(a, x[u])) p = ((uint32_t)key_hash<Plan::KEY_WORDS>(Plan::key(a, x[u])) & a.t.mask) >> a.bucket_shift;
+      a.bucket_ids[r] = (uint16_t)p;
+      atomicAdd(&s_hist[p], 1u);
+    }
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < nb; i += T)  // (zero-initialised by the host)
+    if (s_hist[i]) atomicAdd(&a.bucket_hist[(size_t)i * n_chunks + chunk], s_hist[i]);
 }
 
 // two-pass path, pass 1

@@ -166,6 +166,9 @@ struct JitArgs {
   uint32_t* gids;
   int64_t n_rows;
   uint32_t g_cap, cache_slots, n_groups, replicas;
+  uint16_t* bucket_ids;
+  uint32_t* bucket_hist;
+  uint32_t bucket_shift, bucket_chunk;
 };
 
 // Compile one aggregate-argument program. `fields` is the raw input schema. Returns BGPU_OK or fails ctx.

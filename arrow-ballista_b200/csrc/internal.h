@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include <atomic>
+#include <functional>
 #include <memory>
 #include <string>
 #include <vector>
@@ -153,6 +154,11 @@ struct KCol {
 
 // dictionary.cu: dictionary columns on the move (decode to values, move, re-encode with identity indices)
 namespace bgpu {
+// partition.cu: scan + stable scatter of every column of `in` by the 16-bit partition ids `pass1` leaves behind
+// (pass1(grid, chunk_rows, hist[p][chunk], ids[row]) launches the kernel that computes them on ctx->stream)
+using PartitionPass1 = std::function<int(int64_t, int64_t, uint32_t*, uint16_t*)>;
+int partition_rows(bgpu_ctx* ctx, const bgpu_batch* in, uint32_t n_partitions, const PartitionPass1& pass1,
+                   bgpu_batch** out_partitioned, uint64_t* out_offsets);
 bool batch_has_dictionary(const bgpu_batch* b);
 int dict_decode_column(bgpu_ctx* ctx, const Column& c, int64_t n, Column* out);
 int dict_decode_batch(bgpu_ctx* ctx, const bgpu_batch* in, std::unique_ptr<bgpu_batch>* out, std::vector<size_t>* dict_cols);

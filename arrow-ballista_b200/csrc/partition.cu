@@ -614,12 +614,13 @@ static bool parse_geometry(const char* e, ScatterGeom* geom) {
   return true;
 }
 
-extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const int32_t* key_cols, int32_t n_keys,
-                                   uint32_t n_partitions, bgpu_batch** out_partitioned, uint64_t* out_offsets,
-                                   uint64_t* out_hashes_device) try {
-  if (!ctx || !in || !key_cols || !out_partitioned || !out_offsets) return BGPU_EINVAL;
+// The repartition proper: pass 1 is the caller's (`pass1` launches a kernel that leaves one 16-bit partition id per row and
+// hist[p][chunk], the chunk layout being the scatter's), then scan + scatter of every column. out_offsets == nullptr: the
+// caller does not want the partition offsets on the host (no read-back, no synchronisation unless a utf8 column of unknown
+// extent needs one).
+int bgpu::partition_rows(bgpu_ctx* ctx, const bgpu_batch* in, uint32_t n_partitions, const PartitionPass1& pass1,
+                         bgpu_batch** out_partitioned, uint64_t* out_offsets) {
   *out_partitioned = nullptr;
-  if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
   if (n_partitions == 0) return ctx->fail(BGPU_EINVAL, "n_partitions must be > 0");
   if (n_partitions > kMaxPartitions)
     return ctx->fail(BGPU_EUNSUPPORTED, "n_partitions > " + std::to_string(kMaxPartitions));
@@ -742,16 +743,12 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
   }
 
   if (n_rows == 0) {
-    for (uint32_t p = 0; p <= n; p++) out_offsets[p] = 0;
+    if (out_offsets)
+      for (uint32_t p = 0; p <= n; p++) out_offsets[p] = 0;
     for (auto& up : utf8) BGPU_CUDA(ctx, cudaMemsetAsync(out->cols[up.col].offsets, 0, 4, ctx->stream));
     *out_partitioned = out.release();
     return BGPU_OK;
   }
-
-  KeySet ks{};
-  std::vector<DevAllocPtr> temps;
-  BGPU_TRY(make_keyset(ctx, in, key_cols, n_keys, &ks, &temps));
-  const Modulo mod = make_modulo(n);
 
   // grid: one persistent CTA per resident slot, contiguous chunks of whole tiles
   const size_t smem = scatter_smem_bytes(n, geom.threads, geom.items, args.async_width, args.side_width);
@@ -773,8 +770,7 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
   BGPU_TRY(dev_alloc(ctx, (size_t)(n + 1) * 8, &offs));
   BGPU_TRY(dev_alloc(ctx, (size_t)n_rows * 2, &pids));
 
-  count_kernel<<<(int)g, kCountThreads, n * 4, ctx->stream>>>(ks, mod, n_rows, chunk_rows, (uint32_t*)hist->p,
-                                                        out_hashes_device, (uint16_t*)pids->p);
+  BGPU_TRY(pass1(g, chunk_rows, (uint32_t*)hist->p, (uint16_t*)pids->p));
   scan_kernel<<<1, 1024, 0, ctx->stream>>>((const uint32_t*)hist->p, (uint64_t*)base->p, (uint64_t*)offs->p, n,
                                            (uint32_t)g, n_rows);
   l.pids = (const uint16_t*)pids->p; l.chunk_rows = chunk_rows; l.base = (const uint64_t*)base->p;
@@ -813,12 +809,36 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
     BGPU_CUDA(ctx, cudaGetLastError());
   }
 
-  uint64_t* h_offs = (uint64_t*)ctx->pinned;
-  BGPU_CUDA(ctx, cudaMemcpyAsync(h_offs, offs->p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
-  BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  for (uint32_t p = 0; p <= n; p++) out_offsets[p] = h_offs[p];
+  if (out_offsets) {
+    uint64_t* h_offs = (uint64_t*)ctx->pinned;
+    BGPU_CUDA(ctx, cudaMemcpyAsync(h_offs, offs->p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (uint32_t p = 0; p <= n; p++) out_offsets[p] = h_offs[p];
+  }
   *out_partitioned = out.release();
   return BGPU_OK;
+}
+
+extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const int32_t* key_cols, int32_t n_keys,
+                                   uint32_t n_partitions, bgpu_batch** out_partitioned, uint64_t* out_offsets,
+                                   uint64_t* out_hashes_device) try {
+  if (!ctx || !in || !key_cols || !out_partitioned || !out_offsets) return BGPU_EINVAL;
+  *out_partitioned = nullptr;
+  if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
+  if (n_partitions == 0) return ctx->fail(BGPU_EINVAL, "n_partitions must be > 0");
+  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  KeySet ks{};
+  std::vector<DevAllocPtr> temps;
+  if (in->n_rows) BGPU_TRY(make_keyset(ctx, in, key_cols, n_keys, &ks, &temps));
+  const Modulo mod = make_modulo(n_partitions);
+  const int64_t n_rows = in->n_rows;
+  return partition_rows(ctx, in, n_partitions,
+                        [&](int64_t g, int64_t chunk_rows, uint32_t* hist, uint16_t* pids) {
+                          count_kernel<<<(int)g, kCountThreads, n_partitions * 4, ctx->stream>>>(ks, mod, n_rows, chunk_rows, hist,
+                                                                                               out_hashes_device, pids);
+                          return BGPU_OK;
+                        },
+                        out_partitioned, out_offsets);
 } catch (const std::exception& e) {
   return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
 }

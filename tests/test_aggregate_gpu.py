@@ -110,6 +110,31 @@ def test_high_cardinality_grows_table(bb, ctx, oracle):
              [("sum", "v", "s"), ("count", None, "c"), ("avg", "f", "a")], 2)
 
 
+@pytest.mark.parametrize("groups", [["k64"], ["d", "k64"], ["k64", "dec"]])
+def test_radix_prepass_gives_the_same_groups(bb, ctx, oracle, groups, monkeypatch):
+    """The radix pre-pass of the two-pass path (rows moved into table-bucket order before intern / accumulate; opt-in, see
+    profiles/r2_orderkey.md), forced on for a small input: nullable arguments, a dictionary key, a key wider than 16 bytes (interned ids) and several batches
+    into the same table - bit-exact against the oracle, and the path reports itself."""
+    monkeypatch.setenv("BGPU_RADIX", "1")
+    monkeypatch.setenv("BGPU_RADIX_MIN_MB", "0")
+    monkeypatch.setenv("BGPU_RADIX_MIN_ROWS", "1000")
+    monkeypatch.setenv("BGPU_RADIX_BUCKETS", "64")
+    rng = np.random.default_rng(77)
+    whole = random_batch(rng, 120_000)
+    k = pa.array(rng.integers(0, 90_000, whole.num_rows), type=pa.int64())
+    whole = whole.set_column(whole.schema.names.index("k64"), "k64", k)
+    batches = [whole.slice(0, 70_000), whole.slice(70_000)]
+    gi = [whole.schema.names.index(c) for c in groups]
+    spec = [(op, whole.schema.names.index(c) if c else None, name) for op, c, name in Q1_AGGS]
+    gp = bb.GpuAggregateExec(ctx, bb.AggregateMode.Partial, gi, spec, whole.schema)
+    want = oracle.GroupedAggregate("partial", gi, spec)
+    for b in batches:
+        gp.update(b)
+        assert gp.last_path == "global_radix", gp.last_path
+        want.update(b)
+    assert_same_groups(gp.emit().download(), want.emit(), len(gi))
+
+
 def test_int64_sum_wraps(bb, ctx, oracle):
     b = pa.RecordBatch.from_arrays([pa.array([0, 0, 0, 1], type=pa.int64()),
                                     pa.array([2**62, 2**62, 2**62, -5], type=pa.int64())], names=["k", "v"])
