@@ -27,6 +27,7 @@
 
 #include <algorithm>
 #include <condition_variable>
+#include <pthread.h>
 #include <deque>
 #include <mutex>
 
@@ -279,12 +280,36 @@ int used_columns(bgpu_agg* g, std::vector<IngestCol>* out) {
   return BGPU_OK;
 }
 
+// The widest build of the host packer this CPU runs, starting at `from` (0: AVX-512, 1: AVX2, 2: plain).
+static const bgpu_pack::Ops* pack_ops_for(int from) {
+  if (from <= 0 && __builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512bw") && __builtin_cpu_supports("avx512vl") &&
+      __builtin_cpu_supports("avx512dq"))
+    return &pack_avx512::ops;
+  if (from <= 1 && __builtin_cpu_supports("avx2")) return &pack_avx2::ops;
+  return &pack_base::ops;
+}
+
+// BGPU_INGEST_TRACE=1: one stderr line per state change of the staging pipeline (thread id, chunk slot, sequence number)
+static bool ingest_trace() {
+  static const bool on = getenv("BGPU_INGEST_TRACE") != nullptr;
+  return on;
+}
+#define INGEST_TRACE(...)                                                                   \
+  do {                                                                                      \
+    if (ingest_trace()) {                                                                   \
+      fprintf(stderr, "[bgpu ingest %lx] ", (unsigned long)pthread_self());                 \
+      fprintf(stderr, __VA_ARGS__);                                                         \
+      fputc('\n', stderr);                                                                  \
+    }                                                                                       \
+  } while (0)
+
 int ingest_create(bgpu_agg* g) {
   bgpu_ctx* ctx = g->ctx;
   if (g->final_mode) return ctx->fail(BGPU_EINVAL, "bgpu_agg_push_host takes raw input rows (Partial / Single modes)");
   auto in = std::make_shared<Ingest>();
   in->g = g; in->ctx = ctx;
-  in->ops = __builtin_cpu_supports("avx2") && !getenv("BGPU_INGEST_NO_AVX2") ? &pack_avx2::ops : &pack_base::ops;
+  in->ops = pack_ops_for(getenv("BGPU_INGEST_NO_AVX512") ? 1 : 0);
+  if (getenv("BGPU_INGEST_NO_AVX2")) in->ops = &pack_base::ops;
   BGPU_TRY(used_columns(g, &in->cols));
   const size_t n_cols = in->cols.size();
   in->data_cap = env_size("BGPU_INGEST_CHUNK_MB", 32) << 20;
@@ -337,7 +362,9 @@ int poll_set(Ingest* in, int s) {
   if (!ds.pending) return BGPU_OK;
   ds.pending = false;
   bool replay = false;
+  INGEST_TRACE("poll set %d", s);
   BGPU_TRY(agg_async_result(in->g, &ds.req, &replay));
+  INGEST_TRACE("set %d: %s", s, replay ? "replay" : "committed");
   if (replay) {
     in->st_replays++;
     BGPU_TRY(agg_update_replay(in->g, ds.batch.get()));
@@ -358,6 +385,7 @@ int submit_chunk(Ingest* in, Chunk* ch) {
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
   const int s = (int)(in->seq % kSets);
   DeviceSet& ds = in->sets[s];
+  INGEST_TRACE("submit slot %d as seq %llu (rows %u) into set %d", (int)(ch - in->chunks), (unsigned long long)in->seq, ch->rows, s);
   // this set's previous launch (the oldest one pending) must be known good, or replayed from the set's buffers, before
   // they are overwritten
   BGPU_TRY(poll_set(in, s));
@@ -429,6 +457,7 @@ int submit_chunk(Ingest* in, Chunk* ch) {
   ds.pending = ds.req.launched;
   in->st_async += ds.pending;
   in->seq++;
+  INGEST_TRACE("submitted seq %llu (async %d)", (unsigned long long)in->seq - 1, (int)ds.pending);
   return BGPU_OK;
 }
 
@@ -534,6 +563,7 @@ int push_segment(Ingest* in, const struct ArrowArray* batch, int64_t lo, uint32_
         Chunk& c = in->chunks[in->cur];
         if (c.rows + n <= in->max_rows && c.n_segs < in->max_segs && c.bytes + need <= in->data_cap) { ch = &c; break; }
         c.sealed = true;
+        INGEST_TRACE("seal slot %d (rows %u, writers %d)", in->cur, c.rows, c.writers);
         if (c.writers == 0) to_submit = &c;  // otherwise the last writer to finish submits it
         in->cur = -1;
         if (to_submit) break;  // submit first (outside the lock), then come back for a slot
@@ -543,15 +573,22 @@ int push_segment(Ingest* in, const struct ArrowArray* batch, int64_t lo, uint32_
         if (in->chunks[i].state == Chunk::FREE) free_slot = i;
       for (int i = 0; i < kSlots && free_slot < 0; i++)
         if (in->chunks[i].state == Chunk::IN_FLIGHT) free_slot = i;
-      if (free_slot < 0) { in->cv.wait(lk); continue; }
+      if (free_slot < 0) {
+        INGEST_TRACE("no free slot: wait");
+        in->cv.wait(lk);
+        continue;
+      }
       Chunk& c = in->chunks[free_slot];
       if (c.state == Chunk::IN_FLIGHT) {  // its copies must have left the pinned memory
         lk.unlock();
+        INGEST_TRACE("slot %d in flight: wait for its copies", free_slot);
         const cudaError_t e = cudaEventSynchronize(c.h2d_done);
+        INGEST_TRACE("slot %d copies done", free_slot);
         lk.lock();
         if (e != cudaSuccess) return ctx->fail(BGPU_ECUDA, std::string("cudaEventSynchronize: ") + cudaGetErrorString(e));
         if (c.state != Chunk::IN_FLIGHT || in->cur >= 0) continue;  // somebody else took it meanwhile
       }
+      INGEST_TRACE("open slot %d", free_slot);
       c.state = Chunk::FILLING;
       c.rows = 0; c.n_segs = 0; c.bytes = 0; c.writers = 0; c.sealed = false;
       std::fill(c.str_bytes.begin(), c.str_bytes.end(), 0);
@@ -574,8 +611,11 @@ int push_segment(Ingest* in, const struct ArrowArray* batch, int64_t lo, uint32_
     }
   }
   if (!ch) {  // the chunk this thread sealed had no writers left: submit it, then retry this segment
-    std::lock_guard<std::mutex> sl(in->submit_mu);
-    const int rc = submit_chunk(in, to_submit);
+    int rc;
+    {  // (the retry below may have to submit again: submit_mu must be free by then)
+      std::lock_guard<std::mutex> sl(in->submit_mu);
+      rc = submit_chunk(in, to_submit);
+    }
     if (rc != BGPU_OK) { fail_sticky(in, rc); return rc; }
     return push_segment(in, batch, lo, n);
   }
@@ -704,12 +744,14 @@ extern "C" int bgpu_agg_ingest_stats(const bgpu_agg* g, uint64_t* out8) {
 }
 
 // test hook (host only, no device): the wire form of one fixed-width column segment, as push packs it. format = the
-// column's Arrow C format string; out_packed has room for n * 16 bytes. which = 0: the AVX2 build, 1: the plain one.
+// column's Arrow C format string; out_packed has room for n * 16 bytes. which = 0: the AVX2 build, 1: the plain one,
+// 2: the AVX-512 build (BGPU_EUNSUPPORTED when the CPU cannot run the one asked for).
 extern "C" int bgpu_debug_pack_fixed_host(const char* format, const void* values, int64_t n, int32_t which, int64_t* out_base,
                                           uint32_t* out_code, uint8_t* out_packed) {
   if (!format || !values || !out_base || !out_code || !out_packed || n < 0) return BGPU_EINVAL;
   if (which == 0 && !__builtin_cpu_supports("avx2")) return BGPU_EUNSUPPORTED;
-  const bgpu_pack::Ops* ops = which == 0 ? &pack_avx2::ops : &pack_base::ops;
+  if (which == 2 && pack_ops_for(0) != &pack_avx512::ops) return BGPU_EUNSUPPORTED;
+  const bgpu_pack::Ops* ops = which == 2 ? &pack_avx512::ops : which == 0 ? &pack_avx2::ops : &pack_base::ops;
   const char c0 = format[0];
   int width = 0;
   switch (c0) {

@@ -18,3 +18,4 @@ struct Ops {
 }  // namespace bgpu_pack
 namespace pack_avx2 { extern const bgpu_pack::Ops ops; }
 namespace pack_base { extern const bgpu_pack::Ops ops; }
+namespace pack_avx512 { extern const bgpu_pack::Ops ops; }

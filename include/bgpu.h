@@ -197,7 +197,7 @@ int bgpu_agg_push_host(bgpu_agg* agg, const struct ArrowArray* batch, const stru
 int bgpu_agg_flush(bgpu_agg* agg);
 int bgpu_agg_ingest_stats(const bgpu_agg* agg, uint64_t* out8);
 /* test hook (host only): the wire form of one fixed-width column segment as bgpu_agg_push_host packs it (which = 0: the
- * AVX2 build of the packer, 1: the plain build); out_packed has room for n * 16 bytes */
+ * AVX2 build of the packer, 1: the plain build, 2: the AVX-512 build); out_packed has room for n * 16 bytes */
 int bgpu_debug_pack_fixed_host(const char* format, const void* values, int64_t n, int32_t which, int64_t* out_base,
                                uint32_t* out_code, uint8_t* out_packed);
 /* end of input: state() (Partial) or evaluate() (Final modes and Single). Group order is unspecified, as in the

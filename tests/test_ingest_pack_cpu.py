@@ -17,8 +17,8 @@ def _pack(fmt, arr, which):
     base, code = C.c_int64(), C.c_uint32()
     rc = lib().bgpu_debug_pack_fixed_host(fmt.encode(), arr.ctypes.data_as(C.c_void_p), n if not fmt.startswith("d") else n // 2,
                                           which, C.byref(base), C.byref(code), out.ctypes.data_as(C.c_void_p))
-    if rc == 2 and which == 0:
-        pytest.skip("host without AVX2")
+    if rc == 2 and which in (0, 2):
+        pytest.skip("host without AVX2 / AVX-512")
     assert rc == 0
     return base.value, code.value, out
 
@@ -37,7 +37,7 @@ CASES = [("c", np.int8, -128, 127), ("C", np.uint8, 0, 255), ("s", np.int16, -30
          ("tdD", np.int32, 8036, 10561), ("tsu:", np.int64, 1_600_000_000_000_000, 1_600_000_000_000_000 + 10**9)]
 
 
-@pytest.mark.parametrize("which", [0, 1])
+@pytest.mark.parametrize("which", [0, 1, 2])
 @pytest.mark.parametrize("fmt,dtype,lo,hi", CASES)
 def test_fixed_roundtrip_and_width(which, fmt, dtype, lo, hi):
     rng = np.random.default_rng(1)
@@ -59,7 +59,7 @@ def test_fixed_roundtrip_and_width(which, fmt, dtype, lo, hi):
             assert (got == arr).all()
 
 
-@pytest.mark.parametrize("which", [0, 1])
+@pytest.mark.parametrize("which", [0, 1, 2])
 def test_decimal128_fits64_and_wide(which):
     rng = np.random.default_rng(2)
     n = 5000
@@ -75,7 +75,7 @@ def test_decimal128_fits64_and_wide(which):
     assert code == RAW and (packed[: n * 16].view(np.int64) == dec).all()
 
 
-@pytest.mark.parametrize("which", [0, 1])
+@pytest.mark.parametrize("which", [0, 1, 2])
 def test_floats_travel_raw(which):
     arr = np.random.default_rng(3).random(1000)
     base, code, packed = _pack("g", arr, which)
