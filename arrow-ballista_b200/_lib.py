@@ -54,6 +54,8 @@ SIGNATURES = {
     "bgpu_ctx_synchronize": (C.c_int, [C.c_void_p]),
     "bgpu_ctx_stream": (C.c_void_p, [C.c_void_p]),
     "bgpu_ctx_kernel_launches": (C.c_uint64, [C.c_void_p]),
+    "bgpu_ctx_enable_times": (C.c_int, [C.c_void_p, C.c_int32]),
+    "bgpu_ctx_times": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_int32]),
     "bgpu_batch_upload": (C.c_int, [C.c_void_p, C.POINTER(ArrowArray), C.POINTER(ArrowSchema), C.POINTER(C.c_void_p)]),
     "bgpu_batch_wrap_device": (C.c_int, [C.c_void_p, C.POINTER(ArrowArray), C.POINTER(ArrowSchema),
                                          C.POINTER(C.c_void_p)]),

@@ -1053,6 +1053,7 @@ extern "C" int bgpu_agg_update(bgpu_agg* g, const bgpu_batch* batch) try {
   bgpu_ctx* ctx = g->ctx;
   if (g->emitted) return ctx->fail(BGPU_EINVAL, "aggregate already emitted");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  GpuTimeScope timed(ctx, T_KERNEL);
   if (g->ingest_drain) BGPU_TRY(g->ingest_drain(g));  // streamed input still in flight goes first
   return agg_update_impl(g, batch, nullptr);
 } catch (const std::exception& e) {
@@ -1073,6 +1074,7 @@ extern "C" int bgpu_agg_emit(bgpu_agg* g, bgpu_batch** out_batch) try {
   bgpu_ctx* ctx = g->ctx;
   if (g->emitted) return ctx->fail(BGPU_EINVAL, "aggregate already emitted");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  GpuTimeScope timed(ctx, T_KERNEL);
   if (g->ingest_drain) BGPU_TRY(g->ingest_drain(g));  // end of input: everything pushed so far is aggregated first
   if (g->passthrough) {  // the state rows are the chunks themselves
     if (g->pass_chunks.size() == 1) {

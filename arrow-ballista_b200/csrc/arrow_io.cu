@@ -159,6 +159,8 @@ static int import_batch(bgpu_ctx* ctx, const struct ArrowArray* a, const struct 
 
 extern "C" int bgpu_batch_upload(bgpu_ctx* ctx, const struct ArrowArray* a, const struct ArrowSchema* s,
                                  bgpu_batch** out) try {
+  if (ctx && ctx->has_device) cudaSetDevice(ctx->device);
+  GpuTimeScope timed(ctx, T_H2D);
   return import_batch(ctx, a, s, false, out);
 } catch (const std::exception& e) {
   return bgpu::abi_guard(ctx, e);  // nothing is thrown across the C ABI
@@ -471,6 +473,7 @@ extern "C" int bgpu_batch_download(bgpu_ctx* ctx, const bgpu_batch* b, int64_t r
   if (row_offset < 0 || num_rows < 0 || row_offset + num_rows > b->n_rows)
     return ctx->fail(BGPU_EINVAL, "row range out of bounds");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  GpuTimeScope timed(ctx, T_D2H);
   if (row_offset == 0 && num_rows == b->n_rows && !getenv("BGPU_NO_FAST_DOWNLOAD")) {
     bool done = false;
     BGPU_TRY(download_fast(ctx, b, out, &done));

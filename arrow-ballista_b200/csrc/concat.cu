@@ -95,6 +95,8 @@ extern "C" int bgpu_batch_concat(bgpu_ctx* ctx, const bgpu_batch* const* batches
   if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
   for (int32_t k = 0; k < n; k++)
     if (!batches[k]) return ctx->fail(BGPU_EINVAL, "null batch");
+  cudaSetDevice(ctx->device);
+  GpuTimeScope timed(ctx, T_KERNEL);
   {  // dictionary columns: every input has its own dictionary, so the VALUES are concatenated and re-encoded (dictionary.cu)
     bool any_dict = false;
     for (int32_t k = 0; k < n; k++) any_dict |= batch_has_dictionary(batches[k]);

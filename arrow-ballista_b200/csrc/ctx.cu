@@ -55,7 +55,61 @@ static void ctx_teardown(bgpu_ctx* ctx) {
   }
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   for (auto& b : ctx->pinned_pool) cudaFreeHost(b.first);
+  for (auto& sp : ctx->times_open) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+  for (cudaEvent_t e : ctx->times_pool) cudaEventDestroy(e);
   delete ctx;
+}
+
+// ---- h2d / kernel / d2h accounting -------------------------------------------------------------------------------
+static cudaEvent_t times_event(bgpu_ctx* ctx) {
+  if (!ctx->times_pool.empty()) {
+    cudaEvent_t e = ctx->times_pool.back();
+    ctx->times_pool.pop_back();
+    return e;
+  }
+  cudaEvent_t e = nullptr;
+  if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+  return e;
+}
+GpuTimeScope::GpuTimeScope(bgpu_ctx* c, int cls_, cudaStream_t st) : ctx(c), cls(cls_), stream(st ? st : (c ? c->stream : nullptr)) {
+  if (!ctx || !ctx->times_on || !ctx->has_device) { ctx = nullptr; return; }
+  if (stream == ctx->stream && ctx->times_depth++ > 0) return;  // an enclosing scope accounts for this work
+  a = times_event(ctx);
+  if (a) cudaEventRecord(a, stream);
+}
+GpuTimeScope::~GpuTimeScope() {
+  if (!ctx) return;
+  if (stream == ctx->stream) ctx->times_depth--;
+  if (!a) return;
+  cudaEvent_t b = times_event(ctx);
+  if (!b) { ctx->times_pool.push_back(a); return; }
+  cudaEventRecord(b, stream);
+  ctx->times_open.push_back(bgpu_ctx::TimedSpan{a, b, cls});
+}
+
+extern "C" int bgpu_ctx_enable_times(bgpu_ctx* ctx, int32_t on) {
+  if (!ctx) return BGPU_EINVAL;
+  ctx->times_on = on != 0;
+  return BGPU_OK;
+}
+
+extern "C" int bgpu_ctx_times(bgpu_ctx* ctx, double* out3_ms, int32_t reset) {
+  if (!ctx || !out3_ms) return BGPU_EINVAL;
+  if (ctx->has_device) {
+    BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+    for (auto& sp : ctx->times_open) {
+      float ms = 0.f;
+      BGPU_CUDA(ctx, cudaEventSynchronize(sp.b));
+      if (cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) ctx->times_ms[sp.cls] += ms;
+      ctx->times_pool.push_back(sp.a);
+      ctx->times_pool.push_back(sp.b);
+    }
+    ctx->times_open.clear();
+  }
+  for (int i = 0; i < 3; i++) out3_ms[i] = ctx->times_ms[i];
+  if (reset)
+    for (int i = 0; i < 3; i++) ctx->times_ms[i] = 0.0;
+  return BGPU_OK;
 }
 
 int ctx_pinned_get(bgpu_ctx* ctx, size_t bytes, void** out) {

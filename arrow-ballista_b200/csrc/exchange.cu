@@ -110,6 +110,7 @@ extern "C" int bgpu_all_to_all(bgpu_ctx* ctx, void* comm, int32_t rank, int32_t 
   const Nccl& nc = nccl();
   if (!nc.ok) return ctx->fail(BGPU_ENCCL, "NCCL unavailable: " + nc.why);
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  GpuTimeScope timed(ctx, T_KERNEL);
   if (bgpu::batch_has_dictionary(in)) {
     // dictionary columns (schema-level: the same decision on every rank): the values travel, the received rows are
     // re-encoded against a dictionary of their own (dictionary.cu)

@@ -392,10 +392,14 @@ int submit_chunk(Ingest* in, Chunk* ch) {
   const size_t n_cols = in->cols.size();
   const uint32_t rows = ch->rows, n_segs = ch->n_segs;
   if (ds.used) BGPU_CUDA(ctx, cudaStreamWaitEvent(in->copy_stream, ds.widen_done, 0));
-  BGPU_CUDA(ctx, cudaMemcpyAsync(ds.header->p, ch->pinned, (size_t)n_segs * in->rec_bytes, cudaMemcpyHostToDevice, in->copy_stream));
-  if (ch->bytes)
-    BGPU_CUDA(ctx, cudaMemcpyAsync(ds.wire->p, ch->pinned + in->header_bytes, ch->bytes, cudaMemcpyHostToDevice, in->copy_stream));
+  {
+    GpuTimeScope timed_copy(ctx, T_H2D, in->copy_stream);
+    BGPU_CUDA(ctx, cudaMemcpyAsync(ds.header->p, ch->pinned, (size_t)n_segs * in->rec_bytes, cudaMemcpyHostToDevice, in->copy_stream));
+    if (ch->bytes)
+      BGPU_CUDA(ctx, cudaMemcpyAsync(ds.wire->p, ch->pinned + in->header_bytes, ch->bytes, cudaMemcpyHostToDevice, in->copy_stream));
+  }
   BGPU_CUDA(ctx, cudaEventRecord(ch->h2d_done, in->copy_stream));
+  GpuTimeScope timed(ctx, T_KERNEL);  // widen + the aggregate kernels of this chunk
   BGPU_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ch->h2d_done, 0));
   in->st_chunks++;
   in->st_wire_bytes += ch->bytes + (size_t)n_segs * in->rec_bytes;

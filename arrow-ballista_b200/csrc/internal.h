@@ -59,6 +59,14 @@ struct bgpu_ctx {
   // milliseconds per block, an aggregate per stage must not pay it again
   std::mutex pinned_pool_mu;
   std::vector<std::pair<void*, size_t>> pinned_pool;
+  // opt-in accounting of GPU time per class (bgpu_ctx_enable_times / bgpu_ctx_times: the h2d_time / kernel_time /
+  // d2h_time metrics of an operator): every instrumented entry point brackets its stream work with an event pair
+  bool times_on = false;
+  int times_depth = 0;                       // only the outermost scope of a call chain records
+  double times_ms[3] = {0.0, 0.0, 0.0};      // resolved so far: h2d, kernel, d2h
+  struct TimedSpan { cudaEvent_t a, b; int cls; };
+  std::vector<TimedSpan> times_open;         // recorded, not yet read back
+  std::vector<cudaEvent_t> times_pool;       // events to reuse
 
   int fail(int code, const std::string& msg) {
     err = msg;
@@ -79,6 +87,19 @@ struct bgpu_ctx {
     int _rc = (expr);         \
     if (_rc != BGPU_OK) return _rc; \
   } while (0)
+
+// GPU time of the enclosing scope's stream work, accounted to a class (no-op unless bgpu_ctx_enable_times was called).
+enum TimeClass : int { T_H2D = 0, T_KERNEL = 1, T_D2H = 2 };
+struct GpuTimeScope {
+  bgpu_ctx* ctx;
+  cudaEvent_t a = nullptr;
+  int cls;
+  cudaStream_t stream;
+  GpuTimeScope(bgpu_ctx* c, int cls_, cudaStream_t st = nullptr);
+  ~GpuTimeScope();
+  GpuTimeScope(const GpuTimeScope&) = delete;
+  GpuTimeScope& operator=(const GpuTimeScope&) = delete;
+};
 
 // a pinned host block of at least `bytes` from the context's pool (cudaHostAlloc on a miss) / back into it
 int ctx_pinned_get(bgpu_ctx* ctx, size_t bytes, void** out);

@@ -601,6 +601,7 @@ static int encode_impl(bgpu_ctx* ctx, const bgpu_batch* batch, const uint64_t* o
                        int64_t dict_id, uint8_t** out_bytes, uint64_t* out_msg_off) {
   *out_bytes = nullptr;
   const size_t n_cols = batch->cols.size();
+  std::unique_ptr<GpuTimeScope> timed(new GpuTimeScope(ctx, T_KERNEL));  // framing + compression; the copy-out is d2h_time
 
   // 1. utf8 columns: the byte offsets at the partition boundaries (one small gather, one sync)
   std::vector<size_t> utf8_cols;
@@ -792,7 +793,10 @@ static int encode_impl(bgpu_ctx* ctx, const bgpu_batch* batch, const uint64_t* o
     BGPU_CUDA(ctx, cudaGetLastError());
     uint8_t* chost = nullptr;
     BGPU_CUDA(ctx, pinned_pool().take(ctotal, &chost));
+    timed.reset();
+    timed.reset(new GpuTimeScope(ctx, T_D2H));
     cudaError_t ce = cudaMemcpyAsync(chost, stage2->p, ctotal, cudaMemcpyDeviceToHost, ctx->stream);
+    timed.reset();
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(ctx->stream);
     if (ce != cudaSuccess) {
       pinned_pool().give(chost);
@@ -822,8 +826,11 @@ static int encode_impl(bgpu_ctx* ctx, const bgpu_batch* batch, const uint64_t* o
   uint8_t* host = nullptr;
   BGPU_CUDA(ctx, pinned_pool().take(total, &host));
   std::vector<unsigned long long> set_bits((size_t)std::max(1, n_counters), 0);
+  timed.reset();
+  timed.reset(new GpuTimeScope(ctx, T_D2H));
   cudaError_t e = cudaMemcpyAsync(host, stage->p, total, cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(set_bits.data(), d_cnt->p, set_bits.size() * 8, cudaMemcpyDeviceToHost, ctx->stream);
+  timed.reset();
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
   if (e != cudaSuccess) {
     pinned_pool().give(host);

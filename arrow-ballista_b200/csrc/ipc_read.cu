@@ -629,8 +629,9 @@ static int decode_record_batch(bgpu_ipc_reader* r, Fb& fb, const Table rb, const
     arena_bytes = align_up(arena_bytes + pb.bytes, 256);
   }
 
-  // 2. move / decode
+  // 2. move / decode (accounted as h2d_time: the copy of the file's bytes dominates; the LZ4 decode rides behind it)
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  GpuTimeScope timed(ctx, T_H2D);
   DevAllocPtr arena;
   BGPU_TRY(dev_alloc(ctx, arena_bytes + 16, &arena));  // + 16: 8-byte-window loads at the end of utf8 data stay in bounds
   uint8_t* base = (uint8_t*)arena->p;

@@ -549,6 +549,7 @@ extern "C" int bgpu_create_hashes(bgpu_ctx* ctx, const bgpu_batch* batch, const 
   if (!ctx || !batch || !key_cols || !out_hashes_device) return BGPU_EINVAL;
   if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  GpuTimeScope timed(ctx, T_KERNEL);
   KeySet ks{};
   std::vector<DevAllocPtr> temps;
   BGPU_TRY(make_keyset(ctx, batch, key_cols, n_keys, &ks, &temps));
@@ -827,6 +828,7 @@ extern "C" int bgpu_hash_partition(bgpu_ctx* ctx, const bgpu_batch* in, const in
   if (!ctx->has_device) return ctx->fail(BGPU_ENODEVICE, "context has no device (libbgpu has no CPU fallback)");
   if (n_partitions == 0) return ctx->fail(BGPU_EINVAL, "n_partitions must be > 0");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  GpuTimeScope timed(ctx, T_KERNEL);
   KeySet ks{};
   std::vector<DevAllocPtr> temps;
   if (in->n_rows) BGPU_TRY(make_keyset(ctx, in, key_cols, n_keys, &ks, &temps));

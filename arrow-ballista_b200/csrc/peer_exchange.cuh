@@ -159,6 +159,7 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
   const int world = x->world, me = x->rank;
   if (n == 0 || n > kMaxPartitions) return ctx->fail(BGPU_EINVAL, "n_partitions out of range");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  GpuTimeScope timed(ctx, T_KERNEL);
   const int64_t n_rows = in->n_rows;
   const size_t n_cols = in->cols.size();
   x->exchanges++;

@@ -279,6 +279,8 @@ extern "C" int bgpu_small_exchange(bgpu_ctx* ctx, void* comm, int32_t rank, int3
   const size_t n_cols = in->cols.size();
   if (n_cols > (size_t)kSmallCols || world > kSmallWorld || n_keys < 1 || n_keys > kMaxKeys)
     return ctx->fail(BGPU_EUNSUPPORTED, "bgpu_small_exchange: schema or world beyond the small path");
+  cudaSetDevice(ctx->device);
+  GpuTimeScope timed(ctx, T_KERNEL);
   if (batch_has_dictionary(in)) {  // schema-level, the same on every rank: values travel, re-encoded on arrival (dictionary.cu)
     BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
     std::unique_ptr<bgpu_batch> decoded;

@@ -204,6 +204,7 @@ extern "C" int bgpu_batch_sort(bgpu_ctx* ctx, const bgpu_batch* in, const int32_
   const int64_t n = in->n_rows;
   if (n > 0xfffffff0LL) return ctx->fail(BGPU_EUNSUPPORTED, "sort: more than 2^32 rows");
   BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  GpuTimeScope timed(ctx, T_KERNEL);
   cudaStream_t st = ctx->stream;
   const int64_t n1 = std::max<int64_t>(n, 1);
   DevAllocPtr perm[2], key[2], tmp;

@@ -164,6 +164,10 @@ class GpuQueryStageExec(QueryStageExecutor):
         if ctx is None:
             ctx = self.ctx = Context(0)
         partitions = self.partitions if self.partitions is not None else list(input_partitions or [])
+        if hasattr(ctx, "enable_times"):
+            ctx.enable_times(True)
+            ctx.times(reset=True)
+            self._timed_ctx = ctx
         states = list(self._states(ctx, partitions))
         if not states:
             if self.shuffle_writer.shuffle_output_partitioning is not None:
@@ -189,8 +193,11 @@ class GpuQueryStageExec(QueryStageExecutor):
 
     def collect_plan_metrics(self):
         m = self.shuffle_writer.metrics
+        gpu = {}
+        if getattr(self, "_timed_ctx", None) is not None:  # h2d_time / kernel_time / d2h_time of the whole stage (seconds)
+            gpu = self._timed_ctx.times()
         return [dict(self.metrics), {"write_time": m.write_time, "repart_time": m.repart_time[0], "input_rows": m.input_rows,
-                                     "output_rows": m.output_rows}]
+                                     "output_rows": m.output_rows, **gpu}]
 
     def schema(self):
         """The stage's output schema = the aggregate's (known once the stage has run, or from the decoded plan)."""

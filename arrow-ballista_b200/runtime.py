@@ -38,6 +38,17 @@ class Context:
     def stream(self):
         return lib().bgpu_ctx_stream(self._h)
 
+    def enable_times(self, on=True):
+        """Account the GPU time of every call on this context as h2d / kernel / d2h (bgpu_ctx_enable_times)."""
+        self.check(lib().bgpu_ctx_enable_times(self._h, 1 if on else 0))
+
+    def times(self, reset=False):
+        """{"h2d_time", "kernel_time", "d2h_time"} in seconds of GPU time so far (bgpu_ctx_times): the metrics a GPU
+        operator reports next to the reference's write_time / repart_time (shuffle_writer.rs:139-163)."""
+        out = (C.c_double * 3)()
+        self.check(lib().bgpu_ctx_times(self._h, out, 1 if reset else 0))
+        return {"h2d_time": out[0] * 1e-3, "kernel_time": out[1] * 1e-3, "d2h_time": out[2] * 1e-3}
+
     def close(self):
         if getattr(self, "_h", None):
             lib().bgpu_ctx_destroy(self._h)

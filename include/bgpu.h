@@ -48,6 +48,15 @@ void* bgpu_ctx_stream(bgpu_ctx* ctx); /* the cudaStream_t all work of this ctx i
 const char* bgpu_version(void);
 /* number of kernels this ctx has launched so far (bench.py's gpu_launches) */
 uint64_t bgpu_ctx_kernel_launches(const bgpu_ctx* ctx);
+/* Operator time metrics (what a GPU node adds next to the reference's write_time / repart_time,
+ * /root/reference/ballista/core/src/execution_plans/shuffle_writer.rs:139-163): with accounting enabled every entry point
+ * of this ctx brackets its stream work with a CUDA event pair, and bgpu_ctx_times returns the GPU milliseconds so far as
+ * out3_ms = {h2d_time (bgpu_batch_upload, the streamed input's chunk copies, the IPC reader's upload + decode),
+ * kernel_time (aggregate, repartition, exchange, concat, sort, IPC framing), d2h_time (bgpu_batch_download, the IPC
+ * writer's copy-out)}; reset != 0 zeroes the sums. bgpu_ctx_times waits for the work it accounts for; call it when no
+ * other call on the ctx is running. Off by default (two event records per call). */
+int bgpu_ctx_enable_times(bgpu_ctx* ctx, int32_t on);
+int bgpu_ctx_times(bgpu_ctx* ctx, double* out3_ms, int32_t reset);
 
 /* ---- batches: RecordBatch <-> device -------------------------------------------------------------------
  * The struct-typed ArrowArray/ArrowSchema pair is a RecordBatch exactly as arrow-rs exports one

@@ -72,6 +72,9 @@ extern "C" {
                                    out_sent_bytes: *mut u64) -> i32;
     pub fn bgpu_all_to_all(ctx: *mut BgpuCtx, comm: *mut c_void, rank: i32, world: i32, partitioned: *const BgpuBatch,
                            offsets: *const u64, n_partitions: u32, out: *mut *mut BgpuBatch) -> i32;
+    // h2d_time / kernel_time / d2h_time of the operators that ran on a context (MetricValue::Time next to write_time)
+    pub fn bgpu_ctx_enable_times(ctx: *mut BgpuCtx, on: i32) -> i32;
+    pub fn bgpu_ctx_times(ctx: *mut BgpuCtx, out3_ms: *mut f64, reset: i32) -> i32;
     // callers that may not allocate (no counterpart in the reference)
     pub fn bgpu_partition_offsets_noalloc(ctx: *mut BgpuCtx, keys_device: *const i64, n_rows: i64, n_partitions: u32,
                                           out_offsets_device: *mut u64) -> i32;

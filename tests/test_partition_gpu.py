@@ -95,3 +95,28 @@ def test_unsupported_scheme_is_an_error(bb, ctx):
     with pytest.raises(bb.BgpuError):
         bb.BatchPartitioner.try_new(bb.Partitioning.Hash([0], 5000), ctx).partition(
             random_batch(np.random.default_rng(0), 10), lambda p, b: None)
+
+
+def test_context_time_metrics_account_h2d_kernel_d2h(bb):
+    """bgpu_ctx_enable_times / bgpu_ctx_times: the h2d_time / kernel_time / d2h_time a GPU operator reports next to the
+    reference's write_time / repart_time (shuffle_writer.rs:139-163). Off by default; each class grows only with its own
+    kind of call; reset zeroes the sums."""
+    ctx = bb.Context(0)
+    rng = np.random.default_rng(3)
+    b = pa.RecordBatch.from_arrays([pa.array(rng.integers(0, 1 << 40, 200_000), type=pa.int64()),
+                                    pa.array(rng.random(200_000))], names=["k", "f"])
+    d = bb.DeviceBatch.upload(ctx, b)
+    assert ctx.times() == {"h2d_time": 0.0, "kernel_time": 0.0, "d2h_time": 0.0}   # not enabled: nothing is recorded
+    ctx.enable_times(True)
+    d = bb.DeviceBatch.upload(ctx, b)
+    t1 = ctx.times()
+    assert t1["h2d_time"] > 0 and t1["kernel_time"] == 0 and t1["d2h_time"] == 0, t1
+    part = bb.BatchPartitioner.try_new(bb.Partitioning.Hash([0], 8), ctx)
+    out, offs = part.partition_device(d)
+    t2 = ctx.times()
+    assert t2["kernel_time"] > 0 and t2["h2d_time"] == t1["h2d_time"] and t2["d2h_time"] == 0, t2
+    assert out.download().num_rows == b.num_rows
+    t3 = ctx.times(reset=True)
+    assert t3["d2h_time"] > 0 and t3["kernel_time"] == t2["kernel_time"], t3
+    assert ctx.times() == {"h2d_time": 0.0, "kernel_time": 0.0, "d2h_time": 0.0}
+    ctx.close()

@@ -69,6 +69,9 @@ def run_map_stages(bb, ctx, work_dir, schema, plan3, data, merge_partitions):
         assert m_agg["aggregate_input_rows"] == sum(b.num_rows for p in task_partitions for b in data[p])
         assert m_write["input_rows"] == m_agg["aggregate_output_rows"] == m_write["output_rows"]
         assert m_agg["last_path"] != ""
+        # the GPU node's own time metrics: host batches were uploaded, kernels ran, partition files were copied out
+        assert m_write["h2d_time"] > 0 and m_write["kernel_time"] > 0 and m_write["d2h_time"] > 0, m_write
+        assert m_write["h2d_time"] + m_write["kernel_time"] + m_write["d2h_time"] < 60
         for w in written:
             assert w.partitions == task_partitions and w.path.startswith(work_dir) and os.path.getsize(w.path) > w.num_bytes
             locations[w.output_partition].append(bb.PartitionLocation.from_shuffle_write("q1", 1, w))
