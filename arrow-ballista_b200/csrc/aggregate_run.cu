@@ -882,7 +882,9 @@ static int run_two_pass(bgpu_agg* g, Bound* b, int64_t n_rows, const bgpu_batch*
     // linear counting: distinct ~ -m ln(zero fraction); a saturated bitmap means "at least as many as rows"
     const double est = set >= m ? (double)n_rows : std::min<double>((double)n_rows, -m * log(1.0 - set / m));
     // a first batch that is mostly distinct keys: the Partial pass would be all cost and no reduction
-    double ratio = 0.6;
+    // break-even: the Partial pass costs ~0.22 ns per input row, everything downstream ~0.33 ns per state row (2 GPUs,
+    // config 4b), so passing rows through wins once distinct / rows exceeds ~1/3; measured at 0.43: 4.5-5.5 -> 7.9 G rows/s
+    double ratio = 0.4;
     if (const char* e = getenv("BGPU_PASSTHROUGH_RATIO")) ratio = atof(e);
     if (!g->any_committed && g->pass_chunks.empty() && n_rows >= (1 << 20) && est > ratio * (double)n_rows &&
         passthrough_eligible(g, batch)) {
