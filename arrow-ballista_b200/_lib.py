@@ -88,6 +88,7 @@ SIGNATURES = {
     "bgpu_agg_push_host": (C.c_int, [C.c_void_p, C.POINTER(ArrowArray), C.POINTER(ArrowSchema)]),
     "bgpu_agg_flush": (C.c_int, [C.c_void_p]),
     "bgpu_agg_ingest_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "bgpu_debug_pack_checked_host": (C.c_int, [C.c_char_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_uint32, C.c_void_p]),
     "bgpu_debug_pack_fixed_host": (C.c_int, [C.c_char_p, C.c_void_p, C.c_int64, C.c_int32, C.POINTER(C.c_int64),
                                              C.POINTER(C.c_uint32), C.c_void_p]),
     "bgpu_agg_emit": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),

@@ -123,7 +123,7 @@ class GpuAggregateExec:
     def ingest_stats(self):
         out = (C.c_uint64 * 8)()
         self.ctx.check(lib().bgpu_agg_ingest_stats(self._h, out))
-        keys = ("rows", "batches", "wire_bytes", "arrow_bytes", "chunks", "async_launches", "replays")
+        keys = ("rows", "batches", "wire_bytes", "arrow_bytes", "chunks", "async_launches", "replays", "one_pass_columns")
         return dict(zip(keys, [int(x) for x in out]))
 
     def reset(self):

@@ -219,6 +219,11 @@ struct Ingest {
   uint64_t seq = 0;
   int sticky_error = BGPU_OK;
   std::string sticky_msg;
+  // running value range of every fixed-width column over the segments seen so far: the one-pass packer's guess for the
+  // next segment's base and width (verified while packing; any stale or torn pair only costs the exact two-pass route)
+  std::atomic<int64_t> run_lo[kMaxIngestCols], run_hi[kMaxIngestCols];
+  std::atomic<int32_t> run_set[kMaxIngestCols];
+  std::atomic<uint64_t> st_one_pass{0}, st_two_pass{0};
   // statistics
   uint64_t st_rows = 0, st_batches = 0, st_wire_bytes = 0, st_raw_bytes = 0, st_chunks = 0, st_replays = 0, st_async = 0;
 
@@ -308,6 +313,7 @@ int ingest_create(bgpu_agg* g) {
   if (g->final_mode) return ctx->fail(BGPU_EINVAL, "bgpu_agg_push_host takes raw input rows (Partial / Single modes)");
   auto in = std::make_shared<Ingest>();
   in->g = g; in->ctx = ctx;
+  for (int c = 0; c < kMaxIngestCols; c++) { in->run_lo[c].store(0); in->run_hi[c].store(0); in->run_set[c].store(0); }
   in->ops = pack_ops_for(getenv("BGPU_INGEST_NO_AVX512") ? 1 : 0);
   if (getenv("BGPU_INGEST_NO_AVX2")) in->ops = &pack_base::ops;
   BGPU_TRY(used_columns(g, &in->cols));
@@ -508,10 +514,13 @@ void ingest_reset(bgpu_agg* g) {
   in->sticky_msg.clear();
   for (DeviceSet& s : in->sets) s.pending = false;
   in->st_rows = in->st_batches = in->st_wire_bytes = in->st_raw_bytes = in->st_chunks = in->st_replays = in->st_async = 0;
+  in->st_one_pass.store(0);
+  in->st_two_pass.store(0);
 }
 
 struct SegPlan {  // what pass 1 found for one column of one segment
-  bgpu_pack::FixedStats fs{0, 0};
+  bgpu_pack::FixedStats fs{0, 0, 0, 0, 0};
+  const uint8_t* packed = nullptr;  // the column already packed by the one-pass route (thread-local scratch)
   size_t bytes = 0, bytes2 = 0, valid_bytes = 0;  // wire bytes: packed values / lengths, string bytes, validity bits
   int32_t str_first = 0;
   bool has_validity = false;
@@ -522,6 +531,9 @@ int push_segment(Ingest* in, const struct ArrowArray* batch, int64_t lo, uint32_
   const size_t n_cols = in->cols.size();
   SegPlan plan[kMaxIngestCols];
   size_t need = 0;
+  static const bool one_pass = getenv("BGPU_INGEST_TWO_PASS") == nullptr;  // (measurement knob: always range + pack)
+  static thread_local std::vector<uint8_t> scratch;  // one-pass packed columns of this segment, n x 4 bytes each
+  if (one_pass && scratch.size() < n_cols * (size_t)n * 4) scratch.resize(n_cols * (size_t)n * 4);
   for (size_t c = 0; c < n_cols; c++) {  // pass 1: ranges -> wire widths
     const IngestCol& ic = in->cols[c];
     const struct ArrowArray* a = batch->children[ic.batch_col];
@@ -546,7 +558,40 @@ int push_segment(Ingest* in, const struct ArrowArray* batch, int64_t lo, uint32_
     } else {
       if (a->n_buffers < 2 || !a->buffers[1]) return ctx->fail(BGPU_EINVAL, "primitive column needs 2 buffers");
       const uint8_t* v = (const uint8_t*)a->buffers[1] + (size_t)off * ic.width;
-      in->ops->fixed_stats(v, n, ic.width, ic.is_signed, ic.is_decimal, ic.is_float, &sp.fs);
+      // one pass when the column's running range says how it will pack: pack into scratch against that base and width
+      // and verify on the way (the input is read from DRAM once instead of once + once from cache)
+      if (one_pass && !ic.is_float && in->run_set[c].load(std::memory_order_acquire) == 1) {
+        const int64_t rlo = in->run_lo[c].load(std::memory_order_relaxed), rhi = in->run_hi[c].load(std::memory_order_relaxed);
+        const uint64_t r = (uint64_t)rhi - (uint64_t)rlo;
+        const uint32_t code = rhi < rlo ? 8 : r < (1ULL << 8) ? 1 : r < (1ULL << 16) ? 2 : r < (1ULL << 32) ? 4 : 8;
+        uint8_t* dst = scratch.data() + c * (size_t)n * 4;
+        if (code <= 4 && (int)code < ic.width && in->ops->fixed_pack_checked(v, n, ic.width, ic.is_signed, ic.is_decimal, rlo, code, dst)) {
+          sp.fs.base = rlo;
+          sp.fs.code = code;
+          sp.packed = dst;
+          in->st_one_pass.fetch_add(1, std::memory_order_relaxed);
+        }
+      }
+      if (!sp.packed) {
+        in->ops->fixed_stats(v, n, ic.width, ic.is_signed, ic.is_decimal, ic.is_float, &sp.fs);
+        in->st_two_pass.fetch_add(1, std::memory_order_relaxed);
+        if (sp.fs.has_range) {  // widen the running range (lock-free min / max)
+          if (!in->run_set[c].load(std::memory_order_acquire)) {
+            int32_t expect = 0;
+            if (in->run_set[c].compare_exchange_strong(expect, 2)) {  // first writer initialises, then publishes
+              in->run_lo[c].store(sp.fs.lo, std::memory_order_relaxed);
+              in->run_hi[c].store(sp.fs.hi, std::memory_order_relaxed);
+              in->run_set[c].store(1, std::memory_order_release);
+            }
+          }
+          if (in->run_set[c].load(std::memory_order_acquire) == 1) {
+            int64_t cur = in->run_lo[c].load(std::memory_order_relaxed);
+            while (sp.fs.lo < cur && !in->run_lo[c].compare_exchange_weak(cur, sp.fs.lo, std::memory_order_relaxed)) {}
+            cur = in->run_hi[c].load(std::memory_order_relaxed);
+            while (sp.fs.hi > cur && !in->run_hi[c].compare_exchange_weak(cur, sp.fs.hi, std::memory_order_relaxed)) {}
+          }
+        }
+      }
       sp.bytes = align16((size_t)n * (sp.fs.code == bgpu_pack::kRaw ? (size_t)ic.width : sp.fs.code));
     }
     need += sp.bytes + align16(sp.bytes2) + sp.valid_bytes;
@@ -657,7 +702,8 @@ int push_segment(Ingest* in, const struct ArrowArray* batch, int64_t lo, uint32_
       raw += (size_t)((n + 7) / 8);
     } else {
       const uint8_t* v = (const uint8_t*)a->buffers[1] + (size_t)off * ic.width;
-      in->ops->fixed_pack(v, n, ic.width, ic.is_signed, ic.is_decimal, sp.fs.base, sp.fs.code, data + cursor);
+      if (sp.packed) memcpy(data + cursor, sp.packed, (size_t)n * sp.fs.code);
+      else in->ops->fixed_pack(v, n, ic.width, ic.is_signed, ic.is_decimal, sp.fs.base, sp.fs.code, data + cursor);
       cursor += sp.bytes;
       raw += (size_t)n * ic.width;
     }
@@ -743,13 +789,36 @@ extern "C" int bgpu_agg_ingest_stats(const bgpu_agg* g, uint64_t* out8) {
   if (!in) return BGPU_OK;
   std::lock_guard<std::mutex> lk(in->mu);
   out8[0] = in->st_rows; out8[1] = in->st_batches; out8[2] = in->st_wire_bytes; out8[3] = in->st_raw_bytes;
-  out8[4] = in->st_chunks; out8[5] = in->st_async; out8[6] = in->st_replays;
+  out8[4] = in->st_chunks; out8[5] = in->st_async; out8[6] = in->st_replays; out8[7] = in->st_one_pass.load();
   return BGPU_OK;
 }
 
 // test hook (host only, no device): the wire form of one fixed-width column segment, as push packs it. format = the
 // column's Arrow C format string; out_packed has room for n * 16 bytes. which = 0: the AVX2 build, 1: the plain one,
 // 2: the AVX-512 build (BGPU_EUNSUPPORTED when the CPU cannot run the one asked for).
+// test hook (host only): the one-pass route of the packer - pack `values` against a GIVEN base and code (1, 2 or 4) and
+// say whether every value fitted. Returns 1 (fits, out_packed valid), 0 (does not fit), or a negative error.
+extern "C" int bgpu_debug_pack_checked_host(const char* format, const void* values, int64_t n, int32_t which, int64_t base,
+                                            uint32_t code, uint8_t* out_packed) {
+  if (!format || !values || !out_packed || n < 0) return -BGPU_EINVAL;
+  if (which == 0 && !__builtin_cpu_supports("avx2")) return -BGPU_EUNSUPPORTED;
+  if (which == 2 && pack_ops_for(0) != &pack_avx512::ops) return -BGPU_EUNSUPPORTED;
+  const bgpu_pack::Ops* ops = which == 2 ? &pack_avx512::ops : which == 0 ? &pack_avx2::ops : &pack_base::ops;
+  const char c0 = format[0];
+  int width = 0;
+  switch (c0) {
+    case 'c': case 'C': width = 1; break;
+    case 's': case 'S': width = 2; break;
+    case 'i': case 'I': width = 4; break;
+    case 'l': case 'L': width = 8; break;
+    case 'd': width = 16; break;
+    case 't': width = (format[1] == 'd' && format[2] == 'D') ? 4 : 8; break;
+    default: return -BGPU_EUNSUPPORTED;
+  }
+  const bool is_signed = !(c0 == 'C' || c0 == 'S' || c0 == 'I' || c0 == 'L');
+  return ops->fixed_pack_checked(values, n, width, is_signed, c0 == 'd', base, code, out_packed) ? 1 : 0;
+}
+
 extern "C" int bgpu_debug_pack_fixed_host(const char* format, const void* values, int64_t n, int32_t which, int64_t* out_base,
                                           uint32_t* out_code, uint8_t* out_packed) {
   if (!format || !values || !out_base || !out_code || !out_packed || n < 0) return BGPU_EINVAL;
@@ -769,7 +838,7 @@ extern "C" int bgpu_debug_pack_fixed_host(const char* format, const void* values
   }
   const bool is_float = c0 == 'f' || c0 == 'g', is_dec = c0 == 'd';
   const bool is_signed = !(c0 == 'C' || c0 == 'S' || c0 == 'I' || c0 == 'L');
-  bgpu_pack::FixedStats fs{0, 0};
+  bgpu_pack::FixedStats fs{0, 0, 0, 0, 0};
   ops->fixed_stats(values, n, width, is_signed, is_dec, is_float, &fs);
   ops->fixed_pack(values, n, width, is_signed, is_dec, fs.base, fs.code, out_packed);
   *out_base = fs.base;

@@ -81,6 +81,8 @@ void fixed_stats(const void* values, int64_t n, int width, int is_signed, int is
                  bgpu_pack::FixedStats* out) {
   out->base = 0;
   out->code = bgpu_pack::kRaw;
+  out->lo = out->hi = 0;
+  out->has_range = 0;
   if (is_float || n == 0) {
     if (n == 0) out->code = 0;
     return;
@@ -98,6 +100,9 @@ void fixed_stats(const void* values, int64_t n, int width, int is_signed, int is
     }
   }
   const uint32_t code = code_for_range(lo, hi);
+  out->lo = lo;
+  out->hi = hi;
+  out->has_range = 1;
   if ((int)code >= width) return;  // nothing gained: raw copy
   out->base = lo;
   out->code = code;
@@ -129,6 +134,63 @@ static void pack_to(const Tin* in, int64_t n, int64_t stride, int64_t base, uint
     case 4: pack_loop(in, n, stride, base, (uint32_t*)out); break;
     case 8: pack_loop(in, n, stride, base, (uint64_t*)out); break;
     default: break;
+  }
+}
+
+// One pass instead of range + pack: pack against a GIVEN base and width (the column's running range over the segments
+// seen so far) and check, while packing, that every value fits - every delta below 2^(8 * code), and for Decimal128 every
+// high word the sign extension of its low word. Returns false when some value does not fit (the caller then takes the
+// exact two-pass route); `out` holds garbage in that case.
+template <typename Tin, typename Tout>
+static bool pack_checked_loop(const Tin* in, int64_t n, int64_t stride, int64_t base, Tout* out) {
+  uint64_t bad = 0;
+  int64_t i = 0;
+#ifdef PACK_AVX512
+  if (sizeof(Tin) == 8 && stride == 2) {  // Decimal128: 8 values per step
+    const __m512i vb = _mm512_set1_epi64(base), even = _mm512_set_epi64(14, 12, 10, 8, 6, 4, 2, 0);
+    const __m512i odd = _mm512_set_epi64(15, 13, 11, 9, 7, 5, 3, 1);
+    __m512i vbad = _mm512_setzero_si512();
+    const int64_t* p = (const int64_t*)in;
+    for (; i + 8 <= n; i += 8) {
+      const __m512i a = _mm512_loadu_si512(p + 2 * i), b = _mm512_loadu_si512(p + 2 * i + 8);
+      const __m512i l = _mm512_permutex2var_epi64(a, even, b), h = _mm512_permutex2var_epi64(a, odd, b);
+      const __m512i d = _mm512_sub_epi64(l, vb);
+      vbad = _mm512_or_si512(vbad, _mm512_srli_epi64(d, 8 * (int)sizeof(Tout)));
+      vbad = _mm512_or_si512(vbad, _mm512_xor_si512(h, _mm512_srai_epi64(l, 63)));
+      if (sizeof(Tout) == 1) _mm_storel_epi64((__m128i*)(out + i), _mm512_cvtepi64_epi8(d));
+      else if (sizeof(Tout) == 2) _mm_storeu_si128((__m128i*)(out + i), _mm512_cvtepi64_epi16(d));
+      else _mm256_storeu_si256((__m256i*)(out + i), _mm512_cvtepi64_epi32(d));
+    }
+    bad = (uint64_t)_mm512_reduce_or_epi64(vbad);
+  }
+#endif
+  for (; i < n; i++) {
+    const uint64_t d = (uint64_t)(int64_t)in[i * stride] - (uint64_t)base;
+    bad |= d >> (8 * sizeof(Tout));
+    if (stride == 2) bad |= (uint64_t)((int64_t)in[i * stride + 1] ^ ((int64_t)in[i * stride] >> 63));
+    out[i] = (Tout)d;
+  }
+  return bad == 0;
+}
+template <typename Tin>
+static bool pack_checked_to(const Tin* in, int64_t n, int64_t stride, int64_t base, uint32_t code, void* out) {
+  switch (code) {
+    case 1: return pack_checked_loop(in, n, stride, base, (uint8_t*)out);
+    case 2: return pack_checked_loop(in, n, stride, base, (uint16_t*)out);
+    case 4: return pack_checked_loop(in, n, stride, base, (uint32_t*)out);
+    default: return false;
+  }
+}
+int fixed_pack_checked(const void* values, int64_t n, int width, int is_signed, int is_decimal, int64_t base, uint32_t code,
+                       void* out) {
+  if (code != 1 && code != 2 && code != 4) return 0;
+  if (is_decimal) return pack_checked_to((const int64_t*)values, n, 2, base, code, out);
+  if ((int)code >= width) return 0;
+  switch (width) {
+    case 2: return is_signed ? pack_checked_to((const int16_t*)values, n, 1, base, code, out) : pack_checked_to((const uint16_t*)values, n, 1, base, code, out);
+    case 4: return is_signed ? pack_checked_to((const int32_t*)values, n, 1, base, code, out) : pack_checked_to((const uint32_t*)values, n, 1, base, code, out);
+    case 8: return pack_checked_to((const int64_t*)values, n, 1, base, code, out);
+    default: return 0;
   }
 }
 
@@ -188,5 +250,5 @@ void bits_realign(const uint8_t* src, int64_t off, int64_t n, uint8_t* dst) {
   if (n & 7) dst[bytes - 1] &= (uint8_t)((1u << (n & 7)) - 1);
 }
 
-const bgpu_pack::Ops ops = {fixed_stats, fixed_pack, utf8_stats, utf8_pack_lens, bits_realign};
+const bgpu_pack::Ops ops = {fixed_stats, fixed_pack, utf8_stats, utf8_pack_lens, bits_realign, fixed_pack_checked};
 }  // namespace PACK_NS

@@ -209,6 +209,10 @@ int bgpu_agg_ingest_stats(const bgpu_agg* agg, uint64_t* out8);
  * AVX2 build of the packer, 1: the plain build, 2: the AVX-512 build); out_packed has room for n * 16 bytes */
 int bgpu_debug_pack_fixed_host(const char* format, const void* values, int64_t n, int32_t which, int64_t* out_base,
                                uint32_t* out_code, uint8_t* out_packed);
+/* test hook (host only): the packer's one-pass route - pack against a GIVEN base and code (1, 2 or 4 bytes) and verify on the
+ * way that every value fits. 1 = fits (out_packed valid), 0 = some value does not fit, negative = -error code */
+int bgpu_debug_pack_checked_host(const char* format, const void* values, int64_t n, int32_t which, int64_t base, uint32_t code,
+                                 uint8_t* out_packed);
 /* end of input: state() (Partial) or evaluate() (Final modes and Single). Group order is unspecified, as in the
  * reference (GroupValues uses a randomly seeded table). The aggregate may not be updated afterwards. */
 int bgpu_agg_emit(bgpu_agg* agg, bgpu_batch** out);

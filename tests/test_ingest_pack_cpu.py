@@ -80,3 +80,56 @@ def test_floats_travel_raw(which):
     arr = np.random.default_rng(3).random(1000)
     base, code, packed = _pack("g", arr, which)
     assert code == RAW and (packed[:8000].view(np.float64) == arr).all()
+
+
+def _pack_checked(fmt, arr, which, base, code):
+    n = len(arr) if not fmt.startswith("d") else len(arr) // 2
+    out = np.zeros(max(n, 1) * 16, dtype=np.uint8)
+    rc = lib().bgpu_debug_pack_checked_host(fmt.encode(), arr.ctypes.data_as(C.c_void_p), n, which, base, code,
+                                            out.ctypes.data_as(C.c_void_p))
+    if rc == -2 and which in (0, 2):
+        pytest.skip("host without AVX2 / AVX-512")
+    assert rc in (0, 1), rc
+    return rc == 1, out
+
+
+@pytest.mark.parametrize("which", [0, 1, 2])
+@pytest.mark.parametrize("fmt,dtype", [("l", np.int64), ("i", np.int32), ("I", np.uint32), ("s", np.int16), ("tdD", np.int32)])
+def test_one_pass_pack_accepts_what_fits_and_nothing_else(which, fmt, dtype):
+    """The one-pass route packs against a GIVEN (base, width) and verifies on the way: when every value fits the packed
+    bytes decode to the input bit for bit; one value below the base or beyond the width makes it say no."""
+    rng = np.random.default_rng(5)
+    for n in (1, 7, 8, 63, 1000, 8192):
+        for code, span in ((1, 200), (2, 60_000), (4, 2_000_000_000)):
+            if code >= np.dtype(dtype).itemsize:
+                continue
+            base = int(rng.integers(-1000, 1000)) if np.dtype(dtype).kind == "i" else int(rng.integers(0, 1000))
+            hi = min(base + span, np.iinfo(dtype).max)
+            arr = rng.integers(base, hi, n, endpoint=True).astype(dtype)
+            ok, packed = _pack_checked(fmt, arr, which, base, code)
+            assert ok
+            got = _decode(base, code, packed, n, dtype)
+            assert np.array_equal(got, arr)
+            # one value that does not fit: below the base, or beyond the width
+            for bad in ([base - 1] if base - 1 >= np.iinfo(dtype).min else []) + ([base + (1 << (8 * code))] if base + (1 << (8 * code)) <= np.iinfo(dtype).max else []):
+                arr2 = arr.copy()
+                arr2[int(rng.integers(0, n))] = bad
+                ok2, _ = _pack_checked(fmt, arr2, which, base, code)
+                assert not ok2, (n, code, base, bad)
+
+
+@pytest.mark.parametrize("which", [0, 1, 2])
+def test_one_pass_pack_of_decimal128(which):
+    rng = np.random.default_rng(6)
+    for n in (1, 8, 9, 4000):
+        lo = rng.integers(-5000, 5000, n).astype(np.int64)
+        dec = np.empty(2 * n, dtype=np.int64)
+        dec[0::2], dec[1::2] = lo, lo >> 63
+        base = int(lo.min())
+        ok, packed = _pack_checked("d:15,2", dec, which, base, 2)
+        assert ok and np.array_equal(_decode(base, 2, packed, n, np.int64), lo)
+        assert not _pack_checked("d:15,2", dec, which, base + 1, 2)[0]      # the minimum is below the base
+        assert not _pack_checked("d:15,2", dec, which, base, 1)[0] or lo.max() - base < 256
+        wide = dec.copy()
+        wide[2 * int(rng.integers(0, n)) + 1] = 7                            # a value beyond 64 bits
+        assert not _pack_checked("d:38,2", wide, which, base, 2)[0]
