@@ -113,6 +113,7 @@ struct DevAlloc {
   size_t bytes = 0;
   bgpu_ctx* ctx = nullptr;
   bool owned = true;
+  std::shared_ptr<void> keep;  // something else to keep alive with the columns that hold this (a peer-window lease)
   ~DevAlloc() {
     if (p && owned && ctx) {
       cudaSetDevice(ctx->device);

@@ -36,23 +36,47 @@ struct IpcHandle { char reserved[64]; };
 
 }  // namespace bgpu
 
+namespace bgpu {
+// A receive window: cudaMalloc'ed (cudaIpc needs a non-pool allocation), mapped by every peer. A window may be LEASED to the
+// result batch of an exchange (its columns point into the window: no copy-out); the lease ends when the batch dies, and a
+// window replaced while leased lives on until then.
+struct PeerWindow {
+  bgpu_ctx* ctx = nullptr;
+  void* ptr = nullptr;
+  uint64_t bytes = 0;
+  std::atomic<int> leased{0};
+  ~PeerWindow() {
+    if (ptr) {
+      cudaSetDevice(ctx->device);
+      cudaFree(ptr);  // (synchronises the device: nothing still reads the window)
+    }
+    if (ctx) ctx_release(ctx);
+  }
+};
+struct WindowLease {
+  std::shared_ptr<PeerWindow> w;
+  ~WindowLease() { w->leased.store(0, std::memory_order_release); }
+};
+constexpr int kPeerWindows = 2;
+}  // namespace bgpu
+
 struct bgpu_peer_exchange {
   bgpu_ctx* ctx = nullptr;
   void* comm = nullptr;
   int32_t rank = 0, world = 1;
-  void* window = nullptr;  // this rank's receive window (cudaMalloc: cudaIpc needs a non-pool allocation)
-  uint64_t window_bytes = 0;
-  void* peer[bgpu::kMaxPeers] = {};  // peer[d] = rank d's window mapped here (peer[rank] = window)
-  uint64_t exchanges = 0, fused = 0, bytes_sent = 0;
+  std::shared_ptr<bgpu::PeerWindow> win[bgpu::kPeerWindows];      // this rank's receive windows (the second one is made on demand)
+  void* peer[bgpu::kPeerWindows][bgpu::kMaxPeers] = {};          // peer[w][d] = rank d's window w mapped here (nullptr: none)
+  uint64_t exchanges = 0, fused = 0, bytes_sent = 0, leased_results = 0;
 };
 
 namespace bgpu {
 
 static int peer_close(bgpu_peer_exchange* x) {
-  for (int d = 0; d < x->world; d++) {
-    if (d != x->rank && x->peer[d]) cudaIpcCloseMemHandle(x->peer[d]);
-    x->peer[d] = nullptr;
-  }
+  for (int w = 0; w < kPeerWindows; w++)
+    for (int d = 0; d < x->world; d++) {
+      if (d != x->rank && x->peer[w][d]) cudaIpcCloseMemHandle(x->peer[w][d]);
+      x->peer[w][d] = nullptr;
+    }
   return BGPU_OK;
 }
 
@@ -66,44 +90,62 @@ static int peer_barrier(bgpu_peer_exchange* x) {
   return BGPU_OK;
 }
 
-// (Re)allocate this rank's window and map every peer's. Collective: every rank calls it with the same `bytes`.
-static int peer_open(bgpu_peer_exchange* x, uint64_t bytes) {
+// Map every peer's windows (collective; nothing is mapped when it is called).
+static int peer_map(bgpu_peer_exchange* x) {
   bgpu_ctx* ctx = x->ctx;
-  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
-  if (x->window) {
-    // nobody may still hold a mapping of a window that is about to be freed
-    peer_close(x);
-    BGPU_TRY(peer_barrier(x));
-    BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    BGPU_CUDA(ctx, cudaFree(x->window));
-    x->window = nullptr;
-  }
-  bytes = (bytes + (2u << 20) - 1) & ~(uint64_t)((2u << 20) - 1);
-  BGPU_CUDA(ctx, cudaMalloc(&x->window, bytes));
-  x->window_bytes = bytes;
-  x->peer[x->rank] = x->window;
+  for (int w = 0; w < kPeerWindows; w++) x->peer[w][x->rank] = x->win[w] ? x->win[w]->ptr : nullptr;
   if (x->world == 1) return BGPU_OK;
-  IpcHandle mine;
-  BGPU_CUDA(ctx, cudaIpcGetMemHandle((cudaIpcMemHandle_t*)&mine, x->window));
+  struct Mine { IpcHandle h[kPeerWindows]; uint64_t has[kPeerWindows]; } mine;
+  memset(&mine, 0, sizeof mine);
+  for (int w = 0; w < kPeerWindows; w++)
+    if (x->win[w]) {
+      BGPU_CUDA(ctx, cudaIpcGetMemHandle((cudaIpcMemHandle_t*)&mine.h[w], x->win[w]->ptr));
+      mine.has[w] = 1;
+    }
   DevAllocPtr d_mine, d_all;
   BGPU_TRY(dev_alloc(ctx, sizeof mine, &d_mine));
   BGPU_TRY(dev_alloc(ctx, sizeof mine * (size_t)x->world, &d_all));
   BGPU_CUDA(ctx, cudaMemcpyAsync(d_mine->p, &mine, sizeof mine, cudaMemcpyHostToDevice, ctx->stream));
   BGPU_NCCL(ctx, nccl().AllGather(d_mine->p, d_all->p, sizeof mine, kNcclUint8, x->comm, ctx->stream));
-  std::vector<IpcHandle> all((size_t)x->world);
+  std::vector<Mine> all((size_t)x->world);
   BGPU_CUDA(ctx, cudaMemcpyAsync(all.data(), d_all->p, sizeof mine * (size_t)x->world, cudaMemcpyDeviceToHost, ctx->stream));
   BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   for (int d = 0; d < x->world; d++) {
     if (d == x->rank) continue;
-    cudaIpcMemHandle_t h;
-    memcpy(&h, &all[(size_t)d], sizeof h);
-    const cudaError_t e = cudaIpcOpenMemHandle(&x->peer[d], h, cudaIpcMemLazyEnablePeerAccess);
-    if (e != cudaSuccess) {
-      x->peer[d] = nullptr;
-      return ctx->fail(BGPU_ECUDA, std::string("cudaIpcOpenMemHandle(rank ") + std::to_string(d) + "): " + cudaGetErrorString(e));
+    for (int w = 0; w < kPeerWindows; w++) {
+      if (!all[(size_t)d].has[w]) continue;
+      cudaIpcMemHandle_t h;
+      memcpy(&h, &all[(size_t)d].h[w], sizeof h);
+      const cudaError_t e = cudaIpcOpenMemHandle(&x->peer[w][d], h, cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) {
+        x->peer[w][d] = nullptr;
+        return ctx->fail(BGPU_ECUDA, std::string("cudaIpcOpenMemHandle(rank ") + std::to_string(d) + "): " + cudaGetErrorString(e));
+      }
     }
   }
   return BGPU_OK;
+}
+
+// Replace this rank's window w by one of `bytes` (0: keep it) and map everybody's windows again. Collective: every rank
+// calls it (each with its own w / bytes). A window that is leased to a result batch stays alive until that batch dies.
+static int peer_regrow(bgpu_peer_exchange* x, int w, uint64_t bytes) {
+  bgpu_ctx* ctx = x->ctx;
+  BGPU_CUDA(ctx, cudaSetDevice(ctx->device));
+  // nobody may still hold a mapping of a window that is about to be freed
+  peer_close(x);
+  if (x->world > 1) BGPU_TRY(peer_barrier(x));
+  BGPU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (bytes) {
+    bytes = (bytes + (2u << 20) - 1) & ~(uint64_t)((2u << 20) - 1);
+    x->win[w] = nullptr;  // freed now, or when its lease ends
+    auto nw = std::make_shared<PeerWindow>();
+    nw->ctx = ctx;
+    ctx_retain(ctx);
+    BGPU_CUDA(ctx, cudaMalloc(&nw->ptr, bytes));
+    nw->bytes = bytes;
+    x->win[w] = nw;
+  }
+  return peer_map(x);
 }
 
 }  // namespace bgpu
@@ -121,7 +163,7 @@ extern "C" int bgpu_peer_exchange_create(bgpu_ctx* ctx, void* nccl_comm, int32_t
   x->rank = rank;
   x->world = world;
   ctx_retain(ctx);
-  const int rc = peer_open(x, std::max<uint64_t>(window_bytes, 1u << 20));
+  const int rc = peer_regrow(x, 0, std::max<uint64_t>(window_bytes, 1u << 20));
   if (rc != BGPU_OK) {
     bgpu_peer_exchange_destroy(x);
     return rc;
@@ -137,15 +179,22 @@ extern "C" void bgpu_peer_exchange_destroy(bgpu_peer_exchange* x) {
   if (!x) return;
   cudaSetDevice(x->ctx->device);
   // not a collective (it also runs at interpreter shutdown): every exchange ends with all peers' stores landed, so no
-  // peer touches this window any more; the driver keeps the memory alive while a peer still has it mapped
+  // peer touches these windows any more; the driver keeps the memory alive while a peer still has it mapped. A window
+  // leased to a result batch outlives the exchange object (the lease holds it).
   peer_close(x);
   cudaStreamSynchronize(x->ctx->stream);
-  if (x->window) cudaFree(x->window);
+  for (auto& w : x->win) w = nullptr;
   ctx_release(x->ctx);
   delete x;
 }
 
-extern "C" uint64_t bgpu_peer_exchange_window_bytes(const bgpu_peer_exchange* x) { return x ? x->window_bytes : 0; }
+extern "C" uint64_t bgpu_peer_exchange_window_bytes(const bgpu_peer_exchange* x) {
+  uint64_t b = 0;
+  if (x)
+    for (const auto& w : x->win)
+      if (w) b = std::max<uint64_t>(b, w->bytes);
+  return b;
+}
 
 extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* in, const int32_t* key_cols, int32_t n_keys,
                                        uint32_t n_partitions, bgpu_batch** out_received, uint64_t* out_recv_off,
@@ -178,6 +227,16 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
   const int64_t kTile = (int64_t)geom.threads * geom.items;
   const size_t smem = scatter_smem_bytes(n, geom.threads, geom.items, row_bytes, 0, peer_ptrs);
   if (smem > kTwoCtasBudget) can_fuse = 0;
+  // the window this exchange's rows land in: one that no earlier result batch still holds (the largest such)
+  static const bool copy_out = getenv("BGPU_PEER_COPY_OUT") != nullptr;  // round 1's behaviour: one window, copied out
+  int my_w = -1;
+  for (int w = 0; w < kPeerWindows; w++) {
+    const bool free_w = !x->win[w] || x->win[w]->leased.load(std::memory_order_acquire) == 0;
+    if (!free_w) continue;
+    if (my_w < 0 || (x->win[w] ? x->win[w]->bytes : 0) > (x->win[my_w] ? x->win[my_w]->bytes : 0)) my_w = w;
+  }
+  if (my_w < 0) can_fuse = 0;  // both windows are still leased to live result batches: the two-step path, on every rank
+  const uint64_t my_cap = my_w >= 0 && x->win[my_w] ? x->win[my_w]->bytes : 0;
   ScatterArgs args{};
   ScatterLaunch l{&args, nullptr, n, n_rows, 0, nullptr, nullptr, world};
   int occ = 2;
@@ -198,7 +257,7 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
   BGPU_TRY(dev_alloc(ctx, (size_t)std::max<int64_t>(n_rows, 1) * 2, &pids));
   BGPU_TRY(dev_alloc(ctx, (size_t)n * g * 4, &hist));
   BGPU_TRY(dev_alloc(ctx, (size_t)n * g * 8, &base));
-  const size_t hdr_words = (size_t)n + 2;  // offsets[n + 1], can_fuse
+  const size_t hdr_words = (size_t)n + 4;  // offsets[n + 1], can_fuse, the receive window chosen, its capacity
   BGPU_TRY(dev_alloc(ctx, hdr_words * 8, &hdr));
   BGPU_TRY(dev_alloc(ctx, hdr_words * 8 * (size_t)world, &all_hdr));
   if (n_rows > 0) {
@@ -209,7 +268,8 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
   } else {
     BGPU_CUDA(ctx, cudaMemsetAsync(hdr->p, 0, hdr_words * 8, ctx->stream));
   }
-  BGPU_CUDA(ctx, cudaMemcpyAsync((uint64_t*)hdr->p + n + 1, &can_fuse, 8, cudaMemcpyHostToDevice, ctx->stream));
+  const uint64_t tail[3] = {can_fuse, (uint64_t)std::max(my_w, 0), my_cap};
+  BGPU_CUDA(ctx, cudaMemcpyAsync((uint64_t*)hdr->p + n + 1, tail, sizeof tail, cudaMemcpyHostToDevice, ctx->stream));
 
   // 2. everybody's counts
   std::vector<uint64_t> all(hdr_words * (size_t)world);
@@ -230,7 +290,9 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
   for (int s = 0; s < world; s++) memcpy(&offs[(size_t)s * (n + 1)], &all[(size_t)s * hdr_words], (size_t)(n + 1) * 8);
   std::vector<std::vector<uint64_t>> recv((size_t)world);
   std::vector<uint64_t> total((size_t)world);
-  uint64_t need = 0;
+  uint64_t my_need = 0;
+  bool grow = false;  // some rank's chosen window is too small: every rank sees that in the gathered headers
+  std::vector<int> win_of((size_t)world);
   auto region = [&](uint64_t rows, int width) { return (rows * (uint64_t)width + 255) & ~255ULL; };
   for (int d = 0; d < world; d++) {
     const uint32_t owned = (n + (uint32_t)world - 1 - (uint32_t)d) / (uint32_t)world;
@@ -239,9 +301,12 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
     total[(size_t)d] = bgpu_exchange_plan(offs.data(), d, world, n, recv[(size_t)d].data(), &got);
     uint64_t bytes = 0;
     for (const Column& c : in->cols) bytes += region(total[(size_t)d], c.width);
-    need = std::max(need, bytes);
+    win_of[(size_t)d] = (int)all[(size_t)d * hdr_words + n + 2];
+    if (bytes > all[(size_t)d * hdr_words + n + 3]) grow = true;
+    if (d == me) my_need = bytes;
   }
-  if (need > x->window_bytes) BGPU_TRY(peer_open(x, need + need / 4));  // collective: every rank sees the same `need`
+  if (grow) BGPU_TRY(peer_regrow(x, my_w, my_need > my_cap ? my_need + my_need / 4 : 0));  // collective
+  PeerWindow* const mine = x->win[my_w].get();
 
   // 3. window rows for this rank's partitions + the column regions in every owner's window
   std::vector<int64_t> delta(n);
@@ -272,7 +337,7 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
       for (size_t i = 0; i < n_cols; i++) {  // regions in schema order
         size_t a = 0;
         while (order[a] != i) a++;
-        ptrs[a * (size_t)world + d] = (char*)x->peer[d] + at;
+        ptrs[a * (size_t)world + d] = (char*)x->peer[win_of[(size_t)d]][d] + at;
         if (d == me) my_region[i] = at;
         at += region(total[(size_t)d], in->cols[i].width);
       }
@@ -296,21 +361,37 @@ extern "C" int bgpu_partition_exchange(bgpu_peer_exchange* x, const bgpu_batch* 
   // 5. everybody's stores have landed
   if (world > 1) BGPU_TRY(peer_barrier(x));
 
-  // 6. copy out
+  // 6. the result: its columns ARE the window's regions (the window is leased to the batch until the batch dies; the next
+  //    exchange takes the other window) - or, with BGPU_PEER_COPY_OUT, copies of them as in round 1
   std::unique_ptr<bgpu_batch> out(new bgpu_batch(ctx));
   out->n_rows = (int64_t)total[(size_t)me];
   out->cols.resize(n_cols);
+  DevAllocPtr lease;
+  if (!copy_out && out->n_rows && mine) {
+    mine->leased.store(1, std::memory_order_release);
+    auto keep = std::make_shared<WindowLease>();
+    keep->w = x->win[my_w];
+    lease = std::make_shared<DevAlloc>();  // no memory of its own: it only carries the lease
+    lease->owned = false;
+    lease->keep = keep;
+    x->leased_results++;
+  }
   for (size_t i = 0; i < n_cols; i++) {
     const Column& c = in->cols[i];
     Column& o = out->cols[i];
     o.name = c.name; o.format = c.format; o.flags = c.flags; o.kind = c.kind; o.width = c.width;
     o.length = out->n_rows; o.null_count = 0;
+    if (lease) {
+      o.owned.push_back(lease);
+      o.values = (char*)mine->ptr + my_region[i];
+      continue;
+    }
     DevAllocPtr a;
     BGPU_TRY(dev_alloc(ctx, (size_t)out->n_rows * c.width, &a));
     o.owned.push_back(a);
     o.values = a->p;
     if (out->n_rows)
-      BGPU_CUDA(ctx, cudaMemcpyAsync(a->p, (char*)x->window + my_region[i], (size_t)out->n_rows * c.width, cudaMemcpyDeviceToDevice, ctx->stream));
+      BGPU_CUDA(ctx, cudaMemcpyAsync(a->p, (char*)mine->ptr + my_region[i], (size_t)out->n_rows * c.width, cudaMemcpyDeviceToDevice, ctx->stream));
   }
   if (out_recv_off) memcpy(out_recv_off, recv[(size_t)me].data(), recv[(size_t)me].size() * 8);
   if (out_sent_bytes) *out_sent_bytes = sent_rows * (uint64_t)row_bytes;

@@ -286,7 +286,10 @@ uint64_t bgpu_exchange_plan(const uint64_t* all_offsets, int32_t rank, int32_t w
  * All three calls are COLLECTIVE over the ranks of `nccl_comm` (bgpu_peer_exchange_destroy is not).
  * bgpu_partition_exchange accepts batches of null-free fixed-width columns of 4, 8 or 16 bytes (aggregate states),
  * n_partitions <= 128; anything else returns BGPU_EUNSUPPORTED on EVERY rank (the ranks agree through the counts
- * exchange) and the caller takes bgpu_hash_partition + bgpu_all_to_all. out_recv_off (optional, [n_owned * world + 1]):
+ * exchange) and the caller takes bgpu_hash_partition + bgpu_all_to_all. The received batch's columns are the receive
+ * window itself (no copy-out): the batch holds the window until bgpu_batch_destroy, the next exchange uses the rank's
+ * second window, and while a rank still holds the results of its last two exchanges the call returns BGPU_EUNSUPPORTED
+ * on every rank. out_recv_off (optional, [n_owned * world + 1]):
  * as bgpu_exchange_plan; out_sent_bytes (optional): bytes this rank stored into other ranks' windows. */
 typedef struct bgpu_peer_exchange bgpu_peer_exchange;
 int bgpu_peer_exchange_create(bgpu_ctx* ctx, void* nccl_comm, int32_t rank, int32_t world, uint64_t window_bytes,

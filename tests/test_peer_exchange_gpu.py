@@ -65,6 +65,28 @@ def run_rank(bb, oracle, ctx, rank, world):
             sent = sum(b.num_rows for p, b in oracle.partition(make_input(rank, sizes[rank], nulls, seed), KEYS, N_PARTITIONS)[0]
                        if p % world != rank) * (8 + 16 + 16 + 8 + 4 + 8)
             assert ex.last_sent_bytes == sent
+    # Leases: the result batch of a fused exchange IS its receive window (no copy-out), so it holds the window until it
+    # dies; the next exchange lands in the second window; with both windows held the call answers "unsupported" on
+    # every rank together (the two-step path delivers the same rows); a released window is used again.
+    def exchange(sizes, seed):
+        dev = bb.DeviceBatch.upload(ctx, make_input(rank, sizes[rank], False, seed))
+        return ex.partition_exchange(dev, KEYS, N_PARTITIONS, window_bytes=1 << 20), expected_received(oracle, rank, world, sizes, False, seed)
+
+    def same(batch, want):
+        return pa.Table.from_batches([batch.download()], schema=want.schema).equals(want)
+
+    held_a, want_a = exchange([4000 + 10 * r for r in range(world)], 11)
+    assert ex.last_path == "fused_peer" and same(held_a, want_a)
+    held_b, want_b = exchange([90_000] * world, 12)            # the second window (made and grown on demand)
+    assert ex.last_path == "fused_peer" and same(held_b, want_b)
+    assert same(held_a, want_a), "the first result was overwritten while it was still held"
+    third, want_c = exchange([2500] * world, 13)               # both windows are leased: everybody takes the two-step path
+    assert ex.last_path == "nccl" and same(third, want_c)
+    assert same(held_a, want_a) and same(held_b, want_b)
+    del held_a
+    fourth, want_d = exchange([3100] * world, 14)              # the released window serves again
+    assert ex.last_path == "fused_peer" and same(fourth, want_d) and same(held_b, want_b)
+    del held_b, third, fourth
     ex.close()
 
 
